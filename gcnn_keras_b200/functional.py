@@ -1,0 +1,311 @@
+"""PyTorch host binding of the C-ABI: raw launchers + autograd Functions.
+
+Every differentiable primitive's backward is written with the OTHER primitives (gather <-> segment-sum are
+adjoint; the fused gather*weight->segment-sum has itself on the transposed relation and the two-sided
+gather-product as VJPs), so the set is closed under differentiation to any order.  That is what
+``EnergyForceModel`` needs: forces are dE/dx computed inside the step and are then trained on
+(kgcnn/model/force.py:159-176).
+
+torch is plumbing here (device memory, streams, the autograd tape); all arithmetic on ragged data runs in
+libkgcnn_b200.so.  There is no CPU path: CPU tensors raise.
+"""
+import torch
+
+from . import _lib
+from ._lib import KgcnnError, OP_MAX, OP_MEAN, OP_MIN, OP_SUM, check
+
+_OPS = {
+    "segment_sum": OP_SUM, "sum": OP_SUM, "reduce_sum": OP_SUM,
+    "segment_mean": OP_MEAN, "mean": OP_MEAN, "reduce_mean": OP_MEAN,
+    "segment_max": OP_MAX, "max": OP_MAX, "reduce_max": OP_MAX,
+    "segment_min": OP_MIN, "min": OP_MIN, "reduce_min": OP_MIN,
+}
+
+
+def op_code(name):
+    """segment_ops_by_name dispatch (kgcnn/ops/segment.py:39-51): unknown names raise TypeError."""
+    try:
+        return _OPS[name]
+    except KeyError:
+        raise TypeError("Unknown segment operation, choose: 'segment_mean', 'segment_sum', ...")
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t):
+    return None if t is None else t.data_ptr()
+
+
+def _need_cuda(*tensors):
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise KgcnnError("kgcnn_b200 kernels need CUDA tensors (there is no CPU fallback); got %s" % t.device)
+
+
+def _f32c(t):
+    if t.dtype != torch.float32:
+        raise TypeError("kgcnn_b200 kernels compute in float32, got %s" % t.dtype)
+    return t.contiguous()
+
+
+# ------------------------------------------------------------------------------------------------
+# raw launchers (no autograd)
+# ------------------------------------------------------------------------------------------------
+def raw_shift_index(idx64, node_splits, edge_splits, want_i64=False):
+    """a1: batch-indexed indices.  Returns int32 [K, E] (column-major) and optionally int64 [E, K]."""
+    _need_cuda(idx64, node_splits, edge_splits)
+    E, K = int(idx64.shape[0]), int(idx64.shape[1])
+    B = int(edge_splits.shape[0]) - 1
+    if int(node_splits.shape[0]) - 1 != B:
+        raise ValueError("index tensor and node tensor have different batch sizes: %d vs %d"
+                         % (B, int(node_splits.shape[0]) - 1))
+    out32 = torch.empty((K, E), dtype=torch.int32, device=idx64.device)
+    out64 = torch.empty((E, K), dtype=torch.int64, device=idx64.device) if want_i64 else None
+    check(_lib.lib().kgcnn_shift_index(_ptr(idx64), E, K, _ptr(node_splits), _ptr(edge_splits), B, _ptr(out64),
+                                       _ptr(out32), _stream()), "kgcnn_shift_index")
+    return (out32, out64) if want_i64 else out32
+
+
+def raw_value_rowids(row_splits, nvals):
+    _need_cuda(row_splits)
+    ids = torch.empty((nvals,), dtype=torch.int32, device=row_splits.device)
+    check(_lib.lib().kgcnn_value_rowids(_ptr(row_splits), int(row_splits.shape[0]) - 1, nvals, _ptr(ids), _stream()),
+          "kgcnn_value_rowids")
+    return ids
+
+
+def raw_cast_i32(t64):
+    _need_cuda(t64)
+    out = torch.empty(t64.shape, dtype=torch.int32, device=t64.device)
+    check(_lib.lib().kgcnn_cast_i64_i32(_ptr(t64), t64.numel(), _ptr(out), _stream()), "kgcnn_cast_i64_i32")
+    return out
+
+
+def raw_check_sorted(key, n_targets):
+    _need_cuda(key)
+    flags = torch.zeros((2,), dtype=torch.int32, device=key.device)
+    check(_lib.lib().kgcnn_check_sorted(_ptr(key), 1, int(key.shape[0]), n_targets, _ptr(flags), _stream()),
+          "kgcnn_check_sorted")
+    return flags
+
+
+def raw_plan_build(key, n_targets, assume_sorted):
+    """CSR row pointer [N+1] and stable permutation (None when sorted)."""
+    _need_cuda(key)
+    E = int(key.shape[0])
+    rowptr = torch.empty((n_targets + 1,), dtype=torch.int32, device=key.device)
+    if assume_sorted:
+        check(_lib.lib().kgcnn_plan_build(_ptr(key), 1, E, n_targets, 1, _ptr(rowptr), None, None, 0, _stream()),
+              "kgcnn_plan_build")
+        return rowptr, None
+    perm = torch.empty((E,), dtype=torch.int32, device=key.device)
+    nbytes = int(_lib.lib().kgcnn_plan_workspace_bytes(E, n_targets))
+    ws = torch.empty((nbytes,), dtype=torch.uint8, device=key.device)
+    check(_lib.lib().kgcnn_plan_build(_ptr(key), 1, E, n_targets, 0, _ptr(rowptr), _ptr(perm), _ptr(ws), nbytes,
+                                      _stream()), "kgcnn_plan_build")
+    return rowptr, perm
+
+
+def raw_permute_i32(src, perm):
+    out = torch.empty_like(perm)
+    check(_lib.lib().kgcnn_permute_i32(_ptr(src), 1, _ptr(perm), int(perm.shape[0]), _ptr(out), _stream()),
+          "kgcnn_permute_i32")
+    return out
+
+
+def raw_gather_rows(x2d, ids, out=None, col_offset=0):
+    """y[e] = x[ids[e]]; with `out` [E, W] writes into out[:, col_offset:col_offset+F]."""
+    _need_cuda(x2d, ids)
+    N, Fdim = int(x2d.shape[0]), int(x2d.shape[1])
+    E = int(ids.shape[0])
+    if x2d.dtype == torch.int64:
+        y = torch.empty((E, Fdim), dtype=torch.int64, device=x2d.device) if out is None else out
+        ystride = int(y.shape[1])
+        yp = y.data_ptr() + col_offset * 8
+        check(_lib.lib().kgcnn_gather_rows_i64(_ptr(x2d.contiguous()), N, Fdim, _ptr(ids), 1, E, yp, ystride,
+                                               _stream()), "kgcnn_gather_rows_i64")
+        return y
+    x2d = _f32c(x2d)
+    y = torch.empty((E, Fdim), dtype=torch.float32, device=x2d.device) if out is None else out
+    ystride = int(y.shape[1])
+    yp = y.data_ptr() + col_offset * 4
+    check(_lib.lib().kgcnn_gather_rows(_ptr(x2d), N, Fdim, _ptr(ids), 1, E, yp, ystride, _stream()),
+          "kgcnn_gather_rows")
+    return y
+
+
+def raw_gms(x2d, w, rel_out, rel_src, op=OP_SUM):
+    """y[i] = OP_{e in seg_out(i)} x[src(e)] * w[e]; rel_src None -> x is the element tensor itself."""
+    _need_cuda(x2d, w)
+    x2d = _f32c(x2d)
+    Fdim = int(x2d.shape[1])
+    wcols = 0
+    if w is not None:
+        w = _f32c(w)
+        wcols = int(w.shape[1]) if w.dim() == 2 else 1
+    n_out = rel_out.n_targets
+    y = torch.empty((n_out, Fdim), dtype=torch.float32, device=x2d.device)
+    perm = rel_out.perm
+    if rel_src is not None:
+        gidx = rel_out.permuted_ids(rel_src)
+        gperm = 1 if perm is not None else 0
+    else:
+        gidx, gperm = None, 0
+    check(_lib.lib().kgcnn_gather_mul_segment_reduce(_ptr(x2d), Fdim, _ptr(w), wcols, _ptr(rel_out.rowptr),
+                                                     _ptr(perm), _ptr(gidx), 1, gperm, n_out, op, _ptr(y),
+                                                     _stream()), "kgcnn_gather_mul_segment_reduce")
+    return y
+
+
+def raw_g2m(a2d, ids_a, b2d, ids_b, n_elements, reduce):
+    _need_cuda(a2d, b2d)
+    a2d, b2d = _f32c(a2d), _f32c(b2d)
+    Fdim = int(a2d.shape[1])
+    z = torch.empty((n_elements, 1 if reduce else Fdim), dtype=torch.float32, device=a2d.device)
+    check(_lib.lib().kgcnn_gather2_mul(_ptr(a2d), _ptr(ids_a), 1, _ptr(b2d), _ptr(ids_b), 1, Fdim, n_elements,
+                                       1 if reduce else 0, _ptr(z), _stream()), "kgcnn_gather2_mul")
+    return z
+
+
+# ------------------------------------------------------------------------------------------------
+# autograd Functions
+# ------------------------------------------------------------------------------------------------
+def _flat2d(t):
+    return t.reshape(t.shape[0], -1) if t.dim() != 2 else t
+
+
+class _Gather(torch.autograd.Function):
+    """y[e] = x[rel.ids[e]]   (kgcnn/layers/gather.py:228); backward = segment-sum over rel."""
+
+    @staticmethod
+    def forward(ctx, x, rel):
+        ctx.rel = rel
+        ctx.tail = tuple(x.shape[1:])
+        y = raw_gather_rows(_flat2d(x), rel.ids)
+        return y.reshape((rel.n_elements,) + ctx.tail)
+
+    @staticmethod
+    def backward(ctx, g):
+        return _SegmentSum.apply(g.contiguous(), ctx.rel), None
+
+
+class _SegmentSum(torch.autograd.Function):
+    """y[i] = sum_{e: rel.ids[e]==i} v[e]   (sorted segment_sum + scatter_nd pad, pooling.py:63-76)."""
+
+    @staticmethod
+    def forward(ctx, v, rel):
+        ctx.rel = rel
+        tail = tuple(v.shape[1:])
+        y = raw_gms(_flat2d(v), None, rel, None, OP_SUM)
+        return y.reshape((rel.n_targets,) + tail)
+
+    @staticmethod
+    def backward(ctx, g):
+        return _Gather.apply(g.contiguous(), ctx.rel), None
+
+
+class _GMS(torch.autograd.Function):
+    """y[i] = sum_{e: out.ids[e]==i} x[src.ids[e]] * w[e]; w is [E,F] or [E,1]."""
+
+    @staticmethod
+    def forward(ctx, x, w, rel_out, rel_src):
+        ctx.rel_out, ctx.rel_src = rel_out, rel_src
+        ctx.save_for_backward(x, w)
+        return raw_gms(x, w, rel_out, rel_src, OP_SUM)
+
+    @staticmethod
+    def backward(ctx, g):
+        x, w = ctx.saved_tensors
+        g = g.contiguous()
+        gx = gw = None
+        if ctx.needs_input_grad[0]:
+            gx = _GMS.apply(g, w, ctx.rel_src, ctx.rel_out)
+        if ctx.needs_input_grad[1]:
+            reduce = w.shape[1] == 1 and x.shape[1] != 1
+            gw = _G2M.apply(x, g, ctx.rel_src, ctx.rel_out, reduce)
+        return gx, gw, None, None
+
+
+class _G2M(torch.autograd.Function):
+    """z[e] = a[ra.ids[e]] * b[rb.ids[e]] (optionally summed over features -> [E,1])."""
+
+    @staticmethod
+    def forward(ctx, a, b, rel_a, rel_b, reduce):
+        ctx.rel_a, ctx.rel_b, ctx.reduce = rel_a, rel_b, reduce
+        ctx.save_for_backward(a, b)
+        return raw_g2m(a, rel_a.ids, b, rel_b.ids, rel_a.n_elements, reduce)
+
+    @staticmethod
+    def backward(ctx, gz):
+        a, b = ctx.saved_tensors
+        gz = gz.contiguous()
+        ga = gb = None
+        if ctx.needs_input_grad[0]:
+            ga = _GMS.apply(b, gz, ctx.rel_a, ctx.rel_b)
+        if ctx.needs_input_grad[1]:
+            gb = _GMS.apply(a, gz, ctx.rel_b, ctx.rel_a)
+        return ga, gb, None, None, None
+
+
+def gather(x, rel):
+    """Row gather along a relation (any trailing feature shape)."""
+    if x.dtype == torch.int64 or not torch.is_floating_point(x):
+        y = raw_gather_rows(_flat2d(x.to(torch.int64)), rel.ids)
+        return y.reshape((rel.n_elements,) + tuple(x.shape[1:]))
+    return _Gather.apply(x, rel)
+
+
+def segment_reduce(v, rel, op="sum"):
+    """Deterministic CSR segment reduce; empty segments give 0 for every op (F4 in SURVEY.md)."""
+    code = op if isinstance(op, int) else op_code(op)
+    if code == OP_SUM:
+        return _SegmentSum.apply(v, rel)
+    if code == OP_MEAN:
+        s = _SegmentSum.apply(v, rel)
+        inv = rel.inv_count()
+        return s * inv.reshape((-1,) + (1,) * (v.dim() - 1))
+    # max / min: value from the kernel (no tape), gradient split equally among ties like TF's
+    # SegmentMax/SegmentMin gradient.
+    tail = tuple(v.shape[1:])
+    with torch.no_grad():
+        y = raw_gms(_flat2d(v), None, rel, None, code).reshape((rel.n_targets,) + tail)
+    if not (torch.is_grad_enabled() and v.requires_grad):
+        return y
+    yg = gather(y, rel)
+    mask = (v.detach() == yg).to(v.dtype)
+    nties = _SegmentSum.apply(mask, rel).clamp_min(1.0)
+    weights = mask / gather(nties, rel)
+    # value path carries no gradient; gradient path: y = segment_sum(v * weights) has dy/dv = weights
+    return y + (_SegmentSum.apply(v * weights, rel) - _SegmentSum.apply(v.detach() * weights, rel))
+
+
+def gather_mul_segment_sum(x, w, rel_out, rel_src):
+    """Fused  y_i = sum_{e->i} x[s_e] * w_e  (SchNet cfconv, PaiNN scalar channel, GCN)."""
+    tail = tuple(x.shape[1:])
+    x2 = _flat2d(x)
+    if w is None:
+        w2 = None
+        y = _GMS_noW.apply(x2, rel_out, rel_src)
+    else:
+        w2 = _flat2d(w) if w.dim() > 1 else w.unsqueeze(1)
+        y = _GMS.apply(x2, w2, rel_out, rel_src)
+    return y.reshape((rel_out.n_targets,) + tail)
+
+
+class _GMS_noW(torch.autograd.Function):
+    """y[i] = sum_{e: out.ids[e]==i} x[src.ids[e]]  (plain gather + segment-sum; the roofline op)."""
+
+    @staticmethod
+    def forward(ctx, x, rel_out, rel_src):
+        ctx.rel_out, ctx.rel_src = rel_out, rel_src
+        return raw_gms(x, None, rel_out, rel_src, OP_SUM)
+
+    @staticmethod
+    def backward(ctx, g):
+        return _GMS_noW.apply(g.contiguous(), ctx.rel_src, ctx.rel_out), None, None
+
+
+def gather2_mul(a, b, rel_a, rel_b, reduce=False):
+    return _G2M.apply(_flat2d(a), _flat2d(b), rel_a, rel_b, reduce)

@@ -1,0 +1,150 @@
+"""Per-batch graph plan.
+
+The reference recomputes ``partition_row_indexing`` (kgcnn/ops/partition.py:97-161) in every gather and
+every pooling call and ``tf.argsort`` + permutation gathers (kgcnn/layers/pooling.py:63-68) in every
+pooling call, although the index tensor is the same object for all layers of a model.  Here the batch
+indexed int32 indices, the receiver CSR, the sender CSC and the permutations are built ONCE per index
+tensor and cached on it (keyed by tensor identity + node partition identity).
+"""
+import weakref
+
+import torch
+
+from . import functional as F
+from ._lib import KgcnnError
+
+
+class Relation:
+    """'element e belongs to target ids[e]' with its CSR (rowptr, stable perm); e.g. edge -> receiver."""
+
+    def __init__(self, ids, n_targets, rowptr=None, perm=None, is_sorted=None):
+        self.ids = ids                    # int32 [E] contiguous, batch indexing
+        self.n_targets = int(n_targets)
+        self.n_elements = int(ids.shape[0])
+        self._rowptr = rowptr
+        self._perm = perm
+        self._is_sorted = is_sorted
+        self._permuted = {}               # id(other relation) -> other.ids[perm]
+        self._inv_count = None
+
+    def _build(self):
+        if self._rowptr is not None:
+            return
+        if self._is_sorted is None:
+            flags = F.raw_check_sorted(self.ids, self.n_targets)
+            host = flags.cpu()            # one sync per batch and relation
+            if int(host[1]):
+                raise IndexError("index out of range [0, %d) in ragged index tensor" % self.n_targets)
+            self._is_sorted = not bool(int(host[0]))
+        self._rowptr, self._perm = F.raw_plan_build(self.ids, self.n_targets, self._is_sorted)
+
+    @property
+    def is_sorted(self):
+        self._build()
+        return self._is_sorted
+
+    @property
+    def rowptr(self):
+        self._build()
+        return self._rowptr
+
+    @property
+    def perm(self):
+        """int32 [E] stable argsort of ids, or None when ids are already ascending."""
+        self._build()
+        return self._perm
+
+    def permuted_ids(self, other):
+        """other.ids in this relation's CSR order (so the fused kernel reads one index array)."""
+        if self.perm is None:
+            return other.ids
+        key = id(other)
+        if key not in self._permuted:
+            self._permuted[key] = (F.raw_permute_i32(other.ids, self.perm), other)
+        return self._permuted[key][0]
+
+    def inv_count(self):
+        """1/len(segment) (0 for empty) as float32 [n_targets, 1]: backward of segment_mean."""
+        if self._inv_count is None:
+            rp = self.rowptr
+            cnt = (rp[1:] - rp[:-1]).to(torch.float32)
+            self._inv_count = torch.where(cnt > 0, 1.0 / cnt, torch.zeros_like(cnt)).unsqueeze(1)
+        return self._inv_count
+
+
+class IndexPlan:
+    """Batch-indexed view of a ragged index tensor [E, K] that refers to rows of a ragged node tensor."""
+
+    def __init__(self, index_values, index_partition, node_partition):
+        if index_values.dim() != 2:
+            raise ValueError("index tensor values must have shape [E, K]")
+        if not index_values.is_cuda:
+            raise KgcnnError("kgcnn_b200 needs CUDA tensors (no CPU fallback); got index tensor on %s"
+                             % index_values.device)
+        self.E, self.K = int(index_values.shape[0]), int(index_values.shape[1])
+        self.N = int(node_partition.nvals)
+        self.index_partition = index_partition
+        self.node_partition = node_partition
+        idx64 = index_values.to(torch.int64).contiguous()
+        # column-major [K, E] int32, batch indexing (a1)
+        self.idx32 = F.raw_shift_index(idx64, node_partition.row_splits, index_partition.row_splits)
+        self._relations = {}
+
+    def relation(self, col):
+        col = int(col)
+        if col < 0:
+            col += self.K
+        if col not in self._relations:
+            self._relations[col] = Relation(self.idx32[col], self.N)
+        return self._relations[col]
+
+
+_PLAN_CACHE = weakref.WeakKeyDictionary()   # index values tensor -> {(node splits ptr): IndexPlan}
+
+
+def get_plan(index_ragged, node_ragged):
+    """Cached IndexPlan for (index tensor, node partition)."""
+    vals = index_ragged.values
+    node_part = node_ragged.partition
+    key = (id(node_part), vals._version, id(index_ragged.partition))
+    per_tensor = _PLAN_CACHE.get(vals)
+    if per_tensor is None:
+        per_tensor = {}
+        _PLAN_CACHE[vals] = per_tensor
+    entry = per_tensor.get(key)
+    if entry is None:
+        for k in [k for k in per_tensor if k[1] != vals._version]:
+            del per_tensor[k]                # an in-place update of the index tensor invalidates its plans
+        # keep the partitions alive next to the plan so id() keys cannot be recycled
+        entry = (IndexPlan(vals, index_ragged.partition, node_part), node_part, index_ragged.partition)
+        per_tensor[key] = entry
+    return entry[0]
+
+
+def unify_partitions(raggeds):
+    """Make ragged tensors whose row_splits are equal share ONE RowPartition object, so that plans and
+    int32 CSR views are built once per batch (nodes, coordinates and atomic numbers arrive as separate
+    RaggedTensors with equal splits).  One device comparison + sync per distinct pair and batch."""
+    canon = []
+    out = []
+    for r in raggeds:
+        if not hasattr(r, "partition"):
+            out.append(r)
+            continue
+        hit = None
+        for c in canon:
+            if c is r.partition:
+                hit = c
+                break
+            if c.nrows == r.partition.nrows and c.row_splits.device == r.partition.row_splits.device \
+                    and int(c.row_splits.shape[0]) == int(r.partition.row_splits.shape[0]) \
+                    and (c._nvals is None or r.partition._nvals is None or c._nvals == r.partition._nvals) \
+                    and bool(torch.equal(c.row_splits, r.partition.row_splits)):
+                hit = c
+                break
+        if hit is None:
+            canon.append(r.partition)
+            out.append(r)
+        else:
+            out.append(r if hit is r.partition else type(r)(r.values, hit))
+    return out

@@ -1,0 +1,137 @@
+/*
+ * kgcnn_b200.h -- C-ABI of libkgcnn_b200.so: the B200 (sm_100a) kernels behind kgcnn's ragged
+ * message-passing hot path (gather -> per-edge math -> segment aggregation).
+ *
+ * The reference (Tacitus523/gcnn_keras, pure Python on TensorFlow) has no FFI of its own.  Each entry
+ * point below names the reference code (file:line under the reference tree) whose arithmetic it
+ * replaces; a host framework (PyTorch binding in gcnn_keras_b200/, TensorFlow custom-op shim in
+ * tf_shim/) wraps them behind the unchanged kgcnn layer API.
+ *
+ * Conventions
+ *  - every pointer is a DEVICE pointer owned by the caller; outputs and workspaces are pre-allocated
+ *    by the host framework (torch.empty / TF allocate_output);
+ *  - every call is asynchronous on `stream`, never synchronises, never allocates, and is re-entrant
+ *    (the only process-global state is a monotonically increasing launch counter);
+ *  - float tensors are fp32 row-major contiguous; indices are int32 after kgcnn_shift_index (the
+ *    int64 -> int32 conversion happens once per batch, the reference redoes it in every layer);
+ *  - return value: 0 = KGCNN_OK, negative = KGCNN_E_*; no C++ exception crosses the ABI;
+ *  - reductions are deterministic: CSR segments, fixed in-segment order, no floating-point atomics.
+ */
+#ifndef KGCNN_B200_H_
+#define KGCNN_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* kgcnn_stream_t; /* cudaStream_t */
+
+enum {
+  KGCNN_OK = 0,
+  KGCNN_E_INVALID = -1,     /* bad argument (null pointer, negative size, unknown enum) */
+  KGCNN_E_UNSUPPORTED = -2, /* shape outside what the kernels are instantiated for */
+  KGCNN_E_CUDA = -3,        /* a CUDA launch error was pending after the launch */
+  KGCNN_E_WORKSPACE = -4    /* workspace smaller than *_workspace_bytes() */
+};
+
+/* segment_ops_by_name names (kgcnn/ops/segment.py:39-46) */
+enum { KGCNN_OP_SUM = 0, KGCNN_OP_MEAN = 1, KGCNN_OP_MAX = 2, KGCNN_OP_MIN = 3 };
+
+/* radial basis selector for the fused edge-geometry kernels */
+enum { KGCNN_BASIS_NONE = 0, KGCNN_BASIS_GAUSS = 1, KGCNN_BASIS_BESSEL = 2 };
+
+/* activations with f, f', f'' (kgcnn/ops/activ.py:5-107, keras 'tanh', 'linear') */
+enum {
+  KGCNN_ACT_LINEAR = 0,
+  KGCNN_ACT_SHIFTED_SOFTPLUS = 1,
+  KGCNN_ACT_SWISH = 2,
+  KGCNN_ACT_TANH = 3,
+  KGCNN_ACT_RELU = 4,
+  KGCNN_ACT_SOFTPLUS2 = 5
+};
+
+int kgcnn_version(void);
+const char* kgcnn_error_string(int code);
+/* number of kernel launches issued through this library since load / since the last reset */
+long long kgcnn_launch_count(void);
+void kgcnn_launch_count_reset(void);
+
+/* ---------------------------------------------------------------------------------------------
+ * a1  partition_row_indexing(sample -> batch)      kgcnn/ops/partition.py:97-161
+ *     idx_batch[e,k] = idx[e,k] + node_row_splits[graph_of(e)], graph_of from edge_row_splits
+ *     (the reference: repeat(range(B), row_lengths) :29,45 -> gather :146 -> broadcast add :150-155).
+ *     Writes int64 [E,K] (same layout as the input; the bit-exact comparand) and/or int32 [K,E]
+ *     (column-major: each index column is contiguous, which is what every other kernel consumes).
+ * ------------------------------------------------------------------------------------------- */
+int kgcnn_shift_index(const int64_t* idx, int64_t E, int K, const int64_t* node_row_splits,
+                      const int64_t* edge_row_splits, int64_t B, int64_t* out_i64 /*nullable*/,
+                      int32_t* out_i32 /*nullable*/, kgcnn_stream_t stream);
+
+/* value_rowids from row_splits (kgcnn/ops/partition.py:41-45): ids[n] = graph of element n */
+int kgcnn_value_rowids(const int64_t* row_splits, int64_t B, int64_t n_values, int32_t* ids,
+                       kgcnn_stream_t stream);
+
+/* int64 row_splits -> int32 CSR row pointer (PoolingEmbedding, kgcnn/layers/pooling.py:215-218) */
+int kgcnn_cast_i64_i32(const int64_t* src, int64_t n, int32_t* dst, kgcnn_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * plan: replaces tf.argsort(stable) + permutation gathers of PoolingLocalEdges
+ *       kgcnn/layers/pooling.py:63-68 (and :156-159), once per batch instead of once per layer.
+ *  kgcnn_check_sorted : flags[0] = 1 if key is NOT ascending, flags[1] = 1 if any key outside [0,N)
+ *                       (flags must be zeroed by the caller; OR-accumulated)
+ *  kgcnn_plan_build   : rowptr[N+1] = CSR row pointer of key (histogram + scan);
+ *                       perm[E] = stable ascending argsort of key (identity when assume_sorted!=0).
+ *                       key is read with stride `key_stride` (column of an [E,K] int32 tensor).
+ * ------------------------------------------------------------------------------------------- */
+int kgcnn_check_sorted(const int32_t* key, int key_stride, int64_t E, int64_t N, int32_t* flags,
+                       kgcnn_stream_t stream);
+size_t kgcnn_plan_workspace_bytes(int64_t E, int64_t N);
+int kgcnn_plan_build(const int32_t* key, int key_stride, int64_t E, int64_t N, int assume_sorted,
+                     int32_t* rowptr, int32_t* perm /*nullable if assume_sorted*/, void* workspace,
+                     size_t workspace_bytes, kgcnn_stream_t stream);
+/* out[p] = src[perm[p]*src_stride]  (pre-permuted gather index so the CSR kernels read one array) */
+int kgcnn_permute_i32(const int32_t* src, int src_stride, const int32_t* perm, int64_t E,
+                      int32_t* out, kgcnn_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * a2/a3  GatherEmbedding / GatherEmbeddingSelection   kgcnn/layers/gather.py:83, :228
+ *     y[e, 0:F] = x[idx[e*idx_stride], 0:F]; y rows are `y_stride` floats apart so K selections can
+ *     be written side by side (concat_axis=2, gather.py:88-90) without a second pass.
+ * ------------------------------------------------------------------------------------------- */
+int kgcnn_gather_rows(const float* x, int64_t N, int F, const int32_t* idx, int idx_stride, int64_t E,
+                      float* y, int64_t y_stride, kgcnn_stream_t stream);
+/* same for int64 payloads (atomic numbers: acsf_conv.py:204, :488) */
+int kgcnn_gather_rows_i64(const int64_t* x, int64_t N, int F, const int32_t* idx, int idx_stride,
+                          int64_t E, int64_t* y, int64_t y_stride, kgcnn_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * a4/a5/a7/a13/a14/a18  fused gather * weight -> segment reduce (CSR, deterministic)
+ *     y[i, f] = OP_{p in [rowptr[i], rowptr[i+1])}  x[src(p), f] * w[e(p), f or 0]
+ *         e(p)   = perm ? perm[p] : p                      (original edge id, stable order)
+ *         src(p) = gidx ? gidx[e(p)*gidx_stride] : e(p)    (gidx==NULL: x is the edge tensor itself)
+ *         gidx_permuted != 0: gidx is already in CSR order, src(p) = gidx[p*gidx_stride]
+ *     w_cols in {0 (no weight), 1 (per-edge scalar), F (per-edge row)}; op MAX/MIN require w_cols==0.
+ *     Empty segment -> 0 for every op (kgcnn/layers/pooling.py:71-76: sorted segment op + scatter_nd
+ *     zero padding).  MEAN divides by the segment length (kgcnn/ops/segment.py:39-40).
+ *     Replaces: tf.gather (gather.py:228) + LazyMultiply (schnet_conv.py:77) + argsort, permutation gathers,
+ *     sorted segment op and scatter_nd (pooling.py:63-76); PoolingWeightedLocalEdges (pooling.py:152-172);
+ *     PoolingEmbedding (pooling.py:215-218) with rowptr = row_splits.
+ * ------------------------------------------------------------------------------------------- */
+int kgcnn_gather_mul_segment_reduce(const float* x, int F, const float* w, int w_cols,
+                                    const int32_t* rowptr, const int32_t* perm, const int32_t* gidx,
+                                    int gidx_stride, int gidx_permuted, int64_t n_out, int op, float* y,
+                                    kgcnn_stream_t stream);
+
+/* z[e, f] = a[ia[e], f] * b[ib[e], f]   (reduce_f==0)   or   z[e] = sum_f a[ia[e],f]*b[ib[e],f]
+ * ia/ib == NULL means "row e".  VJP of the fused op above with respect to w. */
+int kgcnn_gather2_mul(const float* a, const int32_t* ia, int ia_stride, const float* b,
+                      const int32_t* ib, int ib_stride, int F, int64_t E, int reduce_f, float* z,
+                      kgcnn_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KGCNN_B200_H_ */
