@@ -1,0 +1,347 @@
+#!/usr/bin/env python
+"""bench.py -- driver-facing benchmark of the kgcnn hot path on B200 (contract: see DESIGN.md 'Measurement').
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload schnet|gss] [--impl reference]
+
+Prints ONE JSON line on rank 0.  Workloads:
+  gss     gather + segment-sum forward + backward on GSS-L (C1 pattern scaled to 65 536 graphs,
+          N=1.31 M nodes, E=26.2 M edges, F=64) -> edges/s + HBM roofline
+  schnet  SchNet energy+force training step, C2 (256 ethanol-shaped molecules) -> molecules/s
+`--impl reference` times the oracle (CPU restatement of the reference's TF op chain) on the host cores.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+# ----------------------------------------------------------------------------------------------------
+# helpers
+# ----------------------------------------------------------------------------------------------------
+class ClockSampler:
+    """Samples nvidia-smi SM clocks / throttle reasons DURING the timed region."""
+
+    QUERY = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device_index=0, period=0.2):
+        self.device_index, self.period = device_index, period
+        self.samples, self._stop, self._thread = [], threading.Event(), None
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.device_index), "--query-gpu=" + self.QUERY,
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5)
+                parts = [p.strip() for p in out.stdout.strip().split(",")]
+                if len(parts) >= 7:
+                    self.samples.append(parts)
+            except Exception:
+                pass
+            self._stop.wait(self.period)
+
+    def __enter__(self):
+        self._thread = threading.Thread(target=self._run, daemon=True)
+        self._thread.start()
+        return self
+
+    def __exit__(self, *exc):
+        self._stop.set()
+        self._thread.join(timeout=10)
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        sm = sorted(float(s[0]) for s in self.samples if s[0].replace(".", "").isdigit())
+        mx = [float(s[1]) for s in self.samples if s[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for s in self.samples for n, v in zip(names, s[3:7]) if v.lower().startswith("active")})
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(self.samples)}
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as fh:
+            d = json.load(fh)
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def dist_setup(n_gpus):
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    return rank, world, local
+
+
+def barrier(world):
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+
+
+def max_over_ranks(value, world, device):
+    if world == 1:
+        return value
+    import torch.distributed as dist
+    t = torch.tensor([value], dtype=torch.float64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def sum_over_ranks(value, world, device):
+    if world == 1:
+        return value
+    import torch.distributed as dist
+    t = torch.tensor([value], dtype=torch.float64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    return float(t.item())
+
+
+def timed_region(step_fn, steps, warmup, world, device):
+    """W warm-ups, then K steps bracketed by barrier + synchronize, CUDA events on the launching stream,
+    max over ranks.  Returns (ms_per_step, clocks)."""
+    for _ in range(warmup):
+        step_fn()
+    torch.cuda.synchronize()
+    barrier(world)
+    torch.cuda.synchronize()
+    start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(device.index or 0) as clocks:
+        start.record()
+        for _ in range(steps):
+            step_fn()
+        stop.record()
+        torch.cuda.synchronize()
+        barrier(world)
+        torch.cuda.synchronize()
+    ms = start.elapsed_time(stop)
+    ms = max_over_ranks(ms, world, device)
+    return ms / steps, clocks.summary()
+
+
+# ----------------------------------------------------------------------------------------------------
+# synthetic inputs (seeded, no dataset files)
+# ----------------------------------------------------------------------------------------------------
+def gss_inputs(n_graphs, n_nodes=20, deg=20, feat=64, seed=0):
+    """C1 pattern scaled: every receiver gets `deg` senders from its own graph (19 distinct others in random
+    order + 1 repeat, no self loops), receiver-sorted.  Returns host (numpy) arrays in SAMPLE indexing."""
+    rng = np.random.default_rng(seed)
+    n_total = n_graphs * n_nodes
+    recv_local = np.tile(np.arange(n_nodes, dtype=np.int64), n_graphs)            # [N]
+    offs = rng.permuted(np.tile(np.arange(1, n_nodes, dtype=np.int64), (n_total, 1)), axis=1)   # [N, 19]
+    if deg <= n_nodes - 1:
+        offs = offs[:, :deg]
+    else:
+        extra = rng.integers(1, n_nodes, size=(n_total, deg - (n_nodes - 1)))
+        offs = np.concatenate([offs, extra], axis=1)
+    send_local = (recv_local[:, None] + offs) % n_nodes                            # [N, deg]
+    index = np.stack([np.repeat(recv_local, deg), send_local.reshape(-1)], axis=1)  # [E, 2] int64
+    x = rng.standard_normal((n_total, feat), dtype=np.float32)
+    node_splits = np.arange(n_graphs + 1, dtype=np.int64) * n_nodes
+    edge_splits = np.arange(n_graphs + 1, dtype=np.int64) * (n_nodes * deg)
+    return x, index, node_splits, edge_splits
+
+
+def gss_bytes(E, N, F):
+    """B_plain of SURVEY.md 8d: fwd (4EF + 4E + 4N + 4NF) + bwd (same op on the transposed graph)."""
+    return 8 * E * F + 8 * E + 8 * N * (F + 1)
+
+
+# ----------------------------------------------------------------------------------------------------
+# workload: gather + segment-sum forward + backward
+# ----------------------------------------------------------------------------------------------------
+def run_gss(args, rank, world, device):
+    from gcnn_keras_b200 import RaggedTensor, _lib
+    from gcnn_keras_b200 import functional as F
+    from gcnn_keras_b200.plan import get_plan
+
+    n_graphs, feat = args.gss_graphs, args.gss_feat
+    x_h, idx_h, ns_h, es_h = gss_inputs(n_graphs, feat=feat, seed=rank)
+    N, E = x_h.shape[0], idx_h.shape[0]
+    pin = lambda a: torch.from_numpy(a).pin_memory()
+    x_p, idx_p, ns_p, es_p = pin(x_h), pin(idx_h), pin(ns_h), pin(es_h)
+    dy = torch.randn(N, feat, device=device)
+
+    # ---- resident inputs: plan built once per batch, fwd + bwd through the public autograd API ----
+    x_d = x_p.to(device).requires_grad_(True)
+    nodes = RaggedTensor.from_row_splits(x_d, ns_p.to(device))
+    index = RaggedTensor.from_row_splits(idx_p.to(device), es_p.to(device))
+    plan = get_plan(index, nodes)
+    recv, send = plan.relation(0), plan.relation(1)
+    recv.rowptr, send.rowptr, send.permuted_ids(recv)   # build CSR + CSC before timing
+
+    def step():
+        y = F.gather_mul_segment_sum(x_d, None, recv, send)
+        (gx,) = torch.autograd.grad(y, x_d, dy)
+        return y, gx
+
+    _lib.launch_count_reset()
+    step()
+    launches_per_step = _lib.launch_count()
+    ms_step, clocks = timed_region(step, args.steps, args.warmup, world, device)
+
+    # ---- end to end: host buffers -> H2D -> plan -> fwd -> bwd -> D2H of the results ----
+    y_host = torch.empty((N, feat), dtype=torch.float32).pin_memory()
+    gx_host = torch.empty((N, feat), dtype=torch.float32).pin_memory()
+
+    def e2e_step():
+        xd = x_p.to(device, non_blocking=True).requires_grad_(True)
+        nd = RaggedTensor.from_row_splits(xd, ns_p.to(device, non_blocking=True))
+        ix = RaggedTensor.from_row_splits(idx_p.to(device, non_blocking=True), es_p.to(device, non_blocking=True))
+        pl = get_plan(ix, nd)
+        y = F.gather_mul_segment_sum(xd, None, pl.relation(0), pl.relation(1))
+        (gx,) = torch.autograd.grad(y, xd, dy)
+        y_host.copy_(y.detach(), non_blocking=True)
+        gx_host.copy_(gx, non_blocking=True)
+
+    e2e_steps = max(2, min(args.steps, 10))
+    ms_e2e, _ = timed_region(e2e_step, e2e_steps, 2, world, device)
+
+    total_edges = sum_over_ranks(float(E), world, device)
+    peak, peak_src = measured_peaks()
+    alg_bytes = gss_bytes(E, N, feat)
+    n_kernel_launches = 2   # fwd + bwd are the same kernel on the receiver CSR / sender CSC
+    achieved = (alg_bytes / n_kernel_launches) / (ms_step / n_kernel_launches * 1e-3) / 1e9
+    h2d = x_p.numel() * 4 + idx_p.numel() * 8 + ns_p.numel() * 8 + es_p.numel() * 8
+    d2h = 2 * N * feat * 4
+    line = {
+        "metric": "edges/sec (gather+segment-sum fwd+bwd)", "value": total_edges / (ms_step * 1e-3),
+        "unit": "edges/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "GSS-L: gather+segment-sum fwd+bwd, C1 pattern x %d graphs" % n_graphs,
+                   "graphs_per_gpu": n_graphs, "nodes_per_gpu": N, "edges_per_gpu": E, "features": feat,
+                   "l2_policy": "inputs larger than L2 (%.0f MB working set)" % ((2 * N * feat * 4 + 2 * E * 4) / 1e6),
+                   "parallelism": "graphs sharded across %d rank(s), no data-path collective" % world},
+        "hbm_gbs_algorithmic": alg_bytes / (ms_step * 1e-3) / 1e9,
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": None, "kernel": "gms_kernel<float4,16,1,SumW0,gather>",
+                     "algorithmic_bytes_per_launch": alg_bytes / n_kernel_launches, "peak_source": peak_src},
+        "e2e": {"value": total_edges / (ms_e2e * 1e-3), "unit": "edges/s", "h2d_bytes_per_step": h2d,
+                "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e},
+        "gpu_launches": launches_per_step * args.steps,
+        "clocks": clocks,
+    }
+    return line
+
+
+# ----------------------------------------------------------------------------------------------------
+# CPU baseline: the oracle (op-for-op restatement of the reference's TF chain) on the host cores
+# ----------------------------------------------------------------------------------------------------
+def cpu_gss(n_graphs, feat, steps, warmup, threads):
+    """gather -> PoolingLocalEdges(sum) forward + backward with the reference's op chain
+    (partition_row_indexing in BOTH layers, stable argsort, permutation gathers, sorted segment_sum,
+    zero padding), torch CPU autograd, `threads` host threads.  Returns (edges_per_s, ms_per_step, E)."""
+    from oracle import R
+    from oracle import layers as OL
+    torch.set_num_threads(threads)
+    x_h, idx_h, ns_h, es_h = gss_inputs(n_graphs, feat=feat, seed=0)
+    x = torch.from_numpy(x_h).requires_grad_(True)
+    nodes = R(x, ns_h)
+    index = R(torch.from_numpy(idx_h), es_h)
+    dy = torch.randn(x.shape)
+
+    def step():
+        msg = OL.gather_nodes_outgoing(nodes, index)
+        y = OL.pooling_local_edges(nodes, msg, index, pooling_method="sum").values
+        (gx,) = torch.autograd.grad(y, x, dy)
+        return gx
+
+    for _ in range(warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        step()
+    dt = (time.perf_counter() - t0) / steps
+    return idx_h.shape[0] / dt, dt * 1e3, idx_h.shape[0]
+
+
+def cpu_baseline_gss(args):
+    cores = os.cpu_count() or 1
+    n_graphs = 8192    # bounded sample: 1/8 of GSS-L, ~10-30 s of CPU work
+    eps, ms, E = cpu_gss(n_graphs, args.gss_feat, steps=3, warmup=1, threads=cores)
+    return {"value": eps, "unit": "edges/s", "cores": cores, "kind": "port",
+            "sample": "same op on %d graphs (E=%d, F=%d), oracle torch-CPU fwd+bwd, 3 steps, %.0f ms/step"
+                      % (n_graphs, E, args.gss_feat, ms)}
+
+
+def run_reference_gss(args):
+    cores = os.cpu_count() or 1
+    n_graphs = 8192
+    eps, ms, E = cpu_gss(n_graphs, args.gss_feat, steps=max(1, args.steps), warmup=max(1, min(args.warmup, 2)),
+                         threads=cores)
+    return {"impl": "reference", "metric": "edges/sec (gather+segment-sum fwd+bwd)", "value": eps,
+            "unit": "edges/s", "n_gpus": int(os.environ.get("WORLD_SIZE", "1")), "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "GSS-L: gather+segment-sum fwd+bwd, C1 pattern (CPU sample: %d graphs)" % n_graphs,
+                       "features": args.gss_feat, "edges_per_step": E},
+            "cpu_baseline": {"value": eps, "unit": "edges/s", "cores": cores, "kind": "port",
+                             "sample": "oracle torch-CPU restatement of the reference TF op chain, %d graphs" % n_graphs},
+            "e2e": {"value": eps, "unit": "edges/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "note": "TensorFlow is not installable here; the reference arm is the oracle port on the host cores"}
+
+
+# ----------------------------------------------------------------------------------------------------
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default=os.environ.get("KGCNN_BENCH_WORKLOAD", "gss"), choices=["gss", "schnet"])
+    ap.add_argument("--gss-graphs", type=int, default=65536)
+    ap.add_argument("--gss-feat", type=int, default=64)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+
+    if args.impl == "reference":
+        if int(os.environ.get("RANK", "0")) != 0:
+            return 0
+        fn = {"gss": run_reference_gss, "schnet": globals().get("run_reference_schnet", run_reference_gss)}[args.workload]
+        print(json.dumps(fn(args)))
+        return 0
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product path has no CPU fallback "
+                         "(use --impl reference for the CPU oracle)")
+    rank, world, local = dist_setup(args.gpus)
+    device = torch.device("cuda", local)
+    torch.cuda.set_device(device)
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+    fn = {"gss": run_gss, "schnet": globals().get("run_schnet", run_gss)}[args.workload]
+    line = fn(args, rank, world, device)
+    if rank == 0:
+        if world == 1 and not args.no_cpu_baseline:
+            cb = {"gss": cpu_baseline_gss, "schnet": globals().get("cpu_baseline_schnet", cpu_baseline_gss)}[args.workload]
+            line["cpu_baseline"] = cb(args)
+        print(json.dumps(line))
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -229,13 +229,13 @@ class _GMS(torch.autograd.Function):
 
 
 class _G2M(torch.autograd.Function):
-    """z[e] = a[ra.ids[e]] * b[rb.ids[e]] (optionally summed over features -> [E,1])."""
+    """z[e] = a[ra.ids[e]] * b[rb.ids[e]] (optionally summed over features -> [E,1]); rb None = 'row e'."""
 
     @staticmethod
     def forward(ctx, a, b, rel_a, rel_b, reduce):
         ctx.rel_a, ctx.rel_b, ctx.reduce = rel_a, rel_b, reduce
         ctx.save_for_backward(a, b)
-        return raw_g2m(a, rel_a.ids, b, rel_b.ids, rel_a.n_elements, reduce)
+        return raw_g2m(a, rel_a.ids, b, None if rel_b is None else rel_b.ids, rel_a.n_elements, reduce)
 
     @staticmethod
     def backward(ctx, gz):
@@ -243,10 +243,38 @@ class _G2M(torch.autograd.Function):
         gz = gz.contiguous()
         ga = gb = None
         if ctx.needs_input_grad[0]:
-            ga = _GMS.apply(b, gz, ctx.rel_a, ctx.rel_b)
+            ga = _GMS.apply(b, gz, ctx.rel_a, ctx.rel_b) if ctx.rel_b is not None \
+                else _GMS_edge.apply(b, gz, ctx.rel_a)
         if ctx.needs_input_grad[1]:
-            gb = _GMS.apply(a, gz, ctx.rel_b, ctx.rel_a)
+            if ctx.rel_b is not None:
+                gb = _GMS.apply(a, gz, ctx.rel_b, ctx.rel_a)
+            elif gz.shape[1] == a.shape[1]:
+                gb = _G2M.apply(a, gz, ctx.rel_a, None, False)
+            else:
+                gb = _Gather.apply(a, ctx.rel_a) * gz
         return ga, gb, None, None, None
+
+
+class _GMS_edge(torch.autograd.Function):
+    """y[i] = sum_{e: rel.ids[e]==i} v[e] * w[e]  (PoolingWeightedLocalEdges, pooling.py:152-162)."""
+
+    @staticmethod
+    def forward(ctx, v, w, rel):
+        ctx.rel = rel
+        ctx.save_for_backward(v, w)
+        return raw_gms(v, w, rel, None, OP_SUM)
+
+    @staticmethod
+    def backward(ctx, g):
+        v, w = ctx.saved_tensors
+        g = g.contiguous()
+        gv = gw = None
+        if ctx.needs_input_grad[0]:
+            gv = _G2M.apply(g, w, ctx.rel, None, False) if w.shape[1] == v.shape[1] \
+                else _Gather.apply(g, ctx.rel) * w
+        if ctx.needs_input_grad[1]:
+            gw = _G2M.apply(g, v, ctx.rel, None, w.shape[1] == 1 and v.shape[1] != 1)
+        return gv, gw, None
 
 
 def gather(x, rel):

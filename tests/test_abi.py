@@ -1,0 +1,65 @@
+"""CPU checks of the drop-in boundary: the C-ABI library loads and exports every symbol the header declares
+(no compute call without a GPU), and the product fails loudly instead of falling back to the CPU."""
+import ctypes
+import os
+
+import pytest
+import torch
+
+from gcnn_keras_b200 import _lib
+
+
+def test_library_exists_and_loads():
+    assert os.path.exists(_lib.LIB_PATH), "run `python -m gcnn_keras_b200.build` first"
+    handle = _lib.lib()
+    assert handle.kgcnn_version() >= 100
+    assert handle.kgcnn_error_string(0) == b"ok"
+    assert handle.kgcnn_error_string(-3) == b"CUDA launch error"
+
+
+def test_every_header_symbol_is_exported_and_bound():
+    declared = _lib.header_symbols()
+    assert len(declared) >= 15
+    raw = ctypes.CDLL(_lib.LIB_PATH)
+    for name in declared:
+        assert hasattr(raw, name), "header declares %s but the library does not export it" % name
+    assert set(declared) == set(_lib.SIGNATURES), \
+        "ctypes table and header disagree: %s" % (set(declared) ^ set(_lib.SIGNATURES))
+
+
+def test_argument_validation_without_gpu():
+    h = _lib.lib()
+    # invalid arguments are rejected before any launch, so these are safe on a CPU-only machine
+    assert h.kgcnn_gather_rows(None, 4, 0, None, 1, 4, None, 4, None) == -1          # F <= 0
+    assert h.kgcnn_gather_rows(None, 4, 8, None, 1, 0, None, 8, None) == 0           # E == 0 is a no-op
+    assert h.kgcnn_gather_mul_segment_reduce(None, 8, None, 3, None, None, None, 1, 0, 4, 0, None, None) == -1
+    assert h.kgcnn_gather_mul_segment_reduce(None, 8, None, 0, None, None, None, 1, 0, 4, 7, None, None) == -1
+    assert h.kgcnn_gather_mul_segment_reduce(None, 8, None, 0, None, None, None, 1, 0, 0, 0, None, None) == 0
+    assert h.kgcnn_plan_workspace_bytes(1000, 100) > 3 * 4000
+
+
+def test_no_cpu_fallback():
+    from gcnn_keras_b200 import functional as F
+    x = torch.zeros(4, 8)
+    ids = torch.zeros(3, dtype=torch.int32)
+    with pytest.raises(_lib.KgcnnError):
+        F.raw_gather_rows(x, ids)
+
+
+def test_product_does_not_import_oracle():
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    pkg = os.path.join(root, "gcnn_keras_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith(".py"):
+                text = open(os.path.join(dirpath, f)).read()
+                assert "import oracle" not in text and "from oracle" not in text, \
+                    "%s imports the oracle" % os.path.join(dirpath, f)
+
+
+def test_segment_name_dispatch_errors():
+    from gcnn_keras_b200 import functional as F
+    assert F.op_code("segment_sum") == F.op_code("sum") == F.op_code("reduce_sum") == 0
+    assert F.op_code("mean") == 1 and F.op_code("segment_max") == 2 and F.op_code("reduce_min") == 3
+    with pytest.raises(TypeError):
+        F.op_code("softmax")
