@@ -151,8 +151,9 @@ void kgcnn_launch_count_reset(void) { g_launches.store(0, std::memory_order_rela
 int kgcnn_shift_index(const int64_t* idx, int64_t E, int K, const int64_t* node_row_splits,
                       const int64_t* edge_row_splits, int64_t B, int64_t* out_i64, int32_t* out_i32,
                       kgcnn_stream_t stream) {
-  if (E < 0 || K <= 0 || B < 0 || (!out_i64 && !out_i32)) return KGCNN_E_INVALID;
+  if (E < 0 || K <= 0 || B < 0) return KGCNN_E_INVALID;
   if (E == 0) return KGCNN_OK;
+  if (!out_i64 && !out_i32) return KGCNN_E_INVALID;
   if (!idx || !node_row_splits || !edge_row_splits || B == 0) return KGCNN_E_INVALID;
   shift_index_kernel<<<blocks_for(E), kThreads, 0, as_stream(stream)>>>(idx, E, K, node_row_splits,
                                                                         edge_row_splits, B, out_i64, out_i32);

@@ -4,11 +4,12 @@
 //   kgcnn/layers/gather.py:228, kgcnn/layers/conv/schnet_conv.py:76-78, kgcnn/layers/pooling.py:63-76,
 //   kgcnn/layers/pooling.py:152-172 (weighted), :215-218 (per-graph pooling).
 //
-// Mapping: one warp owns one output row.  The warp is split into G = 32/LPR lane groups; a group owns
-// a 128-bit (or 32-bit) column slice per lane and walks every G-th edge of the segment, so a warp keeps
-// G*U gathered rows in flight.  Edge ids / source rows for 32 consecutive CSR positions are fetched with
-// one coalesced load and broadcast by shuffle.  The in-group order (p ascending) and the cross-group
-// combine tree are fixed, so results are bitwise reproducible run to run.
+// Mapping: one warp owns one output row.  The warp is split into G = 32/LPR lane groups; a lane owns VPL
+// 128-bit (or 32-bit) column slices and the group walks every G-th edge of the segment with U edges in
+// flight, so a warp keeps G*U gathered rows in flight.  The in-group order (p ascending) and the
+// cross-group combine tree are fixed, so results are bitwise reproducible run to run.
+// r1 ncu (profiles/): with 16 lanes/row + shuffle-broadcast indices the kernel was issue-bound (73 % issue
+// slots, 15 % DRAM); 8 lanes/row with 2-4 vectors per lane halves the per-edge instruction count.
 #pragma once
 #include "common.cuh"
 
@@ -64,7 +65,7 @@ struct Vec<float> {
   static __device__ __forceinline__ float shfl_xor(const float& a, int o) { return __shfl_xor_sync(0xffffffffu, a, o); }
 };
 
-template <typename V, int LPR, int VPL, int MODE, bool GATHER>
+template <typename V, int LPR, int VPL, int MODE, bool GATHER, bool EXACT>
 __global__ void __launch_bounds__(kThreads)
 gms_kernel(const V* __restrict__ x, const V* __restrict__ wv, const float* __restrict__ ws,
            const int32_t* __restrict__ rowptr, const int32_t* __restrict__ perm, const int32_t* __restrict__ gidx,
@@ -78,62 +79,79 @@ gms_kernel(const V* __restrict__ x, const V* __restrict__ wv, const float* __res
   if (row >= n_out) return;  // warp-uniform
   const int cbase = blockIdx.y * (LPR * VPL) + sub;
   const int beg = __ldg(rowptr + row), end = __ldg(rowptr + row + 1);
+  bool cok[VPL];
+#pragma unroll
+  for (int k = 0; k < VPL; ++k) cok[k] = EXACT || (cbase + k * LPR < nvec);
 
   V acc[VPL];
   const float init = (MODE == kMax) ? -INFINITY : (MODE == kMin) ? INFINITY : 0.f;
 #pragma unroll
   for (int k = 0; k < VPL; ++k) acc[k] = T::fill(init);
 
-  for (int pb = beg; pb < end; pb += 32) {
-    const int p = pb + lane;
-    int e_l = 0, s_l = 0;
-    if (p < end) {
-      e_l = perm ? __ldg(perm + p) : p;
-      if (GATHER) s_l = __ldg(gidx + static_cast<int64_t>(gidx_permuted ? p : e_l) * gidx_stride);
-      else s_l = e_l;
-    }
-    const int cnt = min(32, end - pb);
-    for (int j0 = 0; j0 < cnt; j0 += G * U) {
-      V xv[U][VPL];
-      V wvv[U][VPL];
-      float wsv[U];
-      bool ok[U];
+  // e = original edge id (for the weight row), s = source row of x
+  auto resolve = [&](int p, int& e, int& s) {
+    e = perm ? __ldg(perm + p) : p;
+    if (GATHER) s = __ldg(gidx + static_cast<int64_t>(gidx_permuted ? p : e) * gidx_stride);
+    else s = e;
+  };
+  auto accumulate = [&](V (&xv)[VPL], V (&wr)[VPL], float wsc) {
 #pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const int j = j0 + u * G + g;
-        ok[u] = j < cnt;
-        const int64_t sj = __shfl_sync(0xffffffffu, s_l, j & 31);
-        const int64_t ej = __shfl_sync(0xffffffffu, e_l, j & 31);
-        if (ok[u]) {
-#pragma unroll
-          for (int k = 0; k < VPL; ++k) {
-            const int c = cbase + k * LPR;
-            if (c < nvec) {
-              xv[u][k] = GATHER ? T::ld_keep(x + sj * nvec + c) : T::ld_stream(x + sj * nvec + c);
-              if (MODE == kSumW2) wvv[u][k] = T::ld_stream(wv + ej * nvec + c);
-            }
-          }
-          if (MODE == kSumW1) wsv[u] = __ldg(ws + ej);
-        }
-      }
-#pragma unroll
-      for (int u = 0; u < U; ++u) {
-        if (ok[u]) {
-#pragma unroll
-          for (int k = 0; k < VPL; ++k) {
-            const int c = cbase + k * LPR;
-            if (c < nvec) {
-              if (MODE == kSumW0) T::add(acc[k], xv[u][k]);
-              else if (MODE == kSumW1) T::fmas(acc[k], xv[u][k], wsv[u]);
-              else if (MODE == kSumW2) T::fma(acc[k], xv[u][k], wvv[u][k]);
-              else if (MODE == kMax) T::vmax(acc[k], xv[u][k]);
-              else T::vmin(acc[k], xv[u][k]);
-            }
-          }
-        }
+    for (int k = 0; k < VPL; ++k) {
+      if (cok[k]) {
+        if (MODE == kSumW0) T::add(acc[k], xv[k]);
+        else if (MODE == kSumW1) T::fmas(acc[k], xv[k], wsc);
+        else if (MODE == kSumW2) T::fma(acc[k], xv[k], wr[k]);
+        else if (MODE == kMax) T::vmax(acc[k], xv[k]);
+        else T::vmin(acc[k], xv[k]);
       }
     }
+  };
+
+  int p = beg + g;
+  // main loop: U edges per lane group in flight, no predicates on the edge index
+  for (; p + (U - 1) * G < end; p += U * G) {
+    int e[U], s[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) resolve(p + u * G, e[u], s[u]);
+    V xv[U][VPL];
+    V wr[U][VPL];
+    float wsc[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const V* xr = x + static_cast<int64_t>(s[u]) * nvec + cbase;
+      const V* wrow = wv + static_cast<int64_t>(e[u]) * nvec + cbase;
+#pragma unroll
+      for (int k = 0; k < VPL; ++k) {
+        if (cok[k]) {
+          xv[u][k] = GATHER ? T::ld_keep(xr + k * LPR) : T::ld_stream(xr + k * LPR);
+          if (MODE == kSumW2) wr[u][k] = T::ld_stream(wrow + k * LPR);
+        }
+      }
+      if (MODE == kSumW1) wsc[u] = __ldg(ws + e[u]);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) accumulate(xv[u], wr[u], wsc[u]);
   }
+  // tail: one edge per lane group
+  for (; p < end; p += G) {
+    int e, s;
+    resolve(p, e, s);
+    V xv[VPL];
+    V wr[VPL];
+    float wsc = 0.f;
+    const V* xr = x + static_cast<int64_t>(s) * nvec + cbase;
+    const V* wrow = wv + static_cast<int64_t>(e) * nvec + cbase;
+#pragma unroll
+    for (int k = 0; k < VPL; ++k) {
+      if (cok[k]) {
+        xv[k] = GATHER ? T::ld_keep(xr + k * LPR) : T::ld_stream(xr + k * LPR);
+        if (MODE == kSumW2) wr[k] = T::ld_stream(wrow + k * LPR);
+      }
+    }
+    if (MODE == kSumW1) wsc = __ldg(ws + e);
+    accumulate(xv, wr, wsc);
+  }
+  __syncwarp();
   // fixed combine tree across the G lane groups
 #pragma unroll
   for (int o = LPR; o < 32; o <<= 1) {
@@ -147,14 +165,13 @@ gms_kernel(const V* __restrict__ x, const V* __restrict__ wv, const float* __res
   }
   if (g == 0) {
     const bool empty = end <= beg;
-    const float s = (mean && !empty) ? 1.f / static_cast<float>(end - beg) : 1.f;
+    const float sc = (mean && !empty) ? 1.f / static_cast<float>(end - beg) : 1.f;
 #pragma unroll
     for (int k = 0; k < VPL; ++k) {
-      const int c = cbase + k * LPR;
-      if (c < nvec) {
+      if (cok[k]) {
         V out = empty ? T::fill(0.f) : acc[k];
-        if (mean) out = T::scale(out, s);
-        T::st(y + row * nvec + c, out);
+        if (mean) out = T::scale(out, sc);
+        T::st(y + row * nvec + cbase + k * LPR, out);
       }
     }
   }
@@ -165,8 +182,16 @@ int launch_shape(int mode, bool gather, const V* x, const V* wv, const float* ws
                  const int32_t* perm, const int32_t* gidx, int gs, int gp, int64_t n_out, int nvec, int mean, V* y,
                  cudaStream_t st) {
   dim3 grid(static_cast<unsigned>(ceil_div<int64_t>(n_out, kWarps)), static_cast<unsigned>(ceil_div(nvec, LPR * VPL)));
-#define KGCNN_GMS_LAUNCH(M, GA) \
-  gms_kernel<V, LPR, VPL, M, GA><<<grid, kThreads, 0, st>>>(x, wv, ws, rowptr, perm, gidx, gs, gp, n_out, nvec, mean, y)
+  const bool exact = (nvec == LPR * VPL);
+#define KGCNN_GMS_LAUNCH(M, GA)                                                                                  \
+  do {                                                                                                           \
+    if (exact)                                                                                                   \
+      gms_kernel<V, LPR, VPL, M, GA, true><<<grid, kThreads, 0, st>>>(x, wv, ws, rowptr, perm, gidx, gs, gp,     \
+                                                                      n_out, nvec, mean, y);                     \
+    else                                                                                                         \
+      gms_kernel<V, LPR, VPL, M, GA, false><<<grid, kThreads, 0, st>>>(x, wv, ws, rowptr, perm, gidx, gs, gp,    \
+                                                                       n_out, nvec, mean, y);                    \
+  } while (0)
   if (mode == kMax) { if (gather) return KGCNN_E_UNSUPPORTED; KGCNN_GMS_LAUNCH(kMax, false); }
   else if (mode == kMin) { if (gather) return KGCNN_E_UNSUPPORTED; KGCNN_GMS_LAUNCH(kMin, false); }
   else if (mode == kSumW0) { if (gather) KGCNN_GMS_LAUNCH(kSumW0, true); else KGCNN_GMS_LAUNCH(kSumW0, false); }
@@ -182,13 +207,17 @@ int launch(int mode, bool gather, const V* x, const V* wv, const float* ws, cons
            cudaStream_t st) {
 #define KGCNN_GMS_SHAPE(L, P) \
   return launch_shape<V, L, P>(mode, gather, x, wv, ws, rowptr, perm, gidx, gs, gp, n_out, nvec, mean, y, st)
+  // few lanes per row -> many edges per warp instruction (the kernel is issue-bound, not DRAM-bound, when
+  // gathered rows hit in L1/L2); 8 lanes x 128 bit = one full 128 B line per request.
   if (nvec <= 1) KGCNN_GMS_SHAPE(1, 1);
   if (nvec <= 2) KGCNN_GMS_SHAPE(2, 1);
   if (nvec <= 4) KGCNN_GMS_SHAPE(4, 1);
   if (nvec <= 8) KGCNN_GMS_SHAPE(8, 1);
-  if (nvec <= 16) KGCNN_GMS_SHAPE(16, 1);
-  if (nvec <= 32) KGCNN_GMS_SHAPE(32, 1);
-  if (nvec <= 64) KGCNN_GMS_SHAPE(32, 2);
+  if (nvec <= 16) KGCNN_GMS_SHAPE(8, 2);
+  if (nvec <= 24) KGCNN_GMS_SHAPE(8, 3);
+  if (nvec <= 32) KGCNN_GMS_SHAPE(8, 4);
+  if (nvec <= 48) KGCNN_GMS_SHAPE(16, 3);
+  if (nvec <= 64) KGCNN_GMS_SHAPE(16, 4);
   if (nvec <= 96) KGCNN_GMS_SHAPE(32, 3);
   KGCNN_GMS_SHAPE(32, 4);
 #undef KGCNN_GMS_SHAPE

@@ -146,6 +146,8 @@ def raw_gms(x2d, w, rel_out, rel_src, op=OP_SUM):
         w = _f32c(w)
         wcols = int(w.shape[1]) if w.dim() == 2 else 1
     n_out = rel_out.n_targets
+    if rel_out.n_elements == 0 or x2d.shape[0] == 0:      # every segment is empty -> 0 (no launch needed)
+        return torch.zeros((n_out, Fdim), dtype=torch.float32, device=x2d.device)
     y = torch.empty((n_out, Fdim), dtype=torch.float32, device=x2d.device)
     perm = rel_out.perm
     if rel_src is not None:

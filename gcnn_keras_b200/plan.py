@@ -99,7 +99,18 @@ class IndexPlan:
         return self._relations[col]
 
 
-_PLAN_CACHE = weakref.WeakKeyDictionary()   # index values tensor -> {(node splits ptr): IndexPlan}
+_PLAN_CACHE = {}   # id(index values tensor) -> (weakref to it, {key: (IndexPlan, partitions...)})
+
+
+def _cache_slot(vals):
+    """Per-tensor dict keyed by object identity (tensors define == elementwise, so no WeakKeyDictionary)."""
+    key = id(vals)
+    slot = _PLAN_CACHE.get(key)
+    if slot is not None and slot[0]() is vals:
+        return slot[1]
+    per_tensor = {}
+    _PLAN_CACHE[key] = (weakref.ref(vals, lambda _, k=key: _PLAN_CACHE.pop(k, None)), per_tensor)
+    return per_tensor
 
 
 def get_plan(index_ragged, node_ragged):
@@ -107,10 +118,7 @@ def get_plan(index_ragged, node_ragged):
     vals = index_ragged.values
     node_part = node_ragged.partition
     key = (id(node_part), vals._version, id(index_ragged.partition))
-    per_tensor = _PLAN_CACHE.get(vals)
-    if per_tensor is None:
-        per_tensor = {}
-        _PLAN_CACHE[vals] = per_tensor
+    per_tensor = _cache_slot(vals)
     entry = per_tensor.get(key)
     if entry is None:
         for k in [k for k in per_tensor if k[1] != vals._version]:
