@@ -32,7 +32,7 @@ SIGNATURES = {
     "kgcnn_permute_i32": (_i, [_p, _i, _p, _l, _p, _p]),
     "kgcnn_gather_rows": (_i, [_p, _l, _i, _p, _i, _l, _p, _l, _p]),
     "kgcnn_gather_rows_i64": (_i, [_p, _l, _i, _p, _i, _l, _p, _l, _p]),
-    "kgcnn_gather_mul_segment_reduce": (_i, [_p, _i, _p, _i, _p, _p, _p, _i, _i, _l, _i, _p, _p]),
+    "kgcnn_gather_mul_segment_reduce": (_i, [_p, _i, _p, _i, _p, _p, _p, _i, _i, _l, _l, _i, _p, _p]),
     "kgcnn_gather2_mul": (_i, [_p, _p, _i, _p, _p, _i, _i, _l, _i, _p, _p]),
 }
 

@@ -65,7 +65,7 @@ struct Vec<float> {
   static __device__ __forceinline__ float shfl_xor(const float& a, int o) { return __shfl_xor_sync(0xffffffffu, a, o); }
 };
 
-template <typename V, int LPR, int VPL, int MODE, bool GATHER, bool EXACT>
+template <typename V, int LPR, int VPL, int MODE, bool GATHER, bool EXACT, bool GPR>
 __global__ void __launch_bounds__(kThreads)
 gms_kernel(const V* __restrict__ x, const V* __restrict__ wv, const float* __restrict__ ws,
            const int32_t* __restrict__ rowptr, const int32_t* __restrict__ perm, const int32_t* __restrict__ gidx,
@@ -75,10 +75,16 @@ gms_kernel(const V* __restrict__ x, const V* __restrict__ wv, const float* __res
   using T = Vec<V>;
   const int lane = threadIdx.x & 31;
   const int g = lane / LPR, sub = lane % LPR;
-  const int64_t row = static_cast<int64_t>(blockIdx.x) * kWarps + (threadIdx.x >> 5);
-  if (row >= n_out) return;  // warp-uniform
+  // GPR (group per row): every lane group owns its own output row and walks it sequentially -- no
+  // cross-group shuffle tree; used for short segments (molecular graphs).  Otherwise the whole warp owns
+  // one row and the groups interleave its edges.
+  constexpr int PS = GPR ? 1 : G;  // stride of this group's walk over CSR positions
+  const int64_t wrow = static_cast<int64_t>(blockIdx.x) * kWarps + (threadIdx.x >> 5);
+  const int64_t row = GPR ? wrow * G + g : wrow;
+  const bool valid = row < n_out;
+  if (!GPR && !valid) return;  // warp-uniform
   const int cbase = blockIdx.y * (LPR * VPL) + sub;
-  const int beg = __ldg(rowptr + row), end = __ldg(rowptr + row + 1);
+  const int beg = valid ? __ldg(rowptr + row) : 0, end = valid ? __ldg(rowptr + row + 1) : 0;
   bool cok[VPL];
 #pragma unroll
   for (int k = 0; k < VPL; ++k) cok[k] = EXACT || (cbase + k * LPR < nvec);
@@ -107,12 +113,12 @@ gms_kernel(const V* __restrict__ x, const V* __restrict__ wv, const float* __res
     }
   };
 
-  int p = beg + g;
+  int p = beg + (GPR ? 0 : g);
   // main loop: U edges per lane group in flight, no predicates on the edge index
-  for (; p + (U - 1) * G < end; p += U * G) {
+  for (; p + (U - 1) * PS < end; p += U * PS) {
     int e[U], s[U];
 #pragma unroll
-    for (int u = 0; u < U; ++u) resolve(p + u * G, e[u], s[u]);
+    for (int u = 0; u < U; ++u) resolve(p + u * PS, e[u], s[u]);
     V xv[U][VPL];
     V wr[U][VPL];
     float wsc[U];
@@ -133,7 +139,7 @@ gms_kernel(const V* __restrict__ x, const V* __restrict__ wv, const float* __res
     for (int u = 0; u < U; ++u) accumulate(xv[u], wr[u], wsc[u]);
   }
   // tail: one edge per lane group
-  for (; p < end; p += G) {
+  for (; p < end; p += PS) {
     int e, s;
     resolve(p, e, s);
     V xv[VPL];
@@ -154,7 +160,7 @@ gms_kernel(const V* __restrict__ x, const V* __restrict__ wv, const float* __res
   __syncwarp();
   // fixed combine tree across the G lane groups
 #pragma unroll
-  for (int o = LPR; o < 32; o <<= 1) {
+  for (int o = LPR; o < (GPR ? 0 : 32); o <<= 1) {
 #pragma unroll
     for (int k = 0; k < VPL; ++k) {
       V other = T::shfl_xor(acc[k], o);
@@ -163,7 +169,7 @@ gms_kernel(const V* __restrict__ x, const V* __restrict__ wv, const float* __res
       else T::add(acc[k], other);
     }
   }
-  if (g == 0) {
+  if (GPR ? valid : (g == 0)) {
     const bool empty = end <= beg;
     const float sc = (mean && !empty) ? 1.f / static_cast<float>(end - beg) : 1.f;
 #pragma unroll
@@ -180,17 +186,22 @@ gms_kernel(const V* __restrict__ x, const V* __restrict__ wv, const float* __res
 template <typename V, int LPR, int VPL>
 int launch_shape(int mode, bool gather, const V* x, const V* wv, const float* ws, const int32_t* rowptr,
                  const int32_t* perm, const int32_t* gidx, int gs, int gp, int64_t n_out, int nvec, int mean, V* y,
-                 cudaStream_t st) {
-  dim3 grid(static_cast<unsigned>(ceil_div<int64_t>(n_out, kWarps)), static_cast<unsigned>(ceil_div(nvec, LPR * VPL)));
+                 bool short_rows, cudaStream_t st) {
+  constexpr bool kHasGpr = (LPR >= 4 && LPR < 32);
+  const bool gpr = kHasGpr && short_rows;
+  const int64_t rows_per_block = gpr ? kWarps * (32 / LPR) : kWarps;
+  dim3 grid(static_cast<unsigned>(ceil_div<int64_t>(n_out, rows_per_block)),
+            static_cast<unsigned>(ceil_div(nvec, LPR * VPL)));
   const bool exact = (nvec == LPR * VPL);
-#define KGCNN_GMS_LAUNCH(M, GA)                                                                                  \
-  do {                                                                                                           \
-    if (exact)                                                                                                   \
-      gms_kernel<V, LPR, VPL, M, GA, true><<<grid, kThreads, 0, st>>>(x, wv, ws, rowptr, perm, gidx, gs, gp,     \
-                                                                      n_out, nvec, mean, y);                     \
-    else                                                                                                         \
-      gms_kernel<V, LPR, VPL, M, GA, false><<<grid, kThreads, 0, st>>>(x, wv, ws, rowptr, perm, gidx, gs, gp,    \
-                                                                       n_out, nvec, mean, y);                    \
+#define KGCNN_GMS_ARGS x, wv, ws, rowptr, perm, gidx, gs, gp, n_out, nvec, mean, y
+#define KGCNN_GMS_LAUNCH(M, GA)                                                                      \
+  do {                                                                                               \
+    if constexpr (kHasGpr) {                                                                         \
+      if (gpr && exact) gms_kernel<V, LPR, VPL, M, GA, true, true><<<grid, kThreads, 0, st>>>(KGCNN_GMS_ARGS);        \
+      else if (gpr) gms_kernel<V, LPR, VPL, M, GA, false, true><<<grid, kThreads, 0, st>>>(KGCNN_GMS_ARGS);           \
+    }                                                                                                \
+    if (!gpr && exact) gms_kernel<V, LPR, VPL, M, GA, true, false><<<grid, kThreads, 0, st>>>(KGCNN_GMS_ARGS);        \
+    else if (!gpr) gms_kernel<V, LPR, VPL, M, GA, false, false><<<grid, kThreads, 0, st>>>(KGCNN_GMS_ARGS);           \
   } while (0)
   if (mode == kMax) { if (gather) return KGCNN_E_UNSUPPORTED; KGCNN_GMS_LAUNCH(kMax, false); }
   else if (mode == kMin) { if (gather) return KGCNN_E_UNSUPPORTED; KGCNN_GMS_LAUNCH(kMin, false); }
@@ -198,15 +209,16 @@ int launch_shape(int mode, bool gather, const V* x, const V* wv, const float* ws
   else if (mode == kSumW1) { if (gather) KGCNN_GMS_LAUNCH(kSumW1, true); else KGCNN_GMS_LAUNCH(kSumW1, false); }
   else { if (gather) KGCNN_GMS_LAUNCH(kSumW2, true); else KGCNN_GMS_LAUNCH(kSumW2, false); }
 #undef KGCNN_GMS_LAUNCH
+#undef KGCNN_GMS_ARGS
   return finish_launch();
 }
 
 template <typename V>
 int launch(int mode, bool gather, const V* x, const V* wv, const float* ws, const int32_t* rowptr,
            const int32_t* perm, const int32_t* gidx, int gs, int gp, int64_t n_out, int nvec, int mean, V* y,
-           cudaStream_t st) {
+           bool short_rows, cudaStream_t st) {
 #define KGCNN_GMS_SHAPE(L, P) \
-  return launch_shape<V, L, P>(mode, gather, x, wv, ws, rowptr, perm, gidx, gs, gp, n_out, nvec, mean, y, st)
+  return launch_shape<V, L, P>(mode, gather, x, wv, ws, rowptr, perm, gidx, gs, gp, n_out, nvec, mean, y, short_rows, st)
   // few lanes per row -> many edges per warp instruction (the kernel is issue-bound, not DRAM-bound, when
   // gathered rows hit in L1/L2); 8 lanes x 128 bit = one full 128 B line per request.
   if (nvec <= 1) KGCNN_GMS_SHAPE(1, 1);
@@ -225,9 +237,11 @@ int launch(int mode, bool gather, const V* x, const V* wv, const float* ws, cons
 
 // defined in segment_v4.cu / segment_v1.cu
 int launch_v4(int mode, bool gather, const float* x, const float* w, const int32_t* rowptr, const int32_t* perm,
-              const int32_t* gidx, int gs, int gp, int64_t n_out, int F, int mean, float* y, cudaStream_t st);
+              const int32_t* gidx, int gs, int gp, int64_t n_out, int F, int mean, float* y, bool short_rows,
+              cudaStream_t st);
 int launch_v1(int mode, bool gather, const float* x, const float* w, const int32_t* rowptr, const int32_t* perm,
-              const int32_t* gidx, int gs, int gp, int64_t n_out, int F, int mean, float* y, cudaStream_t st);
+              const int32_t* gidx, int gs, int gp, int64_t n_out, int F, int mean, float* y, bool short_rows,
+              cudaStream_t st);
 
 }  // namespace seg
 }  // namespace kgcnn

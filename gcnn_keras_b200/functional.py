@@ -156,7 +156,8 @@ def raw_gms(x2d, w, rel_out, rel_src, op=OP_SUM):
     else:
         gidx, gperm = None, 0
     check(_lib.lib().kgcnn_gather_mul_segment_reduce(_ptr(x2d), Fdim, _ptr(w), wcols, _ptr(rel_out.rowptr),
-                                                     _ptr(perm), _ptr(gidx), 1, gperm, n_out, op, _ptr(y),
+                                                     _ptr(perm), _ptr(gidx), 1, gperm, n_out, rel_out.n_elements, op,
+                                                     _ptr(y),
                                                      _stream()), "kgcnn_gather_mul_segment_reduce")
     return y
 

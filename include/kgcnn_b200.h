@@ -113,6 +113,8 @@ int kgcnn_gather_rows_i64(const int64_t* x, int64_t N, int F, const int32_t* idx
  *         e(p)   = perm ? perm[p] : p                      (original edge id, stable order)
  *         src(p) = gidx ? gidx[e(p)*gidx_stride] : e(p)    (gidx==NULL: x is the edge tensor itself)
  *         gidx_permuted != 0: gidx is already in CSR order, src(p) = gidx[p*gidx_stride]
+ *     n_elements = rowptr[n_out] (number of edges); only used to pick the mapping: short segments
+ *     (n_elements <= 64 n_out) get one lane group per row, long ones one warp per row.
  *     w_cols in {0 (no weight), 1 (per-edge scalar), F (per-edge row)}; op MAX/MIN require w_cols==0.
  *     Empty segment -> 0 for every op (kgcnn/layers/pooling.py:71-76: sorted segment op + scatter_nd
  *     zero padding).  MEAN divides by the segment length (kgcnn/ops/segment.py:39-40).
@@ -122,8 +124,8 @@ int kgcnn_gather_rows_i64(const int64_t* x, int64_t N, int F, const int32_t* idx
  * ------------------------------------------------------------------------------------------- */
 int kgcnn_gather_mul_segment_reduce(const float* x, int F, const float* w, int w_cols,
                                     const int32_t* rowptr, const int32_t* perm, const int32_t* gidx,
-                                    int gidx_stride, int gidx_permuted, int64_t n_out, int op, float* y,
-                                    kgcnn_stream_t stream);
+                                    int gidx_stride, int gidx_permuted, int64_t n_out, int64_t n_elements,
+                                    int op, float* y, kgcnn_stream_t stream);
 
 /* z[e, f] = a[ia[e], f] * b[ib[e], f]   (reduce_f==0)   or   z[e] = sum_f a[ia[e],f]*b[ib[e],f]
  * ia/ib == NULL means "row e".  VJP of the fused op above with respect to w. */

@@ -305,3 +305,28 @@ def test_empty_inputs():
     e = device_ragged(np.zeros((0, 8), dtype=np.float32), edge_len)
     p = PoolingLocalEdges(pooling_method="sum")([nodes, e, idx])
     assert tuple(p.values.shape) == (5, 8) and float(p.values.abs().sum()) == 0.0
+
+
+@pytest.mark.parametrize("feat", [1, 3, 64, 128, 200])
+def test_long_segments_warp_per_row_path(feat):
+    """Average segment length > 64 selects the warp-per-row mapping (hub nodes / per-graph pooling)."""
+    from gcnn_keras_b200 import functional as F
+    from gcnn_keras_b200.layers.pooling import PoolingNodes
+    from gcnn_keras_b200.plan import Relation
+    rng = np.random.default_rng(12)
+    node_len = np.array([300, 0, 150, 97], dtype=np.int64)
+    x = rng.standard_normal((int(node_len.sum()), feat)).astype(np.float32)
+    for method in ("sum", "mean", "max", "min"):
+        want = OL.pooling_embedding(oracle_ragged(x, node_len, torch.float64), method)
+        got = PoolingNodes(pooling_method=method)(device_ragged(x, node_len))
+        assert rel_err(got.cpu().numpy(), want.numpy()) < RTOL
+    # hub graph: 3 receivers, 400 unsorted edges, gather from 50 sources with a per-edge weight row
+    recv = rng.integers(0, 3, size=400).astype(np.int32)
+    send = rng.integers(0, 50, size=400).astype(np.int32)
+    src = rng.standard_normal((50, feat)).astype(np.float32)
+    w = rng.standard_normal((400, feat)).astype(np.float32)
+    r_out, r_src = Relation(torch.tensor(recv).cuda(), 3), Relation(torch.tensor(send).cuda(), 50)
+    got = F.gather_mul_segment_sum(torch.tensor(src).cuda(), torch.tensor(w).cuda(), r_out, r_src)
+    want = np.zeros((3, feat))
+    np.add.at(want, recv, src[send].astype(np.float64) * w.astype(np.float64))
+    assert rel_err(got.cpu().numpy(), want) < RTOL
