@@ -34,11 +34,14 @@ SIGNATURES = {
     "kgcnn_gather_rows_i64": (_i, [_p, _l, _i, _p, _i, _l, _p, _l, _p]),
     "kgcnn_gather_mul_segment_reduce": (_i, [_p, _i, _p, _i, _p, _p, _p, _i, _i, _l, _l, _i, _p, _p]),
     "kgcnn_gather2_mul": (_i, [_p, _p, _i, _p, _p, _i, _i, _l, _i, _p, _p]),
+    "kgcnn_bias_act": (_i, [_p, _p, _p, _p, _i, _i, _l, _i, _p, _p]),
+    "kgcnn_colsum_workspace_bytes": (_z, [_l, _i]),
+    "kgcnn_colsum": (_i, [_p, _l, _i, _p, _p, _z, _p]),
 }
 
 OP_SUM, OP_MEAN, OP_MAX, OP_MIN = 0, 1, 2, 3
 BASIS_NONE, BASIS_GAUSS, BASIS_BESSEL = 0, 1, 2
-ACT_CODES = {"linear": 0, "shifted_softplus": 1, "swish": 2, "tanh": 3, "relu": 4, "softplus2": 5}
+ACT_CODES = {"linear": 0, "shifted_softplus": 1, "swish": 2, "tanh": 3, "relu": 4, "softplus2": 5, "sigmoid": 6}
 
 _lib = None
 

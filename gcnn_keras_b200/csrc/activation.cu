@@ -1,0 +1,180 @@
+// Fused bias + activation (and its derivatives) on the flat values of a ragged tensor:
+//     out = g1 * g2 * f^(order)(pre + bias)         order in {0,1,2,3}
+// f from kgcnn/ops/activ.py:5-107 (shifted_softplus, softplus2, swish) and the keras built-ins the named
+// models use (tanh, relu, sigmoid, linear).  One kernel family is closed under differentiation: the VJP of
+// order k is order k+1 with one more multiplier, which is what the force-training double backward needs
+// (kgcnn/model/force.py:159-176 differentiates dE/dx once more with respect to the weights).
+// Replaces BiasAdd + activation + the Lazy* multiplies around it (kgcnn/layers/modules.py:85).
+#include <algorithm>
+
+#include "common.cuh"
+
+namespace kgcnn {
+namespace {
+
+__device__ __forceinline__ float sigmoidf_acc(float x) {
+  // accurate for both signs (no overflow): 1/(1+e^-x) = e^x/(1+e^x)
+  if (x >= 0.f) return 1.f / (1.f + expf(-x));
+  float e = expf(x);
+  return e / (1.f + e);
+}
+
+template <int ACT>
+__device__ __forceinline__ float act_deriv(float x, int order) {
+  if (ACT == KGCNN_ACT_LINEAR) {
+    return order == 0 ? x : (order == 1 ? 1.f : 0.f);
+  } else if (ACT == KGCNN_ACT_RELU) {
+    return order == 0 ? fmaxf(x, 0.f) : (order == 1 ? (x > 0.f ? 1.f : 0.f) : 0.f);
+  } else if (ACT == KGCNN_ACT_TANH) {
+    float t = tanhf(x);
+    float d = 1.f - t * t;
+    if (order == 0) return t;
+    if (order == 1) return d;
+    if (order == 2) return -2.f * t * d;
+    return -2.f * d * (1.f - 3.f * t * t);
+  } else {
+    float s = sigmoidf_acc(x);
+    float s1 = s * (1.f - s);
+    float s2 = s1 * (1.f - 2.f * s);
+    if (ACT == KGCNN_ACT_SHIFTED_SOFTPLUS || ACT == KGCNN_ACT_SOFTPLUS2) {
+      // softplus(x) - log 2 (activ.py:15) == relu(x) + log(0.5 exp(-|x|) + 0.5) (activ.py:29)
+      if (order == 0) return fmaxf(x, 0.f) + log1pf(expf(-fabsf(x))) - 0.69314718055994530942f;
+      if (order == 1) return s;
+      if (order == 2) return s1;
+      return s2;
+    }
+    if (ACT == KGCNN_ACT_SIGMOID) {
+      if (order == 0) return s;
+      if (order == 1) return s1;
+      if (order == 2) return s2;
+      return s2 * (1.f - 2.f * s) - 2.f * s1 * s1;
+    }
+    // swish x*sigmoid(x) (activ.py:102)
+    if (order == 0) return x * s;
+    if (order == 1) return s + x * s1;
+    if (order == 2) return 2.f * s1 + x * s2;
+    float s3 = s2 * (1.f - 2.f * s) - 2.f * s1 * s1;
+    return 3.f * s2 + x * s3;
+  }
+}
+
+template <int ACT, bool VEC>
+__global__ void __launch_bounds__(256)
+bias_act_kernel(const float* __restrict__ pre, const float* __restrict__ bias, const float* __restrict__ g1,
+                const float* __restrict__ g2, int order, int64_t total, int U, float* __restrict__ out) {
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  if (VEC) {
+    const int64_t nv = total >> 2;
+    for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < nv; i += stride) {
+      float4 p = reinterpret_cast<const float4*>(pre)[i];
+      if (bias) {
+        const int c = static_cast<int>((i << 2) % U);
+        float4 b = *reinterpret_cast<const float4*>(bias + c);
+        p.x += b.x; p.y += b.y; p.z += b.z; p.w += b.w;
+      }
+      float4 r = make_float4(act_deriv<ACT>(p.x, order), act_deriv<ACT>(p.y, order), act_deriv<ACT>(p.z, order),
+                             act_deriv<ACT>(p.w, order));
+      if (g1) { float4 m = reinterpret_cast<const float4*>(g1)[i]; r.x *= m.x; r.y *= m.y; r.z *= m.z; r.w *= m.w; }
+      if (g2) { float4 m = reinterpret_cast<const float4*>(g2)[i]; r.x *= m.x; r.y *= m.y; r.z *= m.z; r.w *= m.w; }
+      reinterpret_cast<float4*>(out)[i] = r;
+    }
+  } else {
+    for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total; i += stride) {
+      float p = pre[i];
+      if (bias) p += bias[i % U];
+      float r = act_deriv<ACT>(p, order);
+      if (g1) r *= g1[i];
+      if (g2) r *= g2[i];
+      out[i] = r;
+    }
+  }
+}
+
+template <int ACT>
+int launch_act(const float* pre, const float* bias, const float* g1, const float* g2, int order, int64_t total,
+               int U, float* out, cudaStream_t st) {
+  auto al = [](const void* p) { return p == nullptr || (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
+  const bool vec = (U % 4 == 0) && al(pre) && al(bias) && al(g1) && al(g2) && al(out);
+  const int64_t work = vec ? (total >> 2) : total;
+  const unsigned grid = static_cast<unsigned>(std::min<int64_t>(ceil_div<int64_t>(work, 256), kNumSM * 16));
+  if (vec) bias_act_kernel<ACT, true><<<grid, 256, 0, st>>>(pre, bias, g1, g2, order, total, U, out);
+  else bias_act_kernel<ACT, false><<<grid, 256, 0, st>>>(pre, bias, g1, g2, order, total, U, out);
+  return finish_launch();
+}
+
+// deterministic column sum: out[u] = sum_m a[m,u]   (bias gradients).  Two fixed-shape stages.
+constexpr int kColTile = 32, kRowThreads = 8, kRowsPerBlock = 512;
+
+__global__ void __launch_bounds__(kColTile * kRowThreads)
+colsum_kernel(const float* __restrict__ a, int64_t M, int U, int64_t rows_per_block, float* __restrict__ out) {
+  __shared__ float sm[kRowThreads][kColTile + 1];
+  const int tx = threadIdx.x % kColTile, ty = threadIdx.x / kColTile;
+  const int col = blockIdx.x * kColTile + tx;
+  const int64_t r0 = blockIdx.y * rows_per_block;
+  const int64_t r1 = min(M, r0 + rows_per_block);
+  float acc = 0.f;
+  if (col < U)
+    for (int64_t r = r0 + ty; r < r1; r += kRowThreads) acc += a[r * U + col];
+  sm[ty][tx] = acc;
+  __syncthreads();
+  if (ty == 0 && col < U) {
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < kRowThreads; ++k) s += sm[k][tx];
+    out[static_cast<int64_t>(blockIdx.y) * U + col] = s;
+  }
+}
+
+}  // namespace
+}  // namespace kgcnn
+
+using namespace kgcnn;
+
+extern "C" {
+
+int kgcnn_bias_act(const float* pre, const float* bias, const float* g1, const float* g2, int act, int order,
+                   int64_t M, int U, float* out, kgcnn_stream_t stream) {
+  if (M < 0 || U <= 0 || order < 0 || order > 3) return KGCNN_E_INVALID;
+  if (M == 0) return KGCNN_OK;
+  if (!pre || !out) return KGCNN_E_INVALID;
+  cudaStream_t st = as_stream(stream);
+  const int64_t total = M * U;
+  switch (act) {
+    case KGCNN_ACT_LINEAR: return launch_act<KGCNN_ACT_LINEAR>(pre, bias, g1, g2, order, total, U, out, st);
+    case KGCNN_ACT_SHIFTED_SOFTPLUS:
+      return launch_act<KGCNN_ACT_SHIFTED_SOFTPLUS>(pre, bias, g1, g2, order, total, U, out, st);
+    case KGCNN_ACT_SOFTPLUS2: return launch_act<KGCNN_ACT_SOFTPLUS2>(pre, bias, g1, g2, order, total, U, out, st);
+    case KGCNN_ACT_SWISH: return launch_act<KGCNN_ACT_SWISH>(pre, bias, g1, g2, order, total, U, out, st);
+    case KGCNN_ACT_TANH: return launch_act<KGCNN_ACT_TANH>(pre, bias, g1, g2, order, total, U, out, st);
+    case KGCNN_ACT_RELU: return launch_act<KGCNN_ACT_RELU>(pre, bias, g1, g2, order, total, U, out, st);
+    case KGCNN_ACT_SIGMOID: return launch_act<KGCNN_ACT_SIGMOID>(pre, bias, g1, g2, order, total, U, out, st);
+    default: return KGCNN_E_INVALID;
+  }
+}
+
+size_t kgcnn_colsum_workspace_bytes(int64_t M, int U) {
+  if (M <= 0 || U <= 0) return 0;
+  return static_cast<size_t>(ceil_div<int64_t>(M, kRowsPerBlock)) * U * sizeof(float);
+}
+
+int kgcnn_colsum(const float* a, int64_t M, int U, float* out, void* workspace, size_t workspace_bytes,
+                 kgcnn_stream_t stream) {
+  if (M < 0 || U <= 0 || !out) return KGCNN_E_INVALID;
+  cudaStream_t st = as_stream(stream);
+  if (M == 0) return cudaMemsetAsync(out, 0, sizeof(float) * U, st) == cudaSuccess ? KGCNN_OK : KGCNN_E_CUDA;
+  if (!a) return KGCNN_E_INVALID;
+  const int64_t nblk = ceil_div<int64_t>(M, kRowsPerBlock);
+  dim3 block(kColTile * kRowThreads);
+  if (nblk == 1) {
+    colsum_kernel<<<dim3(ceil_div(U, kColTile), 1), block, 0, st>>>(a, M, U, kRowsPerBlock, out);
+    return finish_launch();
+  }
+  if (!workspace || workspace_bytes < kgcnn_colsum_workspace_bytes(M, U)) return KGCNN_E_WORKSPACE;
+  float* partial = static_cast<float*>(workspace);
+  colsum_kernel<<<dim3(ceil_div(U, kColTile), static_cast<unsigned>(nblk)), block, 0, st>>>(a, M, U, kRowsPerBlock,
+                                                                                             partial);
+  colsum_kernel<<<dim3(ceil_div(U, kColTile), 1), block, 0, st>>>(partial, nblk, U, nblk, out);
+  return finish_launch(2);
+}
+
+}  // extern "C"

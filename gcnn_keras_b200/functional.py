@@ -340,3 +340,114 @@ class _GMS_noW(torch.autograd.Function):
 
 def gather2_mul(a, b, rel_a, rel_b, reduce=False):
     return _G2M.apply(_flat2d(a), _flat2d(b), rel_a, rel_b, reduce)
+
+
+# ------------------------------------------------------------------------------------------------
+# bias + activation family (a19) and deterministic column sum
+# ------------------------------------------------------------------------------------------------
+def act_code(activation):
+    """Keras/kgcnn activation identifier -> kernel enum ('kgcnn>shifted_softplus', 'swish', None, ...)."""
+    if activation is None:
+        return _lib.ACT_CODES["linear"]
+    if isinstance(activation, dict):
+        activation = activation.get("class_name", activation.get("config", {}).get("name"))
+    name = str(activation)
+    if ">" in name:
+        name = name.split(">")[-1]
+    if name not in _lib.ACT_CODES:
+        raise ValueError("Unknown activation function: %s" % activation)
+    return _lib.ACT_CODES[name]
+
+
+def raw_bias_act(pre, bias, g1, g2, act, order):
+    _need_cuda(pre, bias, g1, g2)
+    pre = _f32c(pre)
+    U = int(pre.shape[-1])
+    M = pre.numel() // U if U else 0
+    out = torch.empty_like(pre)
+    g1 = None if g1 is None else _f32c(g1)
+    g2 = None if g2 is None else _f32c(g2)
+    bias = None if bias is None else _f32c(bias)
+    check(_lib.lib().kgcnn_bias_act(_ptr(pre), _ptr(bias), _ptr(g1), _ptr(g2), act, order, M, U, _ptr(out),
+                                    _stream()), "kgcnn_bias_act")
+    return out
+
+
+def raw_colsum(a2d):
+    _need_cuda(a2d)
+    a2d = _f32c(a2d)
+    M, U = int(a2d.shape[0]), int(a2d.shape[1])
+    out = torch.empty((U,), dtype=torch.float32, device=a2d.device)
+    nbytes = int(_lib.lib().kgcnn_colsum_workspace_bytes(M, U))
+    ws = torch.empty((max(nbytes, 4),), dtype=torch.uint8, device=a2d.device)
+    check(_lib.lib().kgcnn_colsum(_ptr(a2d), M, U, _ptr(out), _ptr(ws), nbytes, _stream()), "kgcnn_colsum")
+    return out
+
+
+class _ColSum(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, a):
+        ctx.rows = int(a.shape[0])
+        return raw_colsum(a)
+
+    @staticmethod
+    def backward(ctx, g):
+        return g.unsqueeze(0).expand(ctx.rows, g.shape[0])
+
+
+def colsum(a):
+    return _ColSum.apply(a.reshape(-1, a.shape[-1]))
+
+
+class _BiasAct(torch.autograd.Function):
+    """out = g1 * g2 * f^(order)(pre + bias); its VJPs are the same kernel at order+1 / with swapped multipliers."""
+
+    @staticmethod
+    def forward(ctx, pre, bias, g1, g2, act, order):
+        ctx.act, ctx.order = act, order
+        ctx.save_for_backward(pre, bias, g1, g2)
+        return raw_bias_act(pre, bias, g1, g2, act, order)
+
+    @staticmethod
+    def backward(ctx, gy):
+        pre, bias, g1, g2 = ctx.saved_tensors
+        gy = gy.contiguous()
+        act, k = ctx.act, ctx.order
+        g_pre = g_bias = g_g1 = g_g2 = None
+        if ctx.needs_input_grad[0] or (bias is not None and ctx.needs_input_grad[1]):
+            if k >= 3:
+                raise NotImplementedError("activation derivatives above order 3 are not instantiated")
+            if g1 is not None and g2 is not None:
+                t = _BiasAct.apply(pre, bias, gy * g1, g2, act, k + 1)
+            else:
+                t = _BiasAct.apply(pre, bias, gy, g1 if g1 is not None else g2, act, k + 1)
+            if ctx.needs_input_grad[0]:
+                g_pre = t
+            if bias is not None and ctx.needs_input_grad[1]:
+                g_bias = colsum(t)
+        if g1 is not None and ctx.needs_input_grad[2]:
+            g_g1 = _BiasAct.apply(pre, bias, gy, g2, act, k)
+        if g2 is not None and ctx.needs_input_grad[3]:
+            g_g2 = _BiasAct.apply(pre, bias, gy, g1, act, k)
+        return g_pre, g_bias, g_g1, g_g2, None, None
+
+
+def bias_act(pre, bias, activation):
+    """activation(pre + bias) with any-order derivatives through our kernels."""
+    code = activation if isinstance(activation, int) else act_code(activation)
+    if code == _lib.ACT_CODES["linear"]:
+        return pre if bias is None else pre + bias
+    return _BiasAct.apply(pre, bias, None, None, code, 0)
+
+
+def dense(x, kernel, bias, activation):
+    """DenseEmbedding on flat values (kgcnn/layers/modules.py:85): activation(x @ kernel + bias).
+    The GEMM is a plain library GEMM (cuBLAS fp32, TF32 off); bias + activation (+ derivatives) are ours."""
+    code = activation if isinstance(activation, int) else act_code(activation)
+    lead = x.shape[:-1]
+    x2 = x.reshape(-1, x.shape[-1])
+    if code == _lib.ACT_CODES["linear"]:
+        out = torch.addmm(bias, x2, kernel) if bias is not None else x2 @ kernel
+    else:
+        out = _BiasAct.apply(x2 @ kernel, bias, None, None, code, 0)
+    return out.reshape(tuple(lead) + (kernel.shape[1],))

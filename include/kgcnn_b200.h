@@ -50,7 +50,8 @@ enum {
   KGCNN_ACT_SWISH = 2,
   KGCNN_ACT_TANH = 3,
   KGCNN_ACT_RELU = 4,
-  KGCNN_ACT_SOFTPLUS2 = 5
+  KGCNN_ACT_SOFTPLUS2 = 5,
+  KGCNN_ACT_SIGMOID = 6
 };
 
 int kgcnn_version(void);
@@ -132,6 +133,18 @@ int kgcnn_gather_mul_segment_reduce(const float* x, int F, const float* w, int w
 int kgcnn_gather2_mul(const float* a, const int32_t* ia, int ia_stride, const float* b,
                       const int32_t* ib, int ib_stride, int F, int64_t E, int reduce_f, float* z,
                       kgcnn_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * a19  bias + activation on flat values (kgcnn/layers/modules.py:85; kgcnn/ops/activ.py:5-107)
+ *     out[m,u] = g1[m,u] * g2[m,u] * f^(order)(pre[m,u] + bias[u]);  bias, g1, g2 nullable; order 0..3.
+ *     order k+1 with one more multiplier is the VJP of order k: closed under differentiation.
+ *  kgcnn_colsum: out[u] = sum_m a[m,u] (bias gradient), deterministic two-stage tree.
+ * ------------------------------------------------------------------------------------------- */
+int kgcnn_bias_act(const float* pre, const float* bias, const float* g1, const float* g2, int act, int order,
+                   int64_t M, int U, float* out, kgcnn_stream_t stream);
+size_t kgcnn_colsum_workspace_bytes(int64_t M, int U);
+int kgcnn_colsum(const float* a, int64_t M, int U, float* out, void* workspace, size_t workspace_bytes,
+                 kgcnn_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -72,3 +72,34 @@ def rel_err(a, b):
 
 
 RTOL = 1e-5   # north_star: fp32 outputs, gradients and forces within 1e-5 relative of the fp64 oracle
+
+
+def schnet_params(cfg, rng, dtype=torch.float64):
+    """Random SchNet weights with gcnn_keras_b200's state_dict names (for CPU-only oracle tests)."""
+    units = cfg["interaction_args"]["units"]
+    emb = cfg["input_embedding"]["node"]
+    bins = cfg["gauss_args"]["bins"]
+    p = {}
+
+    def dense(name, fi, fo, bias=True):
+        lim = np.sqrt(6.0 / (fi + fo))
+        p[name + ".kernel"] = torch.tensor(rng.uniform(-lim, lim, (fi, fo)), dtype=dtype)
+        if bias:
+            p[name + ".bias"] = torch.tensor(rng.normal(0, 0.1, (fo,)), dtype=dtype)
+
+    pre = "layers_by_name."
+    p[pre + "embedding.embeddings"] = torch.tensor(rng.uniform(-0.05, 0.05, (emb["input_dim"], emb["output_dim"])),
+                                                   dtype=dtype)
+    dense(pre + "dense_in", emb["output_dim"], units)
+    for i in range(cfg["depth"]):
+        b = pre + "interaction_%d." % i
+        dense(b + "lay_dense1", units, units, bias=False)
+        dense(b + "lay_cfconv.lay_dense1", bins, units)
+        dense(b + "lay_cfconv.lay_dense2", units, units)
+        dense(b + "lay_dense2", units, units)
+        dense(b + "lay_dense3", units, units)
+    fi = units
+    for k, u in enumerate(cfg["last_mlp"]["units"]):
+        dense(pre + "last_mlp.mlp_dense_layer_list.%d" % k, fi, u)
+        fi = u
+    return p

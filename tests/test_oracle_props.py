@@ -1,0 +1,99 @@
+"""Property checks that pin the UNPINNED parts of the oracle (no reference golden vectors exist for them):
+fp64 gradcheck / gradgradcheck of the op chains, finite-difference forces, invariances."""
+import numpy as np
+import torch
+
+from helpers import c1_batch, oracle_ragged, random_graph_batch, schnet_params
+from oracle import R
+from oracle import conv as OC
+from oracle import layers as OL
+from oracle import models as OM
+from oracle import ops as OO
+
+
+def test_partition_row_indexing_docstring_example():
+    # kgcnn/ops/partition.py:110-121
+    out = OO.partition_row_indexing(torch.tensor([0, 0, 1, 1]), torch.tensor([2, 2]), torch.tensor([3, 1]),
+                                    "row_lengths", "row_lengths")
+    assert out.tolist() == [0, 0, 1, 3]
+
+
+def test_pooling_empty_segments_are_zero_for_every_method():
+    # F4 in SURVEY.md: sorted segment op + scatter_nd padding -> 0, also for max/min
+    nodes = oracle_ragged(np.zeros((5, 1)), [3, 2])
+    edges = oracle_ragged(np.array([[1.0], [-2.0], [3.0]]), [2, 1])
+    index = oracle_ragged(np.array([[0, 1], [0, 2], [0, 1]]), [2, 1])
+    for method, want in [("sum", [-1, 0, 0, 3, 0]), ("mean", [-0.5, 0, 0, 3, 0]), ("max", [1, 0, 0, 3, 0]),
+                         ("min", [-2, 0, 0, 3, 0])]:
+        out = OL.pooling_local_edges(nodes, edges, index, method)
+        assert out.values.flatten().tolist() == [float(w) for w in want]
+
+
+def test_pooling_is_invariant_under_edge_permutation():
+    rng = np.random.default_rng(0)
+    node_len, edge_len, index = c1_batch(rng, n_graphs=3, n_nodes=7, deg=4)
+    e = rng.standard_normal((len(index), 5))
+    nodes = oracle_ragged(np.zeros((21, 1)), node_len)
+    a = OL.pooling_local_edges(nodes, oracle_ragged(e, edge_len), oracle_ragged(index, edge_len), "sum").values
+    perm = np.concatenate([g * 28 + rng.permutation(28) for g in range(3)])
+    b = OL.pooling_local_edges(nodes, oracle_ragged(e[perm], edge_len), oracle_ragged(index[perm], edge_len),
+                               "sum").values
+    assert torch.allclose(a, b, atol=1e-12)
+
+
+def test_cfconv_gradcheck_and_gradgradcheck():
+    rng = np.random.default_rng(1)
+    node_len, edge_len, index = c1_batch(rng, n_graphs=2, n_nodes=4, deg=2)
+    o_idx = oracle_ragged(index, edge_len)
+    x = torch.tensor(rng.standard_normal((8, 3)), requires_grad=True)
+    w = torch.tensor(rng.standard_normal((len(index), 3)), requires_grad=True)
+
+    def fn(x, w):
+        nodes = R.from_row_lengths(x, node_len)
+        msg = OL.gather_nodes_outgoing(nodes, o_idx).values * w
+        return OL.pooling_local_edges(nodes, o_idx.with_values(msg), o_idx, "sum").values
+
+    assert torch.autograd.gradcheck(fn, (x, w))
+    assert torch.autograd.gradgradcheck(fn, (x, w))
+
+
+def _schnet_setup(batch=2, depth=1):
+    from gcnn_keras_b200.synthetic import SCHNET_C2_CONFIG, schnet_c2_batch
+    cfg = dict(SCHNET_C2_CONFIG, depth=depth)
+    cfg["interaction_args"] = dict(cfg["interaction_args"], units=16)
+    cfg["input_embedding"] = {"node": {"input_dim": 95, "output_dim": 16}}
+    cfg["last_mlp"] = {"use_bias": [True, True], "units": [8, 1], "activation": ["shifted_softplus", "linear"]}
+    b = schnet_c2_batch(batch, 0)
+    params = schnet_params(cfg, np.random.default_rng(2))
+    z = oracle_ragged(b["z"], b["node_len"])
+    edi = oracle_ragged(b["index"], b["edge_len"])
+
+    def energy_fn(x):
+        return OM.schnet_energy(params, z, x, edi, cfg["depth"], cfg["gauss_args"], cfg["interaction_args"],
+                                cfg["last_mlp"]["activation"], "sum", None)
+
+    return b, energy_fn
+
+
+def test_schnet_oracle_forces_match_finite_differences():
+    b, energy_fn = _schnet_setup()
+    xyz = oracle_ragged(b["xyz"], b["node_len"], torch.float64)
+    eng, force = OM.energy_force(energy_fn, xyz, create_graph=False)
+    assert eng.shape == (2, 1) and force.shape == (18, 3, 1)
+    h = 1e-6
+    x0 = xyz.values.clone()
+    for a, c in [(0, 0), (5, 2), (13, 1)]:
+        xp, xm = x0.clone(), x0.clone()
+        xp[a, c] += h
+        xm[a, c] -= h
+        fd = (energy_fn(xyz.with_values(xp)).sum() - energy_fn(xyz.with_values(xm)).sum()) / (2 * h)
+        assert abs(force[a, c, 0].item() - fd.item()) < 1e-6 * max(1.0, abs(fd.item()))
+
+
+def test_schnet_oracle_energy_is_rotation_and_translation_invariant():
+    b, energy_fn = _schnet_setup()
+    xyz = oracle_ragged(b["xyz"], b["node_len"], torch.float64)
+    q, _ = np.linalg.qr(np.random.default_rng(3).standard_normal((3, 3)))
+    rot = xyz.with_values(xyz.values @ torch.tensor(q) + torch.tensor([0.3, -1.0, 2.0]))
+    with torch.no_grad():
+        assert torch.allclose(energy_fn(xyz), energy_fn(rot), atol=1e-10)
