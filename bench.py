@@ -301,16 +301,198 @@ def run_reference_gss(args):
 
 
 # ----------------------------------------------------------------------------------------------------
+# workload: SchNet energy + force training step (BASELINE.json configs[1], C2)
+# ----------------------------------------------------------------------------------------------------
+def build_schnet(device, batch, seed):
+    from gcnn_keras_b200.literature.Schnet import make_model
+    from gcnn_keras_b200.model.force import EnergyForceModel
+    from gcnn_keras_b200.synthetic import SCHNET_C2_CONFIG, schnet_c2_batch
+    from gcnn_keras_b200.training import ForceTrainStep
+    torch.manual_seed(1234)                      # identical initial weights on every rank (DP replicas)
+    model = EnergyForceModel(model_energy=make_model(**SCHNET_C2_CONFIG), energy_output=0, output_to_tensor=True,
+                             output_as_dict=False, output_squeeze_states=True, is_physical_force=False)
+    return model, ForceTrainStep(model, lr=1e-3, force_loss_factor=200.0, clipnorm=1.0), schnet_c2_batch(batch, seed)
+
+
+def timed_steps_with_l2_flush(step_fn, steps, warmup, world, device):
+    """Per-step CUDA events with a 256 MB L2 flush between steps (outside the events); max over ranks."""
+    flush = torch.empty(256 * 1024 * 1024 // 4, dtype=torch.float32, device=device)
+    for _ in range(warmup):
+        step_fn()
+    torch.cuda.synchronize()
+    barrier(world)
+    torch.cuda.synchronize()
+    pairs = []
+    with ClockSampler(device.index or 0) as clocks:
+        for _ in range(steps):
+            flush.fill_(0.0)
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            step_fn()
+            b.record()
+            pairs.append((a, b))
+        torch.cuda.synchronize()
+        barrier(world)
+        torch.cuda.synchronize()
+    ms = sum(a.elapsed_time(b) for a, b in pairs)
+    return max_over_ranks(ms, world, device) / steps, clocks.summary()
+
+
+def gss_roofline(device, feat=64, n_graphs=65536, iters=20):
+    """The north-star kernel (fused gather -> segment-sum) timed alone on GSS-L for the roofline object."""
+    from gcnn_keras_b200 import RaggedTensor
+    from gcnn_keras_b200 import functional as F
+    from gcnn_keras_b200.plan import get_plan
+    x_h, idx_h, ns_h, es_h = gss_inputs(n_graphs, feat=feat, seed=0)
+    N, E = x_h.shape[0], idx_h.shape[0]
+    x = torch.from_numpy(x_h).to(device)
+    nodes = RaggedTensor.from_row_splits(x, torch.from_numpy(ns_h).to(device))
+    index = RaggedTensor.from_row_splits(torch.from_numpy(idx_h).to(device), torch.from_numpy(es_h).to(device))
+    plan = get_plan(index, nodes)
+    recv, send = plan.relation(0), plan.relation(1)
+    recv.rowptr, send.rowptr, send.permuted_ids(recv)
+    dy = torch.randn(N, feat, device=device)
+    for _ in range(5):
+        F.raw_gms(x, None, recv, send)
+        F.raw_gms(dy, None, send, recv)
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(iters):
+        F.raw_gms(x, None, recv, send)        # forward  (receiver CSR)
+        F.raw_gms(dy, None, send, recv)       # backward (same kernel on the sender CSC)
+    b.record()
+    torch.cuda.synchronize()
+    ms_launch = a.elapsed_time(b) / (2 * iters)
+    peak, peak_src = measured_peaks()
+    per_launch = gss_bytes(E, N, feat) / 2
+    achieved = per_launch / (ms_launch * 1e-3) / 1e9
+    return {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+            "traffic": 752.2e6, "kernel": "gms_kernel (fused gather*w -> CSR segment-sum), fwd+bwd launches",
+            "workload": "GSS-L (N=%d, E=%d, F=%d): working set > L2" % (N, E, feat),
+            "algorithmic_bytes_per_launch": per_launch, "ms_per_launch": ms_launch, "peak_source": peak_src,
+            "edges_per_s": E / (2 * ms_launch * 1e-3),
+            "note": "algorithmic bytes count every gathered row (4F per edge, no cache credit, SURVEY 8d); ncu "
+                    "DRAM traffic per launch (profiles/) is ~0.75 GB because gathered rows hit in L1/L2, so "
+                    "frac > 1 means cache reuse, not skipped work; the kernel is L1-wavefront bound"}
+
+
+def run_schnet(args, rank, world, device):
+    from gcnn_keras_b200.training import CapturedForceTrainStep
+    batch = args.batch
+    model, train_step, data = build_schnet(device, batch, seed=rank)
+    captured = CapturedForceTrainStep(train_step, data, device)
+    n_params = sum(p.numel() for p in model.parameters())
+
+    ms_step, clocks = timed_steps_with_l2_flush(lambda: captured.run(load=False), args.steps, args.warmup, world,
+                                                device)
+    assert captured.check(), "plan assumptions of the captured graph were violated"
+    ms_e2e, _ = timed_steps_with_l2_flush(lambda: captured.run(load=True), args.steps, args.warmup, world, device)
+    loss_value = float(captured.loss_host)
+    total_mol = sum_over_ranks(float(batch), world, device)
+    line = {
+        "metric": "SchNet force-train molecules/sec", "value": total_mol / (ms_step * 1e-3), "unit": "molecules/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "C2: SchNet energy+force training step (force_schnet.py), synthetic MD17-ethanol-shaped "
+                               "data: 9 atoms, cutoff 5 A (72 edges), batch %d per GPU" % batch,
+                   "batch_per_gpu": batch, "atoms": 9 * batch, "edges": 72 * batch, "depth": 6, "units": 128,
+                   "gauss_bins": 25, "parameters": n_params, "optimizer": "Adam(1e-3), clipnorm 1.0",
+                   "step": "fwd + dE/dx + loss + d loss/d weights through the force + Adam, one CUDA graph",
+                   "l2_policy": "256 MB L2 flush between timed steps (per-step CUDA events)",
+                   "parallelism": "graphs sharded across %d rank(s); weight-gradient all-reduce only" % world},
+        "loss": loss_value,
+        "e2e": {"value": total_mol / (ms_e2e * 1e-3), "unit": "molecules/s",
+                "h2d_bytes_per_step": captured.static.h2d_bytes, "d2h_bytes_per_step": 4 + (
+                    0 if captured.flags is None else captured.flags.numel() * 4), "ms_per_step": ms_e2e},
+        "gpu_launches": captured.kernels_per_step * args.steps,
+        "our_kernels_per_step": captured.kernels_per_step,
+        "clocks": clocks,
+    }
+    if rank == 0 and not args.no_roofline:
+        line["roofline"] = gss_roofline(device)
+    return line
+
+
+def cpu_schnet(batch, steps, warmup, threads):
+    """Oracle SchNet train step (reference op chain, torch-CPU fp32 autograd incl. the double backward + Adam)."""
+    from gcnn_keras_b200.synthetic import SCHNET_C2_CONFIG, schnet_c2_batch
+    from oracle import R
+    from oracle import models as OM
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from helpers import schnet_params
+    torch.set_num_threads(threads)
+    cfg = SCHNET_C2_CONFIG
+    b = schnet_c2_batch(batch, 0)
+    params = schnet_params(cfg, np.random.default_rng(0), dtype=torch.float32)
+    for v in params.values():
+        v.requires_grad_(True)
+    plist = list(params.values())
+    opt = torch.optim.Adam(plist, lr=1e-3, eps=1e-7)
+    z = R.from_row_lengths(torch.from_numpy(b["z"]), b["node_len"])
+    xyz = R.from_row_lengths(torch.from_numpy(b["xyz"]), b["node_len"])
+    edi = R.from_row_lengths(torch.from_numpy(b["index"]), b["edge_len"])
+    e_t, f_t = torch.from_numpy(b["energy"]), torch.from_numpy(b["force"])
+
+    def energy_fn(x):
+        return OM.schnet_energy(params, z, x, edi, cfg["depth"], cfg["gauss_args"], cfg["interaction_args"],
+                                cfg["last_mlp"]["activation"], "sum", None)
+
+    def step():
+        eng, force = OM.energy_force(energy_fn, xyz)
+        loss = OM.force_training_loss(eng, force.squeeze(-1), e_t, f_t)
+        grads = torch.autograd.grad(loss, plist)
+        for p, g in zip(plist, grads):
+            p.grad = g * (1.0 / torch.clamp(g.norm(), min=1.0))
+        opt.step()
+        return loss
+
+    for _ in range(warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        step()
+    dt = (time.perf_counter() - t0) / steps
+    return batch / dt, dt * 1e3
+
+
+def cpu_baseline_schnet(args):
+    cores = os.cpu_count() or 1
+    mps, ms = cpu_schnet(32, steps=3, warmup=1, threads=cores)
+    return {"value": mps, "unit": "molecules/s", "cores": cores, "kind": "port",
+            "sample": "same SchNet C2 train step at batch 32 (oracle: reference op chain on torch-CPU fp32, "
+                      "autograd double backward + Adam), 3 steps, %.0f ms/step" % ms}
+
+
+def run_reference_schnet(args):
+    cores = os.cpu_count() or 1
+    batch = 32
+    mps, ms = cpu_schnet(batch, steps=max(1, args.steps), warmup=max(1, min(args.warmup, 2)), threads=cores)
+    return {"impl": "reference", "metric": "SchNet force-train molecules/sec", "value": mps, "unit": "molecules/s",
+            "n_gpus": int(os.environ.get("WORLD_SIZE", "1")), "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
+            "config": {"workload": "C2: SchNet energy+force training step, synthetic MD17-ethanol-shaped data "
+                                   "(CPU sample: batch %d)" % batch, "batch": batch, "depth": 6, "units": 128},
+            "cpu_baseline": {"value": mps, "unit": "molecules/s", "cores": cores, "kind": "port",
+                             "sample": "oracle torch-CPU restatement of the reference TF op chain, batch %d" % batch},
+            "e2e": {"value": mps, "unit": "molecules/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "note": "TensorFlow is not installable here; the reference arm is the oracle port on the host cores"}
+
+
+# ----------------------------------------------------------------------------------------------------
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default=os.environ.get("KGCNN_BENCH_WORKLOAD", "gss"), choices=["gss", "schnet"])
+    ap.add_argument("--workload", default=os.environ.get("KGCNN_BENCH_WORKLOAD", "schnet"), choices=["gss", "schnet"])
     ap.add_argument("--gss-graphs", type=int, default=65536)
     ap.add_argument("--gss-feat", type=int, default=64)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-roofline", action="store_true")
+    ap.add_argument("--batch", type=int, default=256, help="molecules per GPU (schnet workload)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
 

@@ -14,6 +14,52 @@ from . import functional as F
 from ._lib import KgcnnError
 
 
+class PlanMode:
+    """How relations decide sortedness.
+    None (default)  : check on the device and read the flag on the host (one sync per relation and batch).
+    'record'        : same, and remember the answers in creation order (eager warm-up before a capture).
+    'capture'       : no host sync (CUDA-graph capture): trust the recorded answers, write the device-side
+                      check flags into `flags` so the host can validate the assumption after each replay."""
+
+    def __init__(self, kind, hints=None):
+        self.kind = kind
+        self.hints = [] if hints is None else list(hints)
+        self.cursor = 0
+        self.flags = []          # (assumed_sorted, device int32[2]) per relation, capture mode
+
+    def violated(self, host_flags):
+        """host_flags: list of int32[2] tensors on the host, same order as self.flags."""
+        for (assumed_sorted, _), f in zip(self.flags, host_flags):
+            if int(f[1]) or (assumed_sorted and int(f[0])):
+                return True
+        return False
+
+
+_MODE = None
+
+
+class plan_mode:
+    def __init__(self, mode):
+        self.mode = mode
+
+    def __enter__(self):
+        global _MODE
+        self._prev, _MODE = _MODE, self.mode
+        return self.mode
+
+    def __exit__(self, *exc):
+        global _MODE
+        _MODE = self._prev
+
+
+def current_mode():
+    return _MODE
+
+
+def clear_plan_cache():
+    _PLAN_CACHE.clear()
+
+
 class Relation:
     """'element e belongs to target ids[e]' with its CSR (rowptr, stable perm); e.g. edge -> receiver."""
 
@@ -32,10 +78,20 @@ class Relation:
             return
         if self._is_sorted is None:
             flags = F.raw_check_sorted(self.ids, self.n_targets)
-            host = flags.cpu()            # one sync per batch and relation
-            if int(host[1]):
-                raise IndexError("index out of range [0, %d) in ragged index tensor" % self.n_targets)
-            self._is_sorted = not bool(int(host[0]))
+            mode = _MODE
+            if mode is not None and mode.kind == "capture":
+                if mode.cursor >= len(mode.hints):
+                    raise RuntimeError("CUDA-graph capture met a relation that the warm-up pass did not record")
+                self._is_sorted = bool(mode.hints[mode.cursor])
+                mode.cursor += 1
+                mode.flags.append((self._is_sorted, flags))
+            else:
+                host = flags.cpu()            # one sync per batch and relation
+                if int(host[1]):
+                    raise IndexError("index out of range [0, %d) in ragged index tensor" % self.n_targets)
+                self._is_sorted = not bool(int(host[0]))
+                if mode is not None and mode.kind == "record":
+                    mode.hints.append(self._is_sorted)
         self._rowptr, self._perm = F.raw_plan_build(self.ids, self.n_targets, self._is_sorted)
 
     @property
@@ -65,11 +121,9 @@ class Relation:
 
     def inv_count(self):
         """1/len(segment) (0 for empty) as float32 [n_targets, 1]: backward of segment_mean."""
-        if self._inv_count is None:
-            rp = self.rowptr
-            cnt = (rp[1:] - rp[:-1]).to(torch.float32)
-            self._inv_count = torch.where(cnt > 0, 1.0 / cnt, torch.zeros_like(cnt)).unsqueeze(1)
-        return self._inv_count
+        rp = self.rowptr
+        cnt = (rp[1:] - rp[:-1]).to(torch.float32)
+        return torch.where(cnt > 0, 1.0 / cnt, torch.zeros_like(cnt)).unsqueeze(1)
 
 
 class IndexPlan:
@@ -135,6 +189,7 @@ def unify_partitions(raggeds):
     RaggedTensors with equal splits).  One device comparison + sync per distinct pair and batch."""
     canon = []
     out = []
+    no_sync = _MODE is not None and _MODE.kind == "capture"
     for r in raggeds:
         if not hasattr(r, "partition"):
             out.append(r)
@@ -144,7 +199,7 @@ def unify_partitions(raggeds):
             if c is r.partition:
                 hit = c
                 break
-            if c.nrows == r.partition.nrows and c.row_splits.device == r.partition.row_splits.device \
+            if not no_sync and c.nrows == r.partition.nrows and c.row_splits.device == r.partition.row_splits.device \
                     and int(c.row_splits.shape[0]) == int(r.partition.row_splits.shape[0]) \
                     and (c._nvals is None or r.partition._nvals is None or c._nvals == r.partition._nvals) \
                     and bool(torch.equal(c.row_splits, r.partition.row_splits)):

@@ -14,7 +14,8 @@ import torch
 class RowPartition:
     """row_splits (int64 [B+1]) plus lazily derived views, shared by all tensors of one ragged axis."""
 
-    def __init__(self, row_splits, nvals=None):
+    def __init__(self, row_splits, nvals=None, max_len=None):
+        self.max_len = max_len          # optional host-side hint: longest row (avoids a sync in to_tensor)
         if row_splits.dtype != torch.int64:
             row_splits = row_splits.to(torch.int64)
         self.row_splits = row_splits.contiguous()
@@ -166,7 +167,10 @@ class RaggedTensor:
     def to_tensor(self, default_value=0):
         """Pad to [B, max_len, ...] (casting.py:80)."""
         lengths = self.row_lengths()
-        nmax = int(lengths.max().item()) if lengths.numel() else 0
+        if self.partition.max_len is not None:
+            nmax = int(self.partition.max_len)
+        else:
+            nmax = int(lengths.max().item()) if lengths.numel() else 0
         out = self.values.new_full((self.partition.nrows, nmax) + tuple(self.values.shape[1:]), default_value)
         rowids = self.partition.value_rowids()
         pos = torch.arange(self.values.shape[0], device=self.values.device) - self.row_splits[rowids]

@@ -8,6 +8,10 @@ import torch
 
 
 def keras_mse(pred, target):
+    if isinstance(pred, torch.Tensor) and hasattr(target, "to_tensor"):
+        target = target.to_tensor()          # padded prediction (output_to_tensor=True) vs ragged label
+    pred = getattr(pred, "values", pred)
+    target = getattr(target, "values", target)
     return torch.mean((pred - target) ** 2)
 
 
@@ -37,6 +41,8 @@ class ForceTrainStep:
         self._ensure_optimizer()
         grads = torch.autograd.grad(loss, self.params, allow_unused=True)
         grads = [torch.zeros_like(p) if g is None else g for g, p in zip(grads, self.params)]
+        from .distributed import allreduce_gradients
+        grads = allreduce_gradients(grads)       # data parallel by graph: the only collective of the step
         if self.clipnorm is not None:                     # tf.clip_by_norm per variable (Keras clipnorm)
             norms = torch._foreach_norm(grads)
             scales = [self.clipnorm / torch.clamp(n, min=self.clipnorm) for n in norms]
@@ -45,3 +51,111 @@ class ForceTrainStep:
             p.grad = g
         self.optimizer.step()
         return loss
+
+
+class StaticBatch:
+    """Pinned host staging + fixed device buffers for one batch signature (the shapes a CUDA graph was
+    captured for).  `load()` is asynchronous on the current stream: host arrays -> pinned -> device."""
+
+    def __init__(self, example, device):
+        self.device = device
+        self.shapes = {k: (tuple(v.shape), v.dtype) for k, v in example.items()}
+        self.pinned = {k: torch.from_numpy(v.copy()).pin_memory() for k, v in example.items()}
+        self.dev = {k: t.to(device) for k, t in self.pinned.items()}
+        self.h2d_bytes = sum(t.numel() * t.element_size() for t in self.pinned.values())
+
+    def signature_matches(self, batch):
+        return all(k in batch and tuple(batch[k].shape) == s for k, (s, _) in self.shapes.items())
+
+    def load(self, batch=None):
+        if batch is not None:
+            for k, t in self.pinned.items():
+                t.copy_(torch.from_numpy(batch[k]))
+        for k, t in self.pinned.items():
+            self.dev[k].copy_(t, non_blocking=True)
+
+
+def molecule_batch_to_arrays(b):
+    """synthetic / dataset batch dict -> flat arrays incl. int64 row_splits (host side, NumPy)."""
+    import numpy as np
+    out = {"z": b["z"].astype(np.int64), "xyz": b["xyz"].astype(np.float32), "index": b["index"].astype(np.int64),
+           "node_splits": np.concatenate([[0], np.cumsum(b["node_len"])]).astype(np.int64),
+           "edge_splits": np.concatenate([[0], np.cumsum(b["edge_len"])]).astype(np.int64),
+           "energy": b["energy"].astype(np.float32), "force": b["force"].astype(np.float32)}
+    if "angle_index" in b:
+        out["angle_index"] = b["angle_index"].astype(np.int64)
+        out["angle_splits"] = np.concatenate([[0], np.cumsum(b["angle_len"])]).astype(np.int64)
+    return out
+
+
+def default_model_inputs(dev, max_nodes=None):
+    """[z, xyz, edge_index(, angle_index)] RaggedTensors over the device buffers, sharing ONE node partition."""
+    from .ragged import RaggedTensor, RowPartition
+    node_part = RowPartition(dev["node_splits"], nvals=int(dev["xyz"].shape[0]), max_len=max_nodes)
+    edge_part = RowPartition(dev["edge_splits"], nvals=int(dev["index"].shape[0]))
+    inputs = [RaggedTensor(dev["z"], node_part), RaggedTensor(dev["xyz"], node_part),
+              RaggedTensor(dev["index"], edge_part)]
+    if "angle_index" in dev:
+        inputs.append(RaggedTensor(dev["angle_index"], RowPartition(dev["angle_splits"],
+                                                                    nvals=int(dev["angle_index"].shape[0]))))
+    return inputs, dev["energy"], RaggedTensor(dev["force"], node_part)
+
+
+class CapturedForceTrainStep:
+    """The whole training step (index shift + plan, forward, dE/dx, loss, weight gradients through the force,
+    clipnorm, Adam) captured ONCE in a CUDA graph and replayed per batch of the same signature.
+
+    Sortedness of every relation is detected during an eager warm-up (one sync each), trusted during capture,
+    and re-validated after every replay from device-side flags (`check()`), so no host sync sits inside a step."""
+
+    def __init__(self, train_step, example_batch, device, make_inputs=default_model_inputs, warmup=3):
+        from . import _lib
+        from .plan import PlanMode, clear_plan_cache, plan_mode
+        self.train_step = train_step
+        self.static = StaticBatch(molecule_batch_to_arrays(example_batch), device)
+        self.make_inputs = make_inputs
+        self.max_nodes = int(example_batch["node_len"].max())
+        self.static.load()
+        record = PlanMode("record")
+        side = torch.cuda.Stream(device=device)
+        side.wait_stream(torch.cuda.current_stream(device))
+        with torch.cuda.stream(side):
+            for i in range(warmup):
+                clear_plan_cache()
+                mode = PlanMode("record")
+                with plan_mode(mode):
+                    inputs, e_t, f_t = self.make_inputs(self.static.dev, self.max_nodes)
+                    train_step.step(inputs, e_t, f_t)
+                record = mode
+        torch.cuda.current_stream(device).wait_stream(side)
+        torch.cuda.synchronize(device)
+        clear_plan_cache()
+        self.mode = PlanMode("capture", hints=record.hints)
+        self.graph = torch.cuda.CUDAGraph()
+        _lib.launch_count_reset()
+        with plan_mode(self.mode):
+            with torch.cuda.graph(self.graph):
+                inputs, e_t, f_t = self.make_inputs(self.static.dev, self.max_nodes)
+                self.loss = train_step.step(inputs, e_t, f_t)
+                self.flags = torch.stack([f for _, f in self.mode.flags]) if self.mode.flags else None
+        self.kernels_per_step = _lib.launch_count()      # our kernels recorded in the graph
+        self.loss_host = torch.zeros((), dtype=torch.float32).pin_memory()
+        self.flags_host = None if self.flags is None else torch.zeros_like(self.flags, device="cpu").pin_memory()
+
+    def run(self, batch=None, load=True):
+        """H2D (if load) -> replay -> async D2H of the loss (+ validation flags).  Returns the pinned loss."""
+        if batch is not None and not self.static.signature_matches(molecule_batch_to_arrays(batch)):
+            raise ValueError("batch signature differs from the captured one; capture a new CapturedForceTrainStep")
+        if load:
+            self.static.load(None if batch is None else molecule_batch_to_arrays(batch))
+        self.graph.replay()
+        self.loss_host.copy_(self.loss.detach(), non_blocking=True)
+        if self.flags is not None:
+            self.flags_host.copy_(self.flags, non_blocking=True)
+        return self.loss_host
+
+    def check(self):
+        """After a synchronize: were the sortedness / index-range assumptions of the capture still true?"""
+        if self.flags is None:
+            return True
+        return not self.mode.violated(list(self.flags_host))

@@ -66,6 +66,7 @@ def rel_err(a, b):
     """max |a-b| / max(|b|_max, tiny): the '1e-5 relative' bar of BASELINE.json is applied to this."""
     a = np.asarray(a, dtype=np.float64)
     b = np.asarray(b, dtype=np.float64)
+    assert a.shape == b.shape, (a.shape, b.shape)
     if a.size == 0:
         return 0.0
     return float(np.max(np.abs(a - b)) / max(np.max(np.abs(b)), 1e-30))

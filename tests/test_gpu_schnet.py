@@ -38,7 +38,7 @@ def _oracle(cfg, b, params, dtype=torch.float64):
                                 cfg["last_mlp"]["activation"], "sum", None)
 
     eng, force = OM.energy_force(energy_fn, xyz)
-    return params, eng, force
+    return params, eng, force.squeeze(-1)
 
 
 def test_schnet_energy_and_forces_match_fp64_oracle():
@@ -60,7 +60,7 @@ def test_schnet_force_training_gradients_match_fp64_oracle():
     names = [n for n, _ in model.energy_model.named_parameters()]
     grads = torch.autograd.grad(loss, list(model.energy_model.parameters()), allow_unused=True)
     params, o_eng, o_force = _oracle(cfg, b, model.energy_model.state_dict())
-    o_loss = OM.force_training_loss(o_eng, o_force.squeeze(-1), torch.tensor(b["energy"], dtype=torch.float64),
+    o_loss = OM.force_training_loss(o_eng, o_force, torch.tensor(b["energy"], dtype=torch.float64),
                                     torch.tensor(b["force"], dtype=torch.float64))
     assert rel_err(loss.item(), o_loss.item()) < RTOL
     o_grads = torch.autograd.grad(o_loss, [params[n] for n in names], allow_unused=True)
