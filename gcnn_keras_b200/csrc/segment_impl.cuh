@@ -183,6 +183,74 @@ gms_kernel(const V* __restrict__ x, const V* __restrict__ wv, const float* __res
   }
 }
 
+// Block-per-row mapping for outputs with FEW rows (n_out <= 1024: embedding-table gradients, per-type
+// reductions): segment lengths are then unbounded (thousands of atoms of one element), so one CTA = 32 lane
+// groups walks a row together and the groups are combined through shared memory in a fixed order.
+template <typename V, int MODE, bool GATHER>
+__global__ void __launch_bounds__(kThreads)
+gms_block_kernel(const V* __restrict__ x, const V* __restrict__ wv, const float* __restrict__ ws,
+                 const int32_t* __restrict__ rowptr, const int32_t* __restrict__ perm,
+                 const int32_t* __restrict__ gidx, int gidx_stride, int gidx_permuted, int64_t n_out, int nvec,
+                 int mean, V* __restrict__ y) {
+  constexpr int LPR = 8;
+  constexpr int NG = kThreads / LPR;  // 32 lane groups
+  using T = Vec<V>;
+  __shared__ V red[NG][LPR];
+  const int g = threadIdx.x / LPR, sub = threadIdx.x % LPR;
+  const int64_t row = blockIdx.x;
+  const int beg = __ldg(rowptr + row), end = __ldg(rowptr + row + 1);
+  const float init = (MODE == kMax) ? -INFINITY : (MODE == kMin) ? INFINITY : 0.f;
+  for (int cb = 0; cb < nvec; cb += LPR) {
+    const int c = cb + sub;
+    const bool cok = c < nvec;
+    V acc = T::fill(init);
+    for (int p = beg + g; p < end; p += NG) {
+      const int e = perm ? __ldg(perm + p) : p;
+      const int s = GATHER ? __ldg(gidx + static_cast<int64_t>(gidx_permuted ? p : e) * gidx_stride) : e;
+      if (cok) {
+        V xv = GATHER ? T::ld_keep(x + static_cast<int64_t>(s) * nvec + c)
+                      : T::ld_stream(x + static_cast<int64_t>(s) * nvec + c);
+        if (MODE == kSumW0) T::add(acc, xv);
+        else if (MODE == kSumW1) T::fmas(acc, xv, __ldg(ws + e));
+        else if (MODE == kSumW2) T::fma(acc, xv, T::ld_stream(wv + static_cast<int64_t>(e) * nvec + c));
+        else if (MODE == kMax) T::vmax(acc, xv);
+        else T::vmin(acc, xv);
+      }
+    }
+    red[g][sub] = acc;
+    __syncthreads();
+    if (g == 0 && cok) {
+      V tot = red[0][sub];
+      for (int k = 1; k < NG; ++k) {   // fixed order over the lane groups
+        if (MODE == kMax) T::vmax(tot, red[k][sub]);
+        else if (MODE == kMin) T::vmin(tot, red[k][sub]);
+        else T::add(tot, red[k][sub]);
+      }
+      const bool empty = end <= beg;
+      if (empty) tot = T::fill(0.f);
+      else if (mean) tot = T::scale(tot, 1.f / static_cast<float>(end - beg));
+      T::st(y + row * nvec + c, tot);
+    }
+    __syncthreads();
+  }
+}
+
+template <typename V>
+int launch_block(int mode, bool gather, const V* x, const V* wv, const float* ws, const int32_t* rowptr,
+                 const int32_t* perm, const int32_t* gidx, int gs, int gp, int64_t n_out, int nvec, int mean, V* y,
+                 cudaStream_t st) {
+  const unsigned grid = static_cast<unsigned>(n_out);
+#define KGCNN_BLK(M, GA) \
+  gms_block_kernel<V, M, GA><<<grid, kThreads, 0, st>>>(x, wv, ws, rowptr, perm, gidx, gs, gp, n_out, nvec, mean, y)
+  if (mode == kMax) { if (gather) return KGCNN_E_UNSUPPORTED; KGCNN_BLK(kMax, false); }
+  else if (mode == kMin) { if (gather) return KGCNN_E_UNSUPPORTED; KGCNN_BLK(kMin, false); }
+  else if (mode == kSumW0) { if (gather) KGCNN_BLK(kSumW0, true); else KGCNN_BLK(kSumW0, false); }
+  else if (mode == kSumW1) { if (gather) KGCNN_BLK(kSumW1, true); else KGCNN_BLK(kSumW1, false); }
+  else { if (gather) KGCNN_BLK(kSumW2, true); else KGCNN_BLK(kSumW2, false); }
+#undef KGCNN_BLK
+  return finish_launch();
+}
+
 template <typename V, int LPR, int VPL>
 int launch_shape(int mode, bool gather, const V* x, const V* wv, const float* ws, const int32_t* rowptr,
                  const int32_t* perm, const int32_t* gidx, int gs, int gp, int64_t n_out, int nvec, int mean, V* y,
@@ -217,6 +285,8 @@ template <typename V>
 int launch(int mode, bool gather, const V* x, const V* wv, const float* ws, const int32_t* rowptr,
            const int32_t* perm, const int32_t* gidx, int gs, int gp, int64_t n_out, int nvec, int mean, V* y,
            bool short_rows, cudaStream_t st) {
+  if (n_out <= 1024)
+    return launch_block<V>(mode, gather, x, wv, ws, rowptr, perm, gidx, gs, gp, n_out, nvec, mean, y, st);
 #define KGCNN_GMS_SHAPE(L, P) \
   return launch_shape<V, L, P>(mode, gather, x, wv, ws, rowptr, perm, gidx, gs, gp, n_out, nvec, mean, y, short_rows, st)
   // few lanes per row -> many edges per warp instruction (the kernel is issue-bound, not DRAM-bound, when

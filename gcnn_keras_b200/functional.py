@@ -440,14 +440,131 @@ def bias_act(pre, bias, activation):
     return _BiasAct.apply(pre, bias, None, None, code, 0)
 
 
+def raw_gemm_tn(x2d, g2d, want_colsum=False):
+    """dW = x^T g (and optionally db = colsum(g)) with the split-M deterministic kernel."""
+    _need_cuda(x2d, g2d)
+    x2d, g2d = _f32c(x2d), _f32c(g2d)
+    M, K1, K2 = int(x2d.shape[0]), int(x2d.shape[1]), int(g2d.shape[1])
+    dw = torch.empty((K1, K2), dtype=torch.float32, device=x2d.device)
+    db = torch.empty((K2,), dtype=torch.float32, device=x2d.device) if want_colsum else None
+    nbytes = int(_lib.lib().kgcnn_gemm_tn_workspace_bytes(M, K1, K2))
+    ws = torch.empty((max(nbytes, 4),), dtype=torch.uint8, device=x2d.device)
+    check(_lib.lib().kgcnn_gemm_tn(_ptr(x2d), _ptr(g2d), M, K1, K2, _ptr(dw), _ptr(db), _ptr(ws), nbytes, _stream()),
+          "kgcnn_gemm_tn")
+    return (dw, db) if want_colsum else dw
+
+
+_TN_MIN_ROWS = 512     # below this the reduction axis is short and a library GEMM is as good
+
+
+class _MatMul(torch.autograd.Function):
+    """Bilinear products closed under differentiation.  mode 0: a @ b, 1: a @ b^T, 2: a^T @ b.
+    a @ b and a @ b^T are plain library GEMMs (cuBLAS fp32, TF32 off); a^T @ b with a long reduction axis (the
+    weight gradients: sum over all edges / atoms) is our split-M deterministic kernel."""
+
+    @staticmethod
+    def forward(ctx, a, b, mode):
+        ctx.mode = mode
+        ctx.save_for_backward(a, b)
+        if mode == 0:
+            return a @ b
+        if mode == 1:
+            return a @ b.t()
+        if a.shape[0] >= _TN_MIN_ROWS and a.is_cuda:
+            return raw_gemm_tn(a, b)
+        return a.t() @ b
+
+    @staticmethod
+    def backward(ctx, g):
+        a, b = ctx.saved_tensors
+        ga = gb = None
+        mode = ctx.mode
+        if mode == 0:       # y = a b
+            if ctx.needs_input_grad[0]:
+                ga = _MatMul.apply(g, b, 1)          # g b^T
+            if ctx.needs_input_grad[1]:
+                gb = _MatMul.apply(a, g, 2)          # a^T g
+        elif mode == 1:     # y = a b^T
+            if ctx.needs_input_grad[0]:
+                ga = _MatMul.apply(g, b, 0)          # g b
+            if ctx.needs_input_grad[1]:
+                gb = _MatMul.apply(g, a, 2)          # g^T a
+        else:               # y = a^T b
+            if ctx.needs_input_grad[0]:
+                ga = _MatMul.apply(b, g, 1)          # b g^T
+            if ctx.needs_input_grad[1]:
+                gb = _MatMul.apply(a, g, 0)          # a g
+        return ga, gb, None
+
+
+class _BiasAdd(torch.autograd.Function):
+    """pre + bias with the bias gradient through the deterministic column-sum kernel."""
+
+    @staticmethod
+    def forward(ctx, pre, bias):
+        return pre + bias
+
+    @staticmethod
+    def backward(ctx, g):
+        return g, (colsum(g) if ctx.needs_input_grad[1] else None)
+
+
+def matmul(a, b):
+    return _MatMul.apply(a, b, 0)
+
+
+class _Linear(torch.autograd.Function):
+    """pre = x @ W + b.  Backward: gx = g W^T (library GEMM); (gW, gb) in ONE pass over g by the split-M kernel."""
+
+    @staticmethod
+    def forward(ctx, x, w, b):
+        ctx.save_for_backward(x, w)
+        ctx.has_bias = b is not None
+        return torch.addmm(b, x, w) if b is not None else x @ w
+
+    @staticmethod
+    def backward(ctx, g):
+        x, w = ctx.saved_tensors
+        g = g.contiguous()
+        gx = gw = gb = None
+        if ctx.needs_input_grad[0]:
+            gx = _MatMul.apply(g, w, 1)
+        if ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2]):
+            if ctx.has_bias:
+                gw, gb = _TNCol.apply(x, g)
+            else:
+                gw = _MatMul.apply(x, g, 2)
+        return gx, gw, gb
+
+
+class _TNCol(torch.autograd.Function):
+    """(dW, db) = (x^T g, colsum(g)); its VJP is a Linear again: closed under differentiation."""
+
+    @staticmethod
+    def forward(ctx, x, g):
+        ctx.save_for_backward(x, g)
+        if x.shape[0] >= _TN_MIN_ROWS and x.is_cuda:
+            return raw_gemm_tn(x, g, want_colsum=True)
+        return x.t() @ g, g.sum(0)
+
+    @staticmethod
+    def backward(ctx, ggw, ggb):
+        x, g = ctx.saved_tensors
+        gx = gg = None
+        if ctx.needs_input_grad[0]:
+            gx = _MatMul.apply(g, ggw.contiguous(), 1)              # g ggW^T
+        if ctx.needs_input_grad[1]:
+            gg = _Linear.apply(x, ggw.contiguous(), ggb)            # x ggW + ggb
+        return gx, gg
+
+
 def dense(x, kernel, bias, activation):
     """DenseEmbedding on flat values (kgcnn/layers/modules.py:85): activation(x @ kernel + bias).
-    The GEMM is a plain library GEMM (cuBLAS fp32, TF32 off); bias + activation (+ derivatives) are ours."""
+    x @ W (+ b) and g @ W^T are plain library GEMMs (cuBLAS fp32, TF32 off); the weight + bias gradients (one
+    split-M pass), the activation and all their derivatives run in our kernels."""
     code = activation if isinstance(activation, int) else act_code(activation)
     lead = x.shape[:-1]
     x2 = x.reshape(-1, x.shape[-1])
-    if code == _lib.ACT_CODES["linear"]:
-        out = torch.addmm(bias, x2, kernel) if bias is not None else x2 @ kernel
-    else:
-        out = _BiasAct.apply(x2 @ kernel, bias, None, None, code, 0)
+    pre = _Linear.apply(x2, kernel, bias)
+    out = pre if code == _lib.ACT_CODES["linear"] else _BiasAct.apply(pre, None, None, None, code, 0)
     return out.reshape(tuple(lead) + (kernel.shape[1],))

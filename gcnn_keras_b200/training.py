@@ -10,8 +10,8 @@ import torch
 def keras_mse(pred, target):
     if isinstance(pred, torch.Tensor) and hasattr(target, "to_tensor"):
         target = target.to_tensor()          # padded prediction (output_to_tensor=True) vs ragged label
-    pred = getattr(pred, "values", pred)
-    target = getattr(target, "values", target)
+    pred = pred if isinstance(pred, torch.Tensor) else pred.values
+    target = target if isinstance(target, torch.Tensor) else target.values
     return torch.mean((pred - target) ** 2)
 
 

@@ -146,6 +146,15 @@ size_t kgcnn_colsum_workspace_bytes(int64_t M, int U);
 int kgcnn_colsum(const float* a, int64_t M, int U, float* out, void* workspace, size_t workspace_bytes,
                  kgcnn_stream_t stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * a19  weight gradient of Dense on flat ragged values (backward of kgcnn/layers/modules.py:85):
+ *     dW[K1,K2] = sum_m X[m,K1]^T G[m,K2],  db[K2] = sum_m G[m,K2] (db nullable)
+ *     M (edges / atoms) is split over ~2 CTAs per SM; partial tiles are summed in fixed order.
+ * ------------------------------------------------------------------------------------------- */
+size_t kgcnn_gemm_tn_workspace_bytes(int64_t M, int K1, int K2);
+int kgcnn_gemm_tn(const float* X, const float* G, int64_t M, int K1, int K2, float* dW, float* db,
+                  void* workspace, size_t workspace_bytes, kgcnn_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

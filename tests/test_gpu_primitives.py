@@ -330,3 +330,110 @@ def test_long_segments_warp_per_row_path(feat):
     want = np.zeros((3, feat))
     np.add.at(want, recv, src[send].astype(np.float64) * w.astype(np.float64))
     assert rel_err(got.cpu().numpy(), want) < RTOL
+
+
+@pytest.mark.parametrize("sorted_edges", [True, False])
+@pytest.mark.parametrize("feat,wcols", [(64, 0), (64, 64), (128, 128), (128, 1), (3, 3), (35, 35), (384, 384), (1, 1)])
+def test_fused_many_rows_group_per_row_mapping(sorted_edges, feat, wcols):
+    """n_out > 1024 selects the lane-group-per-row kernel (short segments): value + dx + dw vs fp64 NumPy."""
+    from gcnn_keras_b200 import functional as F
+    from gcnn_keras_b200.plan import get_plan
+    rng = np.random.default_rng(13)
+    node_len, edge_len, index = random_graph_batch(rng, n_graphs=220, max_nodes=14, max_deg=6,
+                                                   sorted_edges=sorted_edges)
+    N, E = int(node_len.sum()), int(edge_len.sum())
+    assert N > 1024
+    x = rng.standard_normal((N, feat)).astype(np.float32)
+    w = rng.standard_normal((E, wcols)).astype(np.float32) if wcols else None
+    nodes, idx = device_ragged(x, node_len), device_ragged(index, edge_len)
+    plan = get_plan(idx, nodes)
+    b_idx = plan.idx32.cpu().numpy().T.astype(np.int64)
+    msg = x[b_idx[:, 1]].astype(np.float64) * (w.astype(np.float64) if w is not None else 1.0)
+    want = np.zeros((N, feat))
+    np.add.at(want, b_idx[:, 0], msg)
+    dx = nodes.values.clone().requires_grad_(True)
+    dw = torch.tensor(w).cuda().requires_grad_(True) if w is not None else None
+    y = F.gather_mul_segment_sum(dx, dw, plan.relation(0), plan.relation(1))
+    assert rel_err(y.detach().cpu().numpy(), want) < RTOL
+    cot = rng.standard_normal((N, feat))
+    grads = torch.autograd.grad(y, [dx] + ([dw] if dw is not None else []), torch.tensor(cot).float().cuda())
+    want_dx = np.zeros((N, feat))
+    np.add.at(want_dx, b_idx[:, 1], cot[b_idx[:, 0]] * (w.astype(np.float64) if w is not None else 1.0))
+    assert rel_err(grads[0].cpu().numpy(), want_dx) < RTOL
+    if w is not None:
+        want_dw = cot[b_idx[:, 0]] * x[b_idx[:, 1]].astype(np.float64)
+        if wcols == 1 and feat > 1:
+            want_dw = want_dw.sum(1, keepdims=True)
+        assert rel_err(grads[1].cpu().numpy(), want_dw) < RTOL
+    for method in ("mean", "max", "min"):
+        e = rng.standard_normal((E, feat)).astype(np.float32)
+        got = F.segment_reduce(torch.tensor(e).cuda(), plan.relation(0), method)
+        want_m = OL.pooling_local_edges(oracle_ragged(x, node_len), oracle_ragged(e, edge_len, torch.float64),
+                                        oracle_ragged(index, edge_len), method).values
+        assert rel_err(got.cpu().numpy(), want_m.numpy()) < RTOL
+
+
+@pytest.mark.parametrize("feat", [1, 64, 128])
+def test_many_long_rows_warp_per_row_mapping(feat):
+    """n_out > 1024 with average segment length > 64 selects the warp-per-row kernel."""
+    from gcnn_keras_b200 import functional as F
+    from gcnn_keras_b200.plan import Relation
+    rng = np.random.default_rng(14)
+    n_out, E = 1100, 1100 * 80
+    ids = np.sort(rng.integers(0, n_out, size=E)).astype(np.int32)
+    v = rng.standard_normal((E, feat)).astype(np.float32)
+    rel = Relation(torch.tensor(ids).cuda(), n_out)
+    for method in ("sum", "mean", "max"):
+        got = F.segment_reduce(torch.tensor(v).cuda(), rel, method)
+        want = OO.segment_ops_by_name(method, torch.tensor(v, dtype=torch.float64), torch.tensor(ids, dtype=torch.int64))
+        want = torch.cat([want, torch.zeros(n_out - want.shape[0], feat, dtype=torch.float64)])
+        assert rel_err(got.cpu().numpy(), want.numpy()) < RTOL
+
+
+@pytest.mark.parametrize("M,K1,K2", [(18432, 128, 128), (5000, 25, 128), (700, 3, 1), (4097, 35, 50), (100, 64, 64),
+                                       (40000, 384, 20)])
+def test_gemm_tn_weight_gradient(M, K1, K2):
+    from gcnn_keras_b200 import functional as F
+    rng = np.random.default_rng(15)
+    x = rng.standard_normal((M, K1)).astype(np.float32)
+    g = rng.standard_normal((M, K2)).astype(np.float32)
+    dw, db = F.raw_gemm_tn(torch.tensor(x).cuda(), torch.tensor(g).cuda(), want_colsum=True)
+    assert rel_err(dw.cpu().numpy(), x.astype(np.float64).T @ g.astype(np.float64)) < RTOL
+    assert rel_err(db.cpu().numpy(), g.astype(np.float64).sum(0)) < RTOL
+    dw2 = F.raw_gemm_tn(torch.tensor(x).cuda(), torch.tensor(g).cuda())
+    assert torch.equal(dw, dw2)                      # deterministic split-M reduction
+    cs = F.raw_colsum(torch.tensor(g).cuda())
+    assert rel_err(cs.cpu().numpy(), g.astype(np.float64).sum(0)) < RTOL
+
+
+@pytest.mark.parametrize("act", ["kgcnn>shifted_softplus", "swish", "tanh", "linear", "relu", "sigmoid",
+                                 "kgcnn>softplus2"])
+def test_dense_forward_backward_double_backward(act):
+    """Dense (library GEMM + our bias/activation family + our weight-gradient GEMM) to second order."""
+    from gcnn_keras_b200 import functional as F
+    from oracle import ops as OOps
+    rng = np.random.default_rng(16)
+    M, K, U = 1500, 25, 32
+    x = rng.standard_normal((M, K)).astype(np.float32)
+    w = (rng.standard_normal((K, U)) / 5).astype(np.float32)
+    b = rng.standard_normal((U,)).astype(np.float32)
+
+    def run(dtype, dev, fn):
+        tx = torch.tensor(x, dtype=dtype, device=dev, requires_grad=True)
+        tw = torch.tensor(w, dtype=dtype, device=dev, requires_grad=True)
+        tb = torch.tensor(b, dtype=dtype, device=dev, requires_grad=True)
+        y = fn(tx, tw, tb)
+        gx, gw, gb = torch.autograd.grad((y ** 2).sum(), [tx, tw, tb], create_graph=True)
+        ggw, ggb = torch.autograd.grad((gx ** 2).sum(), [tw, tb], allow_unused=True)
+        return [t.detach().cpu().numpy() if t is not None else None for t in (y, gx, gw, gb, ggw, ggb)]
+
+    got = run(torch.float32, "cuda", lambda a, k, c: F.dense(a, k, c, act))
+    want = run(torch.float64, "cpu", lambda a, k, c: OOps.activation(act)(a @ k + c))
+    for a, o in zip(got, want):
+        if o is None:
+            assert a is None or float(np.abs(a).max()) == 0.0
+            continue
+        if a is None:
+            assert float(np.abs(o).max()) < 1e-12
+            continue
+        assert rel_err(a, o) < RTOL
