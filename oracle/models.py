@@ -60,3 +60,56 @@ def force_training_loss(eng, force, e_target, f_target, force_loss_factor=200.0)
     """compile(loss=[mse, mse], loss_weights=[1/f, 1-1/f]) of force_schnet.py:194-203 (forces squeezed)."""
     w_e, w_f = 1.0 / force_loss_factor, 1.0 - 1.0 / force_loss_factor
     return w_e * torch.mean((eng - e_target) ** 2) + w_f * torch.mean((force - f_target) ** 2)
+
+
+def painn_energy(params, node_attr, xyz, edi, depth, bessel_basis, conv_args=None, equiv_method="zeros",
+                 output_mlp_act=("swish", "linear"), pooling="sum"):
+    """kgcnn/literature/PAiNN.py:100-155 (graph embedding, no normalization)."""
+    p = P(params, "layers_by_name.")
+    ca = {"cutoff": None, "conv_pool": "sum"}
+    ca.update(conv_args or {})
+    table = p["embedding.embeddings"]
+    z = node_attr.with_values(table[node_attr.values.to(torch.int64)])          # :103-104
+    v = C.equivariant_initialize(z, dim=3, method=equiv_method)                  # :109
+    pos1, pos2 = L.node_position(xyz, edi)                                       # :115
+    rij = L.edge_direction_normalized(pos1, pos2)                                # :116
+    d = L.node_distance_euclidean(pos1, pos2)                                    # :117
+    env = L.cos_cutoff_envelope(d, ca["cutoff"])                                 # :118
+    rbf = L.bessel_basis(d, bessel_basis["num_radial"], bessel_basis["cutoff"],
+                         bessel_basis.get("envelope_exponent", 5), frequencies=p["bessel.frequencies"])   # :119
+    for i in range(depth):                                                       # :121-133
+        ds, dv = C.painn_conv(p.sub("conv_%d" % i), z, v, rbf, env, rij, edi, "swish", ca["cutoff"],
+                              ca["conv_pool"])
+        z = z.with_values(z.values + ds.values)
+        v = v.with_values(v.values + dv.values)
+        ds, dv = C.painn_update(p.sub("update_%d" % i), z, v, "swish")
+        z = z.with_values(z.values + ds.values)
+        v = v.with_values(v.values + dv.values)
+    out = L.pooling_embedding(z, pooling)                                        # :137
+    return _mlp(p.sub("output_mlp"), out, list(output_mlp_act))                  # :138
+
+
+def relational_dense(x, relations, kernel, bias, activation):
+    """RelationalDense.call, kgcnn/layers/relational.py:219-238."""
+    kernel_per_feature = kernel[relations.values.to(torch.int64)]           # :233
+    new = torch.einsum("nf,nfu->nu", x.values, kernel_per_feature)          # :234 batch_dot
+    if bias is not None:
+        new = new + bias                                                     # :235-236
+    return x.with_values(ops.activation(activation)(new))                    # :237
+
+
+def hdnnp2nd_energy(params, z, xyz, eij, ijk, g2_kwargs, g4_kwargs, mlp_activation, pooling="sum"):
+    """make_model_behler, kgcnn/literature/HDNNP2nd.py:206-229 (graph embedding, no normalization)."""
+    p = P(params, "layers_by_name.")
+    g2 = dict(g2_kwargs)
+    g4 = dict(g4_kwargs)
+    mult = g4.pop("multiplicity", None)
+    t2, e2 = C.acsf_g2_param_table(g2["eta"], g2["rs"], g2["rc"], g2["elements"])
+    t4, e4 = C.acsf_g4_param_table(g4["eta"], g4["zeta"], g4["lamda"], g4["rc"], g4["elements"])
+    rep_g2 = C.acsf_g2(z, xyz, eij, t2, e2)                                  # :213
+    rep_g4 = C.acsf_g4(z, xyz, ijk, t4, e4, multiplicity=mult)               # :214
+    n = xyz.with_values(torch.cat([rep_g2.values, rep_g4.values], dim=-1))   # :215
+    for i, act in enumerate(mlp_activation):                                 # :222 RelationalMLP
+        sub = p.sub("mlp.mlp_dense_layer_list.%d" % i)
+        n = relational_dense(n, z, sub["kernel"], sub.get("bias"), act)
+    return L.pooling_embedding(n, pooling)                                   # :226

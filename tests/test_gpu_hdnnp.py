@@ -1,0 +1,88 @@
+"""ACSF G2/G4 through the CUDA path against the reference's golden vectors, and the HDNNP2nd energy+force model
+against the fp64 oracle (BASELINE configs[3])."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import GOLDEN
+from helpers import RTOL, device_ragged, oracle_ragged, rel_err
+from oracle import models as OM
+
+pytestmark = pytest.mark.gpu
+
+
+def _golden_inputs(angle_key="angle_index"):
+    d = np.load(os.path.join(GOLDEN, "acsf.npz"))
+    z = device_ragged(d["atomic_number"], d["atomic_number_lengths"])
+    xyz = device_ragged(d["positions"].astype(np.float32), d["position_lengths"])
+    eij = device_ragged(d["edge_index"], d["edge_index_lengths"])
+    ijk = device_ragged(d[angle_key], d[angle_key + "_lengths"])
+    return d, z, xyz, eij, ijk
+
+
+def test_acsf_g2_reference_golden_vector():
+    # test/test_hdnnp.py:103-111
+    from gcnn_keras_b200.layers.conv.acsf_conv import ACSFG2
+    d, z, xyz, eij, _ = _golden_inputs()
+    layer = ACSFG2(**ACSFG2.make_param_table(eta=d["g2_eta"].tolist(), rs=d["g2_rs"].tolist(), rc=float(d["g2_rc"]),
+                                             elements=d["g2_elements"].tolist()))
+    out = layer([z, xyz, eij])
+    assert np.all(np.abs(out[2][0].cpu().numpy() - d["expected_g2"]) < 1e-4)
+
+
+def test_acsf_g4_reference_golden_vector():
+    # test/test_hdnnp.py:113-134
+    from gcnn_keras_b200.layers.conv.acsf_conv import ACSFG4
+    d, z, xyz, _, ijk = _golden_inputs()
+    layer = ACSFG4(**ACSFG4.make_param_table(eta=d["g4_eta"].tolist(), zeta=d["g4_zeta"].tolist(),
+                                             lamda=d["g4_lamda"].tolist(), rc=float(d["g4_rc"]),
+                                             elements=d["g4_elements"].tolist(),
+                                             multiplicity=float(d["g4_multiplicity"])))
+    out = layer([z, xyz, ijk])
+    assert np.all(np.abs(out[2][0].cpu().numpy() - d["expected_g4"]) < 1e-4)
+
+
+def _setup(batch=3, n_atoms=12, seed=0):
+    from gcnn_keras_b200.literature.HDNNP2nd import make_model_behler
+    from gcnn_keras_b200.model.force import EnergyForceModel
+    from gcnn_keras_b200.synthetic import HDNNP_C4_CONFIG, hdnnp_c4_batch
+    torch.manual_seed(seed)
+    torch.backends.cuda.matmul.allow_tf32 = False
+    b = hdnnp_c4_batch(batch, seed, n_atoms=n_atoms, max_neighbours=8)
+    model = EnergyForceModel(model_energy=make_model_behler(**HDNNP_C4_CONFIG), energy_output=0,
+                             output_to_tensor=False, output_as_dict=False, output_squeeze_states=True,
+                             is_physical_force=False)
+    inputs = [device_ragged(b["z"], b["node_len"]), device_ragged(b["xyz"], b["node_len"]),
+              device_ragged(b["index"], b["edge_len"]), device_ragged(b["angle_index"], b["angle_len"])]
+    return HDNNP_C4_CONFIG, b, model, inputs
+
+
+def test_hdnnp2nd_energy_forces_and_training_gradients():
+    cfg, b, model, inputs = _setup()
+    eng, force = model(inputs, training=True)
+    params = {k: v.detach().cpu().double().requires_grad_(True)
+              for k, v in model.energy_model.state_dict().items() if v.is_floating_point()}
+    z = oracle_ragged(b["z"], b["node_len"])
+    eij = oracle_ragged(b["index"], b["edge_len"])
+    ijk = oracle_ragged(b["angle_index"], b["angle_len"])
+    xyz = oracle_ragged(b["xyz"], b["node_len"], torch.float64)
+
+    def energy_fn(x):
+        return OM.hdnnp2nd_energy(params, z, x, eij, ijk, cfg["g2_kwargs"], cfg["g4_kwargs"],
+                                  cfg["mlp_kwargs"]["activation"])
+
+    o_eng, o_force = OM.energy_force(energy_fn, xyz)
+    o_force = o_force.squeeze(-1)
+    assert rel_err(eng.detach().cpu().numpy(), o_eng.detach().numpy()) < RTOL
+    assert rel_err(force.values.detach().cpu().numpy(), o_force.detach().numpy()) < RTOL
+    e_t, f_t = torch.tensor(b["energy"]).cuda(), torch.tensor(b["force"]).cuda()
+    loss = (1 / 200) * torch.mean((eng - e_t) ** 2) + (199 / 200) * torch.mean((force.values - f_t) ** 2)
+    named = [(n, p) for n, p in model.energy_model.named_parameters() if p.requires_grad]
+    grads = torch.autograd.grad(loss, [p for _, p in named], allow_unused=True)
+    o_loss = OM.force_training_loss(o_eng, o_force, torch.tensor(b["energy"], dtype=torch.float64),
+                                    torch.tensor(b["force"], dtype=torch.float64))
+    o_grads = torch.autograd.grad(o_loss, [params[n] for n, _ in named], allow_unused=True)
+    for (n, _), g, og in zip(named, grads, o_grads):
+        assert rel_err(g.cpu().numpy(), og.numpy()) < RTOL, n

@@ -1,0 +1,74 @@
+"""PaiNN energy, forces and force-training gradients on the GPU vs the fp64 oracle (BASELINE configs[2])."""
+import numpy as np
+import pytest
+import torch
+
+from helpers import RTOL, device_ragged, oracle_ragged, rel_err
+from oracle import models as OM
+
+pytestmark = pytest.mark.gpu
+
+
+def _setup(batch=4, depth=2, n_atoms=12, seed=0):
+    from gcnn_keras_b200.literature.PAiNN import make_model
+    from gcnn_keras_b200.model.force import EnergyForceModel
+    from gcnn_keras_b200.synthetic import PAINN_C3_CONFIG, painn_c3_batch
+    torch.manual_seed(seed)
+    torch.backends.cuda.matmul.allow_tf32 = False
+    cfg = dict(PAINN_C3_CONFIG, depth=depth)
+    b = painn_c3_batch(batch, seed, n_atoms=n_atoms)
+    model = EnergyForceModel(model_energy=make_model(**cfg), energy_output=0, output_to_tensor=False,
+                             output_as_dict=False, output_squeeze_states=True, is_physical_force=False)
+    inputs = [device_ragged(b["z"], b["node_len"]), device_ragged(b["xyz"], b["node_len"]),
+              device_ragged(b["index"], b["edge_len"])]
+    return cfg, b, model, inputs
+
+
+def _oracle(cfg, b, params):
+    params = {k: v.detach().cpu().double().requires_grad_(True) for k, v in params.items()}
+    z = oracle_ragged(b["z"], b["node_len"])
+    xyz = oracle_ragged(b["xyz"], b["node_len"], torch.float64)
+    edi = oracle_ragged(b["index"], b["edge_len"])
+
+    def energy_fn(x):
+        return OM.painn_energy(params, z, x, edi, cfg["depth"], cfg["bessel_basis"], cfg["conv_args"],
+                               cfg["equiv_initialize_kwargs"]["method"], cfg["output_mlp"]["activation"])
+
+    eng, force = OM.energy_force(energy_fn, xyz)
+    return params, eng, force.squeeze(-1)
+
+
+def test_painn_energy_forces_and_training_gradients():
+    cfg, b, model, inputs = _setup()
+    eng, force = model(inputs, training=True)
+    params, o_eng, o_force = _oracle(cfg, b, model.energy_model.state_dict())
+    assert rel_err(eng.detach().cpu().numpy(), o_eng.detach().numpy()) < RTOL
+    assert rel_err(force.values.detach().cpu().numpy(), o_force.detach().numpy()) < RTOL
+    e_t, f_t = torch.tensor(b["energy"]).cuda(), torch.tensor(b["force"]).cuda()
+    loss = (1 / 95) * torch.mean((eng - e_t) ** 2) + (94 / 95) * torch.mean((force.values - f_t) ** 2)
+    names = [n for n, _ in model.energy_model.named_parameters()]
+    grads = torch.autograd.grad(loss, list(model.energy_model.parameters()), allow_unused=True)
+    o_loss = OM.force_training_loss(o_eng, o_force, torch.tensor(b["energy"], dtype=torch.float64),
+                                    torch.tensor(b["force"], dtype=torch.float64), force_loss_factor=95.0)
+    o_grads = torch.autograd.grad(o_loss, [params[n] for n in names], allow_unused=True)
+    checked = 0
+    for n, g, og in zip(names, grads, o_grads):
+        if og is None or float(og.abs().max()) == 0.0:
+            assert g is None or float(g.abs().max()) < 1e-10, n
+            continue
+        assert rel_err(g.cpu().numpy(), og.numpy()) < RTOL, n
+        checked += 1
+    assert checked > 20
+    assert "layers_by_name.bessel.frequencies" in names     # trainable Bessel frequencies (geom.py:766-770)
+
+
+def test_painn_rotation_equivariance_of_forces():
+    cfg, b, model, inputs = _setup(batch=2, depth=1)
+    _, f0 = model(inputs, training=False)
+    q, _ = np.linalg.qr(np.random.default_rng(5).standard_normal((3, 3)))
+    q = q.astype(np.float32)
+    rot_inputs = [inputs[0], device_ragged(b["xyz"] @ q, b["node_len"]), inputs[2]]
+    e1, f1 = model(rot_inputs, training=False)
+    e0, _ = model(inputs, training=False)
+    assert rel_err(e1.cpu().numpy(), e0.cpu().numpy()) < 1e-4
+    assert rel_err(f1.values.cpu().numpy(), f0.values.cpu().numpy() @ q) < 1e-3
