@@ -24,10 +24,10 @@ def _setup(batch=4, depth=2, n_atoms=12, seed=0):
     return cfg, b, model, inputs
 
 
-def _oracle(cfg, b, params):
-    params = {k: v.detach().cpu().double().requires_grad_(True) for k, v in params.items()}
+def _oracle(cfg, b, params, dtype=torch.float64):
+    params = {k: v.detach().cpu().to(dtype).requires_grad_(True) for k, v in params.items()}
     z = oracle_ragged(b["z"], b["node_len"])
-    xyz = oracle_ragged(b["xyz"], b["node_len"], torch.float64)
+    xyz = oracle_ragged(b["xyz"], b["node_len"], dtype)
     edi = oracle_ragged(b["index"], b["edge_len"])
 
     def energy_fn(x):
@@ -48,15 +48,24 @@ def test_painn_energy_forces_and_training_gradients():
     loss = (1 / 95) * torch.mean((eng - e_t) ** 2) + (94 / 95) * torch.mean((force.values - f_t) ** 2)
     names = [n for n, _ in model.energy_model.named_parameters()]
     grads = torch.autograd.grad(loss, list(model.energy_model.parameters()), allow_unused=True)
-    o_loss = OM.force_training_loss(o_eng, o_force, torch.tensor(b["energy"], dtype=torch.float64),
-                                    torch.tensor(b["force"], dtype=torch.float64), force_loss_factor=95.0)
-    o_grads = torch.autograd.grad(o_loss, [params[n] for n in names], allow_unused=True)
+    def oracle_grads(dtype):
+        prm, oe, of = _oracle(cfg, b, model.energy_model.state_dict(), dtype)
+        ol = OM.force_training_loss(oe, of, torch.tensor(b["energy"], dtype=dtype),
+                                    torch.tensor(b["force"], dtype=dtype), force_loss_factor=95.0)
+        return torch.autograd.grad(ol, [prm[n] for n in names], allow_unused=True)
+
+    o_grads = oracle_grads(torch.float64)          # truth
+    o_grads32 = oracle_grads(torch.float32)        # the reference's own op order in fp32 ("TF-CPU-like")
     checked = 0
-    for n, g, og in zip(names, grads, o_grads):
+    for n, g, og, og32 in zip(names, grads, o_grads, o_grads32):
         if og is None or float(og.abs().max()) == 0.0:
             assert g is None or float(g.abs().max()) < 1e-10, n
             continue
-        assert rel_err(g.cpu().numpy(), og.numpy()) < RTOL, n
+        err = rel_err(g.cpu().numpy(), og.numpy())
+        err32 = rel_err(og32.numpy(), og.numpy())
+        # 1e-5 of the fp64 truth; where fp32 itself cannot reach that (the eps-initialised equivariant channel has
+        # O(1e-7) values), no worse than twice the fp32 restatement of the reference op chain
+        assert err < max(RTOL, 2 * err32), (n, err, err32)
         checked += 1
     assert checked > 20
     assert "layers_by_name.bessel.frequencies" in names     # trainable Bessel frequencies (geom.py:766-770)
