@@ -377,10 +377,52 @@ def gss_roofline(device, feat=64, n_graphs=65536, iters=20):
                     "frac > 1 means cache reuse, not skipped work; the kernel is L1-wavefront bound"}
 
 
+def build_painn(device, batch, seed):
+    from gcnn_keras_b200.literature.PAiNN import make_model
+    from gcnn_keras_b200.model.force import EnergyForceModel
+    from gcnn_keras_b200.synthetic import PAINN_C3_CONFIG, painn_c3_batch
+    from gcnn_keras_b200.training import ForceTrainStep
+    torch.manual_seed(1234)
+    model = EnergyForceModel(model_energy=make_model(**PAINN_C3_CONFIG), energy_output=0, output_to_tensor=True,
+                             output_as_dict=False, output_squeeze_states=True, is_physical_force=False)
+    return model, ForceTrainStep(model, lr=1e-3, force_loss_factor=95.0, clipnorm=1.0), painn_c3_batch(batch, seed)
+
+
+def build_hdnnp(device, batch, seed):
+    from gcnn_keras_b200.literature.HDNNP2nd import make_model_behler
+    from gcnn_keras_b200.model.force import EnergyForceModel
+    from gcnn_keras_b200.synthetic import HDNNP_C4_CONFIG, hdnnp_c4_batch
+    from gcnn_keras_b200.training import ForceTrainStep
+    torch.manual_seed(1234)
+    model = EnergyForceModel(model_energy=make_model_behler(**HDNNP_C4_CONFIG), energy_output=0,
+                             output_to_tensor=True, output_as_dict=False, output_squeeze_states=True,
+                             is_physical_force=False)
+    return model, ForceTrainStep(model, lr=1e-3, force_loss_factor=200.0, clipnorm=1.0), hdnnp_c4_batch(batch, seed)
+
+
+FORCE_WORKLOADS = {
+    "schnet": (build_schnet, 256, "SchNet force-train molecules/sec",
+               "C2: SchNet energy+force training step (force_schnet.py), synthetic MD17-ethanol-shaped data: 9 atoms, "
+               "cutoff 5 A (72 edges)"),
+    "painn": (build_painn, 512, "PaiNN force-train molecules/sec",
+              "C3: PaiNN energy+force training step (force_painn.py), synthetic 30-atom molecules, all pairs < 5 A"),
+    "hdnnp": (build_hdnnp, 256, "HDNNP2nd force-train molecules/sec",
+              "C4: HDNNP2nd ACSF G2/G4 energy+force training step (force_hdnnp2nd.py), synthetic 64-atom systems, "
+              "25 neighbours, 'kj' angle triples"),
+}
+
+
 def run_schnet(args, rank, world, device):
+    return run_force(args, rank, world, device, "schnet")
+
+
+def run_force(args, rank, world, device, kind):
     from gcnn_keras_b200.training import CapturedForceTrainStep
-    batch = args.batch
-    model, train_step, data = build_schnet(device, batch, seed=rank)
+    build, default_batch, metric, workload = FORCE_WORKLOADS[kind]
+    batch = args.batch or default_batch
+    model, train_step, data = build(device, batch, seed=rank)
+    if world > 1:
+        from gcnn_keras_b200.distributed import broadcast_parameters
     captured = CapturedForceTrainStep(train_step, data, device)
     n_params = sum(p.numel() for p in model.parameters())
 
@@ -391,13 +433,13 @@ def run_schnet(args, rank, world, device):
     loss_value = float(captured.loss_host)
     total_mol = sum_over_ranks(float(batch), world, device)
     line = {
-        "metric": "SchNet force-train molecules/sec", "value": total_mol / (ms_step * 1e-3), "unit": "molecules/s",
+        "metric": metric, "value": total_mol / (ms_step * 1e-3), "unit": "molecules/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "C2: SchNet energy+force training step (force_schnet.py), synthetic MD17-ethanol-shaped "
-                               "data: 9 atoms, cutoff 5 A (72 edges), batch %d per GPU" % batch,
-                   "batch_per_gpu": batch, "atoms": 9 * batch, "edges": 72 * batch, "depth": 6, "units": 128,
-                   "gauss_bins": 25, "parameters": n_params, "optimizer": "Adam(1e-3), clipnorm 1.0",
+        "config": {"workload": workload + ", batch %d per GPU" % batch,
+                   "batch_per_gpu": batch, "atoms": int(data["node_len"].sum()), "edges": int(data["edge_len"].sum()),
+                   "triples": int(data["angle_len"].sum()) if "angle_len" in data else 0,
+                   "parameters": n_params, "optimizer": "Adam(1e-3), clipnorm 1.0",
                    "step": "fwd + dE/dx + loss + d loss/d weights through the force + Adam, one CUDA graph",
                    "l2_policy": "256 MB L2 flush between timed steps (per-step CUDA events)",
                    "parallelism": "graphs sharded across %d rank(s); weight-gradient all-reduce only" % world},
@@ -412,6 +454,100 @@ def run_schnet(args, rank, world, device):
     if rank == 0 and not args.no_roofline:
         line["roofline"] = gss_roofline(device)
     return line
+
+
+# ----------------------------------------------------------------------------------------------------
+# workload: GCN layer on one large graph (BASELINE.json configs[4], C5), receiver-range partition
+# ----------------------------------------------------------------------------------------------------
+def gcn_c5_shard(n_nodes, lo, hi, mean_deg=30, window=50000, seed=0):
+    """In-edges of receivers [lo, hi): Poisson(30) senders each, 80 % from a +-50 000 index window, 20 % uniform;
+    weights 1/sqrt(deg_i deg_j) with the expected degree of the sender.  Receiver-sorted."""
+    rng = np.random.default_rng(seed * 1000003 + lo)
+    deg = rng.poisson(mean_deg, size=hi - lo).astype(np.int64)
+    recv = np.repeat(np.arange(lo, hi, dtype=np.int64), deg)
+    e = int(deg.sum())
+    local = rng.random(e) < 0.8
+    near = recv + rng.integers(-window, window + 1, size=e)
+    far = rng.integers(0, n_nodes, size=e)
+    send = np.where(local, np.clip(near, 0, n_nodes - 1), far)
+    w = (1.0 / np.sqrt(np.maximum(np.repeat(deg, deg), 1) * float(mean_deg))).astype(np.float32)
+    return recv, send, w
+
+
+def gcn_bytes(E, N, F):
+    """B_gcn of SURVEY.md 8d (forward + backward, edge weights [E,1] without gradient)."""
+    return 8 * E * F + 8 * N * F + 16 * E + 8 * N
+
+
+def run_gcn(args, rank, world, device):
+    from gcnn_keras_b200 import _lib
+    from gcnn_keras_b200 import functional as F
+    from gcnn_keras_b200.partition import PartitionedGraph, gcn_layer_partitioned, partition_bounds
+    n_nodes, feat = args.gcn_nodes, args.gcn_feat
+    per, bounds = partition_bounds(n_nodes, world)
+    lo, hi = bounds[rank]
+    recv, send, w = gcn_c5_shard(n_nodes, lo, hi, seed=0)
+    # PartitionedGraph slices a global receiver-sorted list; hand it this rank's slice with global ids
+    graph = PartitionedGraph.__new__(PartitionedGraph)
+    graph.n_nodes, graph.rank, graph.world, graph.per, graph.lo, graph.hi = n_nodes, rank, world, per, lo, hi
+    from gcnn_keras_b200.plan import Relation
+    pin = lambda a: torch.from_numpy(a).pin_memory()
+    recv_p, send_p, w_p = pin((recv - rank * per).astype(np.int32)), pin(send.astype(np.int32)), pin(w.reshape(-1, 1))
+    x_p = torch.randn(per, feat).pin_memory()
+    E = len(recv)
+
+    def load():
+        graph.rel_recv = Relation(recv_p.to(device, non_blocking=True), per, is_sorted=True)
+        graph.rel_send = Relation(send_p.to(device, non_blocking=True), per * world)
+        graph.weights = w_p.to(device, non_blocking=True)
+        return x_p.to(device, non_blocking=True).requires_grad_(True)
+
+    torch.manual_seed(0)
+    kernel = (torch.randn(feat, feat, device=device) / feat ** 0.5).requires_grad_(True)
+    bias = torch.zeros(feat, device=device, requires_grad=True)
+    x_d = load()
+    graph.rel_recv.rowptr, graph.rel_send.rowptr, graph.rel_send.permuted_ids(graph.rel_recv)
+    dy = torch.randn(per, feat, device=device)
+
+    def step(x=None):
+        x = x_d if x is None else x
+        y = gcn_layer_partitioned(graph, x, kernel, bias, "relu")
+        return torch.autograd.grad(y, [x, kernel, bias], dy)
+
+    _lib.launch_count_reset()
+    step()
+    launches = _lib.launch_count()
+    ms_step, clocks = timed_region(step, args.steps, args.warmup, world, device)
+    g_host = torch.empty(per, feat).pin_memory()
+
+    def e2e_step():
+        x = load()
+        gx, _, _ = step(x)
+        g_host.copy_(gx, non_blocking=True)
+
+    ms_e2e, _ = timed_region(e2e_step, max(2, min(args.steps, 5)), 2, world, device)
+    total_edges = sum_over_ranks(float(E), world, device)
+    peak, peak_src = measured_peaks()
+    alg = gcn_bytes(E, per, feat)
+    achieved = alg / (ms_step * 1e-3) / 1e9
+    return {
+        "metric": "edges/sec (GCN layer fwd+bwd, one large graph)", "value": total_edges / (ms_step * 1e-3),
+        "unit": "edges/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "C5: GCN layer (Dense -> gather*a_e -> segment-sum -> relu) fwd+bwd on one graph, "
+                               "%d nodes, Poisson(30) in-edges, F=%d, receiver-range partition over %d GPU(s)"
+                               % (n_nodes, feat, world),
+                   "nodes": n_nodes, "edges_this_rank": E, "features": feat,
+                   "l2_policy": "inputs larger than L2 (node features %.0f MB)" % (n_nodes * feat * 4 / 1e6),
+                   "parallelism": "halo all-gather fwd / reduce-scatter bwd per layer (NCCL), weights replicated"},
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": None, "kernel": "whole layer step (gms fwd + gms^T bwd dominate)",
+                     "algorithmic_bytes_per_step": alg, "peak_source": peak_src},
+        "e2e": {"value": total_edges / (ms_e2e * 1e-3), "unit": "edges/s",
+                "h2d_bytes_per_step": recv_p.numel() * 4 + send_p.numel() * 4 + w_p.numel() * 4 + x_p.numel() * 4,
+                "d2h_bytes_per_step": per * feat * 4, "ms_per_step": ms_e2e},
+        "gpu_launches": launches * args.steps, "clocks": clocks,
+    }
 
 
 def cpu_schnet(batch, steps, warmup, threads):
@@ -458,7 +594,7 @@ def cpu_schnet(batch, steps, warmup, threads):
 
 def cpu_baseline_schnet(args):
     cores = os.cpu_count() or 1
-    mps, ms = cpu_schnet(32, steps=3, warmup=1, threads=cores)
+    mps, ms = cpu_schnet(32, steps=3, warmup=1, threads=cores)   # batch 256 -> 32: bounded CPU sample
     return {"value": mps, "unit": "molecules/s", "cores": cores, "kind": "port",
             "sample": "same SchNet C2 train step at batch 32 (oracle: reference op chain on torch-CPU fp32, "
                       "autograd double backward + Adam), 3 steps, %.0f ms/step" % ms}
@@ -487,19 +623,21 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default=os.environ.get("KGCNN_BENCH_WORKLOAD", "schnet"), choices=["gss", "schnet"])
+    ap.add_argument("--workload", default=os.environ.get("KGCNN_BENCH_WORKLOAD", "schnet"), choices=["gss", "schnet", "painn", "hdnnp", "gcn"])
     ap.add_argument("--gss-graphs", type=int, default=65536)
     ap.add_argument("--gss-feat", type=int, default=64)
+    ap.add_argument("--gcn-nodes", type=int, default=2000000)
+    ap.add_argument("--gcn-feat", type=int, default=128)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
-    ap.add_argument("--batch", type=int, default=256, help="molecules per GPU (schnet workload)")
+    ap.add_argument("--batch", type=int, default=0, help="molecules per GPU (0 = the config's batch size)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
 
     if args.impl == "reference":
         if int(os.environ.get("RANK", "0")) != 0:
             return 0
-        fn = {"gss": run_reference_gss, "schnet": globals().get("run_reference_schnet", run_reference_gss)}[args.workload]
+        fn = {"gss": run_reference_gss}.get(args.workload, run_reference_schnet)
         print(json.dumps(fn(args)))
         return 0
 
@@ -511,12 +649,15 @@ def main():
     torch.cuda.set_device(device)
     torch.backends.cuda.matmul.allow_tf32 = False
     torch.backends.cudnn.allow_tf32 = False
-    fn = {"gss": run_gss, "schnet": globals().get("run_schnet", run_gss)}[args.workload]
-    line = fn(args, rank, world, device)
+    if args.workload in FORCE_WORKLOADS:
+        line = run_force(args, rank, world, device, args.workload)
+    else:
+        line = {"gss": run_gss, "gcn": run_gcn}[args.workload](args, rank, world, device)
     if rank == 0:
         if world == 1 and not args.no_cpu_baseline:
-            cb = {"gss": cpu_baseline_gss, "schnet": globals().get("cpu_baseline_schnet", cpu_baseline_gss)}[args.workload]
-            line["cpu_baseline"] = cb(args)
+            cb = {"gss": cpu_baseline_gss, "schnet": cpu_baseline_schnet}.get(args.workload)
+            if cb is not None:
+                line["cpu_baseline"] = cb(args)
         print(json.dumps(line))
     if world > 1:
         import torch.distributed as dist

@@ -43,7 +43,7 @@ SIGNATURES = {
 
 OP_SUM, OP_MEAN, OP_MAX, OP_MIN = 0, 1, 2, 3
 BASIS_NONE, BASIS_GAUSS, BASIS_BESSEL = 0, 1, 2
-ACT_CODES = {"linear": 0, "shifted_softplus": 1, "swish": 2, "tanh": 3, "relu": 4, "softplus2": 5, "sigmoid": 6}
+ACT_CODES = {"linear": 0, "shifted_softplus": 1, "swish": 2, "tanh": 3, "relu": 4, "softplus2": 5, "sigmoid": 6, "leaky_relu": 7}
 
 _lib = None
 

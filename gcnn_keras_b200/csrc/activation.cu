@@ -25,6 +25,8 @@ __device__ __forceinline__ float act_deriv(float x, int order) {
     return order == 0 ? x : (order == 1 ? 1.f : 0.f);
   } else if (ACT == KGCNN_ACT_RELU) {
     return order == 0 ? fmaxf(x, 0.f) : (order == 1 ? (x > 0.f ? 1.f : 0.f) : 0.f);
+  } else if (ACT == KGCNN_ACT_LEAKY_RELU) {   // kgcnn>leaky_relu, alpha = 0.05 (activ.py:61-80)
+    return order == 0 ? (x > 0.f ? x : 0.05f * x) : (order == 1 ? (x > 0.f ? 1.f : 0.05f) : 0.f);
   } else if (ACT == KGCNN_ACT_TANH) {
     float t = tanhf(x);
     float d = 1.f - t * t;
@@ -148,6 +150,8 @@ int kgcnn_bias_act(const float* pre, const float* bias, const float* g1, const f
     case KGCNN_ACT_TANH: return launch_act<KGCNN_ACT_TANH>(pre, bias, g1, g2, order, total, U, out, st);
     case KGCNN_ACT_RELU: return launch_act<KGCNN_ACT_RELU>(pre, bias, g1, g2, order, total, U, out, st);
     case KGCNN_ACT_SIGMOID: return launch_act<KGCNN_ACT_SIGMOID>(pre, bias, g1, g2, order, total, U, out, st);
+    case KGCNN_ACT_LEAKY_RELU:
+      return launch_act<KGCNN_ACT_LEAKY_RELU>(pre, bias, g1, g2, order, total, U, out, st);
     default: return KGCNN_E_INVALID;
   }
 }

@@ -51,7 +51,8 @@ enum {
   KGCNN_ACT_TANH = 3,
   KGCNN_ACT_RELU = 4,
   KGCNN_ACT_SOFTPLUS2 = 5,
-  KGCNN_ACT_SIGMOID = 6
+  KGCNN_ACT_SIGMOID = 6,
+  KGCNN_ACT_LEAKY_RELU = 7 /* alpha = 0.05 */
 };
 
 int kgcnn_version(void);

@@ -145,6 +145,8 @@ ACTIVATIONS = {
     "swish": swish, "kgcnn>swish": swish,
     "tanh": torch.tanh, "relu": torch.relu, "sigmoid": torch.sigmoid, "softplus": softplus,
     "kgcnn>leaky_softplus": leaky_softplus,
+    "kgcnn>leaky_relu": lambda x: torch.nn.functional.leaky_relu(x, 0.05),
+    "leaky_relu": lambda x: torch.nn.functional.leaky_relu(x, 0.05),
 }
 
 
