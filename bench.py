@@ -116,11 +116,33 @@ def sum_over_ranks(value, world, device):
     return float(t.item())
 
 
+PROFILE = False
+
+
+def kernel_table(step_fn, iters=3, rows=30):
+    """Kernel-time breakdown through CUPTI (diagnostics only; never a bench number)."""
+    from torch.profiler import ProfilerActivity, profile
+    torch.cuda.synchronize()
+    with profile(activities=[ProfilerActivity.CUDA]) as prof:
+        for _ in range(iters):
+            step_fn()
+        torch.cuda.synchronize()
+    ev = sorted(prof.key_averages(), key=lambda e: -e.device_time_total)
+    total = sum(e.device_time_total for e in ev)
+    print("[profile] device time per step %.3f ms, %d kernels/step" % (total / iters / 1e3,
+                                                                       sum(e.count for e in ev) // iters), file=sys.stderr)
+    for e in ev[:rows]:
+        print("[profile] %9.1f us/step %5.1f%% x%-4d %s" % (e.device_time_total / iters, 100 * e.device_time_total / total,
+                                                            e.count // iters, e.key[:120]), file=sys.stderr)
+
+
 def timed_region(step_fn, steps, warmup, world, device):
     """W warm-ups, then K steps bracketed by barrier + synchronize, CUDA events on the launching stream,
     max over ranks.  Returns (ms_per_step, clocks)."""
     for _ in range(warmup):
         step_fn()
+    if PROFILE:
+        kernel_table(step_fn)
     torch.cuda.synchronize()
     barrier(world)
     torch.cuda.synchronize()
@@ -469,7 +491,7 @@ def gcn_c5_shard(n_nodes, lo, hi, mean_deg=30, window=50000, seed=0):
     local = rng.random(e) < 0.8
     near = recv + rng.integers(-window, window + 1, size=e)
     far = rng.integers(0, n_nodes, size=e)
-    send = np.where(local, np.clip(near, 0, n_nodes - 1), far)
+    send = np.where(local, np.mod(near, n_nodes), far)      # the index window wraps around (no boundary hubs)
     w = (1.0 / np.sqrt(np.maximum(np.repeat(deg, deg), 1) * float(mean_deg))).astype(np.float32)
     return recv, send, w
 
@@ -631,7 +653,10 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
     ap.add_argument("--batch", type=int, default=0, help="molecules per GPU (0 = the config's batch size)")
+    ap.add_argument("--profile", action="store_true", help="print a CUPTI kernel table to stderr (diagnostics)")
     args = ap.parse_args()
+    global PROFILE
+    PROFILE = args.profile
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
 
     if args.impl == "reference":

@@ -32,7 +32,9 @@ SIGNATURES = {
     "kgcnn_permute_i32": (_i, [_p, _i, _p, _l, _p, _p]),
     "kgcnn_gather_rows": (_i, [_p, _l, _i, _p, _i, _l, _p, _l, _p]),
     "kgcnn_gather_rows_i64": (_i, [_p, _l, _i, _p, _i, _l, _p, _l, _p]),
-    "kgcnn_gather_mul_segment_reduce": (_i, [_p, _i, _p, _i, _p, _p, _p, _i, _i, _l, _l, _i, _p, _p]),
+    "kgcnn_gather_mul_segment_reduce": (_i, [_p, _i, _p, _i, _p, _p, _p, _i, _i, _l, _l, _i, _p, _p, _p, _i, _i, _p]),
+    "kgcnn_row_stats": (_i, [_p, _l, _p, _p]),
+    "kgcnn_long_rows_build": (_i, [_p, _l, _i, _i, _p, _p, _p]),
     "kgcnn_gather2_mul": (_i, [_p, _p, _i, _p, _p, _i, _i, _l, _i, _p, _p]),
     "kgcnn_bias_act": (_i, [_p, _p, _p, _p, _i, _i, _l, _i, _p, _p]),
     "kgcnn_colsum_workspace_bytes": (_z, [_l, _i]),

@@ -21,6 +21,14 @@ constexpr int kWarps = kThreads / 32;
 
 enum Mode { kSumW0 = 0, kSumW1 = 1, kSumW2 = 2, kMax = 3, kMin = 4 };
 
+// optional list of hub rows (segments longer than `thresh`): handled by one CTA each in a second pass
+struct LongRows {
+  const int32_t* rows = nullptr;   // device [cap]
+  const int32_t* count = nullptr;  // device scalar
+  int cap = 0;
+  int thresh = 0;
+};
+
 template <typename V>
 struct Vec;
 template <>
@@ -69,7 +77,8 @@ template <typename V, int LPR, int VPL, int MODE, bool GATHER, bool EXACT, bool 
 __global__ void __launch_bounds__(kThreads)
 gms_kernel(const V* __restrict__ x, const V* __restrict__ wv, const float* __restrict__ ws,
            const int32_t* __restrict__ rowptr, const int32_t* __restrict__ perm, const int32_t* __restrict__ gidx,
-           int gidx_stride, int gidx_permuted, int64_t n_out, int nvec, int mean, V* __restrict__ y) {
+           int gidx_stride, int gidx_permuted, int64_t n_out, int nvec, int mean, V* __restrict__ y,
+           int long_thresh) {
   constexpr int G = 32 / LPR;
   constexpr int U = (VPL >= 3) ? 2 : 4;  // gathered rows in flight per lane group
   using T = Vec<V>;
@@ -84,7 +93,10 @@ gms_kernel(const V* __restrict__ x, const V* __restrict__ wv, const float* __res
   const bool valid = row < n_out;
   if (!GPR && !valid) return;  // warp-uniform
   const int cbase = blockIdx.y * (LPR * VPL) + sub;
-  const int beg = valid ? __ldg(rowptr + row) : 0, end = valid ? __ldg(rowptr + row + 1) : 0;
+  int beg = valid ? __ldg(rowptr + row) : 0, end = valid ? __ldg(rowptr + row + 1) : 0;
+  // hub rows (segment longer than long_thresh) are left to the block-per-row pass over the long-row list
+  const bool is_long = long_thresh > 0 && (end - beg) > long_thresh;
+  if (is_long) end = beg;
   bool cok[VPL];
 #pragma unroll
   for (int k = 0; k < VPL; ++k) cok[k] = EXACT || (cbase + k * LPR < nvec);
@@ -169,7 +181,7 @@ gms_kernel(const V* __restrict__ x, const V* __restrict__ wv, const float* __res
       else T::add(acc[k], other);
     }
   }
-  if (GPR ? valid : (g == 0)) {
+  if ((GPR ? valid : (g == 0)) && !is_long) {
     const bool empty = end <= beg;
     const float sc = (mean && !empty) ? 1.f / static_cast<float>(end - beg) : 1.f;
 #pragma unroll
@@ -191,13 +203,15 @@ __global__ void __launch_bounds__(kThreads)
 gms_block_kernel(const V* __restrict__ x, const V* __restrict__ wv, const float* __restrict__ ws,
                  const int32_t* __restrict__ rowptr, const int32_t* __restrict__ perm,
                  const int32_t* __restrict__ gidx, int gidx_stride, int gidx_permuted, int64_t n_out, int nvec,
-                 int mean, V* __restrict__ y) {
+                 int mean, V* __restrict__ y, const int32_t* __restrict__ row_map,
+                 const int32_t* __restrict__ n_rows_dev) {
   constexpr int LPR = 8;
   constexpr int NG = kThreads / LPR;  // 32 lane groups
   using T = Vec<V>;
   __shared__ V red[NG][LPR];
   const int g = threadIdx.x / LPR, sub = threadIdx.x % LPR;
-  const int64_t row = blockIdx.x;
+  if (n_rows_dev && static_cast<int>(blockIdx.x) >= __ldg(n_rows_dev)) return;   // block-uniform
+  const int64_t row = row_map ? __ldg(row_map + blockIdx.x) : blockIdx.x;
   const int beg = __ldg(rowptr + row), end = __ldg(rowptr + row + 1);
   const float init = (MODE == kMax) ? -INFINITY : (MODE == kMin) ? INFINITY : 0.f;
   for (int cb = 0; cb < nvec; cb += LPR) {
@@ -238,10 +252,11 @@ gms_block_kernel(const V* __restrict__ x, const V* __restrict__ wv, const float*
 template <typename V>
 int launch_block(int mode, bool gather, const V* x, const V* wv, const float* ws, const int32_t* rowptr,
                  const int32_t* perm, const int32_t* gidx, int gs, int gp, int64_t n_out, int nvec, int mean, V* y,
-                 cudaStream_t st) {
-  const unsigned grid = static_cast<unsigned>(n_out);
-#define KGCNN_BLK(M, GA) \
-  gms_block_kernel<V, M, GA><<<grid, kThreads, 0, st>>>(x, wv, ws, rowptr, perm, gidx, gs, gp, n_out, nvec, mean, y)
+                 const int32_t* row_map, const int32_t* n_rows_dev, int grid_rows, cudaStream_t st) {
+  const unsigned grid = static_cast<unsigned>(row_map ? grid_rows : n_out);
+#define KGCNN_BLK(M, GA)                                                                                        \
+  gms_block_kernel<V, M, GA><<<grid, kThreads, 0, st>>>(x, wv, ws, rowptr, perm, gidx, gs, gp, n_out, nvec, mean, y, \
+                                                       row_map, n_rows_dev)
   if (mode == kMax) { if (gather) return KGCNN_E_UNSUPPORTED; KGCNN_BLK(kMax, false); }
   else if (mode == kMin) { if (gather) return KGCNN_E_UNSUPPORTED; KGCNN_BLK(kMin, false); }
   else if (mode == kSumW0) { if (gather) KGCNN_BLK(kSumW0, true); else KGCNN_BLK(kSumW0, false); }
@@ -254,14 +269,14 @@ int launch_block(int mode, bool gather, const V* x, const V* wv, const float* ws
 template <typename V, int LPR, int VPL>
 int launch_shape(int mode, bool gather, const V* x, const V* wv, const float* ws, const int32_t* rowptr,
                  const int32_t* perm, const int32_t* gidx, int gs, int gp, int64_t n_out, int nvec, int mean, V* y,
-                 bool short_rows, cudaStream_t st) {
+                 bool short_rows, int long_thresh, cudaStream_t st) {
   constexpr bool kHasGpr = (LPR >= 4 && LPR < 32);
   const bool gpr = kHasGpr && short_rows;
   const int64_t rows_per_block = gpr ? kWarps * (32 / LPR) : kWarps;
   dim3 grid(static_cast<unsigned>(ceil_div<int64_t>(n_out, rows_per_block)),
             static_cast<unsigned>(ceil_div(nvec, LPR * VPL)));
   const bool exact = (nvec == LPR * VPL);
-#define KGCNN_GMS_ARGS x, wv, ws, rowptr, perm, gidx, gs, gp, n_out, nvec, mean, y
+#define KGCNN_GMS_ARGS x, wv, ws, rowptr, perm, gidx, gs, gp, n_out, nvec, mean, y, long_thresh
 #define KGCNN_GMS_LAUNCH(M, GA)                                                                      \
   do {                                                                                               \
     if constexpr (kHasGpr) {                                                                         \
@@ -284,11 +299,19 @@ int launch_shape(int mode, bool gather, const V* x, const V* wv, const float* ws
 template <typename V>
 int launch(int mode, bool gather, const V* x, const V* wv, const float* ws, const int32_t* rowptr,
            const int32_t* perm, const int32_t* gidx, int gs, int gp, int64_t n_out, int nvec, int mean, V* y,
-           bool short_rows, cudaStream_t st) {
+           bool short_rows, const LongRows& lr, cudaStream_t st) {
   if (n_out <= 1024)
-    return launch_block<V>(mode, gather, x, wv, ws, rowptr, perm, gidx, gs, gp, n_out, nvec, mean, y, st);
-#define KGCNN_GMS_SHAPE(L, P) \
-  return launch_shape<V, L, P>(mode, gather, x, wv, ws, rowptr, perm, gidx, gs, gp, n_out, nvec, mean, y, short_rows, st)
+    return launch_block<V>(mode, gather, x, wv, ws, rowptr, perm, gidx, gs, gp, n_out, nvec, mean, y, nullptr,
+                           nullptr, 0, st);
+  const int long_thresh = (lr.rows && lr.cap > 0) ? lr.thresh : 0;
+  if (long_thresh > 0) {
+    int rc = launch_block<V>(mode, gather, x, wv, ws, rowptr, perm, gidx, gs, gp, n_out, nvec, mean, y, lr.rows,
+                             lr.count, lr.cap, st);
+    if (rc != KGCNN_OK) return rc;
+  }
+#define KGCNN_GMS_SHAPE(L, P)                                                                                    \
+  return launch_shape<V, L, P>(mode, gather, x, wv, ws, rowptr, perm, gidx, gs, gp, n_out, nvec, mean, y, short_rows, \
+                               long_thresh, st)
   // few lanes per row -> many edges per warp instruction (the kernel is issue-bound, not DRAM-bound, when
   // gathered rows hit in L1/L2); 8 lanes x 128 bit = one full 128 B line per request.
   if (nvec <= 1) KGCNN_GMS_SHAPE(1, 1);
@@ -308,10 +331,10 @@ int launch(int mode, bool gather, const V* x, const V* wv, const float* ws, cons
 // defined in segment_v4.cu / segment_v1.cu
 int launch_v4(int mode, bool gather, const float* x, const float* w, const int32_t* rowptr, const int32_t* perm,
               const int32_t* gidx, int gs, int gp, int64_t n_out, int F, int mean, float* y, bool short_rows,
-              cudaStream_t st);
+              const LongRows& lr, cudaStream_t st);
 int launch_v1(int mode, bool gather, const float* x, const float* w, const int32_t* rowptr, const int32_t* perm,
               const int32_t* gidx, int gs, int gp, int64_t n_out, int F, int mean, float* y, bool short_rows,
-              cudaStream_t st);
+              const LongRows& lr, cudaStream_t st);
 
 }  // namespace seg
 }  // namespace kgcnn

@@ -108,6 +108,20 @@ def raw_plan_build(key, n_targets, assume_sorted):
     return rowptr, perm
 
 
+def raw_row_stats(rowptr, n_rows):
+    stats = torch.zeros((1,), dtype=torch.int32, device=rowptr.device)
+    check(_lib.lib().kgcnn_row_stats(_ptr(rowptr), n_rows, _ptr(stats), _stream()), "kgcnn_row_stats")
+    return stats
+
+
+def raw_long_rows(rowptr, n_rows, thresh, cap):
+    rows = torch.zeros((cap,), dtype=torch.int32, device=rowptr.device)
+    count = torch.zeros((1,), dtype=torch.int32, device=rowptr.device)
+    check(_lib.lib().kgcnn_long_rows_build(_ptr(rowptr), n_rows, thresh, cap, _ptr(rows), _ptr(count), _stream()),
+          "kgcnn_long_rows_build")
+    return rows, count
+
+
 def raw_permute_i32(src, perm):
     out = torch.empty_like(perm)
     check(_lib.lib().kgcnn_permute_i32(_ptr(src), 1, _ptr(perm), int(perm.shape[0]), _ptr(out), _stream()),
@@ -157,7 +171,8 @@ def raw_gms(x2d, w, rel_out, rel_src, op=OP_SUM):
         gidx, gperm = None, 0
     check(_lib.lib().kgcnn_gather_mul_segment_reduce(_ptr(x2d), Fdim, _ptr(w), wcols, _ptr(rel_out.rowptr),
                                                      _ptr(perm), _ptr(gidx), 1, gperm, n_out, rel_out.n_elements, op,
-                                                     _ptr(y),
+                                                     _ptr(y), _ptr(rel_out.long_rows), _ptr(rel_out.n_long),
+                                                     rel_out.long_cap, rel_out.LONG_THRESH if rel_out.long_cap else 0,
                                                      _stream()), "kgcnn_gather_mul_segment_reduce")
     return y
 

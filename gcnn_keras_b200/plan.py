@@ -72,6 +72,8 @@ class Relation:
         self._is_sorted = is_sorted
         self._permuted = {}               # id(other relation) -> other.ids[perm]
         self._inv_count = None
+        self.long_rows = self.n_long = None
+        self.long_cap = 0
 
     def _build(self):
         if self._rowptr is not None:
@@ -93,6 +95,31 @@ class Relation:
                 if mode is not None and mode.kind == "record":
                     mode.hints.append(self._is_sorted)
         self._rowptr, self._perm = F.raw_plan_build(self.ids, self.n_targets, self._is_sorted)
+        self._find_long_rows()
+
+    LONG_THRESH = 1024      # segments longer than this are reduced by a whole CTA (hub nodes)
+
+    def _find_long_rows(self):
+        """Hub rows would serialise one lane group for thousands of edges; list them once per batch."""
+        self.long_rows = self.n_long = None
+        self.long_cap = 0
+        if self.n_targets <= 1024 or self.n_elements <= self.LONG_THRESH:
+            return                      # few-row outputs already use the block-per-row mapping
+        stats = F.raw_row_stats(self._rowptr, self.n_targets)
+        mode = _MODE
+        if mode is not None and mode.kind == "capture":
+            if mode.cursor >= len(mode.hints):
+                raise RuntimeError("CUDA-graph capture met a relation that the warm-up pass did not record")
+            has_long = bool(mode.hints[mode.cursor])
+            mode.cursor += 1
+        else:
+            has_long = int(stats.cpu()[0]) > self.LONG_THRESH
+            if mode is not None and mode.kind == "record":
+                mode.hints.append(has_long)
+        if has_long:
+            self.long_cap = self.n_elements // self.LONG_THRESH + 1
+            self.long_rows, self.n_long = F.raw_long_rows(self._rowptr, self.n_targets, self.LONG_THRESH,
+                                                          self.long_cap)
 
     @property
     def is_sorted(self):

@@ -127,7 +127,15 @@ int kgcnn_gather_rows_i64(const int64_t* x, int64_t N, int F, const int32_t* idx
 int kgcnn_gather_mul_segment_reduce(const float* x, int F, const float* w, int w_cols,
                                     const int32_t* rowptr, const int32_t* perm, const int32_t* gidx,
                                     int gidx_stride, int gidx_permuted, int64_t n_out, int64_t n_elements,
-                                    int op, float* y, kgcnn_stream_t stream);
+                                    int op, float* y, const int32_t* long_rows /*nullable*/,
+                                    const int32_t* n_long /*nullable*/, int long_cap, int long_thresh,
+                                    kgcnn_stream_t stream);
+/* hub rows: stats[0] = max segment length (atomicMax into a zeroed word); kgcnn_long_rows_build appends every
+ * row longer than `thresh` to rows[cap] (count zeroed by the caller).  Passing the list to the call above makes
+ * the row-parallel kernel skip those rows and reduces each of them with a whole CTA instead. */
+int kgcnn_row_stats(const int32_t* rowptr, int64_t n_rows, int32_t* stats, kgcnn_stream_t stream);
+int kgcnn_long_rows_build(const int32_t* rowptr, int64_t n_rows, int thresh, int cap, int32_t* rows,
+                          int32_t* count, kgcnn_stream_t stream);
 
 /* z[e, f] = a[ia[e], f] * b[ib[e], f]   (reduce_f==0)   or   z[e] = sum_f a[ia[e],f]*b[ib[e],f]
  * ia/ib == NULL means "row e".  VJP of the fused op above with respect to w. */

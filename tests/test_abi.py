@@ -32,9 +32,9 @@ def test_argument_validation_without_gpu():
     # invalid arguments are rejected before any launch, so these are safe on a CPU-only machine
     assert h.kgcnn_gather_rows(None, 4, 0, None, 1, 4, None, 4, None) == -1          # F <= 0
     assert h.kgcnn_gather_rows(None, 4, 8, None, 1, 0, None, 8, None) == 0           # E == 0 is a no-op
-    assert h.kgcnn_gather_mul_segment_reduce(None, 8, None, 3, None, None, None, 1, 0, 4, 9, 0, None, None) == -1
-    assert h.kgcnn_gather_mul_segment_reduce(None, 8, None, 0, None, None, None, 1, 0, 4, 9, 7, None, None) == -1
-    assert h.kgcnn_gather_mul_segment_reduce(None, 8, None, 0, None, None, None, 1, 0, 0, 0, 0, None, None) == 0
+    assert h.kgcnn_gather_mul_segment_reduce(None, 8, None, 3, None, None, None, 1, 0, 4, 9, 0, None, None, None, 0, 0, None) == -1
+    assert h.kgcnn_gather_mul_segment_reduce(None, 8, None, 0, None, None, None, 1, 0, 4, 9, 7, None, None, None, 0, 0, None) == -1
+    assert h.kgcnn_gather_mul_segment_reduce(None, 8, None, 0, None, None, None, 1, 0, 0, 0, 0, None, None, None, 0, 0, None) == 0
     assert h.kgcnn_plan_workspace_bytes(1000, 100) > 3 * 4000
 
 

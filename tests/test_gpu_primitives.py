@@ -437,3 +437,33 @@ def test_dense_forward_backward_double_backward(act):
             assert float(np.abs(o).max()) < 1e-12
             continue
         assert rel_err(a, o) < RTOL
+
+
+def test_hub_rows_are_reduced_by_the_long_row_pass():
+    """A few receivers with tens of thousands of edges among many ordinary rows (power-law graphs)."""
+    from gcnn_keras_b200 import functional as F
+    from gcnn_keras_b200.plan import Relation
+    rng = np.random.default_rng(17)
+    n, feat = 3000, 64
+    recv = np.concatenate([rng.integers(0, n, size=20000), np.full(30000, 7), np.full(5000, 2999),
+                           np.full(1500, 1234)]).astype(np.int32)
+    send = rng.integers(0, n, size=len(recv)).astype(np.int32)
+    perm = rng.permutation(len(recv))
+    recv, send = recv[perm], send[perm]
+    x = rng.standard_normal((n, feat)).astype(np.float32)
+    w = rng.standard_normal((len(recv), 1)).astype(np.float32)
+    r_out, r_src = Relation(torch.tensor(recv).cuda(), n), Relation(torch.tensor(send).cuda(), n)
+    assert r_out.rowptr is not None and r_out.long_cap > 0 and int(r_out.n_long.item()) == 3
+    got = F.gather_mul_segment_sum(torch.tensor(x).cuda(), torch.tensor(w).cuda(), r_out, r_src)
+    want = np.zeros((n, feat))
+    np.add.at(want, recv, x[send].astype(np.float64) * w.astype(np.float64))
+    assert rel_err(got.cpu().numpy(), want) < RTOL
+    got2 = F.gather_mul_segment_sum(torch.tensor(x).cuda(), torch.tensor(w).cuda(), r_out, r_src)
+    assert torch.equal(got, got2)
+    for method in ("mean", "max"):
+        v = rng.standard_normal((len(recv), feat)).astype(np.float32)
+        g = F.segment_reduce(torch.tensor(v).cuda(), r_out, method)
+        order = np.argsort(recv, kind="stable")
+        wm = OO.segment_ops_by_name(method, torch.tensor(v[order], dtype=torch.float64),
+                                    torch.tensor(recv[order], dtype=torch.int64))
+        assert rel_err(g.cpu().numpy()[:wm.shape[0]], wm.numpy()) < RTOL
