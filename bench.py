@@ -360,21 +360,9 @@ def timed_steps_with_l2_flush(step_fn, steps, warmup, world, device):
     return max_over_ranks(ms, world, device) / steps, clocks.summary()
 
 
-def gss_roofline(device, feat=64, n_graphs=65536, iters=20):
-    """The north-star kernel (fused gather -> segment-sum) timed alone on GSS-L for the roofline object."""
-    from gcnn_keras_b200 import RaggedTensor
+def _time_gms_pair(x, dy, recv, send, iters):
     from gcnn_keras_b200 import functional as F
-    from gcnn_keras_b200.plan import get_plan
-    x_h, idx_h, ns_h, es_h = gss_inputs(n_graphs, feat=feat, seed=0)
-    N, E = x_h.shape[0], idx_h.shape[0]
-    x = torch.from_numpy(x_h).to(device)
-    nodes = RaggedTensor.from_row_splits(x, torch.from_numpy(ns_h).to(device))
-    index = RaggedTensor.from_row_splits(torch.from_numpy(idx_h).to(device), torch.from_numpy(es_h).to(device))
-    plan = get_plan(index, nodes)
-    recv, send = plan.relation(0), plan.relation(1)
-    recv.rowptr, send.rowptr, send.permuted_ids(recv)
-    dy = torch.randn(N, feat, device=device)
-    for _ in range(5):
+    for _ in range(3):
         F.raw_gms(x, None, recv, send)
         F.raw_gms(dy, None, send, recv)
     torch.cuda.synchronize()
@@ -385,18 +373,55 @@ def gss_roofline(device, feat=64, n_graphs=65536, iters=20):
         F.raw_gms(dy, None, send, recv)       # backward (same kernel on the sender CSC)
     b.record()
     torch.cuda.synchronize()
-    ms_launch = a.elapsed_time(b) / (2 * iters)
+    return a.elapsed_time(b) / (2 * iters)
+
+
+def gss_roofline(device, iters=10):
+    """The north-star kernel (fused gather -> CSR segment-sum) timed alone, forward + backward launches, on
+      GSS-R: N = 2 M nodes, 16 uniformly random senders per receiver, F = 128 (1 GB of features, every gathered row
+             comes from DRAM: algorithmic bytes ~ real traffic) -> the HBM roofline fraction;
+      GSS-L: C1 pattern x 65 536 graphs, F = 64 (gathered rows hit in L1/L2) -> reported beside it."""
+    from gcnn_keras_b200 import RaggedTensor
+    from gcnn_keras_b200.plan import Relation, get_plan
     peak, peak_src = measured_peaks()
-    per_launch = gss_bytes(E, N, feat) / 2
-    achieved = per_launch / (ms_launch * 1e-3) / 1e9
-    return {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-            "traffic": 752.2e6, "kernel": "gms_kernel (fused gather*w -> CSR segment-sum), fwd+bwd launches",
-            "workload": "GSS-L (N=%d, E=%d, F=%d): working set > L2" % (N, E, feat),
-            "algorithmic_bytes_per_launch": per_launch, "ms_per_launch": ms_launch, "peak_source": peak_src,
-            "edges_per_s": E / (2 * ms_launch * 1e-3),
-            "note": "algorithmic bytes count every gathered row (4F per edge, no cache credit, SURVEY 8d); ncu "
-                    "DRAM traffic per launch (profiles/) is ~0.75 GB because gathered rows hit in L1/L2, so "
-                    "frac > 1 means cache reuse, not skipped work; the kernel is L1-wavefront bound"}
+    # ---- GSS-R ----
+    rng = np.random.default_rng(0)
+    n, deg, feat = 2_000_000, 16, 128
+    recv_r = torch.from_numpy(np.repeat(np.arange(n, dtype=np.int32), deg)).to(device)
+    send_r = torch.from_numpy(rng.integers(0, n, size=n * deg, dtype=np.int32)).to(device)
+    r_recv, r_send = Relation(recv_r, n, is_sorted=True), Relation(send_r, n)
+    r_recv.rowptr, r_send.rowptr, r_send.permuted_ids(r_recv)
+    x = torch.randn(n, feat, device=device)
+    dy = torch.randn(n, feat, device=device)
+    ms_r = _time_gms_pair(x, dy, r_recv, r_send, iters)
+    e_r = n * deg
+    bytes_r = gss_bytes(e_r, n, feat) / 2
+    ach_r = bytes_r / (ms_r * 1e-3) / 1e9
+    del x, dy, r_recv, r_send, recv_r, send_r
+    # ---- GSS-L ----
+    x_h, idx_h, ns_h, es_h = gss_inputs(65536, feat=64, seed=0)
+    N, E = x_h.shape[0], idx_h.shape[0]
+    x = torch.from_numpy(x_h).to(device)
+    nodes = RaggedTensor.from_row_splits(x, torch.from_numpy(ns_h).to(device))
+    index = RaggedTensor.from_row_splits(torch.from_numpy(idx_h).to(device), torch.from_numpy(es_h).to(device))
+    plan = get_plan(index, nodes)
+    recv, send = plan.relation(0), plan.relation(1)
+    recv.rowptr, send.rowptr, send.permuted_ids(recv)
+    ms_l = _time_gms_pair(x, torch.randn(N, 64, device=device), recv, send, iters)
+    bytes_l = gss_bytes(E, N, 64) / 2
+    ach_l = bytes_l / (ms_l * 1e-3) / 1e9
+    return {"bound": "hbm", "achieved": ach_r, "peak": peak, "unit": "GB/s", "frac": ach_r / peak, "traffic": None,
+            "kernel": "gms_kernel (fused gather*w -> CSR segment-sum), mean of the fwd and bwd launch",
+            "workload": "GSS-R (N=%d, E=%d uniform random senders, F=%d): gathered rows miss L2" % (n, e_r, feat),
+            "algorithmic_bytes_per_launch": bytes_r, "ms_per_launch": ms_r, "peak_source": peak_src,
+            "edges_per_s": e_r / (2 * ms_r * 1e-3),
+            "cached_shape": {"workload": "GSS-L (N=%d, E=%d, F=64, C1 pattern x 65536 graphs)" % (N, E),
+                             "achieved": ach_l, "frac": ach_l / peak, "ms_per_launch": ms_l,
+                             "algorithmic_bytes_per_launch": bytes_l, "traffic": 752.2e6,
+                             "edges_per_s": E / (2 * ms_l * 1e-3),
+                             "note": "algorithmic bytes count every gathered row (no cache credit, SURVEY 8d); ncu "
+                                     "DRAM traffic is 0.75 GB per launch because the rows hit in L1/L2, so frac > 1 "
+                                     "here is cache reuse, not skipped work"}}
 
 
 def build_painn(device, batch, seed):

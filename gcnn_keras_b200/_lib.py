@@ -41,6 +41,7 @@ SIGNATURES = {
     "kgcnn_colsum": (_i, [_p, _l, _i, _p, _p, _z, _p]),
     "kgcnn_gemm_tn_workspace_bytes": (_z, [_l, _i, _i]),
     "kgcnn_gemm_tn": (_i, [_p, _p, _l, _i, _i, _p, _p, _p, _z, _p]),
+    "kgcnn_adam_clipnorm": (_i, [_p, _p, _p, _p, _p, _p, _l, _f, _f, _f, _f, _f, _p, _p]),
 }
 
 OP_SUM, OP_MEAN, OP_MAX, OP_MIN = 0, 1, 2, 3

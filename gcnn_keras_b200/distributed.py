@@ -56,6 +56,15 @@ def allreduce_gradients(grads, group=None, average=True):
     return out
 
 
+def allreduce_flat(flat, group=None, average=True):
+    """All-reduce of the already flat gradient buffer (one NCCL call, captured inside the step's CUDA graph)."""
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return flat
+    dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
+    return flat / dist.get_world_size(group) if average else flat
+
+
 def broadcast_parameters(module, src=0, group=None):
     """Make every replica start from rank `src`'s weights."""
     import torch.distributed as dist

@@ -15,6 +15,47 @@ def keras_mse(pred, target):
     return torch.mean((pred - target) ** 2)
 
 
+class FlatAdam:
+    """Keras Adam + per-variable clipnorm over ONE flat parameter buffer: cat(grads) -> [all-reduce] -> per-variable
+    squared norms (CSR segment kernel) -> fused clip + Adam kernel.  4 launches instead of ~200."""
+
+    def __init__(self, params, lr=1e-3, beta1=0.9, beta2=0.999, eps=1e-7, clipnorm=1.0):
+        from . import functional as F
+        from .plan import Relation
+        self.params = list(params)
+        dev = self.params[0].device
+        sizes = [p.numel() for p in self.params]
+        self.total = sum(sizes)
+        self.flat = torch.empty(self.total, dtype=torch.float32, device=dev)
+        off = 0
+        for p, n in zip(self.params, sizes):
+            self.flat[off:off + n].copy_(p.data.reshape(-1))
+            p.data = self.flat[off:off + n].view_as(p)          # parameters become views of the flat buffer
+            off += n
+        self.m = torch.zeros_like(self.flat)
+        self.v = torch.zeros_like(self.flat)
+        offsets = torch.tensor([0] + list(torch.tensor(sizes).cumsum(0)), dtype=torch.int32, device=dev)
+        var_of = torch.repeat_interleave(torch.arange(len(sizes), device=dev), torch.tensor(sizes, device=dev))
+        self.var_of = var_of.to(torch.int32)
+        self.rel = Relation(self.var_of, len(sizes), rowptr=offsets, perm=None, is_sorted=True)
+        self.step_count = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.hyper = (float(lr), float(beta1), float(beta2), float(eps), float(clipnorm or 0.0))
+        self._F = F
+
+    def step(self, grads):
+        from . import _lib
+        from .distributed import allreduce_flat
+        F = self._F
+        g = torch.cat([gr.reshape(-1) for gr in grads])
+        g = allreduce_flat(g)                                    # data parallel by graph: the step's only collective
+        lr, b1, b2, eps, clip = self.hyper
+        sumsq = F.raw_gms(g.unsqueeze(1), g.unsqueeze(1), self.rel, None) if clip > 0 else None
+        _lib.check(_lib.lib().kgcnn_adam_clipnorm(
+            self.flat.data_ptr(), g.data_ptr(), self.m.data_ptr(), self.v.data_ptr(), self.var_of.data_ptr(),
+            None if sumsq is None else sumsq.data_ptr(), self.total, lr, b1, b2, eps, clip,
+            self.step_count.data_ptr(), torch.cuda.current_stream().cuda_stream), "kgcnn_adam_clipnorm")
+
+
 class ForceTrainStep:
     def __init__(self, model, lr=1e-3, force_loss_factor=200.0, clipnorm=1.0, eps=1e-7):
         self.model = model
@@ -28,8 +69,7 @@ class ForceTrainStep:
     def _ensure_optimizer(self):
         if self.optimizer is None:
             self.params = [p for p in self.model.parameters() if p.requires_grad]
-            self.optimizer = torch.optim.Adam(self.params, lr=self.lr, betas=(0.9, 0.999), eps=self.eps,
-                                              capturable=True, foreach=True)
+            self.optimizer = FlatAdam(self.params, lr=self.lr, eps=self.eps, clipnorm=self.clipnorm)
 
     def loss(self, inputs, e_target, f_target):
         out = self.model(inputs, training=True)
@@ -41,15 +81,7 @@ class ForceTrainStep:
         self._ensure_optimizer()
         grads = torch.autograd.grad(loss, self.params, allow_unused=True)
         grads = [torch.zeros_like(p) if g is None else g for g, p in zip(grads, self.params)]
-        from .distributed import allreduce_gradients
-        grads = allreduce_gradients(grads)       # data parallel by graph: the only collective of the step
-        if self.clipnorm is not None:                     # tf.clip_by_norm per variable (Keras clipnorm)
-            norms = torch._foreach_norm(grads)
-            scales = [self.clipnorm / torch.clamp(n, min=self.clipnorm) for n in norms]
-            grads = torch._foreach_mul(grads, scales)
-        for p, g in zip(self.params, grads):
-            p.grad = g
-        self.optimizer.step()
+        self.optimizer.step(grads)
         return loss
 
 

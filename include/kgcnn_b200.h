@@ -164,6 +164,15 @@ size_t kgcnn_gemm_tn_workspace_bytes(int64_t M, int K1, int K2);
 int kgcnn_gemm_tn(const float* X, const float* G, int64_t M, int K1, int K2, float* dW, float* db,
                   void* workspace, size_t workspace_bytes, kgcnn_stream_t stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * optimizer of the force_*.py drivers (force_schnet.py:196-203): Keras Adam with per-variable clipnorm on one
+ * flat parameter buffer.  sumsq[var] = sum of squared gradients of variable var (from the segment kernel with
+ * rowptr = variable offsets), var_of[i] = variable of element i, *step = device-resident step counter.
+ * ------------------------------------------------------------------------------------------- */
+int kgcnn_adam_clipnorm(float* params, const float* grads, float* m, float* v, const int32_t* var_of,
+                        const float* sumsq, int64_t n, float lr, float beta1, float beta2, float eps,
+                        float clipnorm, int32_t* step, kgcnn_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
