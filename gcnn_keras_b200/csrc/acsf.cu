@@ -1,0 +1,272 @@
+// Fused atom-centred symmetry functions (ACSF) of HDNNP: radial G2 and angular G4, each as forward G, VJP
+// (dG -> dxyz) and JVP (u -> dG).  Replaces the ~25-op TF chains of
+//   kgcnn/layers/conv/acsf_conv.py:199-211 (ACSFG2.call) and :473-494 (ACSFG4.call)
+// which materialise the per-bond parameter gather [M,m,3] / [A,m,4] and >= 10 tensors of shape [A,m] (2 GB each at
+// batch 256), and end in tensor_scatter_nd_add (atomic on GPU TF, kgcnn/layers/pooling.py:658-663).
+// Here nothing of size [pairs|triples, m] ever reaches HBM: one warp owns one centre atom, walks its CSR segment
+// of pairs / triples in the original order, lanes run over the m parameter sets, and the (relation, parameter)
+// accumulators live in shared memory private to the warp -> deterministic, no atomics.
+// The parameters are not trainable in the drivers (param_trainable=False, acsf_conv.py:62,274), so force
+// training needs exactly these three maps: G, J^T v and J u.
+#include "common.cuh"
+
+namespace kgcnn {
+namespace {
+
+constexpr int kWarpsPerBlock = 4;
+constexpr int kMaxAcc = 1024;   // R*m accumulators per warp in shared memory (G4 of the drivers: 10*50 = 500)
+constexpr float kPi = 3.14159265358979323846f;
+
+enum { kFwd = 0, kVjp = 1, kJvp = 2 };
+
+struct V3 { float x, y, z; };
+__device__ __forceinline__ V3 ld3(const float* p) { return {__ldg(p), __ldg(p + 1), __ldg(p + 2)}; }
+__device__ __forceinline__ V3 sub(V3 a, V3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
+__device__ __forceinline__ float dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+__device__ __forceinline__ V3 axpy(float a, V3 x, V3 y) { return {a * x.x + y.x, a * x.y + y.y, a * x.z + y.z}; }
+__device__ __forceinline__ V3 scale(float a, V3 x) { return {a * x.x, a * x.y, a * x.z}; }
+__device__ __forceinline__ float norm_ref(V3 v, float eps) {
+  // EuclideanNorm: sqrt(relu(sum(v^2)) + eps)   (kgcnn/layers/geom.py:181-187)
+  return sqrtf(fmaxf(dot(v, v), 0.f) + eps);
+}
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+// f_c(r) = 0.5 (cos(pi clip(r,-Rc,Rc)/Rc) + 1) and its derivative (0 outside the clip)   acsf_conv.py:159-166
+__device__ __forceinline__ void cutoff(float r, float rc, float& f, float& df) {
+  const float rr = fminf(fmaxf(r, -rc), rc);
+  float s, c;
+  sincosf(rr * kPi / rc, &s, &c);
+  f = 0.5f * (c + 1.f);
+  df = (r > -rc && r < rc) ? -0.5f * kPi / rc * s : 0.f;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// G2:  G[i, rel(j), k] = sum_j exp(-eta_k (r_ij - mu_k)^2) f_c(r_ij; Rc_k)
+// ---------------------------------------------------------------------------------------------------------
+template <int MODE>
+__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+acsf_g2_kernel(const float* __restrict__ xyz, const int32_t* __restrict__ rel_atom,
+               const int32_t* __restrict__ tset_atom, const int32_t* __restrict__ rowptr,
+               const int32_t* __restrict__ perm, const int32_t* __restrict__ send, int send_permuted,
+               const float* __restrict__ table, int R, int m, float eps, int64_t N,
+               const float* __restrict__ cot, float* __restrict__ out, float* __restrict__ edge_out) {
+  __shared__ float acc_s[kWarpsPerBlock][kMaxAcc];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t i = static_cast<int64_t>(blockIdx.x) * kWarpsPerBlock + warp;
+  if (i >= N) return;
+  float* acc = acc_s[warp];
+  const int RM = R * m;
+  if (MODE == kVjp) for (int t = lane; t < RM; t += 32) acc[t] = __ldg(cot + i * RM + t);   // dG[i, :, :]
+  else for (int t = lane; t < RM; t += 32) acc[t] = 0.f;
+  __syncwarp();
+  const V3 xi = ld3(xyz + 3 * i);
+  V3 ui = {0.f, 0.f, 0.f};
+  if (MODE == kJvp) ui = ld3(cot + 3 * i);
+  const float* tab_i = table + (tset_atom ? static_cast<int64_t>(max(__ldg(tset_atom + i), 0)) * RM * 3 : 0);
+  const bool centre_ok = !tset_atom || __ldg(tset_atom + i) >= 0;
+  V3 gi = {0.f, 0.f, 0.f};
+  const int beg = __ldg(rowptr + i), end = __ldg(rowptr + i + 1);
+  for (int p = beg; p < end; ++p) {
+    const int e = perm ? __ldg(perm + p) : p;
+    const int j = __ldg(send + (send_permuted ? p : e));
+    const int r = __ldg(rel_atom + j);
+    V3 gj = {0.f, 0.f, 0.f};
+    if (r >= 0 && r < R && centre_ok) {               // unmapped neighbour elements contribute nothing
+      const V3 v = sub(xi, ld3(xyz + 3 * j));
+      const float d = norm_ref(v, eps);
+      float ddot = 0.f;
+      if (MODE == kJvp) ddot = dot(v, sub(ui, ld3(cot + 3 * j))) / d;
+      float a = 0.f;                                   // VJP: sum_k dG * dphi/dd
+      for (int k = lane; k < m; k += 32) {
+        const float* prm = tab_i + (static_cast<int64_t>(r) * m + k) * 3;
+        const float eta = __ldg(prm), mu = __ldg(prm + 1), rc = __ldg(prm + 2);
+        float f, df;
+        cutoff(d, rc, f, df);
+        const float t = d - mu;
+        const float g = expf(-eta * t * t);
+        if (MODE == kFwd) acc[r * m + k] += g * f;
+        else {
+          const float dphi = g * (-2.f * eta * t * f + df);
+          if (MODE == kVjp) a += acc[r * m + k] * dphi;
+          else acc[r * m + k] += dphi * ddot;
+        }
+      }
+      if (MODE == kVjp) {
+        a = warp_sum(a);
+        const V3 gv = scale(a / d, v);                 // d/dx_i = +gv, d/dx_j = -gv
+        gi = axpy(1.f, gv, gi);
+        gj = scale(-1.f, gv);
+      }
+    }
+    if (MODE == kVjp && lane == 0) {
+      edge_out[3 * static_cast<int64_t>(e) + 0] = gj.x;
+      edge_out[3 * static_cast<int64_t>(e) + 1] = gj.y;
+      edge_out[3 * static_cast<int64_t>(e) + 2] = gj.z;
+    }
+  }
+  __syncwarp();
+  if (MODE == kVjp) {
+    if (lane == 0) { out[3 * i] = gi.x; out[3 * i + 1] = gi.y; out[3 * i + 2] = gi.z; }
+  } else {
+    for (int t = lane; t < RM; t += 32) out[i * RM + t] = acc[t];
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// G4:  G[i, pair(Z_j,Z_k), p] = sum_{jk} 2^(1-zeta)(1+lambda cos)^zeta / mult * exp(-eta (rij^2+rik^2+rjk^2)) fc fc fc
+//      (acsf_conv.py:419-446, 473-494)
+// ---------------------------------------------------------------------------------------------------------
+template <int MODE>
+__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+acsf_g4_kernel(const float* __restrict__ xyz, const int32_t* __restrict__ z_atom,
+               const int32_t* __restrict__ tset_atom, const int32_t* __restrict__ rev_pair, int zmax,
+               const int32_t* __restrict__ rowptr, const int32_t* __restrict__ perm,
+               const int32_t* __restrict__ idx_j, const int32_t* __restrict__ idx_k,
+               const float* __restrict__ table, int R, int m, float eps, float inv_mult, int64_t N,
+               const float* __restrict__ cot, float* __restrict__ out, float* __restrict__ triple_out) {
+  __shared__ float acc_s[kWarpsPerBlock][kMaxAcc];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t i = static_cast<int64_t>(blockIdx.x) * kWarpsPerBlock + warp;
+  if (i >= N) return;
+  float* acc = acc_s[warp];
+  const int RM = R * m;
+  if (MODE == kVjp) for (int t = lane; t < RM; t += 32) acc[t] = __ldg(cot + i * RM + t);
+  else for (int t = lane; t < RM; t += 32) acc[t] = 0.f;
+  __syncwarp();
+  const V3 xi = ld3(xyz + 3 * i);
+  V3 ui = {0.f, 0.f, 0.f};
+  if (MODE == kJvp) ui = ld3(cot + 3 * i);
+  const float* tab_i = table + (tset_atom ? static_cast<int64_t>(max(__ldg(tset_atom + i), 0)) * RM * 4 : 0);
+  const bool centre_ok = !tset_atom || __ldg(tset_atom + i) >= 0;
+  V3 gi = {0.f, 0.f, 0.f};
+  const int beg = __ldg(rowptr + i), end = __ldg(rowptr + i + 1);
+  for (int p = beg; p < end; ++p) {
+    const int e = perm ? __ldg(perm + p) : p;
+    const int j = __ldg(idx_j + e), k = __ldg(idx_k + e);
+    const int zj = __ldg(z_atom + j), zk = __ldg(z_atom + k);
+    int r = -1;
+    if (zj >= 0 && zj < zmax && zk >= 0 && zk < zmax) r = __ldg(rev_pair + zj * zmax + zk);
+    V3 gj = {0.f, 0.f, 0.f}, gk = {0.f, 0.f, 0.f};
+    if (r >= 0 && r < R && centre_ok) {
+      const V3 xj = ld3(xyz + 3 * j), xk = ld3(xyz + 3 * k);
+      const V3 vij = sub(xi, xj), vik = sub(xi, xk), vjk = sub(xj, xk);
+      const float rij = norm_ref(vij, eps), rik = norm_ref(vik, eps), rjk = norm_ref(vjk, eps);
+      const float inv = 1.f / (rij * rik);
+      const float c = dot(vij, vik) / rij / rik;                       // acsf_conv.py:439
+      const float r2 = rij * rij + rik * rik + rjk * rjk;
+      // d cos / d vij = vik/(rij rik) - c vij/rij^2 ;  d cos / d vik = vij/(rij rik) - c vik/rik^2
+      const V3 dc_ij = axpy(-c / (rij * rij), vij, scale(inv, vik));
+      const V3 dc_ik = axpy(-c / (rik * rik), vik, scale(inv, vij));
+      float t_ij = 0.f, t_ik = 0.f, t_jk = 0.f, t_c = 0.f;             // JVP tangents of (rij, rik, rjk, cos)
+      if (MODE == kJvp) {
+        const V3 uj = ld3(cot + 3 * j), uk = ld3(cot + 3 * k);
+        const V3 uij = sub(ui, uj), uik = sub(ui, uk), ujk = sub(uj, uk);
+        t_ij = dot(vij, uij) / rij;
+        t_ik = dot(vik, uik) / rik;
+        t_jk = dot(vjk, ujk) / rjk;
+        t_c = dot(dc_ij, uij) + dot(dc_ik, uik);
+      }
+      float a_ij = 0.f, a_ik = 0.f, a_jk = 0.f, a_c = 0.f;             // VJP: sums over the parameter sets
+      for (int q = lane; q < m; q += 32) {
+        const float4 prm = __ldg(reinterpret_cast<const float4*>(tab_i + (static_cast<int64_t>(r) * m + q) * 4));
+        const float eta = prm.x, zeta = prm.y, lam = prm.z, rc = prm.w;
+        float fij, dfij, fik, dfik, fjk, dfjk;
+        cutoff(rij, rc, fij, dfij);
+        cutoff(rik, rc, fik, dfik);
+        cutoff(rjk, rc, fjk, dfjk);
+        const float base = c * lam + 1.f;
+        const float pre = exp2f(1.f - zeta) * inv_mult;
+        const float A = pre * powf(base, zeta);
+        const float E = expf(-eta * r2);
+        const float fff = fij * fik * fjk;
+        if (MODE == kFwd) {
+          acc[r * m + q] += A * E * fff;
+        } else {
+          const float dA = pre * zeta * lam * powf(base, zeta - 1.f);   // dA / dcos
+          // d rep / d r_ab = A (dE/dr_ab fff + E f'_ab f f)
+          const float d_ij = A * E * (-2.f * eta * rij * fff + dfij * fik * fjk);
+          const float d_ik = A * E * (-2.f * eta * rik * fff + fij * dfik * fjk);
+          const float d_jk = A * E * (-2.f * eta * rjk * fff + fij * fik * dfjk);
+          const float d_c = dA * E * fff;
+          if (MODE == kVjp) {
+            const float g = acc[r * m + q];
+            a_ij += g * d_ij; a_ik += g * d_ik; a_jk += g * d_jk; a_c += g * d_c;
+          } else {
+            acc[r * m + q] += d_ij * t_ij + d_ik * t_ik + d_jk * t_jk + d_c * t_c;
+          }
+        }
+      }
+      if (MODE == kVjp) {
+        a_ij = warp_sum(a_ij); a_ik = warp_sum(a_ik); a_jk = warp_sum(a_jk); a_c = warp_sum(a_c);
+        const V3 g_vij = axpy(a_ij / rij, vij, scale(a_c, dc_ij));
+        const V3 g_vik = axpy(a_ik / rik, vik, scale(a_c, dc_ik));
+        const V3 g_vjk = scale(a_jk / rjk, vjk);
+        gi = axpy(1.f, g_vij, axpy(1.f, g_vik, gi));
+        gj = sub(g_vjk, g_vij);
+        gk = scale(-1.f, axpy(1.f, g_vik, g_vjk));
+      }
+    }
+    if (MODE == kVjp && lane == 0) {
+      float* o = triple_out + 6 * static_cast<int64_t>(e);
+      o[0] = gj.x; o[1] = gj.y; o[2] = gj.z; o[3] = gk.x; o[4] = gk.y; o[5] = gk.z;
+    }
+  }
+  __syncwarp();
+  if (MODE == kVjp) {
+    if (lane == 0) { out[3 * i] = gi.x; out[3 * i + 1] = gi.y; out[3 * i + 2] = gi.z; }
+  } else {
+    for (int t = lane; t < RM; t += 32) out[i * RM + t] = acc[t];
+  }
+}
+
+}  // namespace
+}  // namespace kgcnn
+
+using namespace kgcnn;
+
+extern "C" {
+
+int kgcnn_acsf_g2(const float* xyz, const int32_t* rel_atom, const int32_t* tset_atom, const int32_t* rowptr,
+                  const int32_t* perm, const int32_t* send, int send_permuted, const float* table, int R, int m,
+                  float eps, int64_t N, int mode, const float* cot, float* out, float* edge_out,
+                  kgcnn_stream_t stream) {
+  if (N < 0 || R <= 0 || m <= 0 || mode < kFwd || mode > kJvp) return KGCNN_E_INVALID;
+  if (R * m > kMaxAcc) return KGCNN_E_UNSUPPORTED;
+  if (N == 0) return KGCNN_OK;
+  if (!xyz || !rel_atom || !rowptr || !send || !table || !out) return KGCNN_E_INVALID;
+  if (mode != kFwd && !cot) return KGCNN_E_INVALID;
+  if (mode == kVjp && !edge_out) return KGCNN_E_INVALID;
+  const unsigned grid = static_cast<unsigned>(ceil_div<int64_t>(N, kWarpsPerBlock));
+  cudaStream_t st = as_stream(stream);
+#define KGCNN_G2(M) acsf_g2_kernel<M><<<grid, kWarpsPerBlock * 32, 0, st>>>(xyz, rel_atom, tset_atom, rowptr, perm, \
+    send, send_permuted, table, R, m, eps, N, cot, out, edge_out)
+  if (mode == kFwd) KGCNN_G2(kFwd); else if (mode == kVjp) KGCNN_G2(kVjp); else KGCNN_G2(kJvp);
+#undef KGCNN_G2
+  return finish_launch();
+}
+
+int kgcnn_acsf_g4(const float* xyz, const int32_t* z_atom, const int32_t* tset_atom, const int32_t* rev_pair,
+                  int zmax, const int32_t* rowptr, const int32_t* perm, const int32_t* idx_j, const int32_t* idx_k,
+                  const float* table, int R, int m, float eps, float multiplicity, int64_t N, int mode,
+                  const float* cot, float* out, float* triple_out, kgcnn_stream_t stream) {
+  if (N < 0 || R <= 0 || m <= 0 || zmax <= 0 || mode < kFwd || mode > kJvp) return KGCNN_E_INVALID;
+  if (R * m > kMaxAcc) return KGCNN_E_UNSUPPORTED;
+  if (N == 0) return KGCNN_OK;
+  if (!xyz || !z_atom || !rev_pair || !rowptr || !idx_j || !idx_k || !table || !out) return KGCNN_E_INVALID;
+  if ((reinterpret_cast<uintptr_t>(table) & 15) != 0) return KGCNN_E_UNSUPPORTED;
+  if (mode != kFwd && !cot) return KGCNN_E_INVALID;
+  if (mode == kVjp && !triple_out) return KGCNN_E_INVALID;
+  const float inv_mult = multiplicity > 0.f ? 1.f / multiplicity : 1.f;
+  const unsigned grid = static_cast<unsigned>(ceil_div<int64_t>(N, kWarpsPerBlock));
+  cudaStream_t st = as_stream(stream);
+#define KGCNN_G4(M) acsf_g4_kernel<M><<<grid, kWarpsPerBlock * 32, 0, st>>>(xyz, z_atom, tset_atom, rev_pair, zmax, \
+    rowptr, perm, idx_j, idx_k, table, R, m, eps, inv_mult, N, cot, out, triple_out)
+  if (mode == kFwd) KGCNN_G4(kFwd); else if (mode == kVjp) KGCNN_G4(kVjp); else KGCNN_G4(kJvp);
+#undef KGCNN_G4
+  return finish_launch();
+}
+
+}  // extern "C"

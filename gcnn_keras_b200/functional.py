@@ -583,3 +583,129 @@ def dense(x, kernel, bias, activation):
     pre = _Linear.apply(x2, kernel, bias)
     out = pre if code == _lib.ACT_CODES["linear"] else _BiasAct.apply(pre, None, None, None, code, 0)
     return out.reshape(tuple(lead) + (kernel.shape[1],))
+
+
+# ------------------------------------------------------------------------------------------------
+# fused ACSF G2 / G4 (a15, a16): G, J^T v, J u
+# ------------------------------------------------------------------------------------------------
+COORDINATE_HESSIAN = True     # False inside a training step: coordinates are not trained, d2/dx2 is never needed
+
+
+class no_coordinate_hessian:
+    """Inside this context the fused geometry kernels do not provide second derivatives with respect to the
+    coordinates (only what force TRAINING needs: gradients of the force with respect to the weights)."""
+
+    def __enter__(self):
+        global COORDINATE_HESSIAN
+        self._prev, COORDINATE_HESSIAN = COORDINATE_HESSIAN, False
+
+    def __exit__(self, *exc):
+        global COORDINATE_HESSIAN
+        COORDINATE_HESSIAN = self._prev
+
+
+def _no_hessian(what):
+    if COORDINATE_HESSIAN:
+        raise NotImplementedError(
+            "second derivatives with respect to the coordinates through the fused %s kernels are not implemented; "
+            "wrap weight-gradient computations in functional.no_coordinate_hessian() (ForceTrainStep does) or use "
+            "the unfused layer path (layers.conv.acsf_conv.FUSED = False)" % what)
+    return None
+
+
+class ACSFSpec:
+    """Per-batch constants of one ACSF layer call (index relations, element maps, parameter table)."""
+
+    def __init__(self, kind, rel_centre, table, R, m, eps, rel_atom=None, tset_atom=None, rel_send=None,
+                 z_atom=None, rev_pair=None, zmax=31, rel_j=None, rel_k=None, multiplicity=0.0):
+        self.kind, self.rel_centre, self.table, self.R, self.m, self.eps = kind, rel_centre, table, R, m, eps
+        self.rel_atom, self.tset_atom, self.rel_send = rel_atom, tset_atom, rel_send
+        self.z_atom, self.rev_pair, self.zmax, self.rel_j, self.rel_k = z_atom, rev_pair, zmax, rel_j, rel_k
+        self.multiplicity = multiplicity
+
+
+def raw_acsf(xyz, spec, mode, cot=None):
+    _need_cuda(xyz, cot)
+    xyz = _f32c(xyz)
+    N = int(xyz.shape[0])
+    RM = spec.R * spec.m
+    rc = spec.rel_centre
+    out = torch.empty((N, 3 if mode == 1 else RM), dtype=torch.float32, device=xyz.device)
+    cot = None if cot is None else _f32c(cot)
+    if spec.kind == 2:
+        M = rc.n_elements
+        edge_out = torch.empty((M, 3), dtype=torch.float32, device=xyz.device) if mode == 1 else None
+        send = rc.permuted_ids(spec.rel_send)
+        check(_lib.lib().kgcnn_acsf_g2(_ptr(xyz), _ptr(spec.rel_atom), _ptr(spec.tset_atom), _ptr(rc.rowptr),
+                                       _ptr(rc.perm), _ptr(send), 1 if rc.perm is not None else 0, _ptr(spec.table),
+                                       spec.R, spec.m, spec.eps, N, mode, _ptr(cot), _ptr(out), _ptr(edge_out),
+                                       _stream()), "kgcnn_acsf_g2")
+        return out, edge_out
+    A = rc.n_elements
+    tri = torch.empty((A, 2, 3), dtype=torch.float32, device=xyz.device) if mode == 1 else None
+    check(_lib.lib().kgcnn_acsf_g4(_ptr(xyz), _ptr(spec.z_atom), _ptr(spec.tset_atom), _ptr(spec.rev_pair), spec.zmax,
+                                   _ptr(rc.rowptr), _ptr(rc.perm), _ptr(spec.rel_j.ids), _ptr(spec.rel_k.ids),
+                                   _ptr(spec.table), spec.R, spec.m, spec.eps, float(spec.multiplicity or 0.0), N, mode,
+                                   _ptr(cot), _ptr(out), _ptr(tri), _stream()), "kgcnn_acsf_g4")
+    return out, tri
+
+
+def _acsf_vjp_raw(xyz, dG, spec):
+    centre, nb = raw_acsf(xyz, spec, 1, dG)
+    if spec.kind == 2:
+        return centre + raw_gms(nb, None, spec.rel_send, None)
+    return centre + raw_gms(nb[:, 0].contiguous(), None, spec.rel_j, None) \
+        + raw_gms(nb[:, 1].contiguous(), None, spec.rel_k, None)
+
+
+class _ACSF(torch.autograd.Function):
+    """G(xyz) for one ACSF layer (parameters constant)."""
+
+    @staticmethod
+    def forward(ctx, xyz, spec):
+        ctx.spec = spec
+        ctx.save_for_backward(xyz)
+        return raw_acsf(xyz, spec, 0)[0]
+
+    @staticmethod
+    def backward(ctx, dG):
+        (xyz,) = ctx.saved_tensors
+        return _ACSFVjp.apply(xyz, dG.contiguous(), ctx.spec), None
+
+
+class _ACSFVjp(torch.autograd.Function):
+    """J(xyz)^T dG; linear in dG, so its VJP with respect to dG is J h (the JVP kernel)."""
+
+    @staticmethod
+    def forward(ctx, xyz, dG, spec):
+        ctx.spec = spec
+        ctx.save_for_backward(xyz)
+        return _acsf_vjp_raw(xyz, dG, spec)
+
+    @staticmethod
+    def backward(ctx, h):
+        (xyz,) = ctx.saved_tensors
+        g_xyz = _no_hessian("ACSF") if ctx.needs_input_grad[0] else None
+        g_dG = _ACSFJvp.apply(xyz, h.contiguous(), ctx.spec) if ctx.needs_input_grad[1] else None
+        return g_xyz, g_dG, None
+
+
+class _ACSFJvp(torch.autograd.Function):
+    """J(xyz) u; its VJP with respect to u is J^T g."""
+
+    @staticmethod
+    def forward(ctx, xyz, u, spec):
+        ctx.spec = spec
+        ctx.save_for_backward(xyz)
+        return raw_acsf(xyz, spec, 2, u)[0]
+
+    @staticmethod
+    def backward(ctx, g):
+        (xyz,) = ctx.saved_tensors
+        g_xyz = _no_hessian("ACSF") if ctx.needs_input_grad[0] else None
+        g_u = _ACSFVjp.apply(xyz, g.contiguous(), ctx.spec) if ctx.needs_input_grad[1] else None
+        return g_xyz, g_u, None
+
+
+def acsf(xyz, spec):
+    return _ACSF.apply(xyz, spec)

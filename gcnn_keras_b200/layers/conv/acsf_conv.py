@@ -16,6 +16,7 @@ from ...plan import Relation, get_plan
 from ..base import GraphBaseLayer, register_keras_serializable
 
 _MAX_ATOMIC_NUMBER = 31
+FUSED = True    # fused sm_100a kernels (G, J^T v, J u); False -> op-by-op chain (trainable parameters, Hessians)
 
 
 def _reverse_mapping(element_mapping):
@@ -77,6 +78,15 @@ class ACSFG2(GraphBaseLayer):
         plan = get_plan(eij, xyz)
         ri, rj = plan.relation(0), plan.relation(1)
         zv = z.values.to(torch.int64)                                               # acsf_conv.py:200
+        if FUSED and not self.param_trainable:
+            zc = torch.clamp(zv, 0, _MAX_ATOMIC_NUMBER - 1)
+            rel_atom = self.weight_reverse_mapping[zc]
+            bad = (zv < 0) | (zv >= _MAX_ATOMIC_NUMBER) | (rel_atom < 0) | (rel_atom >= _MAX_ATOMIC_NUMBER)
+            rel_atom = torch.where(bad, torch.full_like(rel_atom, -1), rel_atom).to(torch.int32)
+            spec = F.ACSFSpec(2, ri, self.weight_eta_rs_rc.detach().contiguous(), self.num_relations,
+                              int(self.eta_rs_rc.shape[-2]), 1e-7 if self.add_eps else 0.0, rel_atom=rel_atom,
+                              tset_atom=rel_atom if self.use_target_set else None, rel_send=rj)
+            return xyz.with_values(F.acsf(xyz.values, spec))
         xi, xj = F.gather(xyz.values, ri), F.gather(xyz.values, rj)                 # :201
         diff = xi - xj
         rij = torch.sqrt(torch.relu(torch.sum(diff * diff, dim=1, keepdim=True))
@@ -166,6 +176,21 @@ class ACSFG4(GraphBaseLayer):
         plan = get_plan(ijk, xyz)
         ri, rj, rk = plan.relation(0), plan.relation(1), plan.relation(2)
         zv = z.values.to(torch.int64)                                               # acsf_conv.py:474
+        if FUSED and not self.param_trainable:
+            big = torch.iinfo(torch.int32).max
+            rev_pair = torch.where(self.weight_reverse_pair_mapping > big, torch.full_like(
+                self.weight_reverse_pair_mapping, -1), self.weight_reverse_pair_mapping).to(torch.int32).contiguous()
+            tset = None
+            if self.use_target_set:
+                zc = torch.clamp(zv, 0, _MAX_ATOMIC_NUMBER - 1)
+                t = self.weight_reverse_mapping[zc]
+                bad = (zv < 0) | (zv >= _MAX_ATOMIC_NUMBER) | (t < 0) | (t >= _MAX_ATOMIC_NUMBER)
+                tset = torch.where(bad, torch.full_like(t, -1), t).to(torch.int32)
+            spec = F.ACSFSpec(4, ri, self.weight_eta_zeta_lambda_rc.detach().contiguous(), self.num_relations,
+                              int(self.eta_zeta_lambda_rc.shape[-2]), 1e-7 if self.add_eps else 0.0,
+                              tset_atom=tset, z_atom=zv.to(torch.int32), rev_pair=rev_pair, zmax=_MAX_ATOMIC_NUMBER,
+                              rel_j=rj, rel_k=rk, multiplicity=self.multiplicity or 0.0)
+            return xyz.with_values(F.acsf(xyz.values, spec))
         zi, zj, zk = F.gather(zv, ri), F.gather(zv, rj), F.gather(zv, rk)           # :475
         xi, xj, xk = (F.gather(xyz.values, r) for r in (ri, rj, rk))               # :476
         valid_z = (zj >= 0) & (zj < _MAX_ATOMIC_NUMBER) & (zk >= 0) & (zk < _MAX_ATOMIC_NUMBER)

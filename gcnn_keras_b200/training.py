@@ -79,7 +79,9 @@ class ForceTrainStep:
     def step(self, inputs, e_target, f_target):
         loss = self.loss(inputs, e_target, f_target)
         self._ensure_optimizer()
-        grads = torch.autograd.grad(loss, self.params, allow_unused=True)
+        from .functional import no_coordinate_hessian
+        with no_coordinate_hessian():       # weights only: no d2/dx2 through the fused geometry kernels
+            grads = torch.autograd.grad(loss, self.params, allow_unused=True)
         grads = [torch.zeros_like(p) if g is None else g for g, p in zip(grads, self.params)]
         self.optimizer.step(grads)
         return loss

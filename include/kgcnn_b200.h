@@ -165,6 +165,28 @@ int kgcnn_gemm_tn(const float* X, const float* G, int64_t M, int K1, int K2, flo
                   void* workspace, size_t workspace_bytes, kgcnn_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * a15/a16  fused ACSF symmetry functions (kgcnn/layers/conv/acsf_conv.py:199-211 and :473-494)
+ *   mode 0: G[N, R*m]                  (out)
+ *   mode 1: VJP, cot = dG[N, R*m]   -> out = d/dx of the CENTRE atoms [N,3]; the neighbour parts are written per
+ *           pair (edge_out [M,3], for the sender) / per triple (triple_out [A,2,3], for j and k) in the ORIGINAL
+ *           pair / triple order and are summed by the caller with the deterministic segment kernel
+ *   mode 2: JVP, cot = u[N,3]       -> out = J u  [N, R*m]   (what force training needs: parameters are constants)
+ *   rel_atom[n]  : relation of atom n as a NEIGHBOUR (reverse_mapping[Z_n], < 0 = element not mapped -> skipped)
+ *   tset_atom[n] : nullable; index of atom n as a CENTRE into a (N_el, R, m, .) table (use_target_set)
+ *   z_atom[n]    : atomic number; rev_pair[zmax*zmax]: pair relation of (Z_j, Z_k), < 0 = not mapped
+ *   rowptr/perm  : CSR of the pairs / triples by centre atom; table: [T][R][m][3] (eta, mu, Rc) / [T][R][m][4]
+ *   (eta, zeta, lambda, Rc); eps: added under the square root when add_eps (else 0).
+ * ------------------------------------------------------------------------------------------- */
+int kgcnn_acsf_g2(const float* xyz, const int32_t* rel_atom, const int32_t* tset_atom, const int32_t* rowptr,
+                  const int32_t* perm, const int32_t* send, int send_permuted, const float* table, int R, int m,
+                  float eps, int64_t N, int mode, const float* cot, float* out, float* edge_out,
+                  kgcnn_stream_t stream);
+int kgcnn_acsf_g4(const float* xyz, const int32_t* z_atom, const int32_t* tset_atom, const int32_t* rev_pair,
+                  int zmax, const int32_t* rowptr, const int32_t* perm, const int32_t* idx_j, const int32_t* idx_k,
+                  const float* table, int R, int m, float eps, float multiplicity, int64_t N, int mode,
+                  const float* cot, float* out, float* triple_out, kgcnn_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
  * optimizer of the force_*.py drivers (force_schnet.py:196-203): Keras Adam with per-variable clipnorm on one
  * flat parameter buffer.  sumsq[var] = sum of squared gradients of variable var (from the segment kernel with
  * rowptr = variable offsets), var_of[i] = variable of element i, *step = device-resident step counter.

@@ -80,9 +80,47 @@ def test_hdnnp2nd_energy_forces_and_training_gradients():
     e_t, f_t = torch.tensor(b["energy"]).cuda(), torch.tensor(b["force"]).cuda()
     loss = (1 / 200) * torch.mean((eng - e_t) ** 2) + (199 / 200) * torch.mean((force.values - f_t) ** 2)
     named = [(n, p) for n, p in model.energy_model.named_parameters() if p.requires_grad]
-    grads = torch.autograd.grad(loss, [p for _, p in named], allow_unused=True)
+    from gcnn_keras_b200.functional import no_coordinate_hessian
+    with no_coordinate_hessian():
+        grads = torch.autograd.grad(loss, [p for _, p in named], allow_unused=True)
     o_loss = OM.force_training_loss(o_eng, o_force, torch.tensor(b["energy"], dtype=torch.float64),
                                     torch.tensor(b["force"], dtype=torch.float64))
     o_grads = torch.autograd.grad(o_loss, [params[n] for n, _ in named], allow_unused=True)
     for (n, _), g, og in zip(named, grads, o_grads):
         assert rel_err(g.cpu().numpy(), og.numpy()) < RTOL, n
+
+
+def test_fused_acsf_matches_unfused_chain_and_guards_hessian():
+    """Fused G / J^T v / J u kernels vs the op-by-op chain (same GPU), incl. unmapped elements and unsorted triples."""
+    from gcnn_keras_b200.layers.conv import acsf_conv
+    from gcnn_keras_b200.layers.conv.acsf_conv import ACSFG2, ACSFG4
+    d, z, xyz, eij, ijk = _golden_inputs()
+    rng = np.random.default_rng(3)
+    g2 = ACSFG2(**ACSFG2.make_param_table(eta=[0.1, 0.3, 0.9], rs=[0.0, 1.5, 3.0], rc=6.0, elements=[1, 6, 16]))
+    g4 = ACSFG4(**ACSFG4.make_param_table(eta=[0.05, 0.3], zeta=[1.0, 2.0, 8.0], lamda=[-1.0, 1.0], rc=6.0,
+                                          elements=[1, 6, 16], multiplicity=2.0))
+    perm = torch.tensor(np.concatenate([o + rng.permutation(n) for o, n in zip(
+        np.concatenate([[0], np.cumsum(d["angle_index_lengths"])[:-1]]), d["angle_index_lengths"])])).cuda()
+    ijk_shuffled = ijk.with_values(ijk.values[perm])
+    for layer, idx in ((g2, eij), (g4, ijk), (g4, ijk_shuffled)):
+        res = {}
+        for fused in (True, False):
+            acsf_conv.FUSED = fused
+            x = xyz.values.clone().requires_grad_(True)
+            out = layer([z, xyz.with_values(x), idx]).values
+            cot = torch.tensor(np.random.default_rng(4).standard_normal(tuple(out.shape)), dtype=torch.float32).cuda()
+            wgt = cot.clone().requires_grad_(True)
+            (fx,) = torch.autograd.grad(out, x, wgt, create_graph=True)          # J^T w
+            h = torch.tensor(np.random.default_rng(5).standard_normal(tuple(fx.shape)), dtype=torch.float32).cuda()
+            if fused:
+                with pytest.raises(NotImplementedError):                         # d2/dx2 is guarded, not silently 0
+                    torch.autograd.grad(fx, [wgt], h, retain_graph=True)
+                from gcnn_keras_b200.functional import no_coordinate_hessian
+                with no_coordinate_hessian():
+                    (jh,) = torch.autograd.grad(fx, [wgt], h)                    # J h
+            else:
+                (jh,) = torch.autograd.grad(fx, [wgt], h)
+            res[fused] = (out.detach(), fx.detach(), jh)
+        acsf_conv.FUSED = True
+        for a, b in zip(res[True], res[False]):
+            assert rel_err(a.cpu().numpy(), b.cpu().numpy()) < 2e-5
