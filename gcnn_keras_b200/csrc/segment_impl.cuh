@@ -198,15 +198,14 @@ gms_kernel(const V* __restrict__ x, const V* __restrict__ wv, const float* __res
 // Block-per-row mapping for outputs with FEW rows (n_out <= 1024: embedding-table gradients, per-type
 // reductions): segment lengths are then unbounded (thousands of atoms of one element), so one CTA = 32 lane
 // groups walks a row together and the groups are combined through shared memory in a fixed order.
-template <typename V, int MODE, bool GATHER>
+template <typename V, int MODE, bool GATHER, int LPR>
 __global__ void __launch_bounds__(kThreads)
 gms_block_kernel(const V* __restrict__ x, const V* __restrict__ wv, const float* __restrict__ ws,
                  const int32_t* __restrict__ rowptr, const int32_t* __restrict__ perm,
                  const int32_t* __restrict__ gidx, int gidx_stride, int gidx_permuted, int64_t n_out, int nvec,
                  int mean, V* __restrict__ y, const int32_t* __restrict__ row_map,
                  const int32_t* __restrict__ n_rows_dev) {
-  constexpr int LPR = 8;
-  constexpr int NG = kThreads / LPR;  // 32 lane groups
+  constexpr int NG = kThreads / LPR;  // lane groups walking the row together (32 .. 256)
   using T = Vec<V>;
   __shared__ V red[NG][LPR];
   const int g = threadIdx.x / LPR, sub = threadIdx.x % LPR;
@@ -254,15 +253,23 @@ int launch_block(int mode, bool gather, const V* x, const V* wv, const float* ws
                  const int32_t* perm, const int32_t* gidx, int gs, int gp, int64_t n_out, int nvec, int mean, V* y,
                  const int32_t* row_map, const int32_t* n_rows_dev, int grid_rows, cudaStream_t st) {
   const unsigned grid = static_cast<unsigned>(row_map ? grid_rows : n_out);
+#define KGCNN_BLK_L(M, GA, L)                                                                                   \
+  gms_block_kernel<V, M, GA, L><<<grid, kThreads, 0, st>>>(x, wv, ws, rowptr, perm, gidx, gs, gp, n_out, nvec, mean, \
+                                                          y, row_map, n_rows_dev)
 #define KGCNN_BLK(M, GA)                                                                                        \
-  gms_block_kernel<V, M, GA><<<grid, kThreads, 0, st>>>(x, wv, ws, rowptr, perm, gidx, gs, gp, n_out, nvec, mean, y, \
-                                                       row_map, n_rows_dev)
+  do {                                                                                                          \
+    if (nvec <= 1) KGCNN_BLK_L(M, GA, 1);                                                                       \
+    else if (nvec <= 2) KGCNN_BLK_L(M, GA, 2);                                                                  \
+    else if (nvec <= 4) KGCNN_BLK_L(M, GA, 4);                                                                  \
+    else KGCNN_BLK_L(M, GA, 8);                                                                                 \
+  } while (0)
   if (mode == kMax) { if (gather) return KGCNN_E_UNSUPPORTED; KGCNN_BLK(kMax, false); }
   else if (mode == kMin) { if (gather) return KGCNN_E_UNSUPPORTED; KGCNN_BLK(kMin, false); }
   else if (mode == kSumW0) { if (gather) KGCNN_BLK(kSumW0, true); else KGCNN_BLK(kSumW0, false); }
   else if (mode == kSumW1) { if (gather) KGCNN_BLK(kSumW1, true); else KGCNN_BLK(kSumW1, false); }
   else { if (gather) KGCNN_BLK(kSumW2, true); else KGCNN_BLK(kSumW2, false); }
 #undef KGCNN_BLK
+#undef KGCNN_BLK_L
   return finish_launch();
 }
 
