@@ -125,7 +125,7 @@ acsf_g4_kernel(const float* __restrict__ xyz, const int32_t* __restrict__ z_atom
                const int32_t* __restrict__ tset_atom, const int32_t* __restrict__ rev_pair, int zmax,
                const int32_t* __restrict__ rowptr, const int32_t* __restrict__ perm,
                const int32_t* __restrict__ idx_j, const int32_t* __restrict__ idx_k,
-               const float* __restrict__ table, int R, int m, float eps, float inv_mult, int64_t N,
+               const float* __restrict__ table, int R, int m, float eps, float inv_mult, int uniform_rc, int64_t N,
                const float* __restrict__ cot, float* __restrict__ out, float* __restrict__ triple_out) {
   __shared__ float acc_s[kWarpsPerBlock][kMaxAcc];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -170,22 +170,34 @@ acsf_g4_kernel(const float* __restrict__ xyz, const int32_t* __restrict__ z_atom
         t_c = dot(dc_ij, uij) + dot(dc_ik, uik);
       }
       float a_ij = 0.f, a_ik = 0.f, a_jk = 0.f, a_c = 0.f;             // VJP: sums over the parameter sets
+      float fij, dfij, fik, dfik, fjk, dfjk;
+      if (uniform_rc) {                                                // one cutoff radius for the whole table
+        const float rc0 = __ldg(tab_i + 3);
+        cutoff(rij, rc0, fij, dfij);
+        cutoff(rik, rc0, fik, dfik);
+        cutoff(rjk, rc0, fjk, dfjk);
+      }
       for (int q = lane; q < m; q += 32) {
         const float4 prm = __ldg(reinterpret_cast<const float4*>(tab_i + (static_cast<int64_t>(r) * m + q) * 4));
         const float eta = prm.x, zeta = prm.y, lam = prm.z, rc = prm.w;
-        float fij, dfij, fik, dfik, fjk, dfjk;
-        cutoff(rij, rc, fij, dfij);
-        cutoff(rik, rc, fik, dfik);
-        cutoff(rjk, rc, fjk, dfjk);
-        const float base = c * lam + 1.f;
+        if (!uniform_rc) {
+          cutoff(rij, rc, fij, dfij);
+          cutoff(rik, rc, fik, dfik);
+          cutoff(rjk, rc, fjk, dfjk);
+        }
+        // (1 + lambda cos)^zeta as exp2(zeta log2(base)); base is clamped at 0 (it can only be negative by
+        // rounding of cos) -> 0^zeta = 0 like pow
+        const float base = fmaxf(c * lam + 1.f, 0.f);
         const float pre = exp2f(1.f - zeta) * inv_mult;
-        const float A = pre * powf(base, zeta);
+        const float pw = (base > 0.f) ? exp2f(zeta * log2f(base)) : (zeta == 0.f ? 1.f : 0.f);
+        const float A = pre * pw;
         const float E = expf(-eta * r2);
         const float fff = fij * fik * fjk;
         if (MODE == kFwd) {
           acc[r * m + q] += A * E * fff;
         } else {
-          const float dA = pre * zeta * lam * powf(base, zeta - 1.f);   // dA / dcos
+          const float pw1 = (base > 0.f) ? pw / base : (zeta == 1.f ? 1.f : 0.f);   // base^(zeta-1)
+          const float dA = pre * zeta * lam * pw1;                      // dA / dcos
           // d rep / d r_ab = A (dE/dr_ab fff + E f'_ab f f)
           const float d_ij = A * E * (-2.f * eta * rij * fff + dfij * fik * fjk);
           const float d_ik = A * E * (-2.f * eta * rik * fff + fij * dfik * fjk);
@@ -250,8 +262,8 @@ int kgcnn_acsf_g2(const float* xyz, const int32_t* rel_atom, const int32_t* tset
 
 int kgcnn_acsf_g4(const float* xyz, const int32_t* z_atom, const int32_t* tset_atom, const int32_t* rev_pair,
                   int zmax, const int32_t* rowptr, const int32_t* perm, const int32_t* idx_j, const int32_t* idx_k,
-                  const float* table, int R, int m, float eps, float multiplicity, int64_t N, int mode,
-                  const float* cot, float* out, float* triple_out, kgcnn_stream_t stream) {
+                  const float* table, int R, int m, float eps, float multiplicity, int uniform_rc, int64_t N,
+                  int mode, const float* cot, float* out, float* triple_out, kgcnn_stream_t stream) {
   if (N < 0 || R <= 0 || m <= 0 || zmax <= 0 || mode < kFwd || mode > kJvp) return KGCNN_E_INVALID;
   if (R * m > kMaxAcc) return KGCNN_E_UNSUPPORTED;
   if (N == 0) return KGCNN_OK;
@@ -263,7 +275,7 @@ int kgcnn_acsf_g4(const float* xyz, const int32_t* z_atom, const int32_t* tset_a
   const unsigned grid = static_cast<unsigned>(ceil_div<int64_t>(N, kWarpsPerBlock));
   cudaStream_t st = as_stream(stream);
 #define KGCNN_G4(M) acsf_g4_kernel<M><<<grid, kWarpsPerBlock * 32, 0, st>>>(xyz, z_atom, tset_atom, rev_pair, zmax, \
-    rowptr, perm, idx_j, idx_k, table, R, m, eps, inv_mult, N, cot, out, triple_out)
+    rowptr, perm, idx_j, idx_k, table, R, m, eps, inv_mult, uniform_rc, N, cot, out, triple_out)
   if (mode == kFwd) KGCNN_G4(kFwd); else if (mode == kVjp) KGCNN_G4(kVjp); else KGCNN_G4(kJvp);
 #undef KGCNN_G4
   return finish_launch();

@@ -189,7 +189,8 @@ class ACSFG4(GraphBaseLayer):
             spec = F.ACSFSpec(4, ri, self.weight_eta_zeta_lambda_rc.detach().contiguous(), self.num_relations,
                               int(self.eta_zeta_lambda_rc.shape[-2]), 1e-7 if self.add_eps else 0.0,
                               tset_atom=tset, z_atom=zv.to(torch.int32), rev_pair=rev_pair, zmax=_MAX_ATOMIC_NUMBER,
-                              rel_j=rj, rel_k=rk, multiplicity=self.multiplicity or 0.0)
+                              rel_j=rj, rel_k=rk, multiplicity=self.multiplicity or 0.0,
+                              uniform_rc=bool(np.all(self.eta_zeta_lambda_rc[..., 3] == self.eta_zeta_lambda_rc.reshape(-1, 4)[0, 3])))
             return xyz.with_values(F.acsf(xyz.values, spec))
         zi, zj, zk = F.gather(zv, ri), F.gather(zv, rj), F.gather(zv, rk)           # :475
         xi, xj, xk = (F.gather(xyz.values, r) for r in (ri, rj, rk))               # :476

@@ -175,7 +175,8 @@ int kgcnn_gemm_tn(const float* X, const float* G, int64_t M, int K1, int K2, flo
  *   tset_atom[n] : nullable; index of atom n as a CENTRE into a (N_el, R, m, .) table (use_target_set)
  *   z_atom[n]    : atomic number; rev_pair[zmax*zmax]: pair relation of (Z_j, Z_k), < 0 = not mapped
  *   rowptr/perm  : CSR of the pairs / triples by centre atom; table: [T][R][m][3] (eta, mu, Rc) / [T][R][m][4]
- *   (eta, zeta, lambda, Rc); eps: added under the square root when add_eps (else 0).
+ *   (eta, zeta, lambda, Rc); eps: added under the square root when add_eps (else 0); uniform_rc != 0 promises
+ *   that every table entry has the same Rc (the three cutoffs are then evaluated once per triple).
  * ------------------------------------------------------------------------------------------- */
 int kgcnn_acsf_g2(const float* xyz, const int32_t* rel_atom, const int32_t* tset_atom, const int32_t* rowptr,
                   const int32_t* perm, const int32_t* send, int send_permuted, const float* table, int R, int m,
@@ -183,8 +184,8 @@ int kgcnn_acsf_g2(const float* xyz, const int32_t* rel_atom, const int32_t* tset
                   kgcnn_stream_t stream);
 int kgcnn_acsf_g4(const float* xyz, const int32_t* z_atom, const int32_t* tset_atom, const int32_t* rev_pair,
                   int zmax, const int32_t* rowptr, const int32_t* perm, const int32_t* idx_j, const int32_t* idx_k,
-                  const float* table, int R, int m, float eps, float multiplicity, int64_t N, int mode,
-                  const float* cot, float* out, float* triple_out, kgcnn_stream_t stream);
+                  const float* table, int R, int m, float eps, float multiplicity, int uniform_rc, int64_t N,
+                  int mode, const float* cot, float* out, float* triple_out, kgcnn_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
  * optimizer of the force_*.py drivers (force_schnet.py:196-203): Keras Adam with per-variable clipnorm on one
