@@ -711,3 +711,28 @@ class _ACSFJvp(torch.autograd.Function):
 
 def acsf(xyz, spec):
     return _ACSF.apply(xyz, spec)
+
+
+# ------------------------------------------------------------------------------------------------
+# Dense contractions on tcgen05 tensor cores (3xTF32)
+# ------------------------------------------------------------------------------------------------
+def raw_dense_tc(op, a, b, bias=None):
+    """op 0: a[M,K] @ b[K,U] (+bias); op 1: a[M,U] @ b[K,U]^T; op 2: a[M,K]^T @ b[M,U]."""
+    _need_cuda(a, b, bias)
+    a, b = _f32c(a), _f32c(b)
+    M = int(a.shape[0])
+    if op == 0:
+        K, U = int(b.shape[0]), int(b.shape[1])
+        out = torch.empty((M, U), dtype=torch.float32, device=a.device)
+    elif op == 1:
+        K, U = int(b.shape[0]), int(b.shape[1])
+        out = torch.empty((M, K), dtype=torch.float32, device=a.device)
+    else:
+        K, U = int(a.shape[1]), int(b.shape[1])
+        out = torch.empty((K, U), dtype=torch.float32, device=a.device)
+    nbytes = int(_lib.lib().kgcnn_dense_tc_workspace_bytes(op, M, K, U))
+    ws = torch.empty((max(nbytes, 4),), dtype=torch.uint8, device=a.device) if nbytes else None
+    bias = None if bias is None else _f32c(bias)
+    check(_lib.lib().kgcnn_dense_tc(op, _ptr(a), _ptr(b), M, K, U, _ptr(bias), _ptr(out), _ptr(ws), nbytes, _stream()),
+          "kgcnn_dense_tc")
+    return out

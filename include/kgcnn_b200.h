@@ -165,6 +165,16 @@ int kgcnn_gemm_tn(const float* X, const float* G, int64_t M, int K1, int K2, flo
                   void* workspace, size_t workspace_bytes, kgcnn_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * a19  Dense contractions on the tcgen05 tensor cores (3xTF32 split, fp32 TMEM accumulators):
+ *   op 0 (NN): out[M,U] = A[M,K] B[K,U] + bias[U] (bias nullable)      forward, kgcnn/layers/modules.py:85
+ *   op 1 (NT): out[M,K] = A[M,U] B[K,U]^T                              input gradient
+ *   op 2 (TN): out[K,U] = A[M,K]^T B[M,U]                              weight gradient (needs the workspace)
+ * ------------------------------------------------------------------------------------------- */
+size_t kgcnn_dense_tc_workspace_bytes(int op, int64_t M, int K, int U);
+int kgcnn_dense_tc(int op, const float* A, const float* B, int64_t M, int K, int U, const float* bias, float* out,
+                   void* workspace, size_t workspace_bytes, kgcnn_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
  * a15/a16  fused ACSF symmetry functions (kgcnn/layers/conv/acsf_conv.py:199-211 and :473-494)
  *   mode 0: G[N, R*m]                  (out)
  *   mode 1: VJP, cot = dG[N, R*m]   -> out = d/dx of the CENTRE atoms [N,3]; the neighbour parts are written per
