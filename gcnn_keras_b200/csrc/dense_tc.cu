@@ -10,8 +10,9 @@
 // fp32 TMEM accumulator ("3xTF32"); the dropped lo*lo term is < 2^-20 relative.
 //
 // Data path: these GEMMs are skinny (K, U <= 640) and memory-bound, and the split needs a register pass anyway, so
-// tiles go global -> registers -> (hi, lo) -> shared memory in the canonical no-swizzle UMMA layout (8 x 16 B core
-// matrices); no TMA descriptor is needed.  One elected thread issues tcgen05.mma (kind::tf32, cta_group::1,
+// tiles go global -> registers -> (hi, lo) -> shared memory in the canonical no-swizzle K-major UMMA layout (8 x 16 B
+// core matrices); operands whose reduction index is the ROW of the global matrix (W in NN, X and G in TN) are
+// transposed on the way into shared memory, so every descriptor is K-major; no TMA descriptor is needed.  One elected thread issues tcgen05.mma (kind::tf32, cta_group::1,
 // M = 128), tcgen05.commit signals an mbarrier, the four warps read their 32 TMEM lanes back with tcgen05.ld.
 #include <algorithm>
 
@@ -72,38 +73,60 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   }
 }
 
-// Stage a row-major [rows x feats] region of a global matrix (leading dimension ld) into the hi / lo planes.
-// Element (row r, 4-feature chunk c) -> float4 slot c*NRP + r, NRP = NR + 1 (odd pitch: conflict-free stores).
-//   operand whose MMA "MN" index is the row and K index the feature  (K-major) : SBO = 8,   LBO = NRP
-//   operand whose MMA "MN" index is the feature and K index the row (MN-major) : SBO = NRP, LBO = 8
-template <int NR>
-__device__ __forceinline__ void stage(const float* __restrict__ g, int64_t row0, int64_t row_end, int f0, int f_end,
-                                      int ld, int nchunks, bool vec_ok, float4* __restrict__ hi,
-                                      float4* __restrict__ lo) {
-  constexpr int NRP = NR + 1;
-  const int total = NR * nchunks;
-  for (int it = threadIdx.x; it < total; it += kThreads) {
-    const int c = it % nchunks, r = it / nchunks;
-    const int64_t row = row0 + r;
-    const int f = f0 + 4 * c;
-    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (row < row_end) {
-      const float* p = g + row * ld + f;
-      if (vec_ok && f + 3 < f_end) v = __ldg(reinterpret_cast<const float4*>(p));
-      else {
-        if (f + 0 < f_end) v.x = __ldg(p + 0);
-        if (f + 1 < f_end) v.y = __ldg(p + 1);
-        if (f + 2 < f_end) v.z = __ldg(p + 2);
-        if (f + 3 < f_end) v.w = __ldg(p + 3);
-      }
+// K-major operand plane: element (mn, k) lives in float4 slot (k/4)*NRP + mn, component k%4, NRP = NR + 1
+// (odd pitch).  Descriptor: LBO = NRP (next 16 B k-chunk), SBO = 8 (next 8 mn), +2*NRP per MMA k-step of 8.
+__device__ __forceinline__ float4 load4(const float* __restrict__ g, int64_t row, int64_t row_end, int f, int f_end,
+                                        int ld, bool vec_ok) {
+  float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (row < row_end) {
+    const float* p = g + row * ld + f;
+    if (vec_ok && f + 3 < f_end) v = __ldg(reinterpret_cast<const float4*>(p));
+    else {
+      if (f + 0 < f_end) v.x = __ldg(p + 0);
+      if (f + 1 < f_end) v.y = __ldg(p + 1);
+      if (f + 2 < f_end) v.z = __ldg(p + 2);
+      if (f + 3 < f_end) v.w = __ldg(p + 3);
     }
-    float4 h;
-    h.x = __uint_as_float(__float_as_uint(v.x) & 0xffffe000u);
-    h.y = __uint_as_float(__float_as_uint(v.y) & 0xffffe000u);
-    h.z = __uint_as_float(__float_as_uint(v.z) & 0xffffe000u);
-    h.w = __uint_as_float(__float_as_uint(v.w) & 0xffffe000u);
+  }
+  return v;
+}
+__device__ __forceinline__ float tf32_hi(float x) { return __uint_as_float(__float_as_uint(x) & 0xffffe000u); }
+
+// mn = row of the global matrix, k = feature: rows [row0, row0+NR), features [f0, f0+kKC)
+template <int NR>
+__device__ __forceinline__ void stage_direct(const float* __restrict__ g, int64_t row0, int64_t row_end, int f0,
+                                             int f_end, int ld, bool vec_ok, float4* __restrict__ hi,
+                                             float4* __restrict__ lo) {
+  constexpr int NRP = NR + 1, NCH = kKC / 4;
+  for (int it = threadIdx.x; it < NR * NCH; it += kThreads) {
+    const int c = it % NCH, r = it / NCH;                 // consecutive threads: consecutive 16 B of one row
+    const float4 v = load4(g, row0 + r, row_end, f0 + 4 * c, f_end, ld, vec_ok);
+    const float4 h = make_float4(tf32_hi(v.x), tf32_hi(v.y), tf32_hi(v.z), tf32_hi(v.w));
     hi[c * NRP + r] = h;
     lo[c * NRP + r] = make_float4(v.x - h.x, v.y - h.y, v.z - h.z, v.w - h.w);
+  }
+}
+
+// mn = feature, k = row of the global matrix (transposed on the way in): rows [row0, row0+kKC), features
+// [f0, f0+4*nchunks).  Consecutive threads take consecutive rows -> the scalar stores hit 32 different banks.
+template <int NR>
+__device__ __forceinline__ void stage_transposed(const float* __restrict__ g, int64_t row0, int64_t row_end, int f0,
+                                                 int f_end, int ld, int nchunks, bool vec_ok, float4* __restrict__ hi,
+                                                 float4* __restrict__ lo) {
+  constexpr int NRP = NR + 1;
+  float* hs = reinterpret_cast<float*>(hi);
+  float* ls = reinterpret_cast<float*>(lo);
+  for (int it = threadIdx.x; it < kKC * nchunks; it += kThreads) {
+    const int k = it % kKC, j = it / kKC;
+    const float4 v = load4(g, row0 + k, row_end, f0 + 4 * j, f_end, ld, vec_ok);
+    const float vv[4] = {v.x, v.y, v.z, v.w};
+    const int base = ((k >> 2) * NRP + 4 * j) * 4 + (k & 3);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float h = tf32_hi(vv[i]);
+      hs[base + 4 * i] = h;
+      ls[base + 4 * i] = vv[i] - h;
+    }
   }
 }
 
@@ -116,8 +139,7 @@ dense_tc_kernel(const float* __restrict__ A, const float* __restrict__ B, int64_
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ __align__(8) uint64_t mbar;
   __shared__ uint32_t tmem_base_s;
-  constexpr int PLANE = 32 * (kKC + 1);            // float4 slots per plane: max(8 chunks x 129, 32 chunks x 33)
-  static_assert(PLANE >= (kKC / 4) * (kBM + 1), "plane too small");
+  constexpr int PLANE = (kKC / 4) * (kBM + 1);     // float4 slots per plane: 8 k-chunks x (128 + 1) mn
   float4* a_hi = reinterpret_cast<float4*>(smem_raw);
   float4* a_lo = a_hi + PLANE;
   float4* b_hi = a_lo + PLANE;
@@ -153,32 +175,25 @@ dense_tc_kernel(const float* __restrict__ A, const float* __restrict__ B, int64_
   const uint32_t tmem_d = tmem_base_s;
   const uint32_t bar = smem_u32(&mbar);
 
-  // operand majors and descriptor strides (units of 16 B)
-  constexpr int a_mn = (OP == kTN) ? 1 : 0;                   // A: K-major for NN/NT, MN-major for TN
-  constexpr int b_mn = (OP == kNT) ? 0 : 1;                   // B: MN-major for NN/TN, K-major for NT
-  // plane pitch NRP per operand (rows staged + 1)
-  constexpr int A_NR = (OP == kTN) ? kKC : kBM;
-  constexpr int B_NR = (OP == kNT) ? kMaxN : kKC;
-  constexpr int A_NRP = A_NR + 1, B_NRP = B_NR + 1;
-  const uint32_t a_lbo = a_mn ? 8 : A_NRP, a_sbo = a_mn ? A_NRP : 8;
-  const uint32_t b_lbo = b_mn ? 8 : B_NRP, b_sbo = b_mn ? B_NRP : 8;
-  const uint32_t a_kstep = a_mn ? 8 : 2 * A_NRP;              // descriptor advance per MMA k-step (8 elements)
-  const uint32_t b_kstep = b_mn ? 8 : 2 * B_NRP;
-  const uint32_t idesc = make_idesc(a_mn, b_mn, nt);
+  // every operand is K-major with 128 (+1) mn slots per k-chunk: LBO = 129, SBO = 8 (units of 16 B)
+  constexpr int NRP = kBM + 1;
+  static_assert(kMaxN == kBM, "A and B planes share one pitch");
+  constexpr uint32_t kstep = 2 * NRP;                          // descriptor advance per MMA k-step (8 elements)
+  const uint32_t idesc = make_idesc(0, 0, nt);
 
   uint32_t parity = 0;
   bool first = true;
   for (int64_t k0 = 0; k0 < red_len; k0 += kKC) {
     // ---- stage A and B (hi / lo) ----
     if (OP == kNN) {
-      stage<kBM>(A, m0, M, static_cast<int>(k0), K, K, kKC / 4, vec_a, a_hi, a_lo);                 // X rows, K feats
-      stage<kKC>(B, k0, K, n0, U, U, nt / 4, vec_b, b_hi, b_lo);                                    // W rows k, feats u
+      stage_direct<kBM>(A, m0, M, static_cast<int>(k0), K, K, vec_a, a_hi, a_lo);                 // X rows, K feats
+      stage_transposed<kMaxN>(B, k0, K, n0, U, U, nt / 4, vec_b, b_hi, b_lo);                     // W rows k -> K dim
     } else if (OP == kNT) {
-      stage<kBM>(A, m0, M, static_cast<int>(k0), U, U, kKC / 4, vec_a, a_hi, a_lo);                 // G rows, U feats
-      stage<kMaxN>(B, n0, K, static_cast<int>(k0), U, U, kKC / 4, vec_b, b_hi, b_lo);               // W rows n, feats u
+      stage_direct<kBM>(A, m0, M, static_cast<int>(k0), U, U, vec_a, a_hi, a_lo);                 // G rows, U feats
+      stage_direct<kMaxN>(B, n0, K, static_cast<int>(k0), U, U, vec_b, b_hi, b_lo);               // W rows n, U feats
     } else {
-      stage<kKC>(A, row_beg + k0, row_end, a0, K, K, kBM / 4, vec_a, a_hi, a_lo);                   // X rows, feats a
-      stage<kKC>(B, row_beg + k0, row_end, n0, U, U, nt / 4, vec_b, b_hi, b_lo);                    // G rows, feats n
+      stage_transposed<kBM>(A, row_beg + k0, row_end, a0, K, K, kBM / 4, vec_a, a_hi, a_lo);      // X rows -> K dim
+      stage_transposed<kMaxN>(B, row_beg + k0, row_end, n0, U, U, nt / 4, vec_b, b_hi, b_lo);     // G rows -> K dim
     }
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // generic-proxy stores -> async proxy (MMA)
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -189,10 +204,10 @@ dense_tc_kernel(const float* __restrict__ A, const float* __restrict__ B, int64_
         const uint32_t ah = smem_u32(a_hi), al = smem_u32(a_lo), bh = smem_u32(b_hi), bl = smem_u32(b_lo);
 #pragma unroll
         for (int ks = 0; ks < kKC / 8; ++ks) {
-          const uint64_t dah = make_desc(ah + ks * a_kstep * 16, a_lbo, a_sbo);
-          const uint64_t dal = make_desc(al + ks * a_kstep * 16, a_lbo, a_sbo);
-          const uint64_t dbh = make_desc(bh + ks * b_kstep * 16, b_lbo, b_sbo);
-          const uint64_t dbl = make_desc(bl + ks * b_kstep * 16, b_lbo, b_sbo);
+          const uint64_t dah = make_desc(ah + ks * kstep * 16, NRP, 8);
+          const uint64_t dal = make_desc(al + ks * kstep * 16, NRP, 8);
+          const uint64_t dbh = make_desc(bh + ks * kstep * 16, NRP, 8);
+          const uint64_t dbl = make_desc(bl + ks * kstep * 16, NRP, 8);
           mma_tf32(tmem_d, dah, dbh, idesc, (first && ks == 0) ? 0u : 1u);     // hi * hi
           mma_tf32(tmem_d, dal, dbh, idesc, 1u);                                // lo * hi
           mma_tf32(tmem_d, dah, dbl, idesc, 1u);                                // hi * lo
@@ -274,7 +289,7 @@ tn_split_reduce_kernel(const float* __restrict__ partial, int S, int64_t n, floa
   out[i] = (s0 + s1) + (s2 + s3);
 }
 
-constexpr size_t kSmemBytes = 4 * 32 * (kKC + 1) * sizeof(float4);   // 4 planes (A hi/lo, B hi/lo) = 66 KB
+constexpr size_t kSmemBytes = 4 * (kKC / 4) * (kBM + 1) * sizeof(float4);   // 4 planes (A hi/lo, B hi/lo) = 64.5 KB
 
 inline int tn_splits(int64_t M, int K, int U) {
   const int tiles = ceil_div(K, kBM) * ceil_div(U, kMaxN);

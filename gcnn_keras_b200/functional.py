@@ -473,20 +473,19 @@ _TN_MIN_ROWS = 512     # below this the reduction axis is short and a library GE
 
 
 class _MatMul(torch.autograd.Function):
-    """Bilinear products closed under differentiation.  mode 0: a @ b, 1: a @ b^T, 2: a^T @ b.
-    a @ b and a @ b^T are plain library GEMMs (cuBLAS fp32, TF32 off); a^T @ b with a long reduction axis (the
-    weight gradients: sum over all edges / atoms) is our split-M deterministic kernel."""
+    """Bilinear products closed under differentiation.  mode 0: a @ b, 1: a @ b^T, 2: a^T @ b, all three on the
+    tcgen05 tensor cores (3xTF32 split, fp32 TMEM accumulation; dense_tc.cu)."""
 
     @staticmethod
     def forward(ctx, a, b, mode):
         ctx.mode = mode
         ctx.save_for_backward(a, b)
+        if a.is_cuda and a.dtype == torch.float32 and a.dim() == 2 and b.dim() == 2:
+            return raw_dense_tc(mode, a, b)          # tcgen05 tensor cores, 3xTF32
         if mode == 0:
             return a @ b
         if mode == 1:
             return a @ b.t()
-        if a.shape[0] >= _TN_MIN_ROWS and a.is_cuda:
-            return raw_gemm_tn(a, b)
         return a.t() @ b
 
     @staticmethod
@@ -535,6 +534,8 @@ class _Linear(torch.autograd.Function):
     def forward(ctx, x, w, b):
         ctx.save_for_backward(x, w)
         ctx.has_bias = b is not None
+        if x.is_cuda and x.dtype == torch.float32:
+            return raw_dense_tc(0, x, w, b)          # tcgen05 tensor cores, 3xTF32, bias in the epilogue
         return torch.addmm(b, x, w) if b is not None else x @ w
 
     @staticmethod
@@ -558,8 +559,8 @@ class _TNCol(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, g):
         ctx.save_for_backward(x, g)
-        if x.shape[0] >= _TN_MIN_ROWS and x.is_cuda:
-            return raw_gemm_tn(x, g, want_colsum=True)
+        if x.is_cuda and x.dtype == torch.float32:
+            return raw_dense_tc(2, x, g), raw_colsum(g)
         return x.t() @ g, g.sum(0)
 
     @staticmethod
@@ -575,8 +576,8 @@ class _TNCol(torch.autograd.Function):
 
 def dense(x, kernel, bias, activation):
     """DenseEmbedding on flat values (kgcnn/layers/modules.py:85): activation(x @ kernel + bias).
-    x @ W (+ b) and g @ W^T are plain library GEMMs (cuBLAS fp32, TF32 off); the weight + bias gradients (one
-    split-M pass), the activation and all their derivatives run in our kernels."""
+    x @ W (+ b), g @ W^T and x^T g run on the tcgen05 tensor cores (3xTF32); the activation and all its derivatives
+    in the fused bias/activation kernel family."""
     code = activation if isinstance(activation, int) else act_code(activation)
     lead = x.shape[:-1]
     x2 = x.reshape(-1, x.shape[-1])
