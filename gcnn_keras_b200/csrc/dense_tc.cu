@@ -5,9 +5,10 @@
 // M = edges / atoms of the batch (1e4 .. 1e6), K and U = layer widths (1 .. 640).
 //
 // Precision: the parity bar is 1e-5 of an fp64 oracle, single-pass TF32 (10-bit mantissa) is ~1e-3.  Every operand
-// tile is therefore split while it is staged into shared memory, x = hi + lo with hi = x & 0xffffe000 (exactly
-// representable in TF32) and lo = x - hi (exact in fp32), and three MMAs accumulate hi*hi + lo*hi + hi*lo in the
-// fp32 TMEM accumulator ("3xTF32"); the dropped lo*lo term is < 2^-20 relative.
+// tile is therefore split while it is staged into shared memory, x ~ hi + lo with hi = nearest TF32 value and
+// lo = nearest TF32 value of x - hi (|x - hi - lo| <= 2^-23 |x|), and four MMAs accumulate lo*lo + lo*hi + hi*lo +
+// hi*hi in the fp32 TMEM accumulator, drained to fp32 registers every kFlush reduction elements.  The MMAs
+// are not the bottleneck of these skinny, memory-bound products, so the fourth one is free.
 //
 // Data path: these GEMMs are skinny (K, U <= 640) and memory-bound, and the split needs a register pass anyway, so
 // tiles go global -> registers -> (hi, lo) -> shared memory in the canonical no-swizzle K-major UMMA layout (8 x 16 B
@@ -21,10 +22,12 @@
 namespace kgcnn {
 namespace tc {
 
-constexpr int kThreads = 128;   // 4 warps = 128 TMEM lanes
+constexpr int kThreads = 256;   // 8 warps stage operands; warp w reads TMEM lanes 32*(w%4)..+31 in the epilogue
 constexpr int kBM = 128;        // MMA M
-constexpr int kKC = 32;         // reduction elements staged per chunk (4 MMA k-steps of 8)
+constexpr int kKC = 64;         // reduction elements staged per chunk (8 MMA k-steps of 8)
+constexpr int kLd = 8;          // float4 loads in flight per thread and operand (= 128*16/256 = 64*32/256)
 constexpr int kMaxN = 128;      // MMA N per CTA (TMEM columns)
+constexpr int kFlush = 64;      // reduction length accumulated inside the tensor core before an fp32 (RN) flush
 
 enum { kNN = 0, kNT = 1, kTN = 2 };
 
@@ -90,42 +93,67 @@ __device__ __forceinline__ float4 load4(const float* __restrict__ g, int64_t row
   }
   return v;
 }
-__device__ __forceinline__ float tf32_hi(float x) { return __uint_as_float(__float_as_uint(x) & 0xffffe000u); }
+// nearest TF32 value (round half away in magnitude): |x - hi| <= 2^-11 |x|, and x - hi is exact in fp32.  lo is
+// rounded the same way (the tensor core would truncate it, a one-sided 2^-22 |x| bias that adds up coherently over
+// a reduction); after RN the residual x - hi - lo is <= 2^-23 |x| and unbiased, i.e. fp32-like.
+__device__ __forceinline__ float tf32_hi(float x) {
+  return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xffffe000u);
+}
 
-// mn = row of the global matrix, k = feature: rows [row0, row0+NR), features [f0, f0+kKC)
-template <int NR>
-__device__ __forceinline__ void stage_direct(const float* __restrict__ g, int64_t row0, int64_t row_end, int f0,
-                                             int f_end, int ld, bool vec_ok, float4* __restrict__ hi,
-                                             float4* __restrict__ lo) {
-  constexpr int NRP = NR + 1, NCH = kKC / 4;
-  for (int it = threadIdx.x; it < NR * NCH; it += kThreads) {
+// mn = row of the global matrix, k = feature: rows [row0, row0+128), features [f0, f0+kKC).  Loads are issued as
+// one batch of kLd independent float4 per thread (registers), the split + shared-memory stores follow later, so
+// the next chunk's global latency overlaps the MMAs of the current one.
+__device__ __forceinline__ void load_direct(float4 (&v)[kLd], const float* __restrict__ g, int64_t row0,
+                                            int64_t row_end, int f0, int f_end, int ld, bool vec_ok) {
+  constexpr int NCH = kKC / 4;
+#pragma unroll
+  for (int i = 0; i < kLd; ++i) {
+    const int it = threadIdx.x + i * kThreads;
     const int c = it % NCH, r = it / NCH;                 // consecutive threads: consecutive 16 B of one row
-    const float4 v = load4(g, row0 + r, row_end, f0 + 4 * c, f_end, ld, vec_ok);
-    const float4 h = make_float4(tf32_hi(v.x), tf32_hi(v.y), tf32_hi(v.z), tf32_hi(v.w));
+    v[i] = load4(g, row0 + r, row_end, f0 + 4 * c, f_end, ld, vec_ok);
+  }
+}
+__device__ __forceinline__ void store_direct(const float4 (&v)[kLd], float4* __restrict__ hi, float4* __restrict__ lo) {
+  constexpr int NRP = kBM + 1, NCH = kKC / 4;
+#pragma unroll
+  for (int i = 0; i < kLd; ++i) {
+    const int it = threadIdx.x + i * kThreads;
+    const int c = it % NCH, r = it / NCH;
+    const float4 h = make_float4(tf32_hi(v[i].x), tf32_hi(v[i].y), tf32_hi(v[i].z), tf32_hi(v[i].w));
     hi[c * NRP + r] = h;
-    lo[c * NRP + r] = make_float4(v.x - h.x, v.y - h.y, v.z - h.z, v.w - h.w);
+    lo[c * NRP + r] = make_float4(tf32_hi(v[i].x - h.x), tf32_hi(v[i].y - h.y), tf32_hi(v[i].z - h.z),
+                                  tf32_hi(v[i].w - h.w));
   }
 }
 
 // mn = feature, k = row of the global matrix (transposed on the way in): rows [row0, row0+kKC), features
 // [f0, f0+4*nchunks).  Consecutive threads take consecutive rows -> the scalar stores hit 32 different banks.
-template <int NR>
-__device__ __forceinline__ void stage_transposed(const float* __restrict__ g, int64_t row0, int64_t row_end, int f0,
-                                                 int f_end, int ld, int nchunks, bool vec_ok, float4* __restrict__ hi,
+__device__ __forceinline__ void load_transposed(float4 (&v)[kLd], const float* __restrict__ g, int64_t row0,
+                                                int64_t row_end, int f0, int f_end, int ld, int nchunks, bool vec_ok) {
+#pragma unroll
+  for (int i = 0; i < kLd; ++i) {
+    const int it = threadIdx.x + i * kThreads;
+    const int k = it % kKC, j = it / kKC;
+    v[i] = (j < nchunks) ? load4(g, row0 + k, row_end, f0 + 4 * j, f_end, ld, vec_ok) : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+}
+__device__ __forceinline__ void store_transposed(const float4 (&v)[kLd], int nchunks, float4* __restrict__ hi,
                                                  float4* __restrict__ lo) {
-  constexpr int NRP = NR + 1;
+  constexpr int NRP = kBM + 1;
   float* hs = reinterpret_cast<float*>(hi);
   float* ls = reinterpret_cast<float*>(lo);
-  for (int it = threadIdx.x; it < kKC * nchunks; it += kThreads) {
+#pragma unroll
+  for (int i = 0; i < kLd; ++i) {
+    const int it = threadIdx.x + i * kThreads;
     const int k = it % kKC, j = it / kKC;
-    const float4 v = load4(g, row0 + k, row_end, f0 + 4 * j, f_end, ld, vec_ok);
-    const float vv[4] = {v.x, v.y, v.z, v.w};
+    if (j >= nchunks) continue;
+    const float vv[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
     const int base = ((k >> 2) * NRP + 4 * j) * 4 + (k & 3);
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const float h = tf32_hi(vv[i]);
-      hs[base + 4 * i] = h;
-      ls[base + 4 * i] = vv[i] - h;
+    for (int q = 0; q < 4; ++q) {
+      const float h = tf32_hi(vv[q]);
+      hs[base + 4 * q] = h;
+      ls[base + 4 * q] = tf32_hi(vv[q] - h);
     }
   }
 }
@@ -181,20 +209,58 @@ dense_tc_kernel(const float* __restrict__ A, const float* __restrict__ B, int64_
   constexpr uint32_t kstep = 2 * NRP;                          // descriptor advance per MMA k-step (8 elements)
   const uint32_t idesc = make_idesc(0, 0, nt);
 
+  float4 va[kLd], vb[kLd];
+  auto load_chunk = [&](int64_t k0) {
+    if (OP == kNN) {
+      load_direct(va, A, m0, M, static_cast<int>(k0), K, K, vec_a);                       // X rows, K feats
+      load_transposed(vb, B, k0, K, n0, U, U, nt / 4, vec_b);                             // W rows k -> K dim
+    } else if (OP == kNT) {
+      load_direct(va, A, m0, M, static_cast<int>(k0), U, U, vec_a);                       // G rows, U feats
+      load_direct(vb, B, n0, K, static_cast<int>(k0), U, U, vec_b);                       // W rows n, U feats
+    } else {
+      load_transposed(va, A, row_beg + k0, row_end, a0, K, K, kBM / 4, vec_a);            // X rows -> K dim
+      load_transposed(vb, B, row_beg + k0, row_end, n0, U, U, nt / 4, vec_b);             // G rows -> K dim
+    }
+  };
+  // The tensor core adds into the TMEM accumulator with truncation, which biases long reductions (measured:
+  // ~7e-9 relative per reduction element).  Every kFlush elements the accumulator is drained into fp32 registers
+  // (round-to-nearest adds) and the next MMA starts a fresh accumulation.
+  float racc[2][32];
+#pragma unroll
+  for (int gq = 0; gq < 2; ++gq)
+#pragma unroll
+    for (int i = 0; i < 32; ++i) racc[gq][i] = 0.f;
+  auto drain = [&]() {
+#pragma unroll
+    for (int gq = 0; gq < 2; ++gq) {
+      const int c0 = 32 * (warp >> 2) + 64 * gq;
+      if (c0 < nt) {                                     // warp-uniform
+        uint32_t v[32];
+        const uint32_t taddr = tmem_d + (static_cast<uint32_t>(32 * (warp & 3)) << 16) + static_cast<uint32_t>(c0);
+        asm volatile(
+            "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+            "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+            "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+            : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+              "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+              "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+              "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+            : "r"(taddr)
+            : "memory");
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+        for (int i = 0; i < 32; ++i) racc[gq][i] += __uint_as_float(v[i]);
+      }
+    }
+  };
   uint32_t parity = 0;
   bool first = true;
+  if (red_len > 0) load_chunk(0);
   for (int64_t k0 = 0; k0 < red_len; k0 += kKC) {
-    // ---- stage A and B (hi / lo) ----
-    if (OP == kNN) {
-      stage_direct<kBM>(A, m0, M, static_cast<int>(k0), K, K, vec_a, a_hi, a_lo);                 // X rows, K feats
-      stage_transposed<kMaxN>(B, k0, K, n0, U, U, nt / 4, vec_b, b_hi, b_lo);                     // W rows k -> K dim
-    } else if (OP == kNT) {
-      stage_direct<kBM>(A, m0, M, static_cast<int>(k0), U, U, vec_a, a_hi, a_lo);                 // G rows, U feats
-      stage_direct<kMaxN>(B, n0, K, static_cast<int>(k0), U, U, vec_b, b_hi, b_lo);               // W rows n, U feats
-    } else {
-      stage_transposed<kBM>(A, row_beg + k0, row_end, a0, K, K, kBM / 4, vec_a, a_hi, a_lo);      // X rows -> K dim
-      stage_transposed<kMaxN>(B, row_beg + k0, row_end, n0, U, U, nt / 4, vec_b, b_hi, b_lo);     // G rows -> K dim
-    }
+    // ---- split (hi / lo) and store this chunk ----
+    if (OP == kNN) { store_direct(va, a_hi, a_lo); store_transposed(vb, nt / 4, b_hi, b_lo); }
+    else if (OP == kNT) { store_direct(va, a_hi, a_lo); store_direct(vb, b_hi, b_lo); }
+    else { store_transposed(va, kBM / 4, a_hi, a_lo); store_transposed(vb, nt / 4, b_hi, b_lo); }
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // generic-proxy stores -> async proxy (MMA)
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
@@ -202,15 +268,23 @@ dense_tc_kernel(const float* __restrict__ A, const float* __restrict__ B, int64_
       if (lane == 0) {
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const uint32_t ah = smem_u32(a_hi), al = smem_u32(a_lo), bh = smem_u32(b_hi), bl = smem_u32(b_lo);
-#pragma unroll
-        for (int ks = 0; ks < kKC / 8; ++ks) {
+        const int64_t left = red_len - k0;
+        const int ksteps = (static_cast<int>(left < kKC ? left : kKC) + 7) / 8;           // skip all-zero k-steps
+        // small terms first: while they accumulate, the accumulator is ~2^-11 of its final size and so are the
+        // truncation errors of the tensor core's adds; only the ksteps hi*hi adds see the full magnitude
+        for (int ks = 0; ks < ksteps; ++ks) {
           const uint64_t dah = make_desc(ah + ks * kstep * 16, NRP, 8);
           const uint64_t dal = make_desc(al + ks * kstep * 16, NRP, 8);
           const uint64_t dbh = make_desc(bh + ks * kstep * 16, NRP, 8);
           const uint64_t dbl = make_desc(bl + ks * kstep * 16, NRP, 8);
-          mma_tf32(tmem_d, dah, dbh, idesc, (first && ks == 0) ? 0u : 1u);     // hi * hi
+          mma_tf32(tmem_d, dal, dbl, idesc, (first && ks == 0) ? 0u : 1u);     // lo * lo
           mma_tf32(tmem_d, dal, dbh, idesc, 1u);                                // lo * hi
           mma_tf32(tmem_d, dah, dbl, idesc, 1u);                                // hi * lo
+        }
+        for (int ks = 0; ks < ksteps; ++ks) {
+          const uint64_t dah = make_desc(ah + ks * kstep * 16, NRP, 8);
+          const uint64_t dbh = make_desc(bh + ks * kstep * 16, NRP, 8);
+          mma_tf32(tmem_d, dah, dbh, idesc, 1u);                                // hi * hi
         }
         asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar)
                      : "memory");
@@ -218,44 +292,51 @@ dense_tc_kernel(const float* __restrict__ A, const float* __restrict__ B, int64_
       __syncwarp();
     }
     first = false;
-    mbar_wait(bar, parity);          // MMAs of this chunk are done: shared memory may be overwritten
+    if (k0 + kKC < red_len) load_chunk(k0 + kKC);      // next chunk's global loads fly while the MMAs run
+    mbar_wait(bar, parity);                             // MMAs of this chunk are done: planes may be overwritten
     parity ^= 1;
-  }
-  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-
-  // ---- epilogue: TMEM lane (32*warp + lane) = output row, columns = n ----
-  const int d_row = 32 * warp + lane;
-  for (int c0 = 0; c0 < nt; c0 += 32) {
-    uint32_t v[32];
-    if (red_len > 0) {
-      const uint32_t taddr = tmem_d + (static_cast<uint32_t>(32 * warp) << 16) + static_cast<uint32_t>(c0);
-      asm volatile(
-          "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-          "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-          "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-          : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
-            "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
-            "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
-            "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
-          : "r"(taddr)
-          : "memory");
-      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-    } else {
-#pragma unroll
-      for (int i = 0; i < 32; ++i) v[i] = 0u;
+    if ((k0 + kKC) % kFlush == 0 || k0 + kKC >= red_len) {
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      drain();
+      first = true;                                     // the next MMA overwrites the accumulator
     }
+  }
+
+  // ---- epilogue: TMEM lane 32*(warp%4) + lane = output row; warps 0-3 take the even 32-column groups, 4-7 the odd ----
+  const int d_row = 32 * (warp & 3) + lane;
+#pragma unroll
+  for (int gq = 0; gq < 2; ++gq) {
+    const int c0 = 32 * (warp >> 2) + 64 * gq;
+    if (c0 >= nt) continue;
+    uint32_t v[32];
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(racc[gq][i]);
+    float* o = nullptr;
+    bool row_ok;
     if (OP == kTN) {
       const int feat = a0 + d_row;
-      if (feat < K) {
-        float* o = out + (static_cast<int64_t>(blockIdx.z) * K + feat) * U + n0 + c0;
-#pragma unroll
-        for (int i = 0; i < 32; ++i)
-          if (n0 + c0 + i < U) o[i] = __uint_as_float(v[i]);
-      }
+      row_ok = feat < K;
+      o = out + (static_cast<int64_t>(blockIdx.z) * K + feat) * U + n0 + c0;
     } else {
       const int64_t row = m0 + d_row;
-      if (row < M) {
-        float* o = out + row * n_total + n0 + c0;
+      row_ok = row < M;
+      o = out + row * n_total + n0 + c0;
+    }
+    if (row_ok) {
+      const bool vec_out = (n_total % 4 == 0) && (n0 + c0 + 32 <= n_total) &&
+                           ((reinterpret_cast<uintptr_t>(out) & 15) == 0);
+      if (vec_out) {
+#pragma unroll
+        for (int i = 0; i < 32; i += 4) {
+          float4 r = make_float4(__uint_as_float(v[i]), __uint_as_float(v[i + 1]), __uint_as_float(v[i + 2]),
+                                 __uint_as_float(v[i + 3]));
+          if (OP == kNN && bias) {       // scalar loads: the bias may be an unaligned view of a flat buffer
+            const float* bp = bias + n0 + c0 + i;
+            r.x += __ldg(bp); r.y += __ldg(bp + 1); r.z += __ldg(bp + 2); r.w += __ldg(bp + 3);
+          }
+          *reinterpret_cast<float4*>(o + i) = r;
+        }
+      } else {
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
           const int col = n0 + c0 + i;
@@ -294,7 +375,7 @@ constexpr size_t kSmemBytes = 4 * (kKC / 4) * (kBM + 1) * sizeof(float4);   // 4
 inline int tn_splits(int64_t M, int K, int U) {
   const int tiles = ceil_div(K, kBM) * ceil_div(U, kMaxN);
   int64_t s = std::max<int64_t>(1, (2 * kNumSM) / tiles);
-  s = std::min<int64_t>(s, std::max<int64_t>(1, ceil_div<int64_t>(M, 4 * kKC)));
+  s = std::min<int64_t>(s, std::max<int64_t>(1, ceil_div<int64_t>(M, 2 * kKC)));
   return static_cast<int>(s);
 }
 

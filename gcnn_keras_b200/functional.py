@@ -470,6 +470,7 @@ def raw_gemm_tn(x2d, g2d, want_colsum=False):
 
 
 _TN_MIN_ROWS = 512     # below this the reduction axis is short and a library GEMM is as good
+DENSE_LIBRARY = False  # diagnostics only (tools/diag_hdnnp.py): route Dense through the library GEMM instead of dense_tc
 
 
 class _MatMul(torch.autograd.Function):
@@ -480,7 +481,7 @@ class _MatMul(torch.autograd.Function):
     def forward(ctx, a, b, mode):
         ctx.mode = mode
         ctx.save_for_backward(a, b)
-        if a.is_cuda and a.dtype == torch.float32 and a.dim() == 2 and b.dim() == 2:
+        if a.is_cuda and a.dtype == torch.float32 and a.dim() == 2 and b.dim() == 2 and not DENSE_LIBRARY:
             return raw_dense_tc(mode, a, b)          # tcgen05 tensor cores, 3xTF32
         if mode == 0:
             return a @ b
@@ -534,7 +535,7 @@ class _Linear(torch.autograd.Function):
     def forward(ctx, x, w, b):
         ctx.save_for_backward(x, w)
         ctx.has_bias = b is not None
-        if x.is_cuda and x.dtype == torch.float32:
+        if x.is_cuda and x.dtype == torch.float32 and not DENSE_LIBRARY:
             return raw_dense_tc(0, x, w, b)          # tcgen05 tensor cores, 3xTF32, bias in the epilogue
         return torch.addmm(b, x, w) if b is not None else x @ w
 
@@ -559,7 +560,7 @@ class _TNCol(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, g):
         ctx.save_for_backward(x, g)
-        if x.is_cuda and x.dtype == torch.float32:
+        if x.is_cuda and x.dtype == torch.float32 and not DENSE_LIBRARY:
             return raw_dense_tc(2, x, g), raw_colsum(g)
         return x.t() @ g, g.sum(0)
 

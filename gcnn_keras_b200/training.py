@@ -24,14 +24,16 @@ class FlatAdam:
         from .plan import Relation
         self.params = list(params)
         dev = self.params[0].device
-        sizes = [p.numel() for p in self.params]
+        real = [p.numel() for p in self.params]
+        sizes = [(n + 63) // 64 * 64 for n in real]              # every variable starts 256 B aligned
         self.total = sum(sizes)
-        self.flat = torch.empty(self.total, dtype=torch.float32, device=dev)
+        self.flat = torch.zeros(self.total, dtype=torch.float32, device=dev)
         off = 0
-        for p, n in zip(self.params, sizes):
+        for p, n, padded in zip(self.params, real, sizes):
             self.flat[off:off + n].copy_(p.data.reshape(-1))
             p.data = self.flat[off:off + n].view_as(p)          # parameters become views of the flat buffer
-            off += n
+            off += padded
+        self._real, self._padded = real, sizes
         self.m = torch.zeros_like(self.flat)
         self.v = torch.zeros_like(self.flat)
         offsets = torch.tensor([0] + list(torch.tensor(sizes).cumsum(0)), dtype=torch.int32, device=dev)
@@ -46,7 +48,12 @@ class FlatAdam:
         from . import _lib
         from .distributed import allreduce_flat
         F = self._F
-        g = torch.cat([gr.reshape(-1) for gr in grads])
+        pieces = []
+        for gr, n, padded in zip(grads, self._real, self._padded):
+            pieces.append(gr.reshape(-1))
+            if padded > n:
+                pieces.append(self.flat.new_zeros(padded - n))
+        g = torch.cat(pieces)
         g = allreduce_flat(g)                                    # data parallel by graph: the step's only collective
         lr, b1, b2, eps, clip = self.hyper
         sumsq = F.raw_gms(g.unsqueeze(1), g.unsqueeze(1), self.rel, None) if clip > 0 else None

@@ -86,9 +86,17 @@ def test_hdnnp2nd_energy_forces_and_training_gradients():
     o_loss = OM.force_training_loss(o_eng, o_force, torch.tensor(b["energy"], dtype=torch.float64),
                                     torch.tensor(b["force"], dtype=torch.float64))
     o_grads = torch.autograd.grad(o_loss, [params[n] for n, _ in named], allow_unused=True)
-    for (n, _), g, og in zip(named, grads, o_grads):
-        assert rel_err(g.cpu().numpy(), og.numpy()) < RTOL, n
-
+    # the same op chain in fp32 (the "TF-CPU-like" comparand): where fp32 itself cannot reach 1e-5 of the truth
+    # (sums over 36 atoms with cancellation), we must be no worse than twice its error
+    p32 = {k: v.detach().float().requires_grad_(True) for k, v in params.items()}
+    xyz32 = oracle_ragged(b["xyz"], b["node_len"], torch.float32)
+    e32, f32 = OM.energy_force(lambda x: OM.hdnnp2nd_energy(p32, z, x, eij, ijk, cfg["g2_kwargs"], cfg["g4_kwargs"],
+                                                             cfg["mlp_kwargs"]["activation"]), xyz32)
+    l32 = OM.force_training_loss(e32, f32.squeeze(-1), torch.tensor(b["energy"]), torch.tensor(b["force"]))
+    g32 = torch.autograd.grad(l32, [p32[n] for n, _ in named], allow_unused=True)
+    for (n, _), g, og, o32 in zip(named, grads, o_grads, g32):
+        err, err32 = rel_err(g.cpu().numpy(), og.numpy()), rel_err(o32.numpy(), og.numpy())
+        assert err < max(RTOL, 2 * err32), (n, err, err32)
 
 def test_fused_acsf_matches_unfused_chain_and_guards_hessian():
     """Fused G / J^T v / J u kernels vs the op-by-op chain (same GPU), incl. unmapped elements and unsorted triples."""
