@@ -738,3 +738,107 @@ def raw_dense_tc(op, a, b, bias=None):
     check(_lib.lib().kgcnn_dense_tc(op, _ptr(a), _ptr(b), M, K, U, _ptr(bias), _ptr(out), _ptr(ws), nbytes, _stream()),
           "kgcnn_dense_tc")
     return out
+
+
+# ------------------------------------------------------------------------------------------------
+# fused PaiNN message (a14): one multilinear form, three kernels, closed under differentiation
+# ------------------------------------------------------------------------------------------------
+_PM_ORDER = ("gs", "gv", "phi", "v", "w", "r")
+_PM_TERMS = {"gs": 1, "gv": 6, "phi": 7, "v": 2, "w": 7, "r": 4}        # terms of M that contain the operand
+_PM_SLOTS = {"G": ("gs", "gv"), "J": ("phi", "v"), "E": ("w", "r")}     # kernel -> the two derivatives it writes
+
+
+def raw_painn_msg(slot, mask, want_a, want_b, ops, recv, send, F_dim):
+    """(dM/dXa, dM/dXb) for the operand pair of `slot` (csrc/painn.cu); None for an output that is not wanted."""
+    t = {k: (None if x is None else _f32c(x)) for k, x in ops.items()}
+    _need_cuda(*[x for x in t.values() if x is not None])
+    dev = recv.ids.device
+    N, E = recv.n_targets, recv.n_elements
+    L = _lib.lib()
+
+    def new(rows, cols, want):
+        return torch.empty((rows, cols), dtype=torch.float32, device=dev) if want else None
+
+    if slot == "G":
+        a, b = new(N, F_dim, want_a), new(N, 3 * F_dim, want_b)
+        m = mask & ((1 if want_a else 0) | (6 if want_b else 0))
+        check(L.kgcnn_painn_msg_nodes(_ptr(t["phi"]), _ptr(t["v"]), _ptr(t["w"]), _ptr(t["r"]), _ptr(recv.rowptr),
+                                      _ptr(recv.perm), _ptr(recv.permuted_ids(send)), 1 if recv.perm is not None else 0,
+                                      N, E, F_dim, m, _ptr(a), _ptr(b), _stream()), "kgcnn_painn_msg_nodes")
+        if b is not None:
+            b = b.view(N, 3, F_dim)
+    elif slot == "J":
+        a, b = new(N, 3 * F_dim, want_a), new(N, 3 * F_dim, want_b)
+        check(L.kgcnn_painn_msg_senders(_ptr(t["gs"]), _ptr(t["gv"]), _ptr(t["phi"]), _ptr(t["v"]), _ptr(t["w"]),
+                                        _ptr(t["r"]), _ptr(send.rowptr), _ptr(send.perm),
+                                        _ptr(send.permuted_ids(recv)), 1 if send.perm is not None else 0,
+                                        N, E, F_dim, mask, _ptr(a), _ptr(b), _stream()), "kgcnn_painn_msg_senders")
+        if b is not None:
+            b = b.view(N, 3, F_dim)
+    else:
+        a, b = new(E, 3 * F_dim, want_a), new(E, 3, want_b)        # gr of an inactive term 3 is written as zeros
+        check(L.kgcnn_painn_msg_edges(_ptr(t["gs"]), _ptr(t["gv"]), _ptr(t["phi"]), _ptr(t["v"]), _ptr(t["w"]),
+                                      _ptr(t["r"]), _ptr(recv.ids), _ptr(send.ids), E, F_dim, mask, _ptr(a), _ptr(b),
+                                      _stream()), "kgcnn_painn_msg_edges")
+    return a, b
+
+
+class _PainnMsg(torch.autograd.Function):
+    """dM/d(operand pair of `slot`) of the PaiNN message form M(Gs,Gv,Phi,V,W,R) (csrc/painn.cu).  slot 'G' with
+    (Gs,Gv) absent is the layer's forward (ds, dv) of painn_conv.py:104-114.  Because M is linear in every operand,
+    the derivative of any output with respect to any other operand is again such a partial derivative with the
+    cotangent substituted for the differentiated operand: the class is closed under differentiation."""
+
+    @staticmethod
+    def forward(ctx, slot, mask, want_a, want_b, gs, gv, phi, v, w, r, recv, send, F_dim):
+        ctx.slot, ctx.mask, ctx.recv, ctx.send, ctx.F_dim = slot, mask, recv, send, F_dim
+        ctx.save_for_backward(gs, gv, phi, v, w, r)
+        ops = dict(zip(_PM_ORDER, (gs, gv, phi, v, w, r)))
+        a, b = raw_painn_msg(slot, mask, want_a, want_b, ops, recv, send, F_dim)
+        return a, b
+
+    @staticmethod
+    def backward(ctx, ca, cb):
+        ops = dict(zip(_PM_ORDER, ctx.saved_tensors))
+        needs = dict(zip(_PM_ORDER, ctx.needs_input_grad[4:10]))
+        if not COORDINATE_HESSIAN:
+            needs["r"] = False          # r_hat depends on the coordinates only
+        grads = dict.fromkeys(_PM_ORDER)
+        xa, xb = _PM_SLOTS[ctx.slot]
+        subs = []                       # (active terms, operands with the cotangent substituted, replaced names)
+        if ctx.slot == "G":             # Gs and Gv share no term: substitute both at once
+            m, o = 0, dict(ops)
+            if ca is not None:
+                m |= ctx.mask & 1
+                o["gs"] = ca.contiguous()
+            if cb is not None:
+                m |= ctx.mask & 6
+                o["gv"] = cb.contiguous()
+            if m:
+                subs.append((m, o, (xa, xb)))
+        else:
+            for x, c in ((xa, ca), (xb, cb)):
+                m = ctx.mask & _PM_TERMS[x]
+                if c is not None and m:
+                    o = dict(ops)
+                    o[x] = c.contiguous()
+                    subs.append((m, o, (x,)))
+        for m, o, replaced in subs:
+            for slot, (ya, yb) in _PM_SLOTS.items():
+                wa = ya not in replaced and needs[ya] and bool(_PM_TERMS[ya] & m)
+                wb = yb not in replaced and needs[yb] and bool(_PM_TERMS[yb] & m)
+                if not (wa or wb):
+                    continue
+                ra, rb = _PainnMsg.apply(slot, m, wa, wb, o["gs"], o["gv"], o["phi"], o["v"], o["w"], o["r"],
+                                         ctx.recv, ctx.send, ctx.F_dim)
+                for y, res, wanted in ((ya, ra, wa), (yb, rb, wb)):
+                    if wanted:
+                        res = res.reshape(ops[y].shape)
+                        grads[y] = res if grads[y] is None else grads[y] + res
+        return (None, None, None, None) + tuple(grads[k] for k in _PM_ORDER) + (None, None, None)
+
+
+def painn_message(phi, v, w, r, recv, send):
+    """(ds [N,F], dv [N,3,F]) of PAiNNconv (painn_conv.py:104-114) for phi [N,3F], v [N,3,F], w [E,3F], r [E,3]."""
+    F_dim = int(phi.shape[1]) // 3
+    return _PainnMsg.apply("G", 7, True, True, None, None, phi, v, w, r, recv, send, F_dim)

@@ -12,6 +12,7 @@ from ..geom import compute_euclidean_norm
 from ..modules import Dense
 
 KERAS_EPSILON = 1e-7
+FUSED = True      # False: compose the message from the gather / segment primitives (test comparand)
 
 
 @register_keras_serializable(package="kgcnn", name="PAiNNconv")
@@ -48,11 +49,19 @@ class PAiNNconv(GraphBaseLayer):
         if self.cutoff is not None:                                          # :102-103
             w = w * envelope.values
         u = self.units
+        v = equivariant.values
+        if (FUSED and code in (F.OP_SUM, F.OP_MEAN) and u % 4 == 0 and v.dim() == 3 and v.shape[1] == 3 and r_ij.values.shape[-1] == 3):
+            # :100-114 as ONE pass over the edges (csrc/painn.cu): no [E,3F] / [E,3,F] intermediate reaches HBM
+            ds, dv = F.painn_message(s.values, v, w, r_ij.values, recv, send)
+            if code == F.OP_MEAN:
+                inv = recv.inv_count()
+                ds, dv = ds * inv, dv * inv.unsqueeze(-1)
+            return node.with_values(ds), equivariant.with_values(dv)
         s_j = F.gather(s.values, send)                                       # :100
         sw = s_j * w                                                         # :104
         sw1, sw2, sw3 = sw[:, :u], sw[:, u:2 * u], sw[:, 2 * u:]             # :105
         ds = F.segment_reduce(sw1.contiguous(), recv, code)                  # :106
-        vj = F.gather(equivariant.values, send)                              # :107  [E,3,F]
+        vj = F.gather(v, send)                                               # :107  [E,3,F]
         dv = sw2.unsqueeze(-2) * vj + sw3.unsqueeze(-2) * r_ij.values.unsqueeze(-1)   # :108-113
         dv = F.segment_reduce(dv, recv, code)                                # :114
         return node.with_values(ds), equivariant.with_values(dv)

@@ -198,6 +198,31 @@ int kgcnn_acsf_g4(const float* xyz, const int32_t* z_atom, const int32_t* tset_a
                   int mode, const float* cot, float* out, float* triple_out, kgcnn_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * a14  fused PaiNN message (kgcnn/layers/conv/painn_conv.py:97-115) and its derivatives of any order.
+ *   M(Gs,Gv,Phi,V,W,R) = sum_e sum_f  Gs[i,f] P1[j,f] W1[e,f]                         term 1 (mask bit 0)
+ *                                    + sum_c Gv[i,c,f] P2[j,f] V[j,c,f] W2[e,f]        term 2 (mask bit 1)
+ *                                    + sum_c Gv[i,c,f] P3[j,f] W3[e,f] R[e,c]          term 3 (mask bit 2)
+ *   i = receiver, j = sender of edge e; Phi = (P1|P2|P3) [N,3F]; W = (W1|W2|W3) [E,3F]; V, Gv [N,3,F]; Gs [N,F];
+ *   R [E,3].  F % 4 == 0, all float pointers 16 B aligned.  Operands of inactive terms may be NULL; output blocks
+ *   of inactive terms are written as zeros; a NULL output is skipped.
+ *   _nodes   : (ds, dv)   = dM/d(Gs, Gv)   the layer's forward; rowptr/perm = CSR of the RECEIVER relation,
+ *                                          nbr = sender ids (in CSR order when nbr_permuted)
+ *   _senders : (gphi, gvv) = dM/d(Phi, V)  rowptr/perm = CSR of the SENDER relation, nbr = receiver ids
+ *   _edges   : (gw, gr)   = dM/d(W, R)     recv/send = the two id columns in the original edge order
+ * ------------------------------------------------------------------------------------------- */
+int kgcnn_painn_msg_nodes(const float* phi, const float* v, const float* w, const float* r, const int32_t* rowptr,
+                          const int32_t* perm /*nullable*/, const int32_t* nbr, int nbr_permuted, int64_t N,
+                          int64_t E, int F, int mask, float* ds /*nullable*/, float* dv /*nullable*/,
+                          kgcnn_stream_t stream);
+int kgcnn_painn_msg_senders(const float* gs, const float* gv, const float* phi, const float* v, const float* w,
+                            const float* r, const int32_t* rowptr, const int32_t* perm /*nullable*/,
+                            const int32_t* nbr, int nbr_permuted, int64_t N, int64_t E, int F, int mask,
+                            float* gphi /*nullable*/, float* gvv /*nullable*/, kgcnn_stream_t stream);
+int kgcnn_painn_msg_edges(const float* gs, const float* gv, const float* phi, const float* v, const float* w,
+                          const float* r, const int32_t* recv, const int32_t* send, int64_t E, int F, int mask,
+                          float* gw /*nullable*/, float* gr /*nullable*/, kgcnn_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
  * optimizer of the force_*.py drivers (force_schnet.py:196-203): Keras Adam with per-variable clipnorm on one
  * flat parameter buffer.  sumsq[var] = sum of squared gradients of variable var (from the segment kernel with
  * rowptr = variable offsets), var_of[i] = variable of element i, *step = device-resident step counter.
