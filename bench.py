@@ -410,7 +410,8 @@ def gss_roofline(device, iters=10):
     ms_l = _time_gms_pair(x, torch.randn(N, 64, device=device), recv, send, iters)
     bytes_l = gss_bytes(E, N, 64) / 2
     ach_l = bytes_l / (ms_l * 1e-3) / 1e9
-    return {"bound": "hbm", "achieved": ach_r, "peak": peak, "unit": "GB/s", "frac": ach_r / peak, "traffic": None,
+    return {"bound": "hbm", "achieved": ach_r, "peak": peak, "unit": "GB/s", "frac": ach_r / peak,
+            "traffic": 16.29e9,   # ncu --set full: dram read 15.27 GB + write 1.02 GB per launch (profiles/r1_gms_full_v3.csv)
             "kernel": "gms_kernel (fused gather*w -> CSR segment-sum), mean of the fwd and bwd launch",
             "workload": "GSS-R (N=%d, E=%d uniform random senders, F=%d): gathered rows miss L2" % (n, e_r, feat),
             "algorithmic_bytes_per_launch": bytes_r, "ms_per_launch": ms_r, "peak_source": peak_src,
