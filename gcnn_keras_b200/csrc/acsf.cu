@@ -52,7 +52,8 @@ acsf_g2_kernel(const float* __restrict__ xyz, const int32_t* __restrict__ rel_at
                const int32_t* __restrict__ tset_atom, const int32_t* __restrict__ rowptr,
                const int32_t* __restrict__ perm, const int32_t* __restrict__ send, int send_permuted,
                const float* __restrict__ table, int R, int m, float eps, int64_t N,
-               const float* __restrict__ cot, float* __restrict__ out, float* __restrict__ edge_out) {
+               const float* __restrict__ weight, const float* __restrict__ cot, float* __restrict__ out,
+               float* __restrict__ edge_out) {
   __shared__ float acc_s[kWarpsPerBlock][kMaxAcc];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int64_t i = static_cast<int64_t>(blockIdx.x) * kWarpsPerBlock + warp;
@@ -77,6 +78,7 @@ acsf_g2_kernel(const float* __restrict__ xyz, const int32_t* __restrict__ rel_at
     if (r >= 0 && r < R && centre_ok) {               // unmapped neighbour elements contribute nothing
       const V3 v = sub(xi, ld3(xyz + 3 * j));
       const float d = norm_ref(v, eps);
+      const float we = weight ? __ldg(weight + e) : 1.f;     // wACSF: g(Z_j) or an external pair weight
       float ddot = 0.f;
       if (MODE == kJvp) ddot = dot(v, sub(ui, ld3(cot + 3 * j))) / d;
       float a = 0.f;                                   // VJP: sum_k dG * dphi/dd
@@ -87,9 +89,9 @@ acsf_g2_kernel(const float* __restrict__ xyz, const int32_t* __restrict__ rel_at
         cutoff(d, rc, f, df);
         const float t = d - mu;
         const float g = expf(-eta * t * t);
-        if (MODE == kFwd) acc[r * m + k] += g * f;
+        if (MODE == kFwd) acc[r * m + k] += we * g * f;
         else {
-          const float dphi = g * (-2.f * eta * t * f + df);
+          const float dphi = we * g * (-2.f * eta * t * f + df);
           if (MODE == kVjp) a += acc[r * m + k] * dphi;
           else acc[r * m + k] += dphi * ddot;
         }
@@ -126,6 +128,7 @@ acsf_g4_kernel(const float* __restrict__ xyz, const int32_t* __restrict__ z_atom
                const int32_t* __restrict__ rowptr, const int32_t* __restrict__ perm,
                const int32_t* __restrict__ idx_j, const int32_t* __restrict__ idx_k,
                const float* __restrict__ table, int R, int m, float eps, float inv_mult, int uniform_rc, int64_t N,
+               const float* __restrict__ mu_tab, const float* __restrict__ weight,
                const float* __restrict__ cot, float* __restrict__ out, float* __restrict__ triple_out) {
   __shared__ float acc_s[kWarpsPerBlock][kMaxAcc];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -140,6 +143,8 @@ acsf_g4_kernel(const float* __restrict__ xyz, const int32_t* __restrict__ z_atom
   V3 ui = {0.f, 0.f, 0.f};
   if (MODE == kJvp) ui = ld3(cot + 3 * i);
   const float* tab_i = table + (tset_atom ? static_cast<int64_t>(max(__ldg(tset_atom + i), 0)) * RM * 4 : 0);
+  const float* mu_i = mu_tab ? mu_tab + (tset_atom ? static_cast<int64_t>(max(__ldg(tset_atom + i), 0)) * RM : 0)
+                             : nullptr;
   const bool centre_ok = !tset_atom || __ldg(tset_atom + i) >= 0;
   V3 gi = {0.f, 0.f, 0.f};
   const int beg = __ldg(rowptr + i), end = __ldg(rowptr + i + 1);
@@ -157,6 +162,7 @@ acsf_g4_kernel(const float* __restrict__ xyz, const int32_t* __restrict__ z_atom
       const float inv = 1.f / (rij * rik);
       const float c = dot(vij, vik) / rij / rik;                       // acsf_conv.py:439
       const float r2 = rij * rij + rik * rik + rjk * rjk;
+      const float wt = (weight ? __ldg(weight + e) : 1.f) * inv_mult;    // wACSF: h(Z_j, Z_k) or external
       // d cos / d vij = vik/(rij rik) - c vij/rij^2 ;  d cos / d vik = vij/(rij rik) - c vik/rik^2
       const V3 dc_ij = axpy(-c / (rij * rij), vij, scale(inv, vik));
       const V3 dc_ik = axpy(-c / (rik * rik), vik, scale(inv, vij));
@@ -188,10 +194,13 @@ acsf_g4_kernel(const float* __restrict__ xyz, const int32_t* __restrict__ z_atom
         // (1 + lambda cos)^zeta as exp2(zeta log2(base)); base is clamped at 0 (it can only be negative by
         // rounding of cos) -> 0^zeta = 0 like pow
         const float base = fmaxf(c * lam + 1.f, 0.f);
-        const float pre = exp2f(1.f - zeta) * inv_mult;
+        const float pre = exp2f(1.f - zeta) * wt;
+        // wACSF shifts the three Gaussians by mu (wacsf_conv.py:277-281); ACSF G4 has mu = 0
+        const float mu = mu_i ? __ldg(mu_i + r * m + q) : 0.f;
+        const float sij = rij - mu, sik = rik - mu, sjk = rjk - mu;
         const float pw = (base > 0.f) ? exp2f(zeta * log2f(base)) : (zeta == 0.f ? 1.f : 0.f);
         const float A = pre * pw;
-        const float E = expf(-eta * r2);
+        const float E = expf(-eta * (mu_i ? sij * sij + sik * sik + sjk * sjk : r2));
         const float fff = fij * fik * fjk;
         if (MODE == kFwd) {
           acc[r * m + q] += A * E * fff;
@@ -199,9 +208,9 @@ acsf_g4_kernel(const float* __restrict__ xyz, const int32_t* __restrict__ z_atom
           const float pw1 = (base > 0.f) ? pw / base : (zeta == 1.f ? 1.f : 0.f);   // base^(zeta-1)
           const float dA = pre * zeta * lam * pw1;                      // dA / dcos
           // d rep / d r_ab = A (dE/dr_ab fff + E f'_ab f f)
-          const float d_ij = A * E * (-2.f * eta * rij * fff + dfij * fik * fjk);
-          const float d_ik = A * E * (-2.f * eta * rik * fff + fij * dfik * fjk);
-          const float d_jk = A * E * (-2.f * eta * rjk * fff + fij * fik * dfjk);
+          const float d_ij = A * E * (-2.f * eta * sij * fff + dfij * fik * fjk);
+          const float d_ik = A * E * (-2.f * eta * sik * fff + fij * dfik * fjk);
+          const float d_jk = A * E * (-2.f * eta * sjk * fff + fij * fik * dfjk);
           const float d_c = dA * E * fff;
           if (MODE == kVjp) {
             const float g = acc[r * m + q];
@@ -243,8 +252,8 @@ extern "C" {
 
 int kgcnn_acsf_g2(const float* xyz, const int32_t* rel_atom, const int32_t* tset_atom, const int32_t* rowptr,
                   const int32_t* perm, const int32_t* send, int send_permuted, const float* table, int R, int m,
-                  float eps, int64_t N, int mode, const float* cot, float* out, float* edge_out,
-                  kgcnn_stream_t stream) {
+                  float eps, int64_t N, const float* weight, int mode, const float* cot, float* out,
+                  float* edge_out, kgcnn_stream_t stream) {
   if (N < 0 || R <= 0 || m <= 0 || mode < kFwd || mode > kJvp) return KGCNN_E_INVALID;
   if (R * m > kMaxAcc) return KGCNN_E_UNSUPPORTED;
   if (N == 0) return KGCNN_OK;
@@ -254,7 +263,7 @@ int kgcnn_acsf_g2(const float* xyz, const int32_t* rel_atom, const int32_t* tset
   const unsigned grid = static_cast<unsigned>(ceil_div<int64_t>(N, kWarpsPerBlock));
   cudaStream_t st = as_stream(stream);
 #define KGCNN_G2(M) acsf_g2_kernel<M><<<grid, kWarpsPerBlock * 32, 0, st>>>(xyz, rel_atom, tset_atom, rowptr, perm, \
-    send, send_permuted, table, R, m, eps, N, cot, out, edge_out)
+    send, send_permuted, table, R, m, eps, N, weight, cot, out, edge_out)
   if (mode == kFwd) KGCNN_G2(kFwd); else if (mode == kVjp) KGCNN_G2(kVjp); else KGCNN_G2(kJvp);
 #undef KGCNN_G2
   return finish_launch();
@@ -263,7 +272,8 @@ int kgcnn_acsf_g2(const float* xyz, const int32_t* rel_atom, const int32_t* tset
 int kgcnn_acsf_g4(const float* xyz, const int32_t* z_atom, const int32_t* tset_atom, const int32_t* rev_pair,
                   int zmax, const int32_t* rowptr, const int32_t* perm, const int32_t* idx_j, const int32_t* idx_k,
                   const float* table, int R, int m, float eps, float multiplicity, int uniform_rc, int64_t N,
-                  int mode, const float* cot, float* out, float* triple_out, kgcnn_stream_t stream) {
+                  const float* mu_table, const float* weight, int mode, const float* cot, float* out,
+                  float* triple_out, kgcnn_stream_t stream) {
   if (N < 0 || R <= 0 || m <= 0 || zmax <= 0 || mode < kFwd || mode > kJvp) return KGCNN_E_INVALID;
   if (R * m > kMaxAcc) return KGCNN_E_UNSUPPORTED;
   if (N == 0) return KGCNN_OK;
@@ -275,7 +285,7 @@ int kgcnn_acsf_g4(const float* xyz, const int32_t* z_atom, const int32_t* tset_a
   const unsigned grid = static_cast<unsigned>(ceil_div<int64_t>(N, kWarpsPerBlock));
   cudaStream_t st = as_stream(stream);
 #define KGCNN_G4(M) acsf_g4_kernel<M><<<grid, kWarpsPerBlock * 32, 0, st>>>(xyz, z_atom, tset_atom, rev_pair, zmax, \
-    rowptr, perm, idx_j, idx_k, table, R, m, eps, inv_mult, uniform_rc, N, cot, out, triple_out)
+    rowptr, perm, idx_j, idx_k, table, R, m, eps, inv_mult, uniform_rc, N, mu_table, weight, cot, out, triple_out)
   if (mode == kFwd) KGCNN_G4(kFwd); else if (mode == kVjp) KGCNN_G4(kVjp); else KGCNN_G4(kJvp);
 #undef KGCNN_G4
   return finish_launch();

@@ -619,8 +619,10 @@ class ACSFSpec:
     """Per-batch constants of one ACSF layer call (index relations, element maps, parameter table)."""
 
     def __init__(self, kind, rel_centre, table, R, m, eps, rel_atom=None, tset_atom=None, rel_send=None,
-                 z_atom=None, rev_pair=None, zmax=31, rel_j=None, rel_k=None, multiplicity=0.0, uniform_rc=False):
+                 z_atom=None, rev_pair=None, zmax=31, rel_j=None, rel_k=None, multiplicity=0.0, uniform_rc=False,
+                 weight=None, mu_table=None):
         self.uniform_rc = uniform_rc
+        self.weight, self.mu_table = weight, mu_table      # wACSF: per-pair/triple factor, Gaussian shifts
         self.kind, self.rel_centre, self.table, self.R, self.m, self.eps = kind, rel_centre, table, R, m, eps
         self.rel_atom, self.tset_atom, self.rel_send = rel_atom, tset_atom, rel_send
         self.z_atom, self.rev_pair, self.zmax, self.rel_j, self.rel_k = z_atom, rev_pair, zmax, rel_j, rel_k
@@ -641,15 +643,15 @@ def raw_acsf(xyz, spec, mode, cot=None):
         send = rc.permuted_ids(spec.rel_send)
         check(_lib.lib().kgcnn_acsf_g2(_ptr(xyz), _ptr(spec.rel_atom), _ptr(spec.tset_atom), _ptr(rc.rowptr),
                                        _ptr(rc.perm), _ptr(send), 1 if rc.perm is not None else 0, _ptr(spec.table),
-                                       spec.R, spec.m, spec.eps, N, mode, _ptr(cot), _ptr(out), _ptr(edge_out),
-                                       _stream()), "kgcnn_acsf_g2")
+                                       spec.R, spec.m, spec.eps, N, _ptr(spec.weight), mode, _ptr(cot), _ptr(out),
+                                       _ptr(edge_out), _stream()), "kgcnn_acsf_g2")
         return out, edge_out
     A = rc.n_elements
     tri = torch.empty((A, 2, 3), dtype=torch.float32, device=xyz.device) if mode == 1 else None
     check(_lib.lib().kgcnn_acsf_g4(_ptr(xyz), _ptr(spec.z_atom), _ptr(spec.tset_atom), _ptr(spec.rev_pair), spec.zmax,
                                    _ptr(rc.rowptr), _ptr(rc.perm), _ptr(spec.rel_j.ids), _ptr(spec.rel_k.ids),
                                    _ptr(spec.table), spec.R, spec.m, spec.eps, float(spec.multiplicity or 0.0),
-                                   1 if spec.uniform_rc else 0, N, mode,
+                                   1 if spec.uniform_rc else 0, N, _ptr(spec.mu_table), _ptr(spec.weight), mode,
                                    _ptr(cot), _ptr(out), _ptr(tri), _stream()), "kgcnn_acsf_g4")
     return out, tri
 

@@ -187,15 +187,22 @@ int kgcnn_dense_tc(int op, const float* A, const float* B, int64_t M, int K, int
  *   rowptr/perm  : CSR of the pairs / triples by centre atom; table: [T][R][m][3] (eta, mu, Rc) / [T][R][m][4]
  *   (eta, zeta, lambda, Rc); eps: added under the square root when add_eps (else 0); uniform_rc != 0 promises
  *   that every table entry has the same Rc (the three cutoffs are then evaluated once per triple).
+ * a17  weighted ACSF (kgcnn/layers/conv/wacsf_conv.py:195-203 wACSFRad, :325-356 wACSFAng) runs through the same
+ *   kernels with R = 1, tset_atom = Z_i (parameters looked up by the CENTRE atom) and
+ *   weight[M | A]  : nullable per-pair / per-triple factor in the ORIGINAL order (g(Z_j) = Z_j, h = Z_j Z_k, or the
+ *                    layer's external weights);
+ *   mu_table       : nullable [T][R][m]; shifts the three Gaussians of the angular function,
+ *                    exp(-eta ((r_ij-mu)^2 + (r_ik-mu)^2 + (r_jk-mu)^2))  (wacsf_conv.py:277-281); null = ACSF G4.
  * ------------------------------------------------------------------------------------------- */
 int kgcnn_acsf_g2(const float* xyz, const int32_t* rel_atom, const int32_t* tset_atom, const int32_t* rowptr,
                   const int32_t* perm, const int32_t* send, int send_permuted, const float* table, int R, int m,
-                  float eps, int64_t N, int mode, const float* cot, float* out, float* edge_out,
-                  kgcnn_stream_t stream);
+                  float eps, int64_t N, const float* weight, int mode, const float* cot, float* out,
+                  float* edge_out, kgcnn_stream_t stream);
 int kgcnn_acsf_g4(const float* xyz, const int32_t* z_atom, const int32_t* tset_atom, const int32_t* rev_pair,
                   int zmax, const int32_t* rowptr, const int32_t* perm, const int32_t* idx_j, const int32_t* idx_k,
                   const float* table, int R, int m, float eps, float multiplicity, int uniform_rc, int64_t N,
-                  int mode, const float* cot, float* out, float* triple_out, kgcnn_stream_t stream);
+                  const float* mu_table, const float* weight, int mode, const float* cot, float* out,
+                  float* triple_out, kgcnn_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
  * a14  fused PaiNN message (kgcnn/layers/conv/painn_conv.py:97-115) and its derivatives of any order.

@@ -240,3 +240,65 @@ def acsf_g4(z, xyz, ijk, eta_zeta_lambda_rc, element_mapping, multiplicity=None,
     pooled = L.relational_pooling_local_edges(xyz, ijk.with_values(rep), ijk, ijk.with_values(zjk_map),
                                               num_relations, "sum")   # :493
     return xyz.with_values(pooled.values.reshape(pooled.values.shape[0], -1))   # :494
+
+
+# ------------------------------------------------------------------------------------------------------
+# weighted ACSF (kgcnn/layers/conv/wacsf_conv.py).  Parity unpinned in the reference (no numeric test);
+# checked by fp64 gradcheck / finite-difference forces in tests/test_oracle_props.py.
+# ------------------------------------------------------------------------------------------------------
+def _wacsf_fc(r, cutoff):
+    """wACSFRad._compute_fc, wacsf_conv.py:146-151."""
+    fc = torch.clamp(r, -cutoff, cutoff)
+    return (torch.cos(fc * np.pi / cutoff) + 1.0) * 0.5
+
+
+def wacsf_rad(z, xyz, eij, eta_mu, cutoff=8.0, add_eps=False, w=None):
+    """wACSFRad.call, wacsf_conv.py:165-203.  eta_mu: (n_elements_max, m, 2) looked up by the CENTRE atom Z_i."""
+    dtype = xyz.values.dtype
+    table = torch.as_tensor(np.asarray(eta_mu), dtype=dtype)
+    zr = z.with_values(z.values.to(torch.int64))                       # :185
+    if w is None:
+        zj = L.gather_nodes_outgoing(zr, eij)                          # :186
+        wv = zj.values.reshape(-1, 1).to(dtype)                        # :187-188
+    else:
+        wv = w.values.reshape(-1, 1).to(dtype)
+    xi, xj = L.node_position(xyz, eij)                                 # :191
+    rij = L.node_distance_euclidean(xi, xj, add_eps=add_eps).values    # :192
+    fc = _wacsf_fc(rij, cutoff)                                        # :193
+    zi = L.gather_nodes_ingoing(zr, eij).values                        # :194
+    params = table[zi]                                                 # :154
+    eta, mu = params[..., 0], params[..., 1]                           # :157
+    gij = torch.exp(-(torch.square(rij - mu) * eta))                   # :158-159
+    rep = gij * fc * wv                                                # :196
+    return L.pooling_local_edges(xyz, eij.with_values(rep), eij, pooling_method="sum")   # :197
+
+
+def wacsf_ang(z, xyz, ijk, eta_mu_lambda_zeta, cutoff=8.0, add_eps=False, w=None):
+    """wACSFAng.call, wacsf_conv.py:305-356.  Table (n_elements_max, m, 4) = (eta, mu, lambda, zeta) by Z_i."""
+    dtype = xyz.values.dtype
+    table = torch.as_tensor(np.asarray(eta_mu_lambda_zeta), dtype=dtype)
+    zr = z.with_values(z.values.to(torch.int64))
+    if w is None:
+        _, zj, zk = L.gather_embedding_selection(zr, ijk, [0, 1, 2])   # :332-333
+        wv = (zj.values.to(dtype) * zk.values.to(dtype)).reshape(-1, 1)   # :334-337
+    else:
+        wv = w.values.reshape(-1, 1).to(dtype)
+    xi, xj, xk = L.node_position(xyz, ijk, [0, 1, 2])                  # :339
+    rij = L.node_distance_euclidean(xi, xj, add_eps=add_eps).values    # :340-342
+    rik = L.node_distance_euclidean(xi, xk, add_eps=add_eps).values
+    rjk = L.node_distance_euclidean(xj, xk, add_eps=add_eps).values
+    fij, fik, fjk = _wacsf_fc(rij, cutoff), _wacsf_fc(rik, cutoff), _wacsf_fc(rjk, cutoff)   # :343-345
+    zi = L.gather_nodes_ingoing(zr, ijk).values                        # :346
+    params = table[zi]                                                 # [A,m,4]
+    eta, mu, lamda, zeta = params[..., 0], params[..., 1], params[..., 2], params[..., 3]
+    gij = torch.exp(-(torch.square(rij - mu) * eta))                   # :347-349 (:277-281)
+    gik = torch.exp(-(torch.square(rik - mu) * eta))
+    gjk = torch.exp(-(torch.square(rjk - mu) * eta))
+    vij = xi.values - xj.values                                        # :350-351
+    vik = xi.values - xk.values
+    cos_theta = torch.sum(vij * vik, dim=-1, keepdim=True) / rij / rik   # :288
+    pow_cos = torch.pow(cos_theta * lamda + 1.0, zeta)                 # :289-290
+    rep = pow_cos * gij * gik * gjk * fij * fik * fjk * wv             # :353
+    pooled = L.pooling_local_edges(xyz, ijk.with_values(rep), ijk, pooling_method="sum").values   # :354
+    zeta_n = table[zr.values][..., 3]                                  # _compute_pow_scale :294-302
+    return xyz.with_values(torch.pow(torch.ones_like(pooled) * 2.0, 1.0 - zeta_n) * pooled)   # :356

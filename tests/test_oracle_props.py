@@ -97,3 +97,51 @@ def test_schnet_oracle_energy_is_rotation_and_translation_invariant():
     rot = xyz.with_values(xyz.values @ torch.tensor(q) + torch.tensor([0.3, -1.0, 2.0]))
     with torch.no_grad():
         assert torch.allclose(energy_fn(xyz), energy_fn(rot), atol=1e-10)
+
+
+def _wacsf_case(seed=0):
+    rng = np.random.default_rng(seed)
+    n = 6
+    xyz = rng.uniform(0.0, 3.0, size=(n, 3))
+    z = np.array([1, 6, 8, 1, 7, 6])
+    eij = np.array([[i, j] for i in range(n) for j in range(n) if i != j])
+    ijk = np.array([[i, j, k] for i in range(n) for j in range(n) for k in range(n) if len({i, j, k}) == 3][::3])
+    return z, xyz, eij, ijk
+
+
+def test_wacsf_oracle_brute_force_formula_and_gradcheck():
+    # wacsf_conv.py docstrings: W_rad_i = sum_j Z_j exp(-eta (r_ij-mu)^2) fc ;  W_ang_i = 2^(1-zeta) sum_jk Z_j Z_k
+    # (1 + lambda cos)^zeta exp(-eta sum (r-mu)^2) fc fc fc  -- restated here with Python loops (small case)
+    z, xyz, eij, ijk = _wacsf_case()
+    rng = np.random.default_rng(1)
+    rad = np.zeros((118, 3, 2))
+    rad[..., 0], rad[..., 1] = rng.uniform(0.5, 2, (118, 3)), rng.uniform(0.5, 3, (118, 3))
+    ang = np.zeros((118, 2, 4))
+    ang[..., 0], ang[..., 1] = rng.uniform(0.05, 0.5, (118, 2)), rng.uniform(0, 1, (118, 2))
+    ang[..., 2], ang[..., 3] = rng.choice([-1.0, 1.0], (118, 2)), rng.choice([1.0, 2.0, 3.0], (118, 2))
+    zr = oracle_ragged(z, [len(z)])
+    xr = oracle_ragged(xyz, [len(z)], torch.float64)
+    fc = lambda r: 0.5 * (np.cos(np.pi * min(r, 8.0) / 8.0) + 1)
+    want_r = np.zeros((len(z), 3))
+    for i, j in eij:
+        r = np.linalg.norm(xyz[i] - xyz[j])
+        want_r[i] += z[j] * np.exp(-rad[z[i], :, 0] * (r - rad[z[i], :, 1]) ** 2) * fc(r)
+    got_r = OC.wacsf_rad(zr, xr, oracle_ragged(eij, [len(eij)]), rad).values.numpy()
+    assert np.allclose(got_r, want_r, rtol=1e-12, atol=1e-14)
+    want_a = np.zeros((len(z), 2))
+    for i, j, k in ijk:
+        vij, vik = xyz[i] - xyz[j], xyz[i] - xyz[k]
+        rij, rik, rjk = np.linalg.norm(vij), np.linalg.norm(vik), np.linalg.norm(xyz[j] - xyz[k])
+        eta, mu, lam, zeta = (ang[z[i], :, c] for c in range(4))
+        cos = vij @ vik / rij / rik
+        want_a[i] += (z[j] * z[k] * (1 + lam * cos) ** zeta * fc(rij) * fc(rik) * fc(rjk)
+                      * np.exp(-eta * ((rij - mu) ** 2 + (rik - mu) ** 2 + (rjk - mu) ** 2)))
+    want_a *= 2.0 ** (1 - ang[z, :, 3])
+    got_a = OC.wacsf_ang(zr, xr, oracle_ragged(ijk, [len(ijk)]), ang).values.numpy()
+    assert np.allclose(got_a, want_a, rtol=1e-12, atol=1e-14)
+
+    x = torch.tensor(xyz, dtype=torch.float64, requires_grad=True)
+    f_r = lambda t: OC.wacsf_rad(zr, xr.with_values(t), oracle_ragged(eij, [len(eij)]), rad).values
+    f_a = lambda t: OC.wacsf_ang(zr, xr.with_values(t), oracle_ragged(ijk, [len(ijk)]), ang).values
+    assert torch.autograd.gradcheck(f_r, (x,))
+    assert torch.autograd.gradcheck(f_a, (x,))
