@@ -159,11 +159,13 @@ __device__ __forceinline__ void store_transposed(const float4 (&v)[kLd], int nch
 }
 
 // One CTA = one 128-row output tile (NN / NT) or one (128-feature tile, split of the rows) (TN).
+// (bx, by, bz) are the tile coordinates (blockIdx of the single-problem kernel; looked up per problem by the grouped
+// TN kernel).  colsum_part (TN only, nullable): this split's column sums of G, written by the a0 == 0 tile.
 template <int OP>
-__global__ void __launch_bounds__(kThreads)
-dense_tc_kernel(const float* __restrict__ A, const float* __restrict__ B, int64_t M, int K, int U,
-                const float* __restrict__ bias, float* __restrict__ out, int64_t rows_per_split, int vec_a,
-                int vec_b) {
+__device__ __forceinline__ void
+dense_tc_body(const float* __restrict__ A, const float* __restrict__ B, int64_t M, int K, int U,
+              const float* __restrict__ bias, float* __restrict__ out, int64_t rows_per_split, int vec_a,
+              int vec_b, int bx, int by, int bz, float* __restrict__ colsum_part) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ __align__(8) uint64_t mbar;
   __shared__ uint32_t tmem_base_s;
@@ -179,11 +181,11 @@ dense_tc_kernel(const float* __restrict__ A, const float* __restrict__ B, int64_
   //   NT: D[rows m0.., cols n0..] = sum_u G[m,u] W[n,u]        reduction over U; n indexes rows of W (K of them)
   //   TN: D[feat a0.., cols n0..] = sum_rows X[row,a] G[row,n] reduction over the rows of this split
   const int n_total = (OP == kNN) ? U : (OP == kNT ? K : U);
-  const int n0 = blockIdx.y * kMaxN;
+  const int n0 = by * kMaxN;
   const int nt = min(kMaxN, ((n_total - n0 + 15) / 16) * 16);        // MMA N (multiple of 16, zero padded)
-  const int64_t m0 = (OP == kTN) ? 0 : static_cast<int64_t>(blockIdx.x) * kBM;
-  const int a0 = (OP == kTN) ? blockIdx.x * kBM : 0;
-  const int64_t row_beg = (OP == kTN) ? static_cast<int64_t>(blockIdx.z) * rows_per_split : 0;
+  const int64_t m0 = (OP == kTN) ? 0 : static_cast<int64_t>(bx) * kBM;
+  const int a0 = (OP == kTN) ? bx * kBM : 0;
+  const int64_t row_beg = (OP == kTN) ? static_cast<int64_t>(bz) * rows_per_split : 0;
   const int64_t row_end = (OP == kTN) ? min(M, row_beg + rows_per_split) : 0;
   const int64_t red_len = (OP == kNN) ? K : (OP == kNT ? U : (row_end > row_beg ? row_end - row_beg : 0));
 
@@ -255,6 +257,8 @@ dense_tc_kernel(const float* __restrict__ A, const float* __restrict__ B, int64_
   };
   uint32_t parity = 0;
   bool first = true;
+  const bool do_colsum = (OP == kTN) && colsum_part != nullptr && a0 == 0;     // CTA-uniform
+  float csum = 0.f;
   if (red_len > 0) load_chunk(0);
   for (int64_t k0 = 0; k0 < red_len; k0 += kKC) {
     // ---- split (hi / lo) and store this chunk ----
@@ -293,8 +297,18 @@ dense_tc_kernel(const float* __restrict__ A, const float* __restrict__ B, int64_
     }
     first = false;
     if (k0 + kKC < red_len) load_chunk(k0 + kKC);      // next chunk's global loads fly while the MMAs run
+    if (OP == kTN && do_colsum && threadIdx.x >= 128 && static_cast<int>(threadIdx.x) - 128 < nt) {
+      // bias gradient from the staged G planes (hi + lo = g to 2^-23): feature n = threadIdx.x - 128, 64 rows
+      const int n = threadIdx.x - 128;
+#pragma unroll 4
+      for (int c = 0; c < kKC / 4; ++c) {
+        const float4 h = b_hi[c * NRP + n], l = b_lo[c * NRP + n];
+        csum += ((h.x + l.x) + (h.y + l.y)) + ((h.z + l.z) + (h.w + l.w));
+      }
+    }
     mbar_wait(bar, parity);                             // MMAs of this chunk are done: planes may be overwritten
     parity ^= 1;
+    if (OP == kTN && do_colsum) __syncthreads();        // the column-sum readers are done with the planes too
     if ((k0 + kKC) % kFlush == 0 || k0 + kKC >= red_len) {
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       drain();
@@ -316,7 +330,7 @@ dense_tc_kernel(const float* __restrict__ A, const float* __restrict__ B, int64_
     if (OP == kTN) {
       const int feat = a0 + d_row;
       row_ok = feat < K;
-      o = out + (static_cast<int64_t>(blockIdx.z) * K + feat) * U + n0 + c0;
+      o = out + (static_cast<int64_t>(bz) * K + feat) * U + n0 + c0;
     } else {
       const int64_t row = m0 + d_row;
       row_ok = row < M;
@@ -345,6 +359,10 @@ dense_tc_kernel(const float* __restrict__ A, const float* __restrict__ B, int64_
       }
     }
   }
+  if (OP == kTN && do_colsum && threadIdx.x >= 128 && static_cast<int>(threadIdx.x) - 128 < nt) {
+    const int col = n0 + static_cast<int>(threadIdx.x) - 128;
+    if (col < U) colsum_part[static_cast<int64_t>(bz) * U + col] = csum;
+  }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
   if (warp == 0) {
@@ -352,6 +370,15 @@ dense_tc_kernel(const float* __restrict__ A, const float* __restrict__ B, int64_
                  "r"(static_cast<uint32_t>(kMaxN))
                  : "memory");
   }
+}
+
+template <int OP>
+__global__ void __launch_bounds__(kThreads)
+dense_tc_kernel(const float* __restrict__ A, const float* __restrict__ B, int64_t M, int K, int U,
+                const float* __restrict__ bias, float* __restrict__ out, int64_t rows_per_split, int vec_a,
+                int vec_b) {
+  dense_tc_body<OP>(A, B, M, K, U, bias, out, rows_per_split, vec_a, vec_b, blockIdx.x, blockIdx.y, blockIdx.z,
+                    nullptr);
 }
 
 __global__ void __launch_bounds__(256)
@@ -370,6 +397,94 @@ tn_split_reduce_kernel(const float* __restrict__ partial, int S, int64_t n, floa
   out[i] = (s0 + s1) + (s2 + s3);
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Grouped weight gradients: all (dW, db) += (X^T G, colsum G) products of one backward sweep in TWO launches.
+// The problems are independent leaves of the backward graph, so the host defers them and hands over the list;
+// CTA -> (problem, feature tile, column tile, row split) through a prefix table passed BY VALUE (baked into a CUDA
+// graph node; nothing is read from host memory at replay).  Partials go to the workspace and are summed in a
+// fixed order (deterministic); several problems may target the same dW (a weight used by the forward Linear and by
+// the force's g W^T): the reduce kernel walks outputs, not problems, so there is no write race.
+// ---------------------------------------------------------------------------------------------------------
+constexpr int kMaxGroup = 64;
+
+struct TnProblem {          // 64 bytes
+  const float* X;           // [M, K]
+  const float* G;           // [M, U]
+  int64_t M;
+  int64_t ws_off;           // float offset of this problem's partials: [splits][K*U] then [splits][U]
+  int32_t K, U;
+  int32_t splits;
+  int32_t rows_per_split;
+  int32_t cta_begin;        // first CTA of this problem in the grouped grid
+  int32_t tiles_k, tiles_u;
+  int32_t want_colsum;
+};
+struct TnOutput {           // 40 bytes: one (dW, db) pair = a contiguous run of problems
+  float* dW;                // [K, U], accumulated into
+  float* db;                // [U] or null
+  int64_t elem_begin;       // first element of this output in the reduce kernel's index space
+  int32_t first, count;     // problems [first, first + count)
+  int32_t K, U;
+};
+struct TnGroup {
+  int32_t n_problems, n_outputs, total_ctas, pad;
+  int64_t total_elems;
+  TnProblem p[kMaxGroup];
+  TnOutput o[kMaxGroup];
+};
+
+__global__ void __launch_bounds__(kThreads)
+tn_grouped_kernel(const __grid_constant__ TnGroup grp, float* __restrict__ ws) {
+  __shared__ int which;
+  if (threadIdx.x == 0) {
+    int lo = 0, hi = grp.n_problems - 1;                  // last problem with cta_begin <= blockIdx.x
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (grp.p[mid].cta_begin <= static_cast<int>(blockIdx.x)) lo = mid; else hi = mid - 1;
+    }
+    which = lo;
+  }
+  __syncthreads();
+  const TnProblem& pr = grp.p[which];
+  int t = static_cast<int>(blockIdx.x) - pr.cta_begin;
+  const int bx = t % pr.tiles_k; t /= pr.tiles_k;
+  const int by = t % pr.tiles_u; t /= pr.tiles_u;
+  const int bz = t;
+  auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
+  float* partial = ws + pr.ws_off;
+  float* cpart = pr.want_colsum ? partial + static_cast<int64_t>(pr.splits) * pr.K * pr.U : nullptr;
+  dense_tc_body<kTN>(pr.X, pr.G, pr.M, pr.K, pr.U, nullptr, partial, pr.rows_per_split,
+                     (pr.K % 4 == 0 && al16(pr.X)) ? 1 : 0, (pr.U % 4 == 0 && al16(pr.G)) ? 1 : 0, bx, by, bz, cpart);
+}
+
+__global__ void __launch_bounds__(256)
+tn_grouped_reduce_kernel(const __grid_constant__ TnGroup grp, const float* __restrict__ ws) {
+  const int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
+  if (i >= grp.total_elems) return;
+  int lo = 0, hi = grp.n_outputs - 1;
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) >> 1;
+    if (grp.o[mid].elem_begin <= i) lo = mid; else hi = mid - 1;
+  }
+  const TnOutput& o = grp.o[lo];
+  const int64_t e = i - o.elem_begin, kw = static_cast<int64_t>(o.K) * o.U;
+  const bool is_w = e < kw;
+  float* dst = is_w ? o.dW + e : o.db + (e - kw);
+  float acc = *dst;
+  for (int q = o.first; q < o.first + o.count; ++q) {     // fixed order: problems, then splits
+    const TnProblem& pr = grp.p[q];
+    if (!is_w && !pr.want_colsum) continue;
+    const float* part = ws + pr.ws_off + (is_w ? e : static_cast<int64_t>(pr.splits) * kw + (e - kw));
+    const int64_t stride = is_w ? kw : o.U;
+    float s0 = 0.f, s1 = 0.f;
+    int sp = 0;
+    for (; sp + 1 < pr.splits; sp += 2) { s0 += part[sp * stride]; s1 += part[(sp + 1) * stride]; }
+    if (sp < pr.splits) s0 += part[sp * stride];
+    acc += s0 + s1;
+  }
+  *dst = acc;
+}
+
 constexpr size_t kSmemBytes = 4 * (kKC / 4) * (kBM + 1) * sizeof(float4);   // 4 planes (A hi/lo, B hi/lo) = 64.5 KB
 
 inline int tn_splits(int64_t M, int K, int U) {
@@ -377,6 +492,17 @@ inline int tn_splits(int64_t M, int K, int U) {
   int64_t s = std::max<int64_t>(1, (2 * kNumSM) / tiles);
   s = std::min<int64_t>(s, std::max<int64_t>(1, ceil_div<int64_t>(M, 2 * kKC)));
   return static_cast<int>(s);
+}
+
+// rows per split for a grouped launch: ~2 waves of one resident CTA per SM (the kernel needs ~230 registers per
+// thread) over all problems, at least 2 chunks each
+inline int64_t grouped_rows_per_split(int n, const int64_t* M, const int32_t* K, const int32_t* U) {
+  int64_t chunk_tiles = 0;
+  for (int i = 0; i < n; ++i)
+    chunk_tiles += ceil_div<int64_t>(std::max<int64_t>(M[i], 1), kKC) * ceil_div(K[i], kBM) * ceil_div(U[i], kMaxN);
+  const int64_t target = 2LL * kNumSM;
+  const int64_t per_cta = std::max<int64_t>(2, ceil_div<int64_t>(chunk_tiles, target));
+  return per_cta * kKC;
 }
 
 }  // namespace tc
@@ -434,6 +560,81 @@ int kgcnn_dense_tc(int op, const float* A, const float* B, int64_t M, int K, int
   const int64_t n = static_cast<int64_t>(K) * U;
   tc::tn_split_reduce_kernel<<<static_cast<unsigned>(ceil_div<int64_t>(n, 256)), 256, 0, st>>>(partial, S, n, out);
   return finish_launch(2);
+}
+
+size_t kgcnn_dense_tn_grouped_workspace_bytes(int n, const int64_t* M, const int32_t* K, const int32_t* U) {
+  if (n <= 0 || !M || !K || !U) return 0;
+  const int64_t rps = tc::grouped_rows_per_split(n, M, K, U);
+  size_t floats = 0;
+  for (int i = 0; i < n; ++i) {
+    const int64_t splits = std::max<int64_t>(1, ceil_div<int64_t>(M[i], rps));
+    floats += static_cast<size_t>(splits) * (static_cast<size_t>(K[i]) * U[i] + U[i]);
+    floats = (floats + 63) / 64 * 64;
+  }
+  return floats * sizeof(float) + 256;
+}
+
+int kgcnn_dense_tn_grouped(int n, const float* const* X, const float* const* G, const int64_t* M, const int32_t* K,
+                           const int32_t* U, float* const* dW, float* const* db, void* workspace,
+                           size_t workspace_bytes, kgcnn_stream_t stream) {
+  if (n < 0) return KGCNN_E_INVALID;
+  if (n == 0) return KGCNN_OK;
+  if (!X || !G || !M || !K || !U || !dW || !db) return KGCNN_E_INVALID;
+  if (!workspace || workspace_bytes < kgcnn_dense_tn_grouped_workspace_bytes(n, M, K, U)) return KGCNN_E_WORKSPACE;
+  if ((reinterpret_cast<uintptr_t>(workspace) & 15) != 0) return KGCNN_E_INVALID;
+  for (int i = 0; i < n; ++i)
+    if (M[i] < 0 || K[i] <= 0 || U[i] <= 0 || !dW[i] || (M[i] > 0 && (!X[i] || !G[i]))) return KGCNN_E_INVALID;
+  cudaStream_t st = as_stream(stream);
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(tc::tn_grouped_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         static_cast<int>(tc::kSmemBytes));
+    attr_set = true;
+  }
+  const int64_t rps = tc::grouped_rows_per_split(n, M, K, U);
+  float* ws = static_cast<float*>(workspace);
+  int64_t ws_off = 0;
+  int launches = 0;
+  for (int base = 0; base < n; base += tc::kMaxGroup) {
+    const int cnt = std::min(tc::kMaxGroup, n - base);
+    tc::TnGroup grp;
+    grp.n_problems = 0; grp.n_outputs = 0; grp.total_ctas = 0; grp.pad = 0; grp.total_elems = 0;
+    for (int q = 0; q < cnt; ++q) {
+      const int i = base + q;
+      if (M[i] == 0) continue;                                     // contributes nothing
+      tc::TnProblem& pr = grp.p[grp.n_problems];
+      pr.X = X[i]; pr.G = G[i]; pr.M = M[i]; pr.K = K[i]; pr.U = U[i];
+      pr.splits = static_cast<int32_t>(std::max<int64_t>(1, ceil_div<int64_t>(M[i], rps)));
+      pr.rows_per_split = static_cast<int32_t>(rps);
+      pr.tiles_k = ceil_div(K[i], tc::kBM); pr.tiles_u = ceil_div(U[i], tc::kMaxN);
+      pr.cta_begin = grp.total_ctas;
+      pr.want_colsum = db[i] ? 1 : 0;
+      pr.ws_off = ws_off;
+      grp.total_ctas += pr.tiles_k * pr.tiles_u * pr.splits;
+      int64_t fl = static_cast<int64_t>(pr.splits) * (static_cast<int64_t>(K[i]) * U[i] + U[i]);
+      ws_off += (fl + 63) / 64 * 64;
+      // same destination as the previous problem of this launch -> same output run
+      const bool same = grp.n_outputs > 0 && grp.o[grp.n_outputs - 1].dW == dW[i] &&
+                        grp.o[grp.n_outputs - 1].K == K[i] && grp.o[grp.n_outputs - 1].U == U[i] &&
+                        (grp.o[grp.n_outputs - 1].db == db[i] || !db[i] || !grp.o[grp.n_outputs - 1].db);
+      if (same) {
+        tc::TnOutput& o = grp.o[grp.n_outputs - 1];
+        o.count += 1;
+        if (!o.db && db[i]) { o.db = db[i]; grp.total_elems += U[i]; }   // it is the last output: no later shift
+      } else {
+        tc::TnOutput& o = grp.o[grp.n_outputs++];
+        o.dW = dW[i]; o.db = db[i]; o.K = K[i]; o.U = U[i];
+        o.first = grp.n_problems; o.count = 1; o.elem_begin = grp.total_elems;
+        grp.total_elems += static_cast<int64_t>(K[i]) * U[i] + (db[i] ? U[i] : 0);
+      }
+      grp.n_problems += 1;
+    }
+    if (grp.n_problems == 0) continue;
+    tc::tn_grouped_kernel<<<static_cast<unsigned>(grp.total_ctas), tc::kThreads, tc::kSmemBytes, st>>>(grp, ws);
+    tc::tn_grouped_reduce_kernel<<<static_cast<unsigned>(ceil_div<int64_t>(grp.total_elems, 256)), 256, 0, st>>>(grp, ws);
+    launches += 2;
+  }
+  return launches ? finish_launch(launches) : KGCNN_OK;
 }
 
 }  // extern "C"

@@ -469,6 +469,99 @@ def raw_gemm_tn(x2d, g2d, want_colsum=False):
     return (dw, db) if want_colsum else dw
 
 
+class WeightGradSink:
+    """Deferred, grouped weight gradients of one backward sweep.
+
+    The (dW, db) = (x^T g, colsum g) products of the Dense layers are leaves of the backward graph: nothing but
+    the optimizer reads them.  While a sink is active (and no graph is being recorded for a further derivative),
+    ``_Linear`` / ``_MatMul`` hand their operands over instead of launching one small GEMM + reduce + column sum
+    each; ``flush()`` submits the whole list to ``kgcnn_dense_tn_grouped`` (two launches), which ACCUMULATES into
+    the registered flat gradient buffer.  Operands are kept alive until the flush; ``max_bytes`` bounds that."""
+
+    def __init__(self, params, flat_grad, offsets, max_bytes=6 << 30, max_items=256):
+        self.flat = flat_grad
+        self.slots = {}
+        for p, off in zip(params, offsets):
+            self.slots[p.data_ptr()] = (off, tuple(p.shape), p)
+        self.items = []          # (slot_offset, x, g, K, U, bias_offset | None)
+        self.bytes = 0
+        self.max_bytes, self.max_items = max_bytes, max_items
+        self.covered = set()
+
+    def lookup(self, w):
+        s = self.slots.get(w.data_ptr())
+        return s if s is not None and s[1] == tuple(w.shape) else None
+
+    def add(self, w, x, g, bias=None):
+        """dW(w) += x^T g (and db(bias) += colsum g).  Returns False if `w` is not a registered variable."""
+        if x.dim() != 2 or g.dim() != 2 or x.dtype != torch.float32 or not x.is_cuda:
+            return False
+        sw = self.lookup(w)
+        sb = self.lookup(bias) if bias is not None else None
+        if sw is None or (bias is not None and sb is None):
+            return False
+        x, g = _f32c(x.detach()), _f32c(g.detach())
+        self.items.append((sw[0], x, g, int(x.shape[1]), int(g.shape[1]), None if sb is None else sb[0]))
+        self.covered.add(sw[0])
+        if sb is not None:
+            self.covered.add(sb[0])
+        self.bytes += (x.numel() + g.numel()) * 4
+        if self.bytes > self.max_bytes or len(self.items) >= self.max_items:
+            self.flush()
+        return True
+
+    def flush(self):
+        import ctypes
+        import numpy as np
+        if not self.items:
+            return
+        items = sorted(self.items, key=lambda it: (it[0], it[5] is None))     # same dW adjacent, bias carrier first
+        n = len(items)
+        base = self.flat.data_ptr()
+        X = np.array([it[1].data_ptr() for it in items], dtype=np.uint64)
+        G = np.array([it[2].data_ptr() for it in items], dtype=np.uint64)
+        M = np.array([it[1].shape[0] for it in items], dtype=np.int64)
+        K = np.array([it[3] for it in items], dtype=np.int32)
+        U = np.array([it[4] for it in items], dtype=np.int32)
+        dW = np.array([base + 4 * it[0] for it in items], dtype=np.uint64)
+        db = np.array([0 if it[5] is None else base + 4 * it[5] for it in items], dtype=np.uint64)
+        hp = lambda a: a.ctypes.data_as(ctypes.c_void_p)
+        nbytes = int(_lib.lib().kgcnn_dense_tn_grouped_workspace_bytes(n, hp(M), hp(K), hp(U)))
+        ws = torch.empty((max(nbytes, 16),), dtype=torch.uint8, device=self.flat.device)
+        check(_lib.lib().kgcnn_dense_tn_grouped(n, hp(X), hp(G), hp(M), hp(K), hp(U), hp(dW), hp(db), _ptr(ws),
+                                                nbytes, _stream()), "kgcnn_dense_tn_grouped")
+        self.items = []
+        self.bytes = 0
+
+
+_SINK = None
+
+
+class weight_grad_sink:
+    """Context: route Dense weight gradients of non-differentiated backward sweeps into `sink`."""
+
+    def __init__(self, sink):
+        self.sink = sink
+
+    def __enter__(self):
+        global _SINK
+        self._prev, _SINK = _SINK, self.sink
+        return self.sink
+
+    def __exit__(self, *exc):
+        global _SINK
+        if exc[0] is None:
+            self.sink.flush()
+        else:
+            self.sink.items, self.sink.bytes = [], 0
+        _SINK = self._prev
+
+
+def _sink():
+    """The active sink, unless this backward sweep is itself being recorded (create_graph=True)."""
+    return _SINK if (_SINK is not None and not torch.is_grad_enabled()) else None
+
+
 _TN_MIN_ROWS = 512     # below this the reduction axis is short and a library GEMM is as good
 DENSE_LIBRARY = False  # diagnostics only (tools/diag_hdnnp.py): route Dense through the library GEMM instead of dense_tc
 
@@ -494,15 +587,16 @@ class _MatMul(torch.autograd.Function):
         a, b = ctx.saved_tensors
         ga = gb = None
         mode = ctx.mode
+        sink = _sink()
         if mode == 0:       # y = a b
             if ctx.needs_input_grad[0]:
                 ga = _MatMul.apply(g, b, 1)          # g b^T
-            if ctx.needs_input_grad[1]:
+            if ctx.needs_input_grad[1] and not (sink is not None and sink.add(b, a, g)):
                 gb = _MatMul.apply(a, g, 2)          # a^T g
         elif mode == 1:     # y = a b^T
             if ctx.needs_input_grad[0]:
                 ga = _MatMul.apply(g, b, 0)          # g b
-            if ctx.needs_input_grad[1]:
+            if ctx.needs_input_grad[1] and not (sink is not None and sink.add(b, g, a)):
                 gb = _MatMul.apply(g, a, 2)          # g^T a
         else:               # y = a^T b
             if ctx.needs_input_grad[0]:
@@ -535,6 +629,7 @@ class _Linear(torch.autograd.Function):
     def forward(ctx, x, w, b):
         ctx.save_for_backward(x, w)
         ctx.has_bias = b is not None
+        ctx.bias_ref = b.detach() if b is not None else None      # identity only (the sink's variable lookup)
         if x.is_cuda and x.dtype == torch.float32 and not DENSE_LIBRARY:
             return raw_dense_tc(0, x, w, b)          # tcgen05 tensor cores, 3xTF32, bias in the epilogue
         return torch.addmm(b, x, w) if b is not None else x @ w
@@ -547,7 +642,10 @@ class _Linear(torch.autograd.Function):
         if ctx.needs_input_grad[0]:
             gx = _MatMul.apply(g, w, 1)
         if ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2]):
-            if ctx.has_bias:
+            sink = _sink()
+            if sink is not None and ctx.needs_input_grad[1] and sink.add(w, x, g, ctx.bias_ref):
+                pass                                  # deferred: accumulated by the grouped kernel at flush
+            elif ctx.has_bias:
                 gw, gb = _TNCol.apply(x, g)
             else:
                 gw = _MatMul.apply(x, g, 2)

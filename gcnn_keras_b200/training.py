@@ -34,6 +34,9 @@ class FlatAdam:
             p.data = self.flat[off:off + n].view_as(p)          # parameters become views of the flat buffer
             off += padded
         self._real, self._padded = real, sizes
+        self.offsets = [int(o) for o in ([0] + list(torch.tensor(sizes).cumsum(0)[:-1]))]
+        self.gflat = torch.zeros_like(self.flat)                 # flat gradient buffer, same layout (padding stays 0)
+        self.grad_views = [self.gflat[o:o + n].view_as(p) for o, n, p in zip(self.offsets, real, self.params)]
         self.m = torch.zeros_like(self.flat)
         self.v = torch.zeros_like(self.flat)
         offsets = torch.tensor([0] + list(torch.tensor(sizes).cumsum(0)), dtype=torch.int32, device=dev)
@@ -44,17 +47,24 @@ class FlatAdam:
         self.hyper = (float(lr), float(beta1), float(beta2), float(eps), float(clipnorm or 0.0))
         self._F = F
 
-    def step(self, grads):
+    def step(self, grads, accumulate=False):
+        """grads: per-variable gradients (None allowed).  With `accumulate` they are ADDED to the flat gradient
+        buffer, which the weight-gradient sink has already accumulated into (after `zero_grad()`)."""
+        if not accumulate:
+            self.zero_grad()
+        pairs = [(v, gr) for v, gr in zip(self.grad_views, grads) if gr is not None]
+        if pairs:
+            torch._foreach_add_([v for v, _ in pairs], [gr.reshape(v.shape) for v, gr in pairs])
+        self.step_flat()
+
+    def zero_grad(self):
+        self.gflat.zero_()
+
+    def step_flat(self):
         from . import _lib
         from .distributed import allreduce_flat
         F = self._F
-        pieces = []
-        for gr, n, padded in zip(grads, self._real, self._padded):
-            pieces.append(gr.reshape(-1))
-            if padded > n:
-                pieces.append(self.flat.new_zeros(padded - n))
-        g = torch.cat(pieces)
-        g = allreduce_flat(g)                                    # data parallel by graph: the step's only collective
+        g = allreduce_flat(self.gflat)                           # data parallel by graph: the step's only collective
         lr, b1, b2, eps, clip = self.hyper
         sumsq = F.raw_gms(g.unsqueeze(1), g.unsqueeze(1), self.rel, None) if clip > 0 else None
         _lib.check(_lib.lib().kgcnn_adam_clipnorm(
@@ -72,6 +82,7 @@ class ForceTrainStep:
         self.lr, self.eps = lr, eps
         self.params = None
         self.optimizer = None
+        self.sink = None
 
     def _ensure_optimizer(self):
         if self.optimizer is None:
@@ -86,11 +97,16 @@ class ForceTrainStep:
     def step(self, inputs, e_target, f_target):
         loss = self.loss(inputs, e_target, f_target)
         self._ensure_optimizer()
-        from .functional import no_coordinate_hessian
-        with no_coordinate_hessian():       # weights only: no d2/dx2 through the fused geometry kernels
+        from .functional import WeightGradSink, no_coordinate_hessian, weight_grad_sink
+        opt = self.optimizer
+        if self.sink is None:
+            self.sink = WeightGradSink(self.params, opt.gflat, opt.offsets)
+        opt.zero_grad()
+        # weights only: no d2/dx2 through the fused geometry kernels; the Dense weight gradients (leaves of this
+        # sweep) are deferred into the sink and computed by ONE grouped tensor-core launch at its exit
+        with no_coordinate_hessian(), weight_grad_sink(self.sink):
             grads = torch.autograd.grad(loss, self.params, allow_unused=True)
-        grads = [torch.zeros_like(p) if g is None else g for g, p in zip(grads, self.params)]
-        self.optimizer.step(grads)
+        opt.step(grads, accumulate=True)
         return loss
 
 

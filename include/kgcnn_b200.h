@@ -175,6 +175,19 @@ int kgcnn_dense_tc(int op, const float* A, const float* B, int64_t M, int K, int
                    void* workspace, size_t workspace_bytes, kgcnn_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * a19  grouped weight gradients: every  dW_i[K_i,U_i] += X_i[M_i,K_i]^T G_i[M_i,U_i],  db_i[U_i] += colsum(G_i)
+ *   of one backward sweep in two launches (tcgen05 3xTF32 + fixed-order reduce).  The products are leaves of the
+ *   backward graph (backward of kgcnn/layers/modules.py:85 for every Dense, once through the energy and once
+ *   through the force), so the host defers them and submits the list.  X, G, M, K, U, dW, db are HOST arrays of
+ *   length n (device pointers inside); db[i] nullable.  Results are ACCUMULATED into dW / db (zero them first);
+ *   problems with the same dW must be adjacent in the list.  Deterministic for a fixed list.
+ * ------------------------------------------------------------------------------------------- */
+size_t kgcnn_dense_tn_grouped_workspace_bytes(int n, const int64_t* M, const int32_t* K, const int32_t* U);
+int kgcnn_dense_tn_grouped(int n, const float* const* X, const float* const* G, const int64_t* M, const int32_t* K,
+                           const int32_t* U, float* const* dW, float* const* db, void* workspace,
+                           size_t workspace_bytes, kgcnn_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
  * a15/a16  fused ACSF symmetry functions (kgcnn/layers/conv/acsf_conv.py:199-211 and :473-494)
  *   mode 0: G[N, R*m]                  (out)
  *   mode 1: VJP, cot = dG[N, R*m]   -> out = d/dx of the CENTRE atoms [N,3]; the neighbour parts are written per
