@@ -429,7 +429,8 @@ class _BiasAct(torch.autograd.Function):
         gy = gy.contiguous()
         act, k = ctx.act, ctx.order
         g_pre = g_bias = g_g1 = g_g2 = None
-        if ctx.needs_input_grad[0] or (bias is not None and ctx.needs_input_grad[1]):
+        want_bias = bias is not None and _want(ctx, 1, bias)
+        if ctx.needs_input_grad[0] or want_bias:
             if k >= 3:
                 raise NotImplementedError("activation derivatives above order 3 are not instantiated")
             if g1 is not None and g2 is not None:
@@ -438,7 +439,7 @@ class _BiasAct(torch.autograd.Function):
                 t = _BiasAct.apply(pre, bias, gy, g1 if g1 is not None else g2, act, k + 1)
             if ctx.needs_input_grad[0]:
                 g_pre = t
-            if bias is not None and ctx.needs_input_grad[1]:
+            if want_bias:
                 g_bias = colsum(t)
         if g1 is not None and ctx.needs_input_grad[2]:
             g_g1 = _BiasAct.apply(pre, bias, gy, g2, act, k)
@@ -534,6 +535,34 @@ class WeightGradSink:
         self.bytes = 0
 
 
+_INPUT_ONLY = None
+
+
+class input_gradients_only:
+    """Context for a derivative with respect to DATA tensors only (the inner dE/dx of EnergyForceModel):
+    ``ctx.needs_input_grad`` of a Python autograd Function is fixed at forward time, so without this the backward
+    of every Dense would also compute its (unused) weight and bias gradients in that sweep.  Inside the context
+    the gradients of LEAF operands other than `wanted` are skipped (returned as None)."""
+
+    def __init__(self, *wanted):
+        self.ptrs = frozenset(t.data_ptr() for t in wanted)
+
+    def __enter__(self):
+        global _INPUT_ONLY
+        self._prev, _INPUT_ONLY = _INPUT_ONLY, self.ptrs
+
+    def __exit__(self, *exc):
+        global _INPUT_ONLY
+        _INPUT_ONLY = self._prev
+
+
+def _want(ctx, i, t):
+    """Does this backward sweep need the gradient of input i (tensor t)?"""
+    if not ctx.needs_input_grad[i]:
+        return False
+    return not (_INPUT_ONLY is not None and t is not None and t.is_leaf and t.data_ptr() not in _INPUT_ONLY)
+
+
 _SINK = None
 
 
@@ -589,19 +618,19 @@ class _MatMul(torch.autograd.Function):
         mode = ctx.mode
         sink = _sink()
         if mode == 0:       # y = a b
-            if ctx.needs_input_grad[0]:
+            if _want(ctx, 0, a):
                 ga = _MatMul.apply(g, b, 1)          # g b^T
-            if ctx.needs_input_grad[1] and not (sink is not None and sink.add(b, a, g)):
+            if _want(ctx, 1, b) and not (sink is not None and sink.add(b, a, g)):
                 gb = _MatMul.apply(a, g, 2)          # a^T g
         elif mode == 1:     # y = a b^T
-            if ctx.needs_input_grad[0]:
+            if _want(ctx, 0, a):
                 ga = _MatMul.apply(g, b, 0)          # g b
-            if ctx.needs_input_grad[1] and not (sink is not None and sink.add(b, g, a)):
+            if _want(ctx, 1, b) and not (sink is not None and sink.add(b, g, a)):
                 gb = _MatMul.apply(g, a, 2)          # g^T a
         else:               # y = a^T b
-            if ctx.needs_input_grad[0]:
+            if _want(ctx, 0, a):
                 ga = _MatMul.apply(b, g, 1)          # b g^T
-            if ctx.needs_input_grad[1]:
+            if _want(ctx, 1, b):
                 gb = _MatMul.apply(a, g, 0)          # a g
         return ga, gb, None
 
@@ -611,11 +640,13 @@ class _BiasAdd(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, pre, bias):
+        ctx.bias_leaf = bias.is_leaf
         return pre + bias
 
     @staticmethod
     def backward(ctx, g):
-        return g, (colsum(g) if ctx.needs_input_grad[1] else None)
+        skip = _INPUT_ONLY is not None and ctx.bias_leaf
+        return g, (colsum(g) if ctx.needs_input_grad[1] and not skip else None)
 
 
 def matmul(a, b):
@@ -630,6 +661,7 @@ class _Linear(torch.autograd.Function):
         ctx.save_for_backward(x, w)
         ctx.has_bias = b is not None
         ctx.bias_ref = b.detach() if b is not None else None      # identity only (the sink's variable lookup)
+        ctx.bias_leaf = b is not None and b.is_leaf
         if x.is_cuda and x.dtype == torch.float32 and not DENSE_LIBRARY:
             return raw_dense_tc(0, x, w, b)          # tcgen05 tensor cores, 3xTF32, bias in the epilogue
         return torch.addmm(b, x, w) if b is not None else x @ w
@@ -639,9 +671,9 @@ class _Linear(torch.autograd.Function):
         x, w = ctx.saved_tensors
         g = g.contiguous()
         gx = gw = gb = None
-        if ctx.needs_input_grad[0]:
+        if _want(ctx, 0, x):
             gx = _MatMul.apply(g, w, 1)
-        if ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2]):
+        if _want(ctx, 1, w) or (ctx.has_bias and _want(ctx, 2, ctx.bias_ref if ctx.bias_leaf else None)):
             sink = _sink()
             if sink is not None and ctx.needs_input_grad[1] and sink.add(w, x, g, ctx.bias_ref):
                 pass                                  # deferred: accumulated by the grouped kernel at flush

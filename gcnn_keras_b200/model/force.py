@@ -67,9 +67,11 @@ class EnergyForceModel(torch.nn.Module):
             states = int(eng.shape[-1]) if eng.dim() > 1 else 1
             eng2 = eng.reshape(eng.shape[0], states)
             cols = []
-            for s in range(states):                              # batch_jacobian, force.py:176
-                (g,) = torch.autograd.grad(eng2[:, s].sum(), xv, create_graph=train, retain_graph=True)
-                cols.append(g)
+            from ..functional import input_gradients_only
+            with input_gradients_only(xv):                       # dE/dx only: no weight gradients in this sweep
+                for s in range(states):                          # batch_jacobian, force.py:176
+                    (g,) = torch.autograd.grad(eng2[:, s].sum(), xv, create_graph=train, retain_graph=True)
+                    cols.append(g)
         de_dr = torch.stack(cols, dim=-1)                        # (N, 3, states) = transpose at force.py:177
         if not train:
             de_dr = de_dr.detach()
