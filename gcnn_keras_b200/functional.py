@@ -974,3 +974,162 @@ def painn_message(phi, v, w, r, recv, send):
     """(ds [N,F], dv [N,3,F]) of PAiNNconv (painn_conv.py:104-114) for phi [N,3F], v [N,3,F], w [E,3F], r [E,3]."""
     F_dim = int(phi.shape[1]) // 3
     return _PainnMsg.apply("G", 7, True, True, None, None, phi, v, w, r, recv, send, F_dim)
+
+
+# ------------------------------------------------------------------------------------------------
+# fused edge geometry (a9-a12): d, u, radial basis, cosine cutoff straight from the coordinates
+# ------------------------------------------------------------------------------------------------
+class GeometrySpec:
+    """What one fused geometry call computes.  want: subset of ("d", "u", "rbf", "fc") in that order."""
+
+    def __init__(self, rel_i, rel_j, want, basis=0, R=0, basis_params=(0.0, 0.0, 0.0), frequencies=None, eps=0.0,
+                 no_nan=True, cos_cutoff=0.0):
+        self.rel_i, self.rel_j = rel_i, rel_j
+        self.want = tuple(w for w in ("d", "u", "rbf", "fc") if w in want)
+        self.basis, self.R = int(basis), int(R)
+        self.basis_params = tuple(float(b) for b in basis_params)
+        self.frequencies = frequencies
+        self.eps, self.no_nan, self.cos_cutoff = float(eps), bool(no_nan), float(cos_cutoff)
+
+    def shapes(self, E):
+        return {"d": (E, 1), "u": (E, 3), "rbf": (E, self.R), "fc": (E, 1)}
+
+
+def raw_edge_geometry(xyz, spec, mode, cots=None, tangent=None):
+    """mode 0 / 2: dict name -> tensor for spec.want; mode 1: g_v [E,3]."""
+    import ctypes
+    _need_cuda(xyz)
+    xyz = _f32c(xyz)
+    E = spec.rel_i.n_elements
+    dev = xyz.device
+    bp = (ctypes.c_float * 3)(*spec.basis_params)
+    outs = {k: None for k in ("d", "u", "rbf", "fc")}
+    gv = None
+    if mode == 1:
+        gv = torch.empty((E, 3), dtype=torch.float32, device=dev)
+        cots = {k: (None if v is None else _f32c(v)) for k, v in cots.items()}
+    else:
+        shp = spec.shapes(E)
+        for k in spec.want:
+            outs[k] = torch.empty(shp[k], dtype=torch.float32, device=dev)
+        cots = {}
+    tangent = None if tangent is None else _f32c(tangent)
+    check(_lib.lib().kgcnn_edge_geometry(
+        _ptr(xyz), _ptr(spec.rel_i.ids), _ptr(spec.rel_j.ids), E, mode, spec.basis, spec.R,
+        ctypes.cast(bp, ctypes.c_void_p), _ptr(spec.frequencies), spec.eps, 1 if spec.no_nan else 0, spec.cos_cutoff,
+        _ptr(cots.get("d")), _ptr(cots.get("u")), _ptr(cots.get("rbf")), _ptr(cots.get("fc")), _ptr(tangent),
+        _ptr(outs["d"]), _ptr(outs["u"]), _ptr(outs["rbf"]), _ptr(outs["fc"]), _ptr(gv), _stream()),
+        "kgcnn_edge_geometry")
+    return gv if mode == 1 else tuple(outs[k] for k in spec.want)
+
+
+def _geom_composite(xyz, spec):
+    """The same quantities with differentiable tensor ops (any derivative order); used for the coordinate Hessian
+    terms the fused kernels do not provide, and as the comparand in the tests."""
+    import math
+    xi, xj = xyz[spec.rel_i.ids.long()], xyz[spec.rel_j.ids.long()]
+    v = xi - xj
+    d = torch.sqrt(torch.relu(torch.sum(v * v, dim=1, keepdim=True)) + spec.eps)
+    out = {}
+    if "d" in spec.want:
+        out["d"] = d
+    if "u" in spec.want:
+        inv = torch.where(d == 0, torch.zeros_like(d), 1.0 / torch.where(d == 0, torch.ones_like(d), d)) \
+            if spec.no_nan else 1.0 / d
+        out["u"] = v * inv
+    if "rbf" in spec.want:
+        if spec.basis == 1:
+            gamma, offset, step = spec.basis_params
+            mu = torch.arange(spec.R, dtype=xyz.dtype, device=xyz.device) * step
+            out["rbf"] = torch.exp(-gamma * torch.square(d - offset - mu))
+        else:
+            inv_c, p = spec.basis_params[0], int(spec.basis_params[1])
+            x = d * inv_c
+            a, b, c = -(p + 1) * (p + 2) / 2, p * (p + 2), -p * (p + 1) / 2
+            env = torch.where(x < 1, 1.0 / x + a * x ** (p - 1) + b * x ** p + c * x ** (p + 1), torch.zeros_like(x))
+            out["rbf"] = env * torch.sin(spec.frequencies.to(xyz.dtype) * x)
+    if "fc" in spec.want:
+        rc = spec.cos_cutoff
+        out["fc"] = (torch.cos(torch.clamp(d, -rc, rc) * math.pi / rc) + 1) * 0.5
+    return tuple(out[k] for k in spec.want)
+
+
+def _geom_hessian_term(xyz, spec, cots, hvec):
+    """d/dxyz <J(xyz)^T cots, hvec> through the composite (only when the caller really differentiates the
+    force with respect to the coordinates; force TRAINING never does)."""
+    with torch.enable_grad():
+        x = xyz.detach().requires_grad_(True)
+        outs = _geom_composite(x, spec)
+        pairs = [(o, c) for o, c in zip(outs, cots) if c is not None]
+        (vjp,) = torch.autograd.grad([o for o, _ in pairs], x, [c for _, c in pairs], create_graph=True)
+        (g,) = torch.autograd.grad(vjp, x, hvec, allow_unused=True)
+    return torch.zeros_like(xyz) if g is None else g
+
+
+def _geom_vjp_raw(xyz, cots, spec):
+    gv = raw_edge_geometry(xyz, spec, 1, cots=dict(zip(spec.want, cots)))
+    return raw_gms(gv, None, spec.rel_i, None) - raw_gms(gv, None, spec.rel_j, None)
+
+
+class _EdgeGeom(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, xyz, spec):
+        ctx.spec = spec
+        ctx.set_materialize_grads(False)
+        ctx.save_for_backward(xyz)
+        return raw_edge_geometry(xyz, spec, 0)
+
+    @staticmethod
+    def backward(ctx, *cots):
+        (xyz,) = ctx.saved_tensors
+        return _EdgeGeomVjp.apply(xyz, ctx.spec, *[None if c is None else c.contiguous() for c in cots]), None
+
+
+class _EdgeGeomVjp(torch.autograd.Function):
+    """J^T (cotangents): linear in the cotangents, so its VJP with respect to them is the JVP kernel."""
+
+    @staticmethod
+    def forward(ctx, xyz, spec, *cots):
+        ctx.spec = spec
+        ctx.present = [c is not None for c in cots]
+        ctx.save_for_backward(xyz, *[c for c in cots if c is not None])
+        return _geom_vjp_raw(xyz, cots, spec)
+
+    @staticmethod
+    def backward(ctx, hvec):
+        xyz, saved = ctx.saved_tensors[0], list(ctx.saved_tensors[1:])
+        g_xyz = None
+        if hvec is not None and ctx.needs_input_grad[0] and COORDINATE_HESSIAN:
+            cots = [saved.pop(0) if p else None for p in ctx.present]
+            g_xyz = _geom_hessian_term(xyz, ctx.spec, [None if c is None else c.detach() for c in cots],
+                                       hvec.detach())
+        g_cots = [None] * len(ctx.present)
+        if any(ctx.needs_input_grad[2:]):
+            tang = _EdgeGeomJvp.apply(xyz, ctx.spec, hvec.contiguous())
+            g_cots = [t if (p and n) else None for t, p, n in zip(tang, ctx.present, ctx.needs_input_grad[2:])]
+        return (g_xyz, None) + tuple(g_cots)
+
+
+class _EdgeGeomJvp(torch.autograd.Function):
+    """J h; its VJP with respect to h is J^T again."""
+
+    @staticmethod
+    def forward(ctx, xyz, spec, hvec):
+        ctx.spec = spec
+        ctx.set_materialize_grads(False)
+        ctx.save_for_backward(xyz)
+        return raw_edge_geometry(xyz, spec, 2, tangent=hvec)
+
+    @staticmethod
+    def backward(ctx, *cots):
+        (xyz,) = ctx.saved_tensors
+        g_xyz = _no_hessian("edge geometry (third order)") if ctx.needs_input_grad[0] else None
+        g_h = None
+        if ctx.needs_input_grad[2]:
+            g_h = _EdgeGeomVjp.apply(xyz, ctx.spec, *[None if c is None else c.contiguous() for c in cots])
+        return g_xyz, None, g_h
+
+
+def edge_geometry(xyz, spec):
+    """Tuple of tensors for spec.want, differentiable to the order force training needs."""
+    return _EdgeGeom.apply(xyz, spec)

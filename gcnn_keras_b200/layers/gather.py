@@ -76,7 +76,12 @@ class GatherEmbeddingSelection(GraphBaseLayer):
         if self.axis != 1 or self.axis_indices != 2:
             raise NotImplementedError("GatherEmbeddingSelection: only axis=1, axis_indices=2 are on the hot path")
         plan = get_plan(index, nodes)
-        return [index.with_values(F.gather(nodes.values, plan.relation(i))) for i in self.selection_index]
+        outs = []
+        for i in self.selection_index:
+            out = index.with_values(F.gather(nodes.values, plan.relation(i)))
+            out.provenance = ("gathered", nodes, plan.relation(i))      # lets the geometry layers fuse (geom.py)
+            outs.append(out)
+        return outs
 
     def get_config(self):
         config = super().get_config()

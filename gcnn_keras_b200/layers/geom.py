@@ -11,11 +11,33 @@ import math
 import numpy as np
 import torch
 
+from .. import functional as F
 from ..ragged import RaggedTensor
 from .base import GraphBaseLayer, register_keras_serializable
 from .gather import GatherNodesSelection
 
 KERAS_EPSILON = 1e-7
+FUSED = True     # fused sm_100a edge-geometry kernel when the inputs carry their provenance; False: op-by-op
+
+
+def _pair_source(a, b):
+    """(coordinates ragged, rel_a, rel_b) if a and b are row gathers of the SAME [N,3] fp32 CUDA tensor."""
+    pa, pb = getattr(a, "provenance", None), getattr(b, "provenance", None)
+    if not FUSED or pa is None or pb is None or pa[0] != "gathered" or pb[0] != "gathered":
+        return None
+    src = pa[1]
+    v = src.values
+    if pb[1].values is not v or v.dim() != 2 or v.shape[1] != 3 or v.dtype != torch.float32 or not v.is_cuda:
+        return None
+    return src, pa[2], pb[2]
+
+
+def _distance_source(ed):
+    """(coordinates ragged, rel_i, rel_j, eps) if `ed` is the untouched output of NodeDistanceEuclidean."""
+    p = getattr(ed, "provenance", None)
+    if not FUSED or p is None or p[0] != "distance":
+        return None
+    return p[1], p[2], p[3], p[4]
 
 
 def _positive_axis(axis, rank):
@@ -128,6 +150,14 @@ class NodeDistanceEuclidean(GraphBaseLayer):
 
     def call(self, inputs, **kwargs):
         a, b = inputs
+        eps = KERAS_EPSILON if self.add_eps else 0.0
+        fused = _pair_source(a, b)
+        if fused is not None:                      # gather + subtract + norm in one launch (csrc/geometry.cu)
+            src, ri, rj = fused
+            (d,) = F.edge_geometry(src.values, F.GeometrySpec(ri, rj, ("d",), eps=eps))
+            out = a.with_values(d)
+            out.provenance = ("distance", src, ri, rj, eps)
+            return out
         diff = a.values - b.values
         return a.with_values(compute_euclidean_norm(diff, axis=1, keepdims=True, add_eps=self.add_eps,
                                                     no_nan=self.no_nan))
@@ -148,6 +178,12 @@ class EdgeDirectionNormalized(GraphBaseLayer):
 
     def call(self, inputs, **kwargs):
         a, b = inputs
+        fused = _pair_source(a, b)
+        if fused is not None:
+            src, ri, rj = fused
+            (u,) = F.edge_geometry(src.values, F.GeometrySpec(ri, rj, ("u",), eps=KERAS_EPSILON if self.add_eps else 0.0,
+                                                              no_nan=self.no_nan))
+            return a.with_values(u)
         diff = a.values - b.values
         inv = compute_euclidean_norm(diff, axis=1, keepdims=True, invert_norm=True, add_eps=self.add_eps,
                                      no_nan=self.no_nan)
@@ -179,6 +215,12 @@ class GaussBasisLayer(GraphBaseLayer):
         return torch.exp(out)
 
     def call(self, inputs, **kwargs):
+        fused = _distance_source(inputs) if isinstance(inputs, RaggedTensor) else None
+        if fused is not None and self.bins <= 64:  # straight from the coordinates: d never becomes a graph node
+            src, ri, rj, eps = fused
+            spec = F.GeometrySpec(ri, rj, ("rbf",), basis=1, R=self.bins, eps=eps,
+                                  basis_params=(self.gamma, self.offset, self.distance / float(self.bins)))
+            return inputs.with_values(F.edge_geometry(src.values, spec)[0])
         return self.map_values(self._compute_gauss_basis, inputs, offset=self.offset, gamma=self.gamma,
                                bins=self.bins, distance=self.distance)
 
@@ -220,7 +262,17 @@ class BesselBasisLayer(GraphBaseLayer):
         return d_cutoff * torch.sin(self.frequencies * d_scaled)
 
     def call(self, inputs, **kwargs):
-        return self.map_values(self.expand_bessel_basis, inputs)
+        fused = _distance_source(inputs) if isinstance(inputs, RaggedTensor) else None
+        trainable = self.frequencies.requires_grad and torch.is_grad_enabled()
+        if fused is not None and not trainable and self.num_radial <= 64:
+            src, ri, rj, eps = fused
+            if self.frequencies.device != src.values.device:
+                self.to(src.values.device)
+            spec = F.GeometrySpec(ri, rj, ("rbf",), basis=2, R=self.num_radial, eps=eps,
+                                  basis_params=(self.inv_cutoff, self.envelope_exponent + 1, 0.0),
+                                  frequencies=self.frequencies.detach().contiguous())
+            return inputs.with_values(F.edge_geometry(src.values, spec)[0])
+        return self.map_values(self.expand_bessel_basis, inputs)   # trainable frequencies: differentiable in f_n
 
     def get_config(self):
         config = super().get_config()
@@ -243,6 +295,11 @@ class CosCutOffEnvelope(GraphBaseLayer):
         return (torch.cos(fc * np.pi / cutoff) + 1) * 0.5
 
     def call(self, inputs, **kwargs):
+        fused = _distance_source(inputs) if isinstance(inputs, RaggedTensor) else None
+        if fused is not None:
+            src, ri, rj, eps = fused
+            spec = F.GeometrySpec(ri, rj, ("fc",), eps=eps, cos_cutoff=self.cutoff)
+            return inputs.with_values(F.edge_geometry(src.values, spec)[0])
         return self.map_values(self._compute_cutoff_envelope, inputs, cutoff=self.cutoff)
 
     def get_config(self):

@@ -83,6 +83,9 @@ class RaggedTensor:
     def __init__(self, values, partition):
         self.values = values
         self.partition = partition
+        # how these values were derived, when a layer can use it to fuse: ("gathered", source ragged, relation) or
+        # ("distance", coordinates ragged, rel_i, rel_j, eps).  Not propagated by with_values().
+        self.provenance = None
 
     # ---- constructors (tf.RaggedTensor.from_*) -------------------------------------------------
     @classmethod

@@ -188,6 +188,28 @@ int kgcnn_dense_tn_grouped(int n, const float* const* X, const float* const* G, 
                            size_t workspace_bytes, kgcnn_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * a9-a12  fused edge geometry: coordinates + index pair -> distance, unit direction, radial basis, cosine cutoff
+ *   v = x_i - x_j; d = sqrt(relu(sum v^2) + eps)        NodePosition + NodeDistanceEuclidean  geom.py:14-73,181-187
+ *   u = v * divide_no_nan(1, d)                          EdgeDirectionNormalized               geom.py:369-371
+ *   basis 1 (gauss):  rbf_k = exp(-gamma (d - offset - k step)^2)      GaussBasisLayer         geom.py:567-570
+ *         basis_params (HOST, 3 floats) = (gamma, offset, distance / bins)
+ *   basis 2 (bessel): rbf_n = env_p(d / c) sin(f_n d / c)              BesselBasisLayer        geom.py:772-785
+ *         basis_params = (1 / c, p = envelope_exponent + 1, unused); frequencies[R] on the device
+ *   cos_cutoff > 0:   fc = 0.5 (cos(pi clip(d, -c, c) / c) + 1)        CosCutOffEnvelope       geom.py:834-835
+ *   mode 0: values into out_d[E], out_u[E,3], out_rbf[E,R], out_fc[E] (each nullable = not wanted)
+ *   mode 1: VJP; cot_d / cot_u / cot_rbf / cot_fc (each nullable) -> out_gv[E,3] = cotangent of v; the caller adds
+ *           it to x_i and subtracts it from x_j with the deterministic segment kernel
+ *   mode 2: JVP; tangent_xyz[N,3] -> tangents of (d, u, rbf, fc) into the mode-0 outputs
+ *   idx_i / idx_j: batch-indexed int32 columns in the ORIGINAL edge order.  Frequencies are constants here (a
+ *   trainable Bessel basis keeps its own differentiable path on top of out_d).
+ * ------------------------------------------------------------------------------------------- */
+int kgcnn_edge_geometry(const float* xyz, const int32_t* idx_i, const int32_t* idx_j, int64_t E, int mode,
+                        int basis, int R, const float* basis_params, const float* frequencies, float eps,
+                        int no_nan, float cos_cutoff, const float* cot_d, const float* cot_u, const float* cot_rbf,
+                        const float* cot_fc, const float* tangent_xyz, float* out_d, float* out_u, float* out_rbf,
+                        float* out_fc, float* out_gv, kgcnn_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
  * a15/a16  fused ACSF symmetry functions (kgcnn/layers/conv/acsf_conv.py:199-211 and :473-494)
  *   mode 0: G[N, R*m]                  (out)
  *   mode 1: VJP, cot = dG[N, R*m]   -> out = d/dx of the CENTRE atoms [N,3]; the neighbour parts are written per
