@@ -6,15 +6,18 @@
 //
 // Precision: the parity bar is 1e-5 of an fp64 oracle, single-pass TF32 (10-bit mantissa) is ~1e-3.  Every operand
 // tile is therefore split while it is staged into shared memory, x ~ hi + lo with hi = nearest TF32 value and
-// lo = nearest TF32 value of x - hi (|x - hi - lo| <= 2^-23 |x|), and four MMAs accumulate lo*lo + lo*hi + hi*lo +
-// hi*hi in the fp32 TMEM accumulator, drained to fp32 registers every kFlush reduction elements.  The MMAs
-// are not the bottleneck of these skinny, memory-bound products, so the fourth one is free.
+// lo = nearest TF32 value of x - hi (|x - hi - lo| <= 2^-23 |x|), and three MMAs accumulate lo*hi + hi*lo + hi*hi
+// (3xTF32; lo*lo is 2^-22 relative, below the fp32 rounding of the result) in an fp32 TMEM accumulator that is
+// drained to fp32 registers every kFlush reduction elements.
 //
-// Data path: these GEMMs are skinny (K, U <= 640) and memory-bound, and the split needs a register pass anyway, so
-// tiles go global -> registers -> (hi, lo) -> shared memory in the canonical no-swizzle K-major UMMA layout (8 x 16 B
-// core matrices); operands whose reduction index is the ROW of the global matrix (W in NN, X and G in TN) are
-// transposed on the way into shared memory, so every descriptor is K-major; no TMA descriptor is needed.  One elected thread issues tcgen05.mma (kind::tf32, cta_group::1,
-// M = 128), tcgen05.commit signals an mbarrier, the four warps read their 32 TMEM lanes back with tcgen05.ld.
+// Data path: these GEMMs are skinny (K, U <= 640) and sit where tensor time ~ memory time, and the split needs a
+// register pass anyway, so tiles go global -> registers -> (hi, lo) -> shared memory in the canonical no-swizzle
+// K-major UMMA layout (8 x 16 B core matrices); operands whose reduction index is the ROW of the global matrix (W in
+// NN, X and G in TN) are transposed on the way into shared memory, so every descriptor is K-major; no TMA descriptor
+// is needed.  The loop over 32-element reduction chunks is a 3-stage software pipeline: while one elected thread's
+// tcgen05.mma (kind::tf32, cta_group::1, M = 128) of chunk c run (tcgen05.commit -> one mbarrier per stage), the
+// CTA splits and stores chunk c+1, has the global loads of chunk c+2 in flight and drains the previous flush group
+// from the second TMEM accumulator with tcgen05.ld.
 #include <algorithm>
 
 #include "common.cuh"
@@ -22,10 +25,13 @@
 namespace kgcnn {
 namespace tc {
 
-constexpr int kThreads = 256;   // 8 warps stage operands; warp w reads TMEM lanes 32*(w%4)..+31 in the epilogue
+constexpr int kThreads = 512;   // 16 warps stage operands (4 per scheduler: the staging code is issue-latency bound);
+                                // warp w reads TMEM lanes 32*(w%4)..+31, columns 32*(w/4)..+31 in the drain / epilogue
+constexpr int kCtaThreads = kThreads + 32;   // + warp 8: waits for full stages and issues the MMAs, nothing else
 constexpr int kBM = 128;        // MMA M
-constexpr int kKC = 64;         // reduction elements staged per chunk (8 MMA k-steps of 8)
-constexpr int kLd = 8;          // float4 loads in flight per thread and operand (= 128*16/256 = 64*32/256)
+constexpr int kKC = 32;         // reduction elements staged per chunk (4 MMA k-steps of 8)
+constexpr int kLd = 2;          // float4 per thread, operand and register set (= 128*8/512 = 32*32/512)
+constexpr int kStages = 3;      // shared-memory stages of (A hi/lo, B hi/lo) planes: 3 x 66 KB
 constexpr int kMaxN = 128;      // MMA N per CTA (TMEM columns)
 constexpr int kFlush = 64;      // reduction length accumulated inside the tensor core before an fp32 (RN) flush
 
@@ -103,14 +109,16 @@ __device__ __forceinline__ float tf32_hi(float x) {
 // mn = row of the global matrix, k = feature: rows [row0, row0+128), features [f0, f0+kKC).  Loads are issued as
 // one batch of kLd independent float4 per thread (registers), the split + shared-memory stores follow later, so
 // the next chunk's global latency overlaps the MMAs of the current one.
+// `fast` (CTA-uniform): the whole tile is in bounds and 16-byte aligned -> plain 128-bit loads, no predicates.
 __device__ __forceinline__ void load_direct(float4 (&v)[kLd], const float* __restrict__ g, int64_t row0,
-                                            int64_t row_end, int f0, int f_end, int ld, bool vec_ok) {
+                                            int64_t row_end, int f0, int f_end, int ld, bool vec_ok, bool fast) {
   constexpr int NCH = kKC / 4;
 #pragma unroll
   for (int i = 0; i < kLd; ++i) {
     const int it = threadIdx.x + i * kThreads;
     const int c = it % NCH, r = it / NCH;                 // consecutive threads: consecutive 16 B of one row
-    v[i] = load4(g, row0 + r, row_end, f0 + 4 * c, f_end, ld, vec_ok);
+    if (fast) v[i] = __ldg(reinterpret_cast<const float4*>(g + (row0 + r) * ld + f0 + 4 * c));
+    else v[i] = load4(g, row0 + r, row_end, f0 + 4 * c, f_end, ld, vec_ok);
   }
 }
 __device__ __forceinline__ void store_direct(const float4 (&v)[kLd], float4* __restrict__ hi, float4* __restrict__ lo) {
@@ -129,12 +137,15 @@ __device__ __forceinline__ void store_direct(const float4 (&v)[kLd], float4* __r
 // mn = feature, k = row of the global matrix (transposed on the way in): rows [row0, row0+kKC), features
 // [f0, f0+4*nchunks).  Consecutive threads take consecutive rows -> the scalar stores hit 32 different banks.
 __device__ __forceinline__ void load_transposed(float4 (&v)[kLd], const float* __restrict__ g, int64_t row0,
-                                                int64_t row_end, int f0, int f_end, int ld, int nchunks, bool vec_ok) {
+                                                int64_t row_end, int f0, int f_end, int ld, int nchunks, bool vec_ok,
+                                                bool fast) {
 #pragma unroll
   for (int i = 0; i < kLd; ++i) {
     const int it = threadIdx.x + i * kThreads;
     const int k = it % kKC, j = it / kKC;
-    v[i] = (j < nchunks) ? load4(g, row0 + k, row_end, f0 + 4 * j, f_end, ld, vec_ok) : make_float4(0.f, 0.f, 0.f, 0.f);
+    if (fast) v[i] = __ldg(reinterpret_cast<const float4*>(g + (row0 + k) * ld + f0 + 4 * j));
+    else v[i] = (j < nchunks) ? load4(g, row0 + k, row_end, f0 + 4 * j, f_end, ld, vec_ok)
+                              : make_float4(0.f, 0.f, 0.f, 0.f);
   }
 }
 __device__ __forceinline__ void store_transposed(const float4 (&v)[kLd], int nchunks, float4* __restrict__ hi,
@@ -167,13 +178,11 @@ dense_tc_body(const float* __restrict__ A, const float* __restrict__ B, int64_t 
               const float* __restrict__ bias, float* __restrict__ out, int64_t rows_per_split, int vec_a,
               int vec_b, int bx, int by, int bz, float* __restrict__ colsum_part) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  __shared__ __align__(8) uint64_t mbar;
+  __shared__ __align__(8) uint64_t mbar[kStages];
+  __shared__ __align__(8) uint64_t full[kStages];
   __shared__ uint32_t tmem_base_s;
   constexpr int PLANE = (kKC / 4) * (kBM + 1);     // float4 slots per plane: 8 k-chunks x (128 + 1) mn
-  float4* a_hi = reinterpret_cast<float4*>(smem_raw);
-  float4* a_lo = a_hi + PLANE;
-  float4* b_hi = a_lo + PLANE;
-  float4* b_lo = b_hi + PLANE;
+  float4* planes = reinterpret_cast<float4*>(smem_raw);          // [stage][a_hi, a_lo, b_hi, b_lo][PLANE]
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   // output-tile coordinates
@@ -189,21 +198,25 @@ dense_tc_body(const float* __restrict__ A, const float* __restrict__ B, int64_t 
   const int64_t row_end = (OP == kTN) ? min(M, row_beg + rows_per_split) : 0;
   const int64_t red_len = (OP == kNN) ? K : (OP == kNT ? U : (row_end > row_beg ? row_end - row_beg : 0));
 
-  if (warp == 0) {
+  if (warp == kThreads / 32) {                                   // two accumulators of kMaxN columns each
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)),
-                 "r"(static_cast<uint32_t>(kMaxN))
+                 "r"(static_cast<uint32_t>(2 * kMaxN))
                  : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
   if (threadIdx.x == 0) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&mbar)) : "memory");
+#pragma unroll
+    for (int st = 0; st < kStages; ++st) {
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&mbar[st])) : "memory");       // MMAs done
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(&full[st])), "r"(kThreads / 32)
+                   : "memory");                                                                        // stage staged
+    }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem_d = tmem_base_s;
-  const uint32_t bar = smem_u32(&mbar);
 
   // every operand is K-major with 128 (+1) mn slots per k-chunk: LBO = 129, SBO = 8 (units of 16 B)
   constexpr int NRP = kBM + 1;
@@ -211,169 +224,218 @@ dense_tc_body(const float* __restrict__ A, const float* __restrict__ B, int64_t 
   constexpr uint32_t kstep = 2 * NRP;                          // descriptor advance per MMA k-step (8 elements)
   const uint32_t idesc = make_idesc(0, 0, nt);
 
-  float4 va[kLd], vb[kLd];
-  auto load_chunk = [&](int64_t k0) {
+  // two register sets: the global loads of chunk c+2 are issued as soon as chunk c has been stored, so every load
+  // has two full pipeline iterations to land (the kernel runs one CTA per SM; registers are not the limit)
+  float4 va0[kLd], vb0[kLd], va1[kLd], vb1[kLd];
+  // interior tiles (every mn index in range, 16-byte aligned rows) take the unpredicated load path
+  const bool in_a = vec_a && ((OP == kTN) ? (a0 + kBM <= K) : (m0 + kBM <= M));
+  const bool in_b = vec_b && ((OP == kNT) ? (n0 + kMaxN <= K) : (n0 + kMaxN <= U)) && nt == kMaxN;
+  auto load_chunk = [&](int64_t k0, float4 (&va)[kLd], float4 (&vb)[kLd]) {
+    const bool in_k = k0 + kKC <= red_len;
     if (OP == kNN) {
-      load_direct(va, A, m0, M, static_cast<int>(k0), K, K, vec_a);                       // X rows, K feats
-      load_transposed(vb, B, k0, K, n0, U, U, nt / 4, vec_b);                             // W rows k -> K dim
+      load_direct(va, A, m0, M, static_cast<int>(k0), K, K, vec_a, in_a && in_k);          // X rows, K feats
+      load_transposed(vb, B, k0, K, n0, U, U, nt / 4, vec_b, in_b && in_k);                // W rows k -> K dim
     } else if (OP == kNT) {
-      load_direct(va, A, m0, M, static_cast<int>(k0), U, U, vec_a);                       // G rows, U feats
-      load_direct(vb, B, n0, K, static_cast<int>(k0), U, U, vec_b);                       // W rows n, U feats
+      load_direct(va, A, m0, M, static_cast<int>(k0), U, U, vec_a, in_a && in_k);          // G rows, U feats
+      load_direct(vb, B, n0, K, static_cast<int>(k0), U, U, vec_b, in_b && in_k);          // W rows n, U feats
     } else {
-      load_transposed(va, A, row_beg + k0, row_end, a0, K, K, kBM / 4, vec_a);            // X rows -> K dim
-      load_transposed(vb, B, row_beg + k0, row_end, n0, U, U, nt / 4, vec_b);             // G rows -> K dim
+      load_transposed(va, A, row_beg + k0, row_end, a0, K, K, kBM / 4, vec_a, in_a && in_k);   // X rows -> K dim
+      load_transposed(vb, B, row_beg + k0, row_end, n0, U, U, nt / 4, vec_b, in_b && in_k);    // G rows -> K dim
     }
   };
   // The tensor core adds into the TMEM accumulator with truncation, which biases long reductions (measured:
   // ~7e-9 relative per reduction element).  Every kFlush elements the accumulator is drained into fp32 registers
-  // (round-to-nearest adds) and the next MMA starts a fresh accumulation.
-  float racc[2][32];
+  // (round-to-nearest adds) and the next MMAs start a fresh accumulation in the OTHER accumulator, so the drain of
+  // group g overlaps the MMAs of group g + 1.
+  float racc[32];
 #pragma unroll
-  for (int gq = 0; gq < 2; ++gq)
+  for (int i = 0; i < 32; ++i) racc[i] = 0.f;
+  const int c0 = 32 * (warp >> 2);                       // this warp's 32 accumulator columns (staging warps only)
+  auto drain = [&](uint32_t acc_col) {
+    if (c0 < nt) {                                       // warp-uniform
+      uint32_t v[32];
+      const uint32_t taddr = tmem_d + (static_cast<uint32_t>(32 * (warp & 3)) << 16) + acc_col +
+                             static_cast<uint32_t>(c0);
+      asm volatile(
+          "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+          "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+          "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+          : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+            "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+            "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+            "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+          : "r"(taddr)
+          : "memory");
+      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 #pragma unroll
-    for (int i = 0; i < 32; ++i) racc[gq][i] = 0.f;
-  auto drain = [&]() {
-#pragma unroll
-    for (int gq = 0; gq < 2; ++gq) {
-      const int c0 = 32 * (warp >> 2) + 64 * gq;
-      if (c0 < nt) {                                     // warp-uniform
-        uint32_t v[32];
-        const uint32_t taddr = tmem_d + (static_cast<uint32_t>(32 * (warp & 3)) << 16) + static_cast<uint32_t>(c0);
-        asm volatile(
-            "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-            "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-            "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-            : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
-              "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
-              "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
-              "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
-            : "r"(taddr)
-            : "memory");
-        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-        for (int i = 0; i < 32; ++i) racc[gq][i] += __uint_as_float(v[i]);
-      }
+      for (int i = 0; i < 32; ++i) racc[i] += __uint_as_float(v[i]);
     }
   };
-  uint32_t parity = 0;
-  bool first = true;
   const bool do_colsum = (OP == kTN) && colsum_part != nullptr && a0 == 0;     // CTA-uniform
-  float csum = 0.f;
-  if (red_len > 0) load_chunk(0);
-  for (int64_t k0 = 0; k0 < red_len; k0 += kKC) {
-    // ---- split (hi / lo) and store this chunk ----
-    if (OP == kNN) { store_direct(va, a_hi, a_lo); store_transposed(vb, nt / 4, b_hi, b_lo); }
-    else if (OP == kNT) { store_direct(va, a_hi, a_lo); store_direct(vb, b_hi, b_lo); }
-    else { store_transposed(va, kBM / 4, a_hi, a_lo); store_transposed(vb, nt / 4, b_hi, b_lo); }
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // generic-proxy stores -> async proxy (MMA)
-    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-    __syncthreads();
-    if (warp == 0) {
+  float4 csum4[kLd];                                     // bias gradient: this thread's (row lane, 4 features) sums
+#pragma unroll
+  for (int i = 0; i < kLd; ++i) csum4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  // Warp-specialised software pipeline over chunks c of kKC reduction elements, kStages shared-memory stages:
+  //   warps 0-7 (staging):  [wait done(c - kStages)]  split+store(c)  load(c+2)  arrive full(c)  [drain group of c-1]
+  //   warp 8   (MMA issue): wait full(c)  tcgen05.mma x 3 x ksteps -> accumulator (group & 1)  commit -> done(c)
+  // No block-wide barrier inside the loop; two TMEM accumulators alternate per flush group so that the drain of
+  // group g (tcgen05.ld by the staging warps) overlaps the MMAs of group g + 1.
+  const int nchunk = static_cast<int>((red_len + kKC - 1) / kKC);
+  constexpr int kPerGroup = kFlush / kKC;
+  auto wait_chunk = [&](int c) { mbar_wait(smem_u32(&mbar[c % kStages]), static_cast<uint32_t>((c / kStages) & 1)); };
+  if (warp == kThreads / 32) {
+    // ------------------------------- MMA-issue warp -------------------------------
+    const uint64_t desc_hi = (static_cast<uint64_t>(NRP & 0x3FFF) << 16) | (static_cast<uint64_t>(8) << 32) | (1ull << 46);
+    for (int c = 0; c < nchunk; ++c) {
+      const int st = c % kStages;
+      mbar_wait(smem_u32(&full[st]), static_cast<uint32_t>((c / kStages) & 1));
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       if (lane == 0) {
-        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        const uint32_t ah = smem_u32(a_hi), al = smem_u32(a_lo), bh = smem_u32(b_hi), bl = smem_u32(b_lo);
-        const int64_t left = red_len - k0;
+        const uint32_t base = smem_u32(planes + static_cast<size_t>(st) * 4 * PLANE);
+        // descriptors differ only in the 14-bit start-address field (16-byte units): + kstep per MMA k-step
+        const uint64_t dah0 = desc_hi | ((base >> 4) & 0x3FFF);
+        const uint64_t dal0 = dah0 + PLANE, dbh0 = dah0 + 2 * PLANE, dbl0 = dah0 + 3 * PLANE;
+        const int64_t left = red_len - static_cast<int64_t>(c) * kKC;
         const int ksteps = (static_cast<int>(left < kKC ? left : kKC) + 7) / 8;           // skip all-zero k-steps
+        const bool fresh = (c % kPerGroup) == 0;          // first chunk of a flush group overwrites the accumulator
+        const uint32_t acc = tmem_d + static_cast<uint32_t>(((c / kPerGroup) & 1) * kMaxN);
         // small terms first: while they accumulate, the accumulator is ~2^-11 of its final size and so are the
-        // truncation errors of the tensor core's adds; only the ksteps hi*hi adds see the full magnitude
-        for (int ks = 0; ks < ksteps; ++ks) {
-          const uint64_t dah = make_desc(ah + ks * kstep * 16, NRP, 8);
-          const uint64_t dal = make_desc(al + ks * kstep * 16, NRP, 8);
-          const uint64_t dbh = make_desc(bh + ks * kstep * 16, NRP, 8);
-          const uint64_t dbl = make_desc(bl + ks * kstep * 16, NRP, 8);
-          mma_tf32(tmem_d, dal, dbl, idesc, (first && ks == 0) ? 0u : 1u);     // lo * lo
-          mma_tf32(tmem_d, dal, dbh, idesc, 1u);                                // lo * hi
-          mma_tf32(tmem_d, dah, dbl, idesc, 1u);                                // hi * lo
+        // truncation errors of the tensor core's adds.  lo*lo (2^-22 relative) is below the fp32 rounding of the
+        // result and is left out (3xTF32).
+#pragma unroll
+        for (int ks = 0; ks < kKC / 8; ++ks) {
+          if (ks < ksteps) {
+            mma_tf32(acc, dal0 + ks * kstep, dbh0 + ks * kstep, idesc, (fresh && ks == 0) ? 0u : 1u);   // lo * hi
+            mma_tf32(acc, dah0 + ks * kstep, dbl0 + ks * kstep, idesc, 1u);                             // hi * lo
+          }
         }
-        for (int ks = 0; ks < ksteps; ++ks) {
-          const uint64_t dah = make_desc(ah + ks * kstep * 16, NRP, 8);
-          const uint64_t dbh = make_desc(bh + ks * kstep * 16, NRP, 8);
-          mma_tf32(tmem_d, dah, dbh, idesc, 1u);                                // hi * hi
-        }
-        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar)
+#pragma unroll
+        for (int ks = 0; ks < kKC / 8; ++ks)
+          if (ks < ksteps) mma_tf32(acc, dah0 + ks * kstep, dbh0 + ks * kstep, idesc, 1u);              // hi * hi
+        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
+                         smem_u32(&mbar[st]))
                      : "memory");
       }
       __syncwarp();
     }
-    first = false;
-    if (k0 + kKC < red_len) load_chunk(k0 + kKC);      // next chunk's global loads fly while the MMAs run
-    if (OP == kTN && do_colsum && threadIdx.x >= 128 && static_cast<int>(threadIdx.x) - 128 < nt) {
-      // bias gradient from the staged G planes (hi + lo = g to 2^-23): feature n = threadIdx.x - 128, 64 rows
-      const int n = threadIdx.x - 128;
-#pragma unroll 4
-      for (int c = 0; c < kKC / 4; ++c) {
-        const float4 h = b_hi[c * NRP + n], l = b_lo[c * NRP + n];
-        csum += ((h.x + l.x) + (h.y + l.y)) + ((h.z + l.z) + (h.w + l.w));
+  } else {
+    // ------------------------------- staging warps -------------------------------
+    if (nchunk > 0) load_chunk(0, va0, vb0);
+    if (nchunk > 1) load_chunk(kKC, va1, vb1);
+    auto step = [&](int c, float4 (&va)[kLd], float4 (&vb)[kLd]) {
+      const int st = c % kStages;
+      float4* a_hi = planes + static_cast<size_t>(st) * 4 * PLANE;
+      float4* a_lo = a_hi + PLANE;
+      float4* b_hi = a_lo + PLANE;
+      float4* b_lo = b_hi + PLANE;
+      if (c >= kStages) wait_chunk(c - kStages);           // the MMAs that read this stage are done (long ago)
+      // ---- split (hi / lo) and store this chunk ----
+      if (OP == kNN) { store_direct(va, a_hi, a_lo); store_transposed(vb, nt / 4, b_hi, b_lo); }
+      else if (OP == kNT) { store_direct(va, a_hi, a_lo); store_direct(vb, b_hi, b_lo); }
+      else { store_transposed(va, kBM / 4, a_hi, a_lo); store_transposed(vb, nt / 4, b_hi, b_lo); }
+      if (OP == kTN && do_colsum) {
+#pragma unroll
+        for (int i = 0; i < kLd; ++i) {
+          csum4[i].x += vb[i].x; csum4[i].y += vb[i].y; csum4[i].z += vb[i].z; csum4[i].w += vb[i].w;
+        }
       }
+      if (c + 2 < nchunk) load_chunk(static_cast<int64_t>(c + 2) * kKC, va, vb);   // refill this register set
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // generic-proxy stores -> async proxy (MMA)
+      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+      __syncwarp();
+      if (lane == 0)
+        asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&full[st])) : "memory");
+      // ---- drain the previous flush group while this chunk's MMAs run ----
+      if (c > 0 && (c % kPerGroup) == 0) {
+        wait_chunk(c - 1);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        drain(static_cast<uint32_t>((((c - 1) / kPerGroup) & 1) * kMaxN));
+      }
+    };
+    for (int c = 0; c < nchunk; c += 2) {
+      step(c, va0, vb0);
+      if (c + 1 < nchunk) step(c + 1, va1, vb1);
     }
-    mbar_wait(bar, parity);                             // MMAs of this chunk are done: planes may be overwritten
-    parity ^= 1;
-    if (OP == kTN && do_colsum) __syncthreads();        // the column-sum readers are done with the planes too
-    if ((k0 + kKC) % kFlush == 0 || k0 + kKC >= red_len) {
+    if (nchunk > 0) {
+      wait_chunk(nchunk - 1);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-      drain();
-      first = true;                                     // the next MMA overwrites the accumulator
+      drain(static_cast<uint32_t>((((nchunk - 1) / kPerGroup) & 1) * kMaxN));
     }
   }
 
   // ---- epilogue: TMEM lane 32*(warp%4) + lane = output row; warps 0-3 take the even 32-column groups, 4-7 the odd ----
+  // The accumulator registers hold one output ROW per lane (TMEM lane = row).  Writing them straight out would make
+  // every store instruction touch 32 different rows with 16 bytes each; instead the tile goes through shared memory
+  // (the operand stages are free: the last MMAs have completed) and leaves as full 512-byte row segments.
   const int d_row = 32 * (warp & 3) + lane;
+  constexpr int OP_PITCH = kMaxN + 4;                              // floats; +4 keeps float4 alignment, spreads banks
+  float* otile = reinterpret_cast<float*>(smem_raw);               // [kBM][OP_PITCH] = 67.6 KB
+  if (warp < kThreads / 32) {
+    if (c0 < nt) {
 #pragma unroll
-  for (int gq = 0; gq < 2; ++gq) {
-    const int c0 = 32 * (warp >> 2) + 64 * gq;
-    if (c0 >= nt) continue;
-    uint32_t v[32];
-#pragma unroll
-    for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(racc[gq][i]);
-    float* o = nullptr;
-    bool row_ok;
-    if (OP == kTN) {
-      const int feat = a0 + d_row;
-      row_ok = feat < K;
-      o = out + (static_cast<int64_t>(bz) * K + feat) * U + n0 + c0;
-    } else {
-      const int64_t row = m0 + d_row;
-      row_ok = row < M;
-      o = out + row * n_total + n0 + c0;
+      for (int i = 0; i < 32; i += 4)
+        *reinterpret_cast<float4*>(otile + d_row * OP_PITCH + c0 + i) =
+            make_float4(racc[i], racc[i + 1], racc[i + 2], racc[i + 3]);
     }
-    if (row_ok) {
-      const bool vec_out = (n_total % 4 == 0) && (n0 + c0 + 32 <= n_total) &&
-                           ((reinterpret_cast<uintptr_t>(out) & 15) == 0);
-      if (vec_out) {
-#pragma unroll
-        for (int i = 0; i < 32; i += 4) {
-          float4 r = make_float4(__uint_as_float(v[i]), __uint_as_float(v[i + 1]), __uint_as_float(v[i + 2]),
-                                 __uint_as_float(v[i + 3]));
-          if (OP == kNN && bias) {       // scalar loads: the bias may be an unaligned view of a flat buffer
-            const float* bp = bias + n0 + c0 + i;
-            r.x += __ldg(bp); r.y += __ldg(bp + 1); r.z += __ldg(bp + 2); r.w += __ldg(bp + 3);
-          }
-          *reinterpret_cast<float4*>(o + i) = r;
-        }
-      } else {
-#pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          const int col = n0 + c0 + i;
-          if (col < n_total) o[i] = __uint_as_float(v[i]) + ((OP == kNN && bias) ? __ldg(bias + col) : 0.f);
-        }
+    asm volatile("bar.sync 1, %0;" ::"r"(kThreads) : "memory");    // staging warps only
+    const int64_t out_rows = (OP == kTN) ? K : M;                  // rows of the output matrix this tile maps to
+    const int64_t row_base = (OP == kTN) ? a0 : m0;
+    float* obase = (OP == kTN) ? out + static_cast<int64_t>(bz) * K * U : out;
+    const bool vec_out = (n_total % 4 == 0) && ((reinterpret_cast<uintptr_t>(out) & 15) == 0);
+    const int col = n0 + 4 * lane;                                 // this lane's 4 columns of every row
+    float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (OP == kNN && bias) {                                       // scalar loads: the bias may be an unaligned view
+      if (col + 0 < n_total) bv.x = __ldg(bias + col + 0);
+      if (col + 1 < n_total) bv.y = __ldg(bias + col + 1);
+      if (col + 2 < n_total) bv.z = __ldg(bias + col + 2);
+      if (col + 3 < n_total) bv.w = __ldg(bias + col + 3);
+    }
+    for (int r = warp; r < kBM; r += kThreads / 32) {              // one full row segment per warp instruction
+      const int64_t row = row_base + r;
+      if (row >= out_rows || 4 * lane >= nt) continue;
+      float4 v = *reinterpret_cast<const float4*>(otile + r * OP_PITCH + 4 * lane);
+      v.x += bv.x; v.y += bv.y; v.z += bv.z; v.w += bv.w;
+      float* o = obase + row * n_total + col;
+      if (vec_out && col + 3 < n_total) *reinterpret_cast<float4*>(o) = v;
+      else {
+        if (col + 0 < n_total) o[0] = v.x;
+        if (col + 1 < n_total) o[1] = v.y;
+        if (col + 2 < n_total) o[2] = v.z;
+        if (col + 3 < n_total) o[3] = v.w;
       }
     }
   }
-  if (OP == kTN && do_colsum && threadIdx.x >= 128 && static_cast<int>(threadIdx.x) - 128 < nt) {
-    const int col = n0 + static_cast<int>(threadIdx.x) - 128;
-    if (col < U) colsum_part[static_cast<int64_t>(bz) * U + col] = csum;
+  if (OP == kTN && do_colsum && warp < kThreads / 32) {
+    // lane = row within a chunk, (warp + 8 i) = 4-feature group: fixed xor tree over the 32 rows -> deterministic
+#pragma unroll
+    for (int i = 0; i < kLd; ++i) {
+      float4 t = csum4[i];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        t.x += __shfl_xor_sync(0xffffffffu, t.x, o); t.y += __shfl_xor_sync(0xffffffffu, t.y, o);
+        t.z += __shfl_xor_sync(0xffffffffu, t.z, o); t.w += __shfl_xor_sync(0xffffffffu, t.w, o);
+      }
+      const int col = n0 + 4 * (warp + (kThreads / 32) * i);
+      if (lane == 0 && 4 * (warp + (kThreads / 32) * i) < nt) {
+        float* dst = colsum_part + static_cast<int64_t>(bz) * U;
+        if (col + 0 < U) dst[col + 0] = t.x;
+        if (col + 1 < U) dst[col + 1] = t.y;
+        if (col + 2 < U) dst[col + 2] = t.z;
+        if (col + 3 < U) dst[col + 3] = t.w;
+      }
+    }
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
-  if (warp == 0) {
+  if (warp == kThreads / 32) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d),
-                 "r"(static_cast<uint32_t>(kMaxN))
+                 "r"(static_cast<uint32_t>(2 * kMaxN))
                  : "memory");
   }
 }
 
 template <int OP>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kCtaThreads)
 dense_tc_kernel(const float* __restrict__ A, const float* __restrict__ B, int64_t M, int K, int U,
                 const float* __restrict__ bias, float* __restrict__ out, int64_t rows_per_split, int vec_a,
                 int vec_b) {
@@ -433,7 +495,7 @@ struct TnGroup {
   TnOutput o[kMaxGroup];
 };
 
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kCtaThreads)
 tn_grouped_kernel(const __grid_constant__ TnGroup grp, float* __restrict__ ws) {
   __shared__ int which;
   if (threadIdx.x == 0) {
@@ -485,12 +547,12 @@ tn_grouped_reduce_kernel(const __grid_constant__ TnGroup grp, const float* __res
   *dst = acc;
 }
 
-constexpr size_t kSmemBytes = 4 * (kKC / 4) * (kBM + 1) * sizeof(float4);   // 4 planes (A hi/lo, B hi/lo) = 64.5 KB
+constexpr size_t kSmemBytes = kStages * 4 * (kKC / 4) * (kBM + 1) * sizeof(float4);   // 3 stages x 4 planes x 16.5 KB
 
 inline int tn_splits(int64_t M, int K, int U) {
   const int tiles = ceil_div(K, kBM) * ceil_div(U, kMaxN);
   int64_t s = std::max<int64_t>(1, (2 * kNumSM) / tiles);
-  s = std::min<int64_t>(s, std::max<int64_t>(1, ceil_div<int64_t>(M, 2 * kKC)));
+  s = std::min<int64_t>(s, std::max<int64_t>(1, ceil_div<int64_t>(M, 4 * kKC)));
   return static_cast<int>(s);
 }
 
@@ -501,7 +563,7 @@ inline int64_t grouped_rows_per_split(int n, const int64_t* M, const int32_t* K,
   for (int i = 0; i < n; ++i)
     chunk_tiles += ceil_div<int64_t>(std::max<int64_t>(M[i], 1), kKC) * ceil_div(K[i], kBM) * ceil_div(U[i], kMaxN);
   const int64_t target = 2LL * kNumSM;
-  const int64_t per_cta = std::max<int64_t>(2, ceil_div<int64_t>(chunk_tiles, target));
+  const int64_t per_cta = std::max<int64_t>(4, ceil_div<int64_t>(chunk_tiles, target));
   return per_cta * kKC;
 }
 
@@ -539,13 +601,13 @@ int kgcnn_dense_tc(int op, const float* A, const float* B, int64_t M, int K, int
   }
   if (op == tc::kNN) {
     dim3 grid(static_cast<unsigned>(ceil_div<int64_t>(M, tc::kBM)), ceil_div(U, tc::kMaxN));
-    tc::dense_tc_kernel<tc::kNN><<<grid, tc::kThreads, tc::kSmemBytes, st>>>(
+    tc::dense_tc_kernel<tc::kNN><<<grid, tc::kCtaThreads, tc::kSmemBytes, st>>>(
         A, B, M, K, U, bias, out, 0, (K % 4 == 0 && al16(A)) ? 1 : 0, (U % 4 == 0 && al16(B)) ? 1 : 0);
     return finish_launch();
   }
   if (op == tc::kNT) {
     dim3 grid(static_cast<unsigned>(ceil_div<int64_t>(M, tc::kBM)), ceil_div(K, tc::kMaxN));
-    tc::dense_tc_kernel<tc::kNT><<<grid, tc::kThreads, tc::kSmemBytes, st>>>(
+    tc::dense_tc_kernel<tc::kNT><<<grid, tc::kCtaThreads, tc::kSmemBytes, st>>>(
         A, B, M, K, U, nullptr, out, 0, (U % 4 == 0 && al16(A)) ? 1 : 0, (U % 4 == 0 && al16(B)) ? 1 : 0);
     return finish_launch();
   }
@@ -554,7 +616,7 @@ int kgcnn_dense_tc(int op, const float* A, const float* B, int64_t M, int K, int
   const int64_t rows_per_split = ceil_div<int64_t>(ceil_div<int64_t>(M, S), tc::kKC) * tc::kKC;
   float* partial = static_cast<float*>(workspace);
   dim3 grid(ceil_div(K, tc::kBM), ceil_div(U, tc::kMaxN), S);
-  tc::dense_tc_kernel<tc::kTN><<<grid, tc::kThreads, tc::kSmemBytes, st>>>(
+  tc::dense_tc_kernel<tc::kTN><<<grid, tc::kCtaThreads, tc::kSmemBytes, st>>>(
       A, B, M, K, U, nullptr, partial, rows_per_split, (K % 4 == 0 && al16(A)) ? 1 : 0,
       (U % 4 == 0 && al16(B)) ? 1 : 0);
   const int64_t n = static_cast<int64_t>(K) * U;
@@ -630,7 +692,7 @@ int kgcnn_dense_tn_grouped(int n, const float* const* X, const float* const* G, 
       grp.n_problems += 1;
     }
     if (grp.n_problems == 0) continue;
-    tc::tn_grouped_kernel<<<static_cast<unsigned>(grp.total_ctas), tc::kThreads, tc::kSmemBytes, st>>>(grp, ws);
+    tc::tn_grouped_kernel<<<static_cast<unsigned>(grp.total_ctas), tc::kCtaThreads, tc::kSmemBytes, st>>>(grp, ws);
     tc::tn_grouped_reduce_kernel<<<static_cast<unsigned>(ceil_div<int64_t>(grp.total_elems, 256)), 256, 0, st>>>(grp, ws);
     launches += 2;
   }
