@@ -135,14 +135,22 @@ __device__ __forceinline__ void store_direct(const float4 (&v)[kLd], float4* __r
 }
 
 // mn = feature, k = row of the global matrix (transposed on the way in): rows [row0, row0+kKC), features
-// [f0, f0+4*nchunks).  Consecutive threads take consecutive rows -> the scalar stores hit 32 different banks.
+// [f0, f0+4*nchunks).  Thread -> (row k, 4-feature group j): within a warp 16 rows x 2 adjacent groups, so a load
+// instruction reads one full 32-byte sector per row and the scalar stores hit 32 different banks; register i is
+// the 16-row block, the warp selects the pair of feature groups.
+__device__ __forceinline__ void transposed_coords(int i, int& k, int& j) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  k = 16 * i + (lane & 15);
+  j = 2 * warp + (lane >> 4);
+}
+static_assert(kLd * 16 == kKC && 2 * (kThreads / 32) == kBM / 4, "transposed staging map covers a 32 x 128 chunk");
 __device__ __forceinline__ void load_transposed(float4 (&v)[kLd], const float* __restrict__ g, int64_t row0,
                                                 int64_t row_end, int f0, int f_end, int ld, int nchunks, bool vec_ok,
                                                 bool fast) {
 #pragma unroll
   for (int i = 0; i < kLd; ++i) {
-    const int it = threadIdx.x + i * kThreads;
-    const int k = it % kKC, j = it / kKC;
+    int k, j;
+    transposed_coords(i, k, j);
     if (fast) v[i] = __ldg(reinterpret_cast<const float4*>(g + (row0 + k) * ld + f0 + 4 * j));
     else v[i] = (j < nchunks) ? load4(g, row0 + k, row_end, f0 + 4 * j, f_end, ld, vec_ok)
                               : make_float4(0.f, 0.f, 0.f, 0.f);
@@ -155,8 +163,8 @@ __device__ __forceinline__ void store_transposed(const float4 (&v)[kLd], int nch
   float* ls = reinterpret_cast<float*>(lo);
 #pragma unroll
   for (int i = 0; i < kLd; ++i) {
-    const int it = threadIdx.x + i * kThreads;
-    const int k = it % kKC, j = it / kKC;
+    int k, j;
+    transposed_coords(i, k, j);
     if (j >= nchunks) continue;
     const float vv[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
     const int base = ((k >> 2) * NRP + 4 * j) * 4 + (k & 3);
@@ -406,23 +414,24 @@ dense_tc_body(const float* __restrict__ A, const float* __restrict__ B, int64_t 
     }
   }
   if (OP == kTN && do_colsum && warp < kThreads / 32) {
-    // lane = row within a chunk, (warp + 8 i) = 4-feature group: fixed xor tree over the 32 rows -> deterministic
+    // registers i = the two 16-row blocks of a chunk; lanes (l & 15) = rows; (2 warp + (l >> 4)) = 4-feature group:
+    // fixed order (i, then xor tree over 16 lanes) -> deterministic
+    float4 t = csum4[0];
 #pragma unroll
-    for (int i = 0; i < kLd; ++i) {
-      float4 t = csum4[i];
+    for (int i = 1; i < kLd; ++i) { t.x += csum4[i].x; t.y += csum4[i].y; t.z += csum4[i].z; t.w += csum4[i].w; }
 #pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        t.x += __shfl_xor_sync(0xffffffffu, t.x, o); t.y += __shfl_xor_sync(0xffffffffu, t.y, o);
-        t.z += __shfl_xor_sync(0xffffffffu, t.z, o); t.w += __shfl_xor_sync(0xffffffffu, t.w, o);
-      }
-      const int col = n0 + 4 * (warp + (kThreads / 32) * i);
-      if (lane == 0 && 4 * (warp + (kThreads / 32) * i) < nt) {
-        float* dst = colsum_part + static_cast<int64_t>(bz) * U;
-        if (col + 0 < U) dst[col + 0] = t.x;
-        if (col + 1 < U) dst[col + 1] = t.y;
-        if (col + 2 < U) dst[col + 2] = t.z;
-        if (col + 3 < U) dst[col + 3] = t.w;
-      }
+    for (int o = 8; o > 0; o >>= 1) {
+      t.x += __shfl_xor_sync(0xffffffffu, t.x, o); t.y += __shfl_xor_sync(0xffffffffu, t.y, o);
+      t.z += __shfl_xor_sync(0xffffffffu, t.z, o); t.w += __shfl_xor_sync(0xffffffffu, t.w, o);
+    }
+    const int j = 2 * warp + (lane >> 4);
+    if ((lane & 15) == 0 && 4 * j < nt) {
+      const int col = n0 + 4 * j;
+      float* dst = colsum_part + static_cast<int64_t>(bz) * U;
+      if (col + 0 < U) dst[col + 0] = t.x;
+      if (col + 1 < U) dst[col + 1] = t.y;
+      if (col + 2 < U) dst[col + 2] = t.z;
+      if (col + 3 < U) dst[col + 3] = t.w;
     }
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
