@@ -15,6 +15,7 @@ _p = ctypes.c_void_p
 _i = ctypes.c_int
 _l = ctypes.c_int64
 _f = ctypes.c_float
+_d = ctypes.c_double
 _z = ctypes.c_size_t
 
 # name -> (restype, argtypes); mirrors include/kgcnn_b200.h one to one (tests/test_abi.py checks it)
@@ -51,6 +52,12 @@ SIGNATURES = {
     "kgcnn_painn_msg_nodes": (_i, [_p, _p, _p, _p, _p, _p, _p, _i, _l, _l, _i, _i, _p, _p, _p]),
     "kgcnn_painn_msg_senders": (_i, [_p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _l, _l, _i, _i, _p, _p, _p]),
     "kgcnn_painn_msg_edges": (_i, [_p, _p, _p, _p, _p, _p, _p, _p, _l, _i, _i, _p, _p, _p]),
+    "kgcnn_offsets_workspace_bytes": (_z, [_l]),
+    "kgcnn_offsets_from_counts": (_i, [_p, _l, _p, _p, _z, _p]),
+    "kgcnn_angle_count": (_i, [_p, _l, _l, _p, _p, _i, _i, _i, _i, _i, _p, _p]),
+    "kgcnn_angle_emit": (_i, [_p, _p, _l, _l, _p, _p, _i, _i, _i, _i, _i, _p, _p, _l, _p, _p, _p, _p]),
+    "kgcnn_range_count": (_i, [_p, _i, _p, _l, _l, _i, _i, _d, _i, _i, _i, _p, _p]),
+    "kgcnn_range_emit": (_i, [_p, _i, _p, _l, _l, _i, _i, _d, _i, _i, _i, _p, _p, _p, _p, _p]),
     "kgcnn_adam_clipnorm": (_i, [_p, _p, _p, _p, _p, _p, _l, _f, _f, _f, _f, _f, _p, _p]),
 }
 

@@ -273,6 +273,47 @@ int kgcnn_adam_clipnorm(float* params, const float* grads, float* m, float* v, c
                         const float* sumsq, int64_t n, float lr, float beta1, float beta2, float eps,
                         float clipnorm, int32_t* step, kgcnn_stream_t stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Batch graph construction (the step in front of the path).  Two-pass: count -> offsets ->
+ * emit; the host reads offsets[n] (one scalar) to size the output.  Integer outputs are bit-exact against the
+ * reference's NumPy code.
+ *
+ * kgcnn_offsets_from_counts: offsets[0] = 0, offsets[i+1] = sum(count[0..i]) in int64.
+ *
+ * Angle triples -- kgcnn/graph/adj.py:300-385 (get_angle_indices, check_sorted=True ordering) for every graph
+ * of the batch at once.  idx_cm = batch-indexed int32 index, column-major [2,M] (kgcnn_shift_index);
+ * (rowptr, perm) = CSR of column pos_fix (kgcnn_plan_build; perm NULL when that column is ascending);
+ * pos_fix / pos_ij follow adj.py:333-335 (pos_k = 1 - pos_fix).  allow_self with pos_fix != pos_ij is
+ * KGCNN_E_UNSUPPORTED.  Outputs in SAMPLE indexing like the reference: ijk[A,3] node triples, ij_k[A,2] edge
+ * labels (nullable), angle_row_splits[B+1] (nullable).
+ *
+ * Range neighbours -- kgcnn/graph/adj.py:466-481 (coordinates_to_distancematrix) + :537-593
+ * (define_adjacency_from_distance) as called by SetRange (kgcnn/graph/preprocessor.py:302-304).  xyz is
+ * [N,3] fp32 or fp64 (is_f64); distances are evaluated in that dtype in NumPy's operation order.
+ * use_max_distance = 0 <=> max_distance=None; max_neighbours < 0 <=> None.  max_nodes >= the largest graph
+ * (one distance row per warp is staged in shared memory; KGCNN_E_UNSUPPORTED beyond ~3000 atoms per graph).
+ * Ties in the neighbour ranking are broken by index (np.argsort leaves them unspecified).  Outputs: edges[M,2]
+ * int64 in sample indexing, row-major order of the adjacency matrix; dist[M] (nullable, coordinate dtype);
+ * edge_row_splits[B+1] (nullable).
+ * ------------------------------------------------------------------------------------------- */
+size_t kgcnn_offsets_workspace_bytes(int64_t n);
+int kgcnn_offsets_from_counts(const int32_t* count, int64_t n, int64_t* offsets /*[n+1]*/, void* workspace,
+                              size_t workspace_bytes, kgcnn_stream_t stream);
+int kgcnn_angle_count(const int32_t* idx_cm, int64_t M, int64_t N, const int32_t* rowptr, const int32_t* perm,
+                      int pos_fix, int pos_ij, int allow_multi, int allow_reverse, int allow_self, int32_t* count,
+                      kgcnn_stream_t stream);
+int kgcnn_angle_emit(const int64_t* idx_sample, const int32_t* idx_cm, int64_t M, int64_t N, const int32_t* rowptr,
+                     const int32_t* perm, int pos_fix, int pos_ij, int allow_multi, int allow_reverse,
+                     int allow_self, const int64_t* offsets, const int64_t* edge_row_splits, int64_t B,
+                     int64_t* ijk, int64_t* ij_k, int64_t* angle_row_splits, kgcnn_stream_t stream);
+int kgcnn_range_count(const void* xyz, int is_f64, const int64_t* node_row_splits, int64_t B, int64_t N,
+                      int max_nodes, int use_max_distance, double max_distance, int max_neighbours, int exclusive,
+                      int self_loops, int32_t* count, kgcnn_stream_t stream);
+int kgcnn_range_emit(const void* xyz, int is_f64, const int64_t* node_row_splits, int64_t B, int64_t N,
+                     int max_nodes, int use_max_distance, double max_distance, int max_neighbours, int exclusive,
+                     int self_loops, const int64_t* offsets, int64_t* edges, void* dist, int64_t* edge_row_splits,
+                     kgcnn_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
