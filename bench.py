@@ -471,7 +471,9 @@ def run_force(args, rank, world, device, kind):
     model, train_step, data = build(device, batch, seed=rank)
     if world > 1:
         from gcnn_keras_b200.distributed import broadcast_parameters
-    captured = CapturedForceTrainStep(train_step, data, device)
+    # C4: the 'kj' angle triples (278 MB per batch) are rebuilt on the device from the pair list in the e2e leg
+    device_angles = "kj" if (kind == "hdnnp" and not args.host_angles) else None
+    captured = CapturedForceTrainStep(train_step, data, device, device_angles=device_angles)
     n_params = sum(p.numel() for p in model.parameters())
 
     ms_step, clocks = timed_steps_with_l2_flush(lambda: captured.run(load=False), args.steps, args.warmup, world,
@@ -494,7 +496,9 @@ def run_force(args, rank, world, device, kind):
         "loss": loss_value,
         "e2e": {"value": total_mol / (ms_e2e * 1e-3), "unit": "molecules/s",
                 "h2d_bytes_per_step": captured.static.h2d_bytes, "d2h_bytes_per_step": 4 + (
-                    0 if captured.flags is None else captured.flags.numel() * 4), "ms_per_step": ms_e2e},
+                    0 if captured.flags is None else captured.flags.numel() * 4), "ms_per_step": ms_e2e,
+                **({"angle_triples": "built on the device from the pair list (kgcnn_angle_count/emit), not copied"}
+                   if device_angles else {})},
         "gpu_launches": captured.kernels_per_step * args.steps,
         "our_kernels_per_step": captured.kernels_per_step,
         "clocks": clocks,
@@ -679,6 +683,8 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
     ap.add_argument("--batch", type=int, default=0, help="molecules per GPU (0 = the config's batch size)")
+    ap.add_argument("--host-angles", action="store_true",
+                    help="hdnnp e2e leg: copy the angle triples from the host instead of building them on the device")
     ap.add_argument("--profile", action="store_true", help="print a CUPTI kernel table to stderr (diagnostics)")
     args = ap.parse_args()
     global PROFILE

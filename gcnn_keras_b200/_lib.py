@@ -58,6 +58,7 @@ SIGNATURES = {
     "kgcnn_angle_emit": (_i, [_p, _p, _l, _l, _p, _p, _i, _i, _i, _i, _i, _p, _p, _l, _p, _p, _p, _p]),
     "kgcnn_range_count": (_i, [_p, _i, _p, _l, _l, _i, _i, _d, _i, _i, _i, _p, _p]),
     "kgcnn_range_emit": (_i, [_p, _i, _p, _l, _l, _i, _i, _d, _i, _i, _i, _p, _p, _p, _p, _p]),
+    "kgcnn_segment_softmax": (_i, [_p, _p, _p, _l, _l, _i, _i, _p, _p]),
     "kgcnn_adam_clipnorm": (_i, [_p, _p, _p, _p, _p, _p, _l, _f, _f, _f, _f, _f, _p, _p]),
 }
 

@@ -327,6 +327,40 @@ def segment_reduce(v, rel, op="sum"):
     return y + (_SegmentSum.apply(v * weights, rel) - _SegmentSum.apply(v.detach() * weights, rel))
 
 
+class _SegmentSoftmax(torch.autograd.Function):
+    """alpha = segment_softmax(a) over rel (kgcnn/ops/segment.py:4-24), one fused launch.  The backward
+    da = alpha * (g - gather(segment_sum(alpha * g))) is written with the closed primitives on the SAVED OUTPUT,
+    so it can be differentiated again (attention layers inside a force model)."""
+
+    @staticmethod
+    def forward(ctx, a, rel, normalize):
+        _need_cuda(a)
+        a2 = _f32c(_flat2d(a))
+        out = torch.zeros_like(a2)
+        perm = rel.perm
+        check(_lib.lib().kgcnn_segment_softmax(_ptr(a2), _ptr(rel.rowptr), _ptr(perm), rel.n_targets, rel.n_elements,
+                                               int(a2.shape[1]), int(bool(normalize)), _ptr(out), _stream()),
+              "kgcnn_segment_softmax")
+        out = out.reshape(a.shape)
+        ctx.rel = rel
+        ctx.save_for_backward(out)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        (alpha,) = ctx.saved_tensors
+        ag = alpha * g
+        t = _SegmentSum.apply(ag.contiguous(), ctx.rel)
+        return ag - alpha * _Gather.apply(t, ctx.rel), None, None
+
+
+def segment_softmax(a, rel, normalize=True):
+    """Softmax of a[E, ...] within the segments of `rel`, returned in the original element order."""
+    if a.shape[0] != rel.n_elements:
+        raise ValueError("segment_softmax: %d rows for a relation of %d elements" % (a.shape[0], rel.n_elements))
+    return _SegmentSoftmax.apply(a, rel, normalize)
+
+
 def gather_mul_segment_sum(x, w, rel_out, rel_src):
     """Fused  y_i = sum_{e->i} x[s_e] * w_e  (SchNet cfconv, PaiNN scalar channel, GCN)."""
     tail = tuple(x.shape[1:])

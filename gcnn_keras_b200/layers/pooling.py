@@ -120,6 +120,54 @@ PoolingWeightedNodes = PoolingWeightedEmbedding
 PoolingWeightedGlobalEdges = PoolingWeightedEmbedding
 
 
+@register_keras_serializable(package="kgcnn", name="PoolingLocalEdgesAttention")
+class PoolingLocalEdgesAttention(GraphBaseLayer):
+    """kgcnn/layers/pooling.py:464-546.  call([nodes, edges, attention, tensor_index]):
+    n_i = sum_j softmax_j(a_ij) e_ij.  Two launches: fused segment softmax (original edge order) and the fused
+    edge*alpha -> CSR segment sum; the reference runs argsort, 3 permutation gathers, segment_max, 2 gathers, exp,
+    2 segment_sums and a scatter."""
+
+    def __init__(self, pooling_index=0, **kwargs):
+        super().__init__(**kwargs)
+        self.pooling_index = pooling_index
+
+    def call(self, inputs, **kwargs):
+        nodes, edges, attention, index = self.assert_ragged_input_rank(inputs)
+        rel = get_plan(index, nodes).relation(self.pooling_index)
+        alpha = F.segment_softmax(attention.values, rel)
+        e = edges.values
+        if e.dim() == 2 and alpha.dim() == 2 and alpha.shape[1] in (1, e.shape[1]):
+            out = F._GMS_edge.apply(e, alpha, rel)
+        else:
+            out = F.segment_reduce(e * alpha, rel, F.OP_SUM)
+        return nodes.with_values(out)
+
+    def get_config(self):
+        config = super().get_config()
+        config.update({"pooling_index": self.pooling_index})
+        return config
+
+
+PoolingLocalMessagesAttention = PoolingLocalEdgesAttention
+
+
+@register_keras_serializable(package="kgcnn", name="PoolingEmbeddingAttention")
+class PoolingEmbeddingAttention(GraphBaseLayer):
+    """kgcnn/layers/pooling.py:550-599.  call([nodes, attention]) -> dense [B, F]: s = sum_i softmax_i(a_i) n_i."""
+
+    def call(self, inputs, **kwargs):
+        nodes, attention = self.assert_ragged_input_rank(inputs)
+        rel = nodes.partition.relation()
+        alpha = F.segment_softmax(attention.values, rel)
+        x = nodes.values
+        if x.dim() == 2 and alpha.dim() == 2 and alpha.shape[1] in (1, x.shape[1]):
+            return F._GMS_edge.apply(x, alpha, rel)
+        return F.segment_reduce(x * alpha, rel, F.OP_SUM)
+
+
+PoolingNodesAttention = PoolingEmbeddingAttention
+
+
 @register_keras_serializable(package="kgcnn", name="RelationalPoolingLocalEdges")
 class RelationalPoolingLocalEdges(GraphBaseLayer):
     """kgcnn/layers/pooling.py:603-675.  The reference scatters with tensor_scatter_nd_add on

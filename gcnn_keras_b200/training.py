@@ -114,11 +114,18 @@ class StaticBatch:
     """Pinned host staging + fixed device buffers for one batch signature (the shapes a CUDA graph was
     captured for).  `load()` is asynchronous on the current stream: host arrays -> pinned -> device."""
 
-    def __init__(self, example, device):
+    def __init__(self, example, device, device_angles=None):
+        """device_angles: None, or the `edge_pairing` with which the angle triples are rebuilt ON THE DEVICE from
+        the pair list after every load (gcnn_keras_b200.graph.get_angle_indices) instead of being copied from
+        the host -- at C4 the triples are 97 % of the bytes of a batch."""
         self.device = device
+        self.device_angles = device_angles
         self.shapes = {k: (tuple(v.shape), v.dtype) for k, v in example.items()}
-        self.pinned = {k: torch.from_numpy(v.copy()).pin_memory() for k, v in example.items()}
+        derived = ("angle_index", "angle_splits") if device_angles else ()
+        self.pinned = {k: torch.from_numpy(v.copy()).pin_memory() for k, v in example.items() if k not in derived}
         self.dev = {k: t.to(device) for k, t in self.pinned.items()}
+        for k in derived:
+            self.dev[k] = torch.zeros(example[k].shape, dtype=torch.from_numpy(example[k][:0]).dtype, device=device)
         self.h2d_bytes = sum(t.numel() * t.element_size() for t in self.pinned.values())
 
     def signature_matches(self, batch):
@@ -130,6 +137,21 @@ class StaticBatch:
                 t.copy_(torch.from_numpy(batch[k]))
         for k, t in self.pinned.items():
             self.dev[k].copy_(t, non_blocking=True)
+        if self.device_angles:
+            self._derive_angles()
+
+    def _derive_angles(self):
+        from .graph import get_angle_indices
+        from .ragged import RaggedTensor, RowPartition
+        dev = self.dev
+        nodes = RaggedTensor(dev["xyz"], RowPartition(dev["node_splits"], nvals=int(dev["xyz"].shape[0])))
+        index = RaggedTensor(dev["index"], RowPartition(dev["edge_splits"], nvals=int(dev["index"].shape[0])))
+        ang = get_angle_indices(index, nodes, edge_pairing=self.device_angles)
+        if tuple(ang.values.shape) != tuple(dev["angle_index"].shape):
+            raise ValueError("batch has %d angle triples, the captured signature has %d"
+                             % (int(ang.values.shape[0]), int(dev["angle_index"].shape[0])))
+        dev["angle_index"].copy_(ang.values)
+        dev["angle_splits"].copy_(ang.row_splits)
 
 
 def molecule_batch_to_arrays(b):
@@ -165,11 +187,12 @@ class CapturedForceTrainStep:
     Sortedness of every relation is detected during an eager warm-up (one sync each), trusted during capture,
     and re-validated after every replay from device-side flags (`check()`), so no host sync sits inside a step."""
 
-    def __init__(self, train_step, example_batch, device, make_inputs=default_model_inputs, warmup=3):
+    def __init__(self, train_step, example_batch, device, make_inputs=default_model_inputs, warmup=3,
+                 device_angles=None):
         from . import _lib
         from .plan import PlanMode, clear_plan_cache, plan_mode
         self.train_step = train_step
-        self.static = StaticBatch(molecule_batch_to_arrays(example_batch), device)
+        self.static = StaticBatch(molecule_batch_to_arrays(example_batch), device, device_angles=device_angles)
         self.make_inputs = make_inputs
         self.max_nodes = int(example_batch["node_len"].max())
         self.static.load()

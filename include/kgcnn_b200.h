@@ -314,6 +314,16 @@ int kgcnn_range_emit(const void* xyz, int is_f64, const int64_t* node_row_splits
                      int self_loops, const int64_t* offsets, int64_t* edges, void* dist, int64_t* edge_row_splits,
                      kgcnn_stream_t stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Segment softmax -- kgcnn/ops/segment.py:4-24 (segment_softmax) behind
+ * PoolingLocalEdgesAttention (kgcnn/layers/pooling.py:521-533).  a, out: [E,H] in the ORIGINAL edge order;
+ * (rowptr, perm) = CSR of the pooling column (perm NULL when ascending).  out[e,h] =
+ * exp(a[e,h] - max_seg) / sum_seg exp(a - max_seg)  (normalize = 0 skips the max shift, segment.py:16).
+ * Elements whose id is outside [0, n_out) are not written.
+ * ------------------------------------------------------------------------------------------- */
+int kgcnn_segment_softmax(const float* a, const int32_t* rowptr, const int32_t* perm /*nullable*/, int64_t n_out,
+                          int64_t n_elements, int H, int normalize, float* out, kgcnn_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -97,6 +97,29 @@ def pooling_weighted_local_edges(nodes, edges, index, weights, pooling_method="m
     return nodes.with_values(get)
 
 
+def pooling_local_edges_attention(nodes, edges, attention, index, pooling_index=0, is_sorted=False,
+                                  has_unconnected=True):
+    """PoolingLocalEdgesAttention.call, pooling.py:505-540."""
+    shiftind = _batch_index(index, nodes)
+    nodind = shiftind[:, pooling_index]
+    dens, ats = edges.values, attention.values
+    if not is_sorted:                                          # :522-527
+        node_order = torch.argsort(nodind, stable=True)
+        nodind, dens, ats = nodind[node_order], dens[node_order], ats[node_order]
+    ats = ops.segment_softmax(ats, nodind)                     # :529
+    get = ops.segment_sum(dens * ats, nodind)                  # :530-531
+    if has_unconnected:
+        get = _pad_rows(get, nodes.values.shape[0])
+    return nodes.with_values(get)
+
+
+def pooling_embedding_attention(nodes, attention):
+    """PoolingEmbeddingAttention.call (= PoolingNodesAttention), pooling.py:583-589: dense [B, F]."""
+    batchi = nodes.value_rowids()
+    ats = ops.segment_softmax(attention.values, batchi)
+    return ops.segment_sum(nodes.values * ats, batchi)
+
+
 def pooling_embedding(inputs, pooling_method="mean"):
     """PoolingEmbedding.call (= PoolingNodes), pooling.py:203-219.  Returns a dense [B, F] tensor.
     Trailing empty graphs are dropped by TF's sorted segment op; the product pads them with 0."""

@@ -72,6 +72,14 @@ def _segment_extreme(data, segment_ids, reduce):
     return out.scatter_reduce(0, idx, data, reduce=reduce, include_self=False)
 
 
+def segment_softmax(data, segment_ids, normalize=True):
+    """kgcnn/ops/segment.py:4-24 on SORTED ids: shift by the segment max (:16-19), exp, divide by the segment sum."""
+    if normalize:
+        data = data - segment_ops_by_name("max", data, segment_ids)[segment_ids]
+    data_exp = torch.exp(data)
+    return data_exp / segment_sum(data_exp, segment_ids)[segment_ids]
+
+
 def segment_ops_by_name(segment_name, data, segment_ids):
     """kgcnn/ops/segment.py:27-52."""
     if segment_name in ["segment_mean", "mean", "reduce_mean"]:

@@ -145,3 +145,23 @@ def test_wacsf_oracle_brute_force_formula_and_gradcheck():
     f_a = lambda t: OC.wacsf_ang(zr, xr.with_values(t), oracle_ragged(ijk, [len(ijk)]), ang).values
     assert torch.autograd.gradcheck(f_r, (x,))
     assert torch.autograd.gradcheck(f_a, (x,))
+
+
+def test_attention_pooling_oracle_properties():
+    """segment_softmax (segment.py:4-24): coefficients sum to 1 per non-empty receiver, are invariant under a
+    per-segment shift, and attention pooling of constant edges returns that constant; gradcheck in fp64."""
+    rng = np.random.default_rng(4)
+    node_len, edge_len, index = random_graph_batch(rng, n_graphs=5, sorted_edges=False)
+    nodes = oracle_ragged(np.zeros((int(node_len.sum()), 1)), node_len)
+    E = int(edge_len.sum())
+    att = oracle_ragged(rng.standard_normal((E, 1)), edge_len, torch.float64)
+    ones = oracle_ragged(np.ones((E, 3)), edge_len, torch.float64)
+    o_idx = oracle_ragged(index, edge_len)
+    out = OL.pooling_local_edges_attention(nodes, ones, att, o_idx).values
+    assert bool(((out - 1.0).abs().max(dim=1).values < 1e-12).logical_or(out.abs().max(dim=1).values == 0).all())
+    shifted = OL.pooling_local_edges_attention(nodes, ones, att.with_values(att.values + 5.0), o_idx).values
+    assert float((shifted - out).abs().max()) < 1e-12
+    e = torch.as_tensor(rng.standard_normal((E, 3)), dtype=torch.float64).requires_grad_(True)
+    a = att.values.clone().requires_grad_(True)
+    fn = lambda e_, a_: OL.pooling_local_edges_attention(nodes, ones.with_values(e_), att.with_values(a_), o_idx).values
+    assert torch.autograd.gradcheck(fn, (e, a))
