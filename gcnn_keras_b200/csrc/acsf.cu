@@ -148,93 +148,130 @@ acsf_g4_kernel(const float* __restrict__ xyz, const int32_t* __restrict__ z_atom
   const bool centre_ok = !tset_atom || __ldg(tset_atom + i) >= 0;
   V3 gi = {0.f, 0.f, 0.f};
   const int beg = __ldg(rowptr + i), end = __ldg(rowptr + i + 1);
-  for (int p = beg; p < end; ++p) {
-    const int e = perm ? __ldg(perm + p) : p;
-    const int j = __ldg(idx_j + e), k = __ldg(idx_k + e);
-    const int zj = __ldg(z_atom + j), zk = __ldg(z_atom + k);
-    int r = -1;
-    if (zj >= 0 && zj < zmax && zk >= 0 && zk < zmax) r = __ldg(rev_pair + zj * zmax + zk);
-    V3 gj = {0.f, 0.f, 0.f}, gk = {0.f, 0.f, 0.f};
-    if (r >= 0 && r < R && centre_ok) {
-      const V3 xj = ld3(xyz + 3 * j), xk = ld3(xyz + 3 * k);
-      const V3 vij = sub(xi, xj), vik = sub(xi, xk), vjk = sub(xj, xk);
-      const float rij = norm_ref(vij, eps), rik = norm_ref(vik, eps), rjk = norm_ref(vjk, eps);
-      const float inv = 1.f / (rij * rik);
-      const float c = dot(vij, vik) / rij / rik;                       // acsf_conv.py:439
-      const float r2 = rij * rij + rik * rik + rjk * rjk;
-      const float wt = (weight ? __ldg(weight + e) : 1.f) * inv_mult;    // wACSF: h(Z_j, Z_k) or external
-      // d cos / d vij = vik/(rij rik) - c vij/rij^2 ;  d cos / d vik = vij/(rij rik) - c vik/rik^2
-      const V3 dc_ij = axpy(-c / (rij * rij), vij, scale(inv, vik));
-      const V3 dc_ik = axpy(-c / (rik * rik), vik, scale(inv, vij));
-      float t_ij = 0.f, t_ik = 0.f, t_jk = 0.f, t_c = 0.f;             // JVP tangents of (rij, rik, rjk, cos)
+  const float rc0 = uniform_rc ? __ldg(tab_i + 3) : 0.f;           // one cutoff radius for the whole table
+  constexpr unsigned kFull = 0xffffffffu;
+  // Triples are processed in batches of 32.  Phase A: lane t evaluates the geometry of triple p0 + t ONCE (distances,
+  // cosine, cutoffs, tangents) instead of all 32 lanes repeating it.  Phase B: the warp walks the valid triples of
+  // the batch in their original order, the owner lane broadcasts its scalars by shuffle and the lanes run over the m
+  // parameter sets (accumulation order per (pair type, parameter) = triple order, as before).  Phase C (VJP): every
+  // lane assembles the coordinate gradients of its own triple.
+  for (int p0 = beg; p0 < end; p0 += 32) {
+    const int p = p0 + lane;
+    const bool have = p < end;
+    int e = 0, j = 0, k = 0, r = -1;
+    float rij = 1.f, rik = 1.f, rjk = 1.f, c = 0.f, wt = 0.f;
+    float fij = 0.f, dfij = 0.f, fik = 0.f, dfik = 0.f, fjk = 0.f, dfjk = 0.f;
+    float t_ij = 0.f, t_ik = 0.f, t_jk = 0.f, t_c = 0.f;             // JVP tangents of (rij, rik, rjk, cos)
+    V3 vij = {0.f, 0.f, 0.f}, vik = vij, vjk = vij, dc_ij = vij, dc_ik = vij;
+    if (have) {
+      e = perm ? __ldg(perm + p) : p;
+      j = __ldg(idx_j + e);
+      k = __ldg(idx_k + e);
+      const int zj = __ldg(z_atom + j), zk = __ldg(z_atom + k);
+      if (zj >= 0 && zj < zmax && zk >= 0 && zk < zmax) r = __ldg(rev_pair + zj * zmax + zk);
+      if (!(r >= 0 && r < R && centre_ok)) r = -1;
+      if (r >= 0) {
+        const V3 xj = ld3(xyz + 3 * j), xk = ld3(xyz + 3 * k);
+        vij = sub(xi, xj); vik = sub(xi, xk); vjk = sub(xj, xk);
+        rij = norm_ref(vij, eps); rik = norm_ref(vik, eps); rjk = norm_ref(vjk, eps);
+        const float inv = 1.f / (rij * rik);
+        c = dot(vij, vik) / rij / rik;                                   // acsf_conv.py:439
+        wt = (weight ? __ldg(weight + e) : 1.f) * inv_mult;              // wACSF: h(Z_j, Z_k) or external
+        // d cos / d vij = vik/(rij rik) - c vij/rij^2 ;  d cos / d vik = vij/(rij rik) - c vik/rik^2
+        dc_ij = axpy(-c / (rij * rij), vij, scale(inv, vik));
+        dc_ik = axpy(-c / (rik * rik), vik, scale(inv, vij));
+        if (MODE == kJvp) {
+          const V3 uj = ld3(cot + 3 * j), uk = ld3(cot + 3 * k);
+          const V3 uij = sub(ui, uj), uik = sub(ui, uk), ujk = sub(uj, uk);
+          t_ij = dot(vij, uij) / rij;
+          t_ik = dot(vik, uik) / rik;
+          t_jk = dot(vjk, ujk) / rjk;
+          t_c = dot(dc_ij, uij) + dot(dc_ik, uik);
+        }
+        if (uniform_rc) {
+          cutoff(rij, rc0, fij, dfij);
+          cutoff(rik, rc0, fik, dfik);
+          cutoff(rjk, rc0, fjk, dfjk);
+        }
+      }
+    }
+    float s_ij = 0.f, s_ik = 0.f, s_jk = 0.f, s_c = 0.f;             // VJP: sums over the parameter sets, own triple
+    for (unsigned rem = __ballot_sync(kFull, r >= 0); rem; rem &= rem - 1) {
+      const int t = __ffs(rem) - 1;
+      const int rr = __shfl_sync(kFull, r, t);
+      const float cc = __shfl_sync(kFull, c, t), wtt = __shfl_sync(kFull, wt, t);
+      const float bij = __shfl_sync(kFull, rij, t), bik = __shfl_sync(kFull, rik, t), bjk = __shfl_sync(kFull, rjk, t);
+      float gij = 0.f, gdij = 0.f, gik = 0.f, gdik = 0.f, gjk = 0.f, gdjk = 0.f;
+      if (uniform_rc) {
+        gij = __shfl_sync(kFull, fij, t); gik = __shfl_sync(kFull, fik, t); gjk = __shfl_sync(kFull, fjk, t);
+        if (MODE != kFwd) {
+          gdij = __shfl_sync(kFull, dfij, t); gdik = __shfl_sync(kFull, dfik, t); gdjk = __shfl_sync(kFull, dfjk, t);
+        }
+      }
+      float u_ij = 0.f, u_ik = 0.f, u_jk = 0.f, u_c = 0.f;
       if (MODE == kJvp) {
-        const V3 uj = ld3(cot + 3 * j), uk = ld3(cot + 3 * k);
-        const V3 uij = sub(ui, uj), uik = sub(ui, uk), ujk = sub(uj, uk);
-        t_ij = dot(vij, uij) / rij;
-        t_ik = dot(vik, uik) / rik;
-        t_jk = dot(vjk, ujk) / rjk;
-        t_c = dot(dc_ij, uij) + dot(dc_ik, uik);
+        u_ij = __shfl_sync(kFull, t_ij, t); u_ik = __shfl_sync(kFull, t_ik, t);
+        u_jk = __shfl_sync(kFull, t_jk, t); u_c = __shfl_sync(kFull, t_c, t);
       }
-      float a_ij = 0.f, a_ik = 0.f, a_jk = 0.f, a_c = 0.f;             // VJP: sums over the parameter sets
-      float fij, dfij, fik, dfik, fjk, dfjk;
-      if (uniform_rc) {                                                // one cutoff radius for the whole table
-        const float rc0 = __ldg(tab_i + 3);
-        cutoff(rij, rc0, fij, dfij);
-        cutoff(rik, rc0, fik, dfik);
-        cutoff(rjk, rc0, fjk, dfjk);
-      }
+      const float r2 = bij * bij + bik * bik + bjk * bjk;
+      float a_ij = 0.f, a_ik = 0.f, a_jk = 0.f, a_c = 0.f;
       for (int q = lane; q < m; q += 32) {
-        const float4 prm = __ldg(reinterpret_cast<const float4*>(tab_i + (static_cast<int64_t>(r) * m + q) * 4));
+        const float4 prm = __ldg(reinterpret_cast<const float4*>(tab_i + (static_cast<int64_t>(rr) * m + q) * 4));
         const float eta = prm.x, zeta = prm.y, lam = prm.z, rc = prm.w;
         if (!uniform_rc) {
-          cutoff(rij, rc, fij, dfij);
-          cutoff(rik, rc, fik, dfik);
-          cutoff(rjk, rc, fjk, dfjk);
+          cutoff(bij, rc, gij, gdij);
+          cutoff(bik, rc, gik, gdik);
+          cutoff(bjk, rc, gjk, gdjk);
         }
         // (1 + lambda cos)^zeta as exp2(zeta log2(base)); base is clamped at 0 (it can only be negative by
         // rounding of cos) -> 0^zeta = 0 like pow
-        const float base = fmaxf(c * lam + 1.f, 0.f);
-        const float pre = exp2f(1.f - zeta) * wt;
+        const float base = fmaxf(cc * lam + 1.f, 0.f);
+        const float pre = exp2f(1.f - zeta) * wtt;
         // wACSF shifts the three Gaussians by mu (wacsf_conv.py:277-281); ACSF G4 has mu = 0
-        const float mu = mu_i ? __ldg(mu_i + r * m + q) : 0.f;
-        const float sij = rij - mu, sik = rik - mu, sjk = rjk - mu;
+        const float mu = mu_i ? __ldg(mu_i + rr * m + q) : 0.f;
+        const float sij = bij - mu, sik = bik - mu, sjk = bjk - mu;
         const float pw = (base > 0.f) ? exp2f(zeta * log2f(base)) : (zeta == 0.f ? 1.f : 0.f);
         const float A = pre * pw;
         const float E = expf(-eta * (mu_i ? sij * sij + sik * sik + sjk * sjk : r2));
-        const float fff = fij * fik * fjk;
+        const float fff = gij * gik * gjk;
         if (MODE == kFwd) {
-          acc[r * m + q] += A * E * fff;
+          acc[rr * m + q] += A * E * fff;
         } else {
           const float pw1 = (base > 0.f) ? pw / base : (zeta == 1.f ? 1.f : 0.f);   // base^(zeta-1)
           const float dA = pre * zeta * lam * pw1;                      // dA / dcos
           // d rep / d r_ab = A (dE/dr_ab fff + E f'_ab f f)
-          const float d_ij = A * E * (-2.f * eta * sij * fff + dfij * fik * fjk);
-          const float d_ik = A * E * (-2.f * eta * sik * fff + fij * dfik * fjk);
-          const float d_jk = A * E * (-2.f * eta * sjk * fff + fij * fik * dfjk);
+          const float d_ij = A * E * (-2.f * eta * sij * fff + gdij * gik * gjk);
+          const float d_ik = A * E * (-2.f * eta * sik * fff + gij * gdik * gjk);
+          const float d_jk = A * E * (-2.f * eta * sjk * fff + gij * gik * gdjk);
           const float d_c = dA * E * fff;
           if (MODE == kVjp) {
-            const float g = acc[r * m + q];
+            const float g = acc[rr * m + q];
             a_ij += g * d_ij; a_ik += g * d_ik; a_jk += g * d_jk; a_c += g * d_c;
           } else {
-            acc[r * m + q] += d_ij * t_ij + d_ik * t_ik + d_jk * t_jk + d_c * t_c;
+            acc[rr * m + q] += d_ij * u_ij + d_ik * u_ik + d_jk * u_jk + d_c * u_c;
           }
         }
       }
       if (MODE == kVjp) {
         a_ij = warp_sum(a_ij); a_ik = warp_sum(a_ik); a_jk = warp_sum(a_jk); a_c = warp_sum(a_c);
-        const V3 g_vij = axpy(a_ij / rij, vij, scale(a_c, dc_ij));
-        const V3 g_vik = axpy(a_ik / rik, vik, scale(a_c, dc_ik));
-        const V3 g_vjk = scale(a_jk / rjk, vjk);
+        if (lane == t) { s_ij = a_ij; s_ik = a_ik; s_jk = a_jk; s_c = a_c; }
+      }
+    }
+    if (MODE == kVjp && have) {
+      V3 gj = {0.f, 0.f, 0.f}, gk = {0.f, 0.f, 0.f};
+      if (r >= 0) {
+        const V3 g_vij = axpy(s_ij / rij, vij, scale(s_c, dc_ij));
+        const V3 g_vik = axpy(s_ik / rik, vik, scale(s_c, dc_ik));
+        const V3 g_vjk = scale(s_jk / rjk, vjk);
         gi = axpy(1.f, g_vij, axpy(1.f, g_vik, gi));
         gj = sub(g_vjk, g_vij);
         gk = scale(-1.f, axpy(1.f, g_vik, g_vjk));
       }
-    }
-    if (MODE == kVjp && lane == 0) {
       float* o = triple_out + 6 * static_cast<int64_t>(e);
       o[0] = gj.x; o[1] = gj.y; o[2] = gj.z; o[3] = gk.x; o[4] = gk.y; o[5] = gk.z;
     }
   }
+  if (MODE == kVjp) { gi.x = warp_sum(gi.x); gi.y = warp_sum(gi.y); gi.z = warp_sum(gi.z); }   // fixed tree
   __syncwarp();
   if (MODE == kVjp) {
     if (lane == 0) { out[3 * i] = gi.x; out[3 * i + 1] = gi.y; out[3 * i + 2] = gi.z; }
