@@ -82,15 +82,13 @@ __global__ void rowptr_from_sorted_kernel(const int32_t* __restrict__ key, int s
   for (int64_t j = kprev + 1; j <= k; ++j) rowptr[j] = static_cast<int32_t>(e);
 }
 
-__global__ void histogram_kernel(const int32_t* __restrict__ key, int stride, int64_t E, int64_t N,
-                                 int32_t* __restrict__ rowptr, int32_t* __restrict__ key_dense,
-                                 int32_t* __restrict__ iota) {
+// unsorted keys: dense copy of the (strided) key column + identity payload for the stable radix sort
+__global__ void key_iota_kernel(const int32_t* __restrict__ key, int stride, int64_t E,
+                                int32_t* __restrict__ key_dense, int32_t* __restrict__ iota) {
   int64_t e = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
   if (e >= E) return;
-  int32_t k = key[e * stride];
-  key_dense[e] = k;
+  key_dense[e] = key[e * stride];
   iota[e] = static_cast<int32_t>(e);
-  if (k >= 0 && k < N) atomicAdd(rowptr + k + 1, 1);  // integer atomics: order-independent result
 }
 
 __global__ void iota_kernel(int32_t* __restrict__ out, int64_t n) {
@@ -220,13 +218,14 @@ int kgcnn_plan_build(const int32_t* key, int key_stride, int64_t E, int64_t N, i
   int32_t* iota = reinterpret_cast<int32_t*>(ws + 2 * seg);
   void* cub_ws = ws + 3 * seg;
   size_t cub_bytes = workspace_bytes - 3 * seg;
-  histogram_kernel<<<blocks_for(E), kThreads, 0, st>>>(key, key_stride, E, N, rowptr, key_dense, iota);
-  if (cub::DeviceScan::InclusiveSum(cub_ws, cub_bytes, rowptr, rowptr, static_cast<int>(N + 1), st) != cudaSuccess)
-    return KGCNN_E_CUDA;
+  key_iota_kernel<<<blocks_for(E), kThreads, 0, st>>>(key, key_stride, E, key_dense, iota);
   // LSD radix sort is stable: equal keys keep their original edge order (tf.argsort(stable=True)).
   if (cub::DeviceRadixSort::SortPairs(cub_ws, cub_bytes, key_dense, key_sorted, iota, perm, static_cast<int>(E), 0,
                                       key_bits(N), st) != cudaSuccess)
     return KGCNN_E_CUDA;
+  // row pointer from the segment boundaries of the sorted keys: no histogram atomics (hot receivers made the
+  // atomicAdd histogram 10x slower than the sort at 11 M triples), no scan
+  rowptr_from_sorted_kernel<<<blocks_for(E + 1), kThreads, 0, st>>>(key_sorted, 1, E, N, rowptr);
   return finish_launch(3);
 }
 
