@@ -48,7 +48,7 @@ SIGNATURES = {
     "kgcnn_dense_tn_grouped": (_i, [_i, _p, _p, _p, _p, _p, _p, _p, _p, _z, _p]),
     "kgcnn_edge_geometry": (_i, [_p, _p, _p, _l, _i, _i, _i, _p, _p, _f, _i, _f, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
     "kgcnn_acsf_g2": (_i, [_p, _p, _p, _p, _p, _p, _i, _p, _i, _i, _f, _l, _p, _i, _p, _p, _p, _p]),
-    "kgcnn_acsf_g4": (_i, [_p, _p, _p, _p, _i, _p, _p, _p, _p, _p, _i, _i, _f, _f, _i, _l, _p, _p, _i, _p, _p, _p, _p]),
+    "kgcnn_acsf_g4": (_i, [_p, _p, _p, _p, _i, _p, _p, _p, _p, _p, _i, _i, _f, _f, _i, _l, _p, _p, _p, _p, _l, _i, _p, _p, _p, _p]),
     "kgcnn_painn_msg_nodes": (_i, [_p, _p, _p, _p, _p, _p, _p, _i, _l, _l, _i, _i, _p, _p, _p]),
     "kgcnn_painn_msg_senders": (_i, [_p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _l, _l, _i, _i, _p, _p, _p]),
     "kgcnn_painn_msg_edges": (_i, [_p, _p, _p, _p, _p, _p, _p, _p, _l, _i, _i, _p, _p, _p]),

@@ -129,7 +129,9 @@ acsf_g4_kernel(const float* __restrict__ xyz, const int32_t* __restrict__ z_atom
                const int32_t* __restrict__ idx_j, const int32_t* __restrict__ idx_k,
                const float* __restrict__ table, int R, int m, float eps, float inv_mult, int uniform_rc, int64_t N,
                const float* __restrict__ mu_tab, const float* __restrict__ weight,
-               const float* __restrict__ cot, float* __restrict__ out, float* __restrict__ triple_out) {
+               const float2* __restrict__ fac, const int32_t* __restrict__ fac_idx,
+               const float* __restrict__ cot, float* __restrict__ out, float* __restrict__ triple_out,
+               int64_t n_triples) {
   __shared__ float acc_s[kWarpsPerBlock][kMaxAcc];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int64_t i = static_cast<int64_t>(blockIdx.x) * kWarpsPerBlock + warp;
@@ -146,6 +148,9 @@ acsf_g4_kernel(const float* __restrict__ xyz, const int32_t* __restrict__ z_atom
   const float* mu_i = mu_tab ? mu_tab + (tset_atom ? static_cast<int64_t>(max(__ldg(tset_atom + i), 0)) * RM : 0)
                              : nullptr;
   const bool centre_ok = !tset_atom || __ldg(tset_atom + i) >= 0;
+  const int tset_i = tset_atom ? max(__ldg(tset_atom + i), 0) : 0;
+  const float2* fac_i = fac ? fac + static_cast<int64_t>(tset_i) * R * 32 : nullptr;
+  const int32_t* idx_i = fac ? fac_idx + static_cast<int64_t>(tset_i) * RM : nullptr;
   V3 gi = {0.f, 0.f, 0.f};
   const int beg = __ldg(rowptr + i), end = __ldg(rowptr + i + 1);
   const float rc0 = uniform_rc ? __ldg(tab_i + 3) : 0.f;           // one cutoff radius for the whole table
@@ -215,6 +220,58 @@ acsf_g4_kernel(const float* __restrict__ xyz, const int32_t* __restrict__ z_atom
       }
       const float r2 = bij * bij + bik * bik + bjk * bjk;
       float a_ij = 0.f, a_ik = 0.f, a_jk = 0.f, a_c = 0.f;
+      if (fac_i) {
+        // Factorised parameter table (uniform cutoff): the m parameter sets of a pair type are products of few
+        // distinct Gaussians exp(-eta sum (r - mu)^2) (slots 0-15) and few distinct angular terms
+        // 2^(1-zeta) (1 + lambda cos)^zeta (slots 16-31), e.g. 5 and 10 for the 50 sets of force_hdnnp2nd.py:49-55.
+        // Lane s evaluates slot s once per triple; each parameter set then needs two shuffles and a product
+        // instead of three transcendental chains.
+        const float fff = gij * gik * gjk;
+        const float2 key = __ldg(fac_i + rr * 32 + lane);
+        float val, dval = 0.f, d1 = 0.f, d2 = 0.f, d3 = 0.f;
+        if (lane < 16) {                                                 // key = (eta, mu)
+          const float sij = bij - key.y, sik = bik - key.y, sjk = bjk - key.y;
+          val = expf(-key.x * (mu_i ? sij * sij + sik * sik + sjk * sjk : r2));
+          if (MODE != kFwd) {                                            // d(E fff)/d r_ab
+            d1 = val * (-2.f * key.x * sij * fff + gdij * gik * gjk);
+            d2 = val * (-2.f * key.x * sik * fff + gij * gdik * gjk);
+            d3 = val * (-2.f * key.x * sjk * fff + gij * gik * gdjk);
+            if (MODE == kJvp) d1 = d1 * u_ij + d2 * u_ik + d3 * u_jk;
+          }
+          val *= fff;
+        } else {                                                         // key = (zeta, lambda)
+          const float base = fmaxf(cc * key.y + 1.f, 0.f);
+          const float pre = exp2f(1.f - key.x) * wtt;
+          const float pw = (base > 0.f) ? exp2f(key.x * log2f(base)) : (key.x == 0.f ? 1.f : 0.f);
+          val = pre * pw;
+          if (MODE != kFwd) {
+            const float pw1 = (base > 0.f) ? pw / base : (key.x == 1.f ? 1.f : 0.f);
+            dval = pre * key.x * key.y * pw1;                            // dA / dcos
+            if (MODE == kJvp) dval *= u_c;
+          }
+        }
+        for (int q0 = 0; q0 < m; q0 += 32) {                             // uniform trip count: shuffles inside
+          const int q = q0 + lane;
+          const bool on = q < m;
+          const int packed = on ? __ldg(idx_i + rr * m + q) : 0x1000;
+          const int se = packed & 0xff, sp = packed >> 8;
+          const float Ef = __shfl_sync(kFull, val, se);                  // E * fff
+          const float P = __shfl_sync(kFull, val, sp);                   // A
+          if (MODE == kFwd) {
+            if (on) acc[rr * m + q] += P * Ef;
+          } else if (MODE == kJvp) {
+            const float W = __shfl_sync(kFull, d1, se), dP = __shfl_sync(kFull, dval, sp);
+            if (on) acc[rr * m + q] += P * W + dP * Ef;
+          } else {
+            const float D1 = __shfl_sync(kFull, d1, se), D2 = __shfl_sync(kFull, d2, se);
+            const float D3 = __shfl_sync(kFull, d3, se), dP = __shfl_sync(kFull, dval, sp);
+            if (on) {
+              const float g = acc[rr * m + q], gP = g * P;
+              a_ij += gP * D1; a_ik += gP * D2; a_jk += gP * D3; a_c += g * dP * Ef;
+            }
+          }
+        }
+      } else
       for (int q = lane; q < m; q += 32) {
         const float4 prm = __ldg(reinterpret_cast<const float4*>(tab_i + (static_cast<int64_t>(rr) * m + q) * 4));
         const float eta = prm.x, zeta = prm.y, lam = prm.z, rc = prm.w;
@@ -267,8 +324,10 @@ acsf_g4_kernel(const float* __restrict__ xyz, const int32_t* __restrict__ z_atom
         gj = sub(g_vjk, g_vij);
         gk = scale(-1.f, axpy(1.f, g_vik, g_vjk));
       }
-      float* o = triple_out + 6 * static_cast<int64_t>(e);
-      o[0] = gj.x; o[1] = gj.y; o[2] = gj.z; o[3] = gk.x; o[4] = gk.y; o[5] = gk.z;
+      float* o = triple_out + 3 * static_cast<int64_t>(e);            // [2, A, 3]: gradients of atom j, then atom k
+      o[0] = gj.x; o[1] = gj.y; o[2] = gj.z;
+      o += 3 * n_triples;
+      o[0] = gk.x; o[1] = gk.y; o[2] = gk.z;
     }
   }
   if (MODE == kVjp) { gi.x = warp_sum(gi.x); gi.y = warp_sum(gi.y); gi.z = warp_sum(gi.z); }   // fixed tree
@@ -309,7 +368,8 @@ int kgcnn_acsf_g2(const float* xyz, const int32_t* rel_atom, const int32_t* tset
 int kgcnn_acsf_g4(const float* xyz, const int32_t* z_atom, const int32_t* tset_atom, const int32_t* rev_pair,
                   int zmax, const int32_t* rowptr, const int32_t* perm, const int32_t* idx_j, const int32_t* idx_k,
                   const float* table, int R, int m, float eps, float multiplicity, int uniform_rc, int64_t N,
-                  const float* mu_table, const float* weight, int mode, const float* cot, float* out,
+                  const float* mu_table, const float* weight, const float* factor_table,
+                  const int32_t* factor_index, int64_t n_triples, int mode, const float* cot, float* out,
                   float* triple_out, kgcnn_stream_t stream) {
   if (N < 0 || R <= 0 || m <= 0 || zmax <= 0 || mode < kFwd || mode > kJvp) return KGCNN_E_INVALID;
   if (R * m > kMaxAcc) return KGCNN_E_UNSUPPORTED;
@@ -317,12 +377,16 @@ int kgcnn_acsf_g4(const float* xyz, const int32_t* z_atom, const int32_t* tset_a
   if (!xyz || !z_atom || !rev_pair || !rowptr || !idx_j || !idx_k || !table || !out) return KGCNN_E_INVALID;
   if ((reinterpret_cast<uintptr_t>(table) & 15) != 0) return KGCNN_E_UNSUPPORTED;
   if (mode != kFwd && !cot) return KGCNN_E_INVALID;
-  if (mode == kVjp && !triple_out) return KGCNN_E_INVALID;
+  if (mode == kVjp && (!triple_out || n_triples < 0)) return KGCNN_E_INVALID;
+  if ((factor_table != nullptr) != (factor_index != nullptr)) return KGCNN_E_INVALID;
+  if (factor_table && (!uniform_rc || (reinterpret_cast<uintptr_t>(factor_table) & 7) != 0)) return KGCNN_E_INVALID;
+  const float2* fac = reinterpret_cast<const float2*>(factor_table);
   const float inv_mult = multiplicity > 0.f ? 1.f / multiplicity : 1.f;
   const unsigned grid = static_cast<unsigned>(ceil_div<int64_t>(N, kWarpsPerBlock));
   cudaStream_t st = as_stream(stream);
 #define KGCNN_G4(M) acsf_g4_kernel<M><<<grid, kWarpsPerBlock * 32, 0, st>>>(xyz, z_atom, tset_atom, rev_pair, zmax, \
-    rowptr, perm, idx_j, idx_k, table, R, m, eps, inv_mult, uniform_rc, N, mu_table, weight, cot, out, triple_out)
+    rowptr, perm, idx_j, idx_k, table, R, m, eps, inv_mult, uniform_rc, N, mu_table, weight, fac, factor_index, cot, \
+    out, triple_out, n_triples)
   if (mode == kFwd) KGCNN_G4(kFwd); else if (mode == kVjp) KGCNN_G4(kVjp); else KGCNN_G4(kJvp);
 #undef KGCNN_G4
   return finish_launch();

@@ -784,13 +784,53 @@ class ACSFSpec:
 
     def __init__(self, kind, rel_centre, table, R, m, eps, rel_atom=None, tset_atom=None, rel_send=None,
                  z_atom=None, rev_pair=None, zmax=31, rel_j=None, rel_k=None, multiplicity=0.0, uniform_rc=False,
-                 weight=None, mu_table=None):
+                 weight=None, mu_table=None, factor=None):
         self.uniform_rc = uniform_rc
+        self.factor = factor       # G4: (factor_table, factor_index) device tensors from g4_factor_tables, or None
         self.weight, self.mu_table = weight, mu_table      # wACSF: per-pair/triple factor, Gaussian shifts
         self.kind, self.rel_centre, self.table, self.R, self.m, self.eps = kind, rel_centre, table, R, m, eps
         self.rel_atom, self.tset_atom, self.rel_send = rel_atom, tset_atom, rel_send
         self.z_atom, self.rev_pair, self.zmax, self.rel_j, self.rel_k = z_atom, rev_pair, zmax, rel_j, rel_k
         self.multiplicity = multiplicity
+
+
+G4_FACTORISE = True        # False: always the unfactorised parameter loop (diagnostics)
+
+
+def g4_factor_tables(table, mu=None):
+    """Host side, once per layer: distinct Gaussian (eta, mu) and angular (zeta, lambda) terms of every (T, R) row
+    of a G4 parameter table [..., m, 4] = (eta, zeta, lambda, Rc) and the slot pair of each of its m parameter sets
+    (include/kgcnn_b200.h, kgcnn_acsf_g4).  Returns (factor_table float32 [rows, 32, 2], factor_index int32
+    [rows, m]) as NumPy arrays, or None when a row has more than 16 distinct terms of either kind or the cutoff
+    radius is not uniform (the kernel then runs its general loop)."""
+    import numpy as np
+    table = np.asarray(table, dtype=np.float32)
+    m = table.shape[-2]
+    t = table.reshape(-1, m, 4)
+    if not np.all(t[..., 3] == t[0, 0, 3]):
+        return None
+    mus = np.zeros(t.shape[:2], np.float32) if mu is None else np.asarray(mu, dtype=np.float32).reshape(-1, m)
+    fac = np.zeros((t.shape[0], 32, 2), np.float32)
+    idx = np.zeros((t.shape[0], m), np.int32)
+    for row in range(t.shape[0]):
+        gauss, ang = {}, {}
+        for q in range(m):
+            ge = gauss.setdefault((float(t[row, q, 0]), float(mus[row, q])), len(gauss))
+            an = ang.setdefault((float(t[row, q, 1]), float(t[row, q, 2])), len(ang))
+            idx[row, q] = ge | ((16 + an) << 8)
+        if len(gauss) > 16 or len(ang) > 16:
+            return None
+        for (a, b), slot in gauss.items():
+            fac[row, slot] = (a, b)
+        for (a, b), slot in ang.items():
+            fac[row, 16 + slot] = (a, b)
+    return fac, idx
+
+
+def _g4_factor_tables(spec):
+    if not (G4_FACTORISE and spec.uniform_rc and spec.factor is not None):
+        return None, None
+    return spec.factor
 
 
 def raw_acsf(xyz, spec, mode, cot=None):
@@ -811,12 +851,13 @@ def raw_acsf(xyz, spec, mode, cot=None):
                                        _ptr(edge_out), _stream()), "kgcnn_acsf_g2")
         return out, edge_out
     A = rc.n_elements
-    tri = torch.empty((A, 2, 3), dtype=torch.float32, device=xyz.device) if mode == 1 else None
+    tri = torch.empty((2, A, 3), dtype=torch.float32, device=xyz.device) if mode == 1 else None
+    fac, fidx = _g4_factor_tables(spec)
     check(_lib.lib().kgcnn_acsf_g4(_ptr(xyz), _ptr(spec.z_atom), _ptr(spec.tset_atom), _ptr(spec.rev_pair), spec.zmax,
                                    _ptr(rc.rowptr), _ptr(rc.perm), _ptr(spec.rel_j.ids), _ptr(spec.rel_k.ids),
                                    _ptr(spec.table), spec.R, spec.m, spec.eps, float(spec.multiplicity or 0.0),
-                                   1 if spec.uniform_rc else 0, N, _ptr(spec.mu_table), _ptr(spec.weight), mode,
-                                   _ptr(cot), _ptr(out), _ptr(tri), _stream()), "kgcnn_acsf_g4")
+                                   1 if spec.uniform_rc else 0, N, _ptr(spec.mu_table), _ptr(spec.weight), _ptr(fac),
+                                   _ptr(fidx), A, mode, _ptr(cot), _ptr(out), _ptr(tri), _stream()), "kgcnn_acsf_g4")
     return out, tri
 
 
@@ -824,8 +865,7 @@ def _acsf_vjp_raw(xyz, dG, spec):
     centre, nb = raw_acsf(xyz, spec, 1, dG)
     if spec.kind == 2:
         return centre + raw_gms(nb, None, spec.rel_send, None)
-    return centre + raw_gms(nb[:, 0].contiguous(), None, spec.rel_j, None) \
-        + raw_gms(nb[:, 1].contiguous(), None, spec.rel_k, None)
+    return centre + raw_gms(nb[0], None, spec.rel_j, None) + raw_gms(nb[1], None, spec.rel_k, None)
 
 
 class _ACSF(torch.autograd.Function):

@@ -160,6 +160,9 @@ class ACSFG4(GraphBaseLayer):
             torch.tensor(self.eta_zeta_lambda_rc, dtype=torch.float32), requires_grad=bool(param_trainable))
         self.register_buffer("weight_reverse_mapping", torch.tensor(self.reverse_mapping))
         self.register_buffer("weight_reverse_pair_mapping", torch.tensor(self.reverse_pair_mapping))
+        fac = None if param_trainable else F.g4_factor_tables(self.eta_zeta_lambda_rc)
+        self.register_buffer("_factor_table", None if fac is None else torch.from_numpy(fac[0]), persistent=False)
+        self.register_buffer("_factor_index", None if fac is None else torch.from_numpy(fac[1]), persistent=False)
 
     @staticmethod
     def make_param_table(eta, zeta, lamda, rc, elements, **kwargs):
@@ -190,7 +193,8 @@ class ACSFG4(GraphBaseLayer):
                               int(self.eta_zeta_lambda_rc.shape[-2]), 1e-7 if self.add_eps else 0.0,
                               tset_atom=tset, z_atom=zv.to(torch.int32), rev_pair=rev_pair, zmax=_MAX_ATOMIC_NUMBER,
                               rel_j=rj, rel_k=rk, multiplicity=self.multiplicity or 0.0,
-                              uniform_rc=bool(np.all(self.eta_zeta_lambda_rc[..., 3] == self.eta_zeta_lambda_rc.reshape(-1, 4)[0, 3])))
+                              uniform_rc=bool(np.all(self.eta_zeta_lambda_rc[..., 3] == self.eta_zeta_lambda_rc.reshape(-1, 4)[0, 3])),
+                              factor=None if self._factor_table is None else (self._factor_table, self._factor_index))
             return xyz.with_values(F.acsf(xyz.values, spec))
         zi, zj, zk = F.gather(zv, ri), F.gather(zv, rj), F.gather(zv, rk)           # :475
         xi, xj, xk = (F.gather(xyz.values, r) for r in (ri, rj, rk))               # :476

@@ -122,6 +122,9 @@ class wACSFAng(GraphBaseLayer):
                              torch.full_like(table[..., 0], float(cutoff))], dim=-1)
         self.register_buffer("_table_eta_zeta_lambda_rc", fused.contiguous(), persistent=False)
         self.register_buffer("_table_mu", table[..., 1].contiguous(), persistent=False)
+        fac = F.g4_factor_tables(fused.numpy(), table[..., 1].numpy())
+        self.register_buffer("_factor_table", None if fac is None else torch.from_numpy(fac[0]), persistent=False)
+        self.register_buffer("_factor_index", None if fac is None else torch.from_numpy(fac[1]), persistent=False)
 
     def call(self, inputs, mask=None, **kwargs):
         if self.use_external_weights:
@@ -147,7 +150,8 @@ class wACSFAng(GraphBaseLayer):
                               z_atom=torch.zeros_like(tset), zmax=1,
                               rev_pair=torch.zeros(1, dtype=torch.int32, device=tset.device), rel_j=rj, rel_k=rk,
                               multiplicity=0.0, uniform_rc=True, weight=wv.reshape(-1).contiguous(),
-                              mu_table=self._table_mu)
+                              mu_table=self._table_mu,
+                              factor=None if self._factor_table is None else (self._factor_table, self._factor_index))
             return xyz.with_values(F.acsf(xyz.values, spec))
         xi, xj, xk = (F.gather(xyz.values, r) for r in (ri, rj, rk))               # :339
         rij, rik, rjk = _distance(xi, xj, eps), _distance(xi, xk, eps), _distance(xj, xk, eps)   # :340-342

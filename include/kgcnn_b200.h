@@ -213,7 +213,7 @@ int kgcnn_edge_geometry(const float* xyz, const int32_t* idx_i, const int32_t* i
  * a15/a16  fused ACSF symmetry functions (kgcnn/layers/conv/acsf_conv.py:199-211 and :473-494)
  *   mode 0: G[N, R*m]                  (out)
  *   mode 1: VJP, cot = dG[N, R*m]   -> out = d/dx of the CENTRE atoms [N,3]; the neighbour parts are written per
- *           pair (edge_out [M,3], for the sender) / per triple (triple_out [A,2,3], for j and k) in the ORIGINAL
+ *           pair (edge_out [M,3], for the sender) / per triple (triple_out [2,A,3], for j and k) in the ORIGINAL
  *           pair / triple order and are summed by the caller with the deterministic segment kernel
  *   mode 2: JVP, cot = u[N,3]       -> out = J u  [N, R*m]   (what force training needs: parameters are constants)
  *   rel_atom[n]  : relation of atom n as a NEIGHBOUR (reverse_mapping[Z_n], < 0 = element not mapped -> skipped)
@@ -228,6 +228,13 @@ int kgcnn_edge_geometry(const float* xyz, const int32_t* idx_i, const int32_t* i
  *                    layer's external weights);
  *   mu_table       : nullable [T][R][m]; shifts the three Gaussians of the angular function,
  *                    exp(-eta ((r_ij-mu)^2 + (r_ik-mu)^2 + (r_jk-mu)^2))  (wacsf_conv.py:277-281); null = ACSF G4.
+ *   factor_table / factor_index : nullable pair (uniform_rc only).  The m parameter sets of one (T, R) row are
+ *                    products of few distinct Gaussians and few distinct angular terms; factor_table [T][R][32][2]
+ *                    holds the distinct (eta, mu) in slots 0-15 and the distinct (zeta, lambda) in slots 16-31
+ *                    (unused slots 0), factor_index [T][R][m] = gaussian_slot | angular_slot << 8.  With it every
+ *                    distinct term is evaluated once per triple (5 + 10 instead of 3 x 50 transcendental chains for
+ *                    force_hdnnp2nd.py:49-55); results agree with the unfactorised path to fp32 rounding.
+ *   n_triples      : A, the stride between the j and k halves of triple_out (mode 1).
  * ------------------------------------------------------------------------------------------- */
 int kgcnn_acsf_g2(const float* xyz, const int32_t* rel_atom, const int32_t* tset_atom, const int32_t* rowptr,
                   const int32_t* perm, const int32_t* send, int send_permuted, const float* table, int R, int m,
@@ -236,7 +243,8 @@ int kgcnn_acsf_g2(const float* xyz, const int32_t* rel_atom, const int32_t* tset
 int kgcnn_acsf_g4(const float* xyz, const int32_t* z_atom, const int32_t* tset_atom, const int32_t* rev_pair,
                   int zmax, const int32_t* rowptr, const int32_t* perm, const int32_t* idx_j, const int32_t* idx_k,
                   const float* table, int R, int m, float eps, float multiplicity, int uniform_rc, int64_t N,
-                  const float* mu_table, const float* weight, int mode, const float* cot, float* out,
+                  const float* mu_table, const float* weight, const float* factor_table,
+                  const int32_t* factor_index, int64_t n_triples, int mode, const float* cot, float* out,
                   float* triple_out, kgcnn_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
