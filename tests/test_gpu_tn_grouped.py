@@ -80,3 +80,26 @@ def test_linear_backward_through_sink_equals_autograd_path():
     assert all(g is None for g in got)                 # everything went through the sink
     for view, r in zip(opt.grad_views, ref):
         assert rel_err(view.cpu().numpy(), r.cpu().numpy()) < RTOL
+
+
+def test_grouped_tn_large_edge_problems_balanced_grid():
+    """PaiNN C3 shapes (405 k edge rows, 20 -> 384 filter Dense, twelve times, plus node-level problems): the
+    launch is large enough for the whole-wave split search of grouped_rows_per_split; results against fp64."""
+    from gcnn_keras_b200.functional import WeightGradSink
+    torch.manual_seed(3)
+    shapes = [(20, 384), (384,), (128, 128), (128,), (128, 384), (384,)]
+    params, opt = _flat_params(shapes)
+    sink = WeightGradSink(params, opt.gflat, opt.offsets)
+    want = [torch.zeros(s, dtype=torch.float64) for s in shapes]
+    cases = [(0, 1, 405180)] * 6 + [(2, 3, 15360)] * 4 + [(4, 5, 15360)] * 2 + [(0, None, 405180)] * 6
+    for wi, bi, M in cases:
+        K, U = shapes[wi]
+        x, g = torch.randn(M, K, device="cuda"), torch.randn(M, U, device="cuda")
+        assert sink.add(params[wi], x, g, None if bi is None else params[bi])
+        want[wi] += (x.double().t() @ g.double()).cpu()
+        if bi is not None:
+            want[bi] += g.double().sum(0).cpu()
+    sink.flush()
+    torch.cuda.synchronize()
+    for view, w in zip(opt.grad_views, want):
+        assert rel_err(view.cpu().numpy(), w.numpy()) < RTOL
