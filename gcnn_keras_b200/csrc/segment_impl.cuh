@@ -321,6 +321,16 @@ int launch(int mode, bool gather, const V* x, const V* wv, const float* ws, cons
                                long_thresh, st)
   // few lanes per row -> many edges per warp instruction (the kernel is issue-bound, not DRAM-bound, when
   // gathered rows hit in L1/L2); 8 lanes x 128 bit = one full 128 B line per request.
+  // Small outputs (SchNet C2: 2304 rows x 128 features = 72 CTAs with 4 vectors per lane) leave half of the 148 SMs
+  // idle and serialise 4 x degree dependent loads per lane: split the feature axis over grid.y instead (1 or 2
+  // vectors per lane) until the grid covers the machine about twice.
+  if (nvec > 8 && nvec <= 32) {
+    const int64_t row_blocks = ceil_div<int64_t>(n_out, short_rows ? kWarps * 4 : kWarps);
+    if (row_blocks * ceil_div(nvec, 32) < 2 * kNumSM) {
+      if (row_blocks * ceil_div(nvec, 16) >= 2 * kNumSM) KGCNN_GMS_SHAPE(8, 2);
+      KGCNN_GMS_SHAPE(8, 1);
+    }
+  }
   if (nvec <= 1) KGCNN_GMS_SHAPE(1, 1);
   if (nvec <= 2) KGCNN_GMS_SHAPE(2, 1);
   if (nvec <= 4) KGCNN_GMS_SHAPE(4, 1);

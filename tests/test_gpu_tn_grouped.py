@@ -82,9 +82,9 @@ def test_linear_backward_through_sink_equals_autograd_path():
         assert rel_err(view.cpu().numpy(), r.cpu().numpy()) < RTOL
 
 
-def test_grouped_tn_large_edge_problems_balanced_grid():
+def test_grouped_tn_large_edge_problems():
     """PaiNN C3 shapes (405 k edge rows, 20 -> 384 filter Dense, twelve times, plus node-level problems): the
-    launch is large enough for the whole-wave split search of grouped_rows_per_split; results against fp64."""
+    launch spans several waves of CTAs with many row splits per problem; results against fp64."""
     from gcnn_keras_b200.functional import WeightGradSink
     torch.manual_seed(3)
     shapes = [(20, 384), (384,), (128, 128), (128,), (128, 384), (384,)]
