@@ -213,7 +213,9 @@ gms_block_kernel(const V* __restrict__ x, const V* __restrict__ wv, const float*
   const int64_t row = row_map ? __ldg(row_map + blockIdx.x) : blockIdx.x;
   const int beg = __ldg(rowptr + row), end = __ldg(rowptr + row + 1);
   const float init = (MODE == kMax) ? -INFINITY : (MODE == kMin) ? INFINITY : 0.f;
-  for (int cb = 0; cb < nvec; cb += LPR) {
+  // column slabs of LPR vectors are spread over grid.y: few, very long rows (3 elements own all atoms of an
+  // ethanol batch) would otherwise walk the slabs one after the other in a single CTA
+  for (int cb = blockIdx.y * LPR; cb < nvec; cb += LPR * gridDim.y) {
     const int c = cb + sub;
     const bool cok = c < nvec;
     V acc = T::fill(init);
@@ -252,9 +254,9 @@ template <typename V>
 int launch_block(int mode, bool gather, const V* x, const V* wv, const float* ws, const int32_t* rowptr,
                  const int32_t* perm, const int32_t* gidx, int gs, int gp, int64_t n_out, int nvec, int mean, V* y,
                  const int32_t* row_map, const int32_t* n_rows_dev, int grid_rows, cudaStream_t st) {
-  const unsigned grid = static_cast<unsigned>(row_map ? grid_rows : n_out);
+  const unsigned grid_x = static_cast<unsigned>(row_map ? grid_rows : n_out);
 #define KGCNN_BLK_L(M, GA, L)                                                                                   \
-  gms_block_kernel<V, M, GA, L><<<grid, kThreads, 0, st>>>(x, wv, ws, rowptr, perm, gidx, gs, gp, n_out, nvec, mean, \
+  gms_block_kernel<V, M, GA, L><<<dim3(grid_x, static_cast<unsigned>(ceil_div(nvec, L))), kThreads, 0, st>>>(x, wv, ws, rowptr, perm, gidx, gs, gp, n_out, nvec, mean, \
                                                           y, row_map, n_rows_dev)
 #define KGCNN_BLK(M, GA)                                                                                        \
   do {                                                                                                          \
