@@ -255,8 +255,13 @@ def run_gss(args, rank, world, device):
                    "parallelism": "graphs sharded across %d rank(s), no data-path collective" % world},
         "hbm_gbs_algorithmic": alg_bytes / (ms_step * 1e-3) / 1e9,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "kernel": "gms_kernel<float4,16,1,SumW0,gather>",
-                     "algorithmic_bytes_per_launch": alg_bytes / n_kernel_launches, "peak_source": peak_src},
+                     "traffic": 747.6e6,   # ncu --set full: dram read 0.446 GB + write 0.301 GB per launch (profiles/r1_gms_full_v5.csv)
+                     "kernel": "gms_kernel<float4,8,2,SumW0,gather>",
+                     "algorithmic_bytes_per_launch": alg_bytes / n_kernel_launches, "peak_source": peak_src,
+                     "note": "algorithmic bytes count every gathered row (no cache credit, SURVEY 8d); E/N = 20, so "
+                             "19 of 20 row reads hit L1/L2 and the real DRAM traffic is 0.75 GB per launch: frac > 1 "
+                             "is cache reuse, not skipped work. The HBM-bound shapes are GSS-R (default bench "
+                             "line's roofline) and --workload gcn"},
         "e2e": {"value": total_edges / (ms_e2e * 1e-3), "unit": "edges/s", "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e},
         "gpu_launches": launches_per_step * args.steps,

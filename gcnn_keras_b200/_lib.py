@@ -44,6 +44,7 @@ SIGNATURES = {
     "kgcnn_gemm_tn": (_i, [_p, _p, _l, _i, _i, _p, _p, _p, _z, _p]),
     "kgcnn_dense_tc_workspace_bytes": (_z, [_i, _l, _i, _i]),
     "kgcnn_dense_tc": (_i, [_i, _p, _p, _l, _i, _i, _p, _p, _p, _z, _p]),
+    "kgcnn_dense_act": (_i, [_p, _p, _l, _i, _i, _p, _i, _p, _p, _p]),
     "kgcnn_dense_tn_grouped_workspace_bytes": (_z, [_i, _p, _p, _p]),
     "kgcnn_dense_tn_grouped": (_i, [_i, _p, _p, _p, _p, _p, _p, _p, _p, _z, _p]),
     "kgcnn_edge_geometry": (_i, [_p, _p, _p, _l, _i, _i, _i, _p, _p, _f, _i, _f, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),

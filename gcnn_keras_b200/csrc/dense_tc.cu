@@ -20,6 +20,7 @@
 // from the second TMEM accumulator with tcgen05.ld.
 #include <algorithm>
 
+#include "activation.cuh"
 #include "common.cuh"
 
 namespace kgcnn {
@@ -184,7 +185,8 @@ template <int OP>
 __device__ __forceinline__ void
 dense_tc_body(const float* __restrict__ A, const float* __restrict__ B, int64_t M, int K, int U,
               const float* __restrict__ bias, float* __restrict__ out, int64_t rows_per_split, int vec_a,
-              int vec_b, int bx, int by, int bz, float* __restrict__ colsum_part) {
+              int vec_b, int bx, int by, int bz, float* __restrict__ colsum_part,
+              float* __restrict__ act_out = nullptr, int act = 0) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ __align__(8) uint64_t mbar[kStages];
   __shared__ __align__(8) uint64_t full[kStages];
@@ -411,6 +413,19 @@ dense_tc_body(const float* __restrict__ A, const float* __restrict__ B, int64_t 
         if (col + 2 < n_total) o[2] = v.z;
         if (col + 3 < n_total) o[3] = v.w;
       }
+      if (OP == kNN && act_out) {          // Dense + activation in one pass: pre (kept for the derivatives) and f(pre)
+        const float4 f = make_float4(act_value(act, v.x), act_value(act, v.y), act_value(act, v.z),
+                                     act_value(act, v.w));
+        float* q = act_out + row * n_total + col;
+        if (vec_out && ((reinterpret_cast<uintptr_t>(act_out) & 15) == 0) && col + 3 < n_total)
+          *reinterpret_cast<float4*>(q) = f;
+        else {
+          if (col + 0 < n_total) q[0] = f.x;
+          if (col + 1 < n_total) q[1] = f.y;
+          if (col + 2 < n_total) q[2] = f.z;
+          if (col + 3 < n_total) q[3] = f.w;
+        }
+      }
     }
   }
   if (OP == kTN && do_colsum && warp < kThreads / 32) {
@@ -447,9 +462,9 @@ template <int OP>
 __global__ void __launch_bounds__(kCtaThreads)
 dense_tc_kernel(const float* __restrict__ A, const float* __restrict__ B, int64_t M, int K, int U,
                 const float* __restrict__ bias, float* __restrict__ out, int64_t rows_per_split, int vec_a,
-                int vec_b) {
+                int vec_b, float* __restrict__ act_out, int act) {
   dense_tc_body<OP>(A, B, M, K, U, bias, out, rows_per_split, vec_a, vec_b, blockIdx.x, blockIdx.y, blockIdx.z,
-                    nullptr);
+                    nullptr, act_out, act);
 }
 
 __global__ void __launch_bounds__(256)
@@ -590,8 +605,9 @@ size_t kgcnn_dense_tc_workspace_bytes(int op, int64_t M, int K, int U) {
   return static_cast<size_t>(tc::tn_splits(M, K, U)) * K * U * sizeof(float) + 256;
 }
 
-int kgcnn_dense_tc(int op, const float* A, const float* B, int64_t M, int K, int U, const float* bias, float* out,
-                   void* workspace, size_t workspace_bytes, kgcnn_stream_t stream) {
+static int dense_tc_launch(int op, const float* A, const float* B, int64_t M, int K, int U, const float* bias,
+                           float* out, void* workspace, size_t workspace_bytes, kgcnn_stream_t stream,
+                           float* act_out, int act) {
   if (op < tc::kNN || op > tc::kTN || M < 0 || K <= 0 || U <= 0 || !out) return KGCNN_E_INVALID;
   cudaStream_t st = as_stream(stream);
   if (M == 0) {
@@ -613,13 +629,14 @@ int kgcnn_dense_tc(int op, const float* A, const float* B, int64_t M, int K, int
   if (op == tc::kNN) {
     dim3 grid(static_cast<unsigned>(ceil_div<int64_t>(M, tc::kBM)), ceil_div(U, tc::kMaxN));
     tc::dense_tc_kernel<tc::kNN><<<grid, tc::kCtaThreads, tc::kSmemBytes, st>>>(
-        A, B, M, K, U, bias, out, 0, (K % 4 == 0 && al16(A)) ? 1 : 0, (U % 4 == 0 && al16(B)) ? 1 : 0);
+        A, B, M, K, U, bias, out, 0, (K % 4 == 0 && al16(A)) ? 1 : 0, (U % 4 == 0 && al16(B)) ? 1 : 0, act_out, act);
     return finish_launch();
   }
   if (op == tc::kNT) {
     dim3 grid(static_cast<unsigned>(ceil_div<int64_t>(M, tc::kBM)), ceil_div(K, tc::kMaxN));
     tc::dense_tc_kernel<tc::kNT><<<grid, tc::kCtaThreads, tc::kSmemBytes, st>>>(
-        A, B, M, K, U, nullptr, out, 0, (U % 4 == 0 && al16(A)) ? 1 : 0, (U % 4 == 0 && al16(B)) ? 1 : 0);
+        A, B, M, K, U, nullptr, out, 0, (U % 4 == 0 && al16(A)) ? 1 : 0, (U % 4 == 0 && al16(B)) ? 1 : 0, nullptr,
+        0);
     return finish_launch();
   }
   const int S = tc::tn_splits(M, K, U);
@@ -629,10 +646,21 @@ int kgcnn_dense_tc(int op, const float* A, const float* B, int64_t M, int K, int
   dim3 grid(ceil_div(K, tc::kBM), ceil_div(U, tc::kMaxN), S);
   tc::dense_tc_kernel<tc::kTN><<<grid, tc::kCtaThreads, tc::kSmemBytes, st>>>(
       A, B, M, K, U, nullptr, partial, rows_per_split, (K % 4 == 0 && al16(A)) ? 1 : 0,
-      (U % 4 == 0 && al16(B)) ? 1 : 0);
+      (U % 4 == 0 && al16(B)) ? 1 : 0, nullptr, 0);
   const int64_t n = static_cast<int64_t>(K) * U;
   tc::tn_split_reduce_kernel<<<static_cast<unsigned>(ceil_div<int64_t>(n, 256)), 256, 0, st>>>(partial, S, n, out);
   return finish_launch(2);
+}
+
+int kgcnn_dense_tc(int op, const float* A, const float* B, int64_t M, int K, int U, const float* bias, float* out,
+                   void* workspace, size_t workspace_bytes, kgcnn_stream_t stream) {
+  return dense_tc_launch(op, A, B, M, K, U, bias, out, workspace, workspace_bytes, stream, nullptr, 0);
+}
+
+int kgcnn_dense_act(const float* X, const float* W, int64_t M, int K, int U, const float* bias, int act, float* pre,
+                    float* y, kgcnn_stream_t stream) {
+  if (act < KGCNN_ACT_LINEAR || act > KGCNN_ACT_LEAKY_RELU || !pre || !y) return KGCNN_E_INVALID;
+  return dense_tc_launch(tc::kNN, X, W, M, K, U, bias, pre, nullptr, 0, stream, y, act);
 }
 
 size_t kgcnn_dense_tn_grouped_workspace_bytes(int n, const int64_t* M, const int32_t* K, const int32_t* U) {

@@ -687,6 +687,9 @@ def matmul(a, b):
     return _MatMul.apply(a, b, 0)
 
 
+DENSE_FUSE_ACT = True      # False: Dense = GEMM launch + bias/activation launch (diagnostics, A/B timing)
+
+
 class _Linear(torch.autograd.Function):
     """pre = x @ W + b.  Backward: gx = g W^T (library GEMM); (gW, gb) in ONE pass over g by the split-M kernel."""
 
@@ -703,19 +706,52 @@ class _Linear(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g):
         x, w = ctx.saved_tensors
-        g = g.contiguous()
-        gx = gw = gb = None
-        if _want(ctx, 0, x):
-            gx = _MatMul.apply(g, w, 1)
-        if _want(ctx, 1, w) or (ctx.has_bias and _want(ctx, 2, ctx.bias_ref if ctx.bias_leaf else None)):
-            sink = _sink()
-            if sink is not None and ctx.needs_input_grad[1] and sink.add(w, x, g, ctx.bias_ref):
-                pass                                  # deferred: accumulated by the grouped kernel at flush
-            elif ctx.has_bias:
-                gw, gb = _TNCol.apply(x, g)
-            else:
-                gw = _MatMul.apply(x, g, 2)
-        return gx, gw, gb
+        return _linear_backward(ctx, x, w, g.contiguous())
+
+
+def _linear_backward(ctx, x, w, g):
+    """(gx, gW, gb) of pre = x W + b for the cotangent g of pre (shared by _Linear and _LinearAct)."""
+    gx = gw = gb = None
+    if _want(ctx, 0, x):
+        gx = _MatMul.apply(g, w, 1)
+    if _want(ctx, 1, w) or (ctx.has_bias and _want(ctx, 2, ctx.bias_ref if ctx.bias_leaf else None)):
+        sink = _sink()
+        if sink is not None and ctx.needs_input_grad[1] and sink.add(w, x, g, ctx.bias_ref):
+            pass                                  # deferred: accumulated by the grouped kernel at flush
+        elif ctx.has_bias:
+            gw, gb = _TNCol.apply(x, g)
+        else:
+            gw = _MatMul.apply(x, g, 2)
+    return gx, gw, gb
+
+
+class _LinearAct(torch.autograd.Function):
+    """(pre, y) = (x W + b, f(x W + b)) in ONE launch (activation in the tcgen05 epilogue, csrc/dense_tc.cu).
+    Backward is the composition the unfused path records: g = g_pre + g_y * f'(pre) through the bias/activation
+    kernel family (differentiable again: `pre` is this node's own output), then the Linear backward."""
+
+    @staticmethod
+    def forward(ctx, x, w, b, act):
+        ctx.has_bias = b is not None
+        ctx.bias_ref = b.detach() if b is not None else None
+        ctx.bias_leaf = b is not None and b.is_leaf
+        ctx.act = act
+        ctx.set_materialize_grads(False)
+        pre, y = raw_dense_act(x, w, b, act)
+        ctx.save_for_backward(x, w, pre)
+        return pre, y
+
+    @staticmethod
+    def backward(ctx, g_pre, g_y):
+        x, w, pre = ctx.saved_tensors
+        g = None
+        if g_y is not None:
+            g = _BiasAct.apply(pre, None, g_y.contiguous(), None, ctx.act, 1)
+        if g_pre is not None:
+            g = g_pre if g is None else g + g_pre
+        if g is None:
+            return None, None, None, None
+        return _linear_backward(ctx, x, w, g.contiguous()) + (None,)
 
 
 class _TNCol(torch.autograd.Function):
@@ -746,8 +782,12 @@ def dense(x, kernel, bias, activation):
     code = activation if isinstance(activation, int) else act_code(activation)
     lead = x.shape[:-1]
     x2 = x.reshape(-1, x.shape[-1])
-    pre = _Linear.apply(x2, kernel, bias)
-    out = pre if code == _lib.ACT_CODES["linear"] else _BiasAct.apply(pre, None, None, None, code, 0)
+    if code != _lib.ACT_CODES["linear"] and DENSE_FUSE_ACT and x2.is_cuda and x2.dtype == torch.float32 \
+            and not DENSE_LIBRARY:
+        _, out = _LinearAct.apply(x2, kernel, bias, code)
+    else:
+        pre = _Linear.apply(x2, kernel, bias)
+        out = pre if code == _lib.ACT_CODES["linear"] else _BiasAct.apply(pre, None, None, None, code, 0)
     return out.reshape(tuple(lead) + (kernel.shape[1],))
 
 
@@ -944,6 +984,19 @@ def raw_dense_tc(op, a, b, bias=None):
     check(_lib.lib().kgcnn_dense_tc(op, _ptr(a), _ptr(b), M, K, U, _ptr(bias), _ptr(out), _ptr(ws), nbytes, _stream()),
           "kgcnn_dense_tc")
     return out
+
+
+def raw_dense_act(x, w, bias, act):
+    """(pre, f(pre)) with pre = x[M,K] @ w[K,U] + bias: the activation runs in the GEMM epilogue (one launch)."""
+    _need_cuda(x, w, bias)
+    x, w = _f32c(x), _f32c(w)
+    M, K, U = int(x.shape[0]), int(w.shape[0]), int(w.shape[1])
+    pre = torch.empty((M, U), dtype=torch.float32, device=x.device)
+    y = torch.empty((M, U), dtype=torch.float32, device=x.device)
+    bias = None if bias is None else _f32c(bias)
+    check(_lib.lib().kgcnn_dense_act(_ptr(x), _ptr(w), M, K, U, _ptr(bias), int(act), _ptr(pre), _ptr(y), _stream()),
+          "kgcnn_dense_act")
+    return pre, y
 
 
 # ------------------------------------------------------------------------------------------------

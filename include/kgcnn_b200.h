@@ -174,6 +174,12 @@ size_t kgcnn_dense_tc_workspace_bytes(int op, int64_t M, int K, int U);
 int kgcnn_dense_tc(int op, const float* A, const float* B, int64_t M, int K, int U, const float* bias, float* out,
                    void* workspace, size_t workspace_bytes, kgcnn_stream_t stream);
 
+/* a19  Dense with its activation in the GEMM epilogue (kgcnn/layers/modules.py:61-85, `activation(x W + b)`):
+ *   pre[M,U] = X[M,K] W[K,U] + bias[U]  (kept: every derivative of the activation is evaluated at pre),
+ *   y[M,U]   = f(pre),  f = enum kgcnn_activation.  One launch instead of GEMM + bias/activation pass. */
+int kgcnn_dense_act(const float* X, const float* W, int64_t M, int K, int U, const float* bias, int act, float* pre,
+                    float* y, kgcnn_stream_t stream);
+
 /* ---------------------------------------------------------------------------------------------
  * a19  grouped weight gradients: every  dW_i[K_i,U_i] += X_i[M_i,K_i]^T G_i[M_i,U_i],  db_i[U_i] += colsum(G_i)
  *   of one backward sweep in two launches (tcgen05 3xTF32 + fixed-order reduce).  The products are leaves of the

@@ -30,3 +30,57 @@ def test_dense_tc_nn_nt_tn(M, K, U):
     dw = F.raw_dense_tc(2, xd, gd)
     assert rel_err(dw.cpu().numpy(), x64.T @ g64) < RTOL
     assert torch.equal(dw, F.raw_dense_tc(2, xd, gd))        # deterministic
+
+
+ACTS = ["kgcnn>shifted_softplus", "swish", "tanh", "relu", "sigmoid", "kgcnn>leaky_relu"]
+
+
+@pytest.mark.parametrize("act", ACTS)
+@pytest.mark.parametrize("M,K,U", [(18432, 128, 128), (1000, 35, 35), (129, 8, 16), (70, 3, 5), (5000, 20, 384)])
+def test_dense_act_epilogue_matches_two_launch_path(M, K, U, act):
+    """kgcnn_dense_act (activation in the GEMM epilogue) == GEMM launch + bias/activation launch (pre bit for bit:
+    same accumulator; the activation to 1e-6), and within RTOL of float64."""
+    from gcnn_keras_b200 import functional as F
+    rng = np.random.default_rng(M + K + U)
+    x = torch.tensor(rng.standard_normal((M, K)).astype(np.float32)).cuda()
+    w = torch.tensor((rng.standard_normal((K, U)) / np.sqrt(K)).astype(np.float32)).cuda()
+    b = torch.tensor(rng.standard_normal((U,)).astype(np.float32)).cuda()
+    code = F.act_code(act)
+    pre, y = F.raw_dense_act(x, w, b, code)
+    pre_ref = F.raw_dense_tc(0, x, w, b)
+    assert torch.equal(pre, pre_ref)
+    assert rel_err(y.cpu().numpy(), F.raw_bias_act(pre_ref, None, None, None, code, 0).cpu().numpy()) < 1e-6
+    p64 = x.double() @ w.double() + b.double()
+    f64 = {"kgcnn>shifted_softplus": lambda t: torch.nn.functional.softplus(t) - np.log(2.0),
+           "swish": lambda t: t * torch.sigmoid(t), "tanh": torch.tanh, "relu": torch.relu, "sigmoid": torch.sigmoid,
+           "kgcnn>leaky_relu": lambda t: torch.where(t > 0, t, 0.05 * t)}[act]
+    assert rel_err(y.cpu().numpy(), f64(p64).cpu().numpy()) < RTOL
+
+
+@pytest.mark.parametrize("act", ["kgcnn>shifted_softplus", "swish", "tanh"])
+def test_dense_fused_activation_first_and_second_derivatives(act):
+    """F.dense with the fused epilogue gives the same value, gradients and double-backward gradients (the force
+    training pattern: d/dW of a function of dy/dx) as the two-launch path."""
+    from gcnn_keras_b200 import functional as F
+    rng = np.random.default_rng(7)
+    M, K, U = 777, 64, 128
+    x0 = torch.tensor(rng.standard_normal((M, K)).astype(np.float32)).cuda()
+    w0 = torch.tensor((rng.standard_normal((K, U)) / np.sqrt(K)).astype(np.float32)).cuda()
+    w1 = torch.tensor((rng.standard_normal((U, 1)) / np.sqrt(U)).astype(np.float32)).cuda()
+    b0 = torch.tensor(rng.standard_normal((U,)).astype(np.float32)).cuda()
+    c = torch.tensor(rng.standard_normal((M, K)).astype(np.float32)).cuda()
+
+    def run(fuse):
+        F.DENSE_FUSE_ACT = fuse
+        try:
+            x, w, b, v = (t.clone().requires_grad_(True) for t in (x0, w0, b0, w1))
+            e = F.dense(F.dense(x, w, b, act), v, None, "linear").sum()
+            (dx,) = torch.autograd.grad(e, x, create_graph=True)
+            loss = (dx * c).sum() + e
+            gw, gb, gv = torch.autograd.grad(loss, (w, b, v))
+            return e.detach(), dx.detach(), gw, gb, gv
+        finally:
+            F.DENSE_FUSE_ACT = True
+
+    for a, r in zip(run(True), run(False)):
+        assert rel_err(a.cpu().numpy(), r.cpu().numpy()) < 1e-6
