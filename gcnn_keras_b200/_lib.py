@@ -38,6 +38,7 @@ SIGNATURES = {
     "kgcnn_long_rows_build": (_i, [_p, _l, _i, _i, _p, _p, _p]),
     "kgcnn_gather2_mul": (_i, [_p, _p, _i, _p, _p, _i, _i, _l, _i, _p, _p]),
     "kgcnn_bias_act": (_i, [_p, _p, _p, _p, _i, _i, _l, _i, _p, _p]),
+    "kgcnn_bias_act_pair": (_i, [_p, _p, _p, _p, _i, _i, _l, _i, _p, _p, _p]),
     "kgcnn_colsum_workspace_bytes": (_z, [_l, _i]),
     "kgcnn_colsum": (_i, [_p, _l, _i, _p, _p, _z, _p]),
     "kgcnn_gemm_tn_workspace_bytes": (_z, [_l, _i, _i]),

@@ -57,6 +57,55 @@ int launch_act(const float* pre, const float* bias, const float* g1, const float
   return finish_launch();
 }
 
+// The two VJPs of an order-k node out = g1 * f^(k)(pre + bias) for the cotangent gy, in one pass over (pre, gy, g1):
+//     d_pre = gy * g1 * f^(k+1)(pre + bias),   d_g1 = gy * f^(k)(pre + bias)
+// (the last sweep of a force-training step evaluates both for every activated Dense).
+template <int ACT, bool VEC>
+__global__ void __launch_bounds__(256)
+bias_act_pair_kernel(const float* __restrict__ pre, const float* __restrict__ bias, const float* __restrict__ gy,
+                     const float* __restrict__ g1, int order, int64_t total, int U, float* __restrict__ d_pre,
+                     float* __restrict__ d_g1) {
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  if (VEC) {
+    const int64_t nv = total >> 2;
+    for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < nv; i += stride) {
+      float4 p = reinterpret_cast<const float4*>(pre)[i];
+      if (bias) {
+        const float4 b = *reinterpret_cast<const float4*>(bias + static_cast<int>((i << 2) % U));
+        p.x += b.x; p.y += b.y; p.z += b.z; p.w += b.w;
+      }
+      const float4 y = reinterpret_cast<const float4*>(gy)[i];
+      const float4 m = reinterpret_cast<const float4*>(g1)[i];
+      reinterpret_cast<float4*>(d_pre)[i] =
+          make_float4(y.x * m.x * act_deriv<ACT>(p.x, order + 1), y.y * m.y * act_deriv<ACT>(p.y, order + 1),
+                      y.z * m.z * act_deriv<ACT>(p.z, order + 1), y.w * m.w * act_deriv<ACT>(p.w, order + 1));
+      reinterpret_cast<float4*>(d_g1)[i] =
+          make_float4(y.x * act_deriv<ACT>(p.x, order), y.y * act_deriv<ACT>(p.y, order),
+                      y.z * act_deriv<ACT>(p.z, order), y.w * act_deriv<ACT>(p.w, order));
+    }
+  } else {
+    for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total; i += stride) {
+      float p = pre[i];
+      if (bias) p += bias[i % U];
+      const float y = gy[i];
+      d_pre[i] = y * g1[i] * act_deriv<ACT>(p, order + 1);
+      d_g1[i] = y * act_deriv<ACT>(p, order);
+    }
+  }
+}
+
+template <int ACT>
+int launch_act_pair(const float* pre, const float* bias, const float* gy, const float* g1, int order, int64_t total,
+                    int U, float* d_pre, float* d_g1, cudaStream_t st) {
+  auto al = [](const void* p) { return p == nullptr || (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
+  const bool vec = (U % 4 == 0) && al(pre) && al(bias) && al(gy) && al(g1) && al(d_pre) && al(d_g1);
+  const int64_t work = vec ? (total >> 2) : total;
+  const unsigned grid = static_cast<unsigned>(std::min<int64_t>(ceil_div<int64_t>(work, 256), kNumSM * 16));
+  if (vec) bias_act_pair_kernel<ACT, true><<<grid, 256, 0, st>>>(pre, bias, gy, g1, order, total, U, d_pre, d_g1);
+  else bias_act_pair_kernel<ACT, false><<<grid, 256, 0, st>>>(pre, bias, gy, g1, order, total, U, d_pre, d_g1);
+  return finish_launch();
+}
+
 // deterministic column sum: out[u] = sum_m a[m,u]   (bias gradients).  Two fixed-shape stages.
 constexpr int kColTile = 32, kRowThreads = 8, kRowsPerBlock = 512;
 
@@ -107,6 +156,28 @@ int kgcnn_bias_act(const float* pre, const float* bias, const float* g1, const f
       return launch_act<KGCNN_ACT_LEAKY_RELU>(pre, bias, g1, g2, order, total, U, out, st);
     default: return KGCNN_E_INVALID;
   }
+}
+
+int kgcnn_bias_act_pair(const float* pre, const float* bias, const float* gy, const float* g1, int act, int order,
+                        int64_t M, int U, float* d_pre, float* d_g1, kgcnn_stream_t stream) {
+  if (M < 0 || U <= 0 || order < 0 || order > 2) return KGCNN_E_INVALID;
+  if (M == 0) return KGCNN_OK;
+  if (!pre || !gy || !g1 || !d_pre || !d_g1) return KGCNN_E_INVALID;
+  cudaStream_t st = as_stream(stream);
+  const int64_t total = M * U;
+#define KGCNN_PAIR(A) case A: return launch_act_pair<A>(pre, bias, gy, g1, order, total, U, d_pre, d_g1, st);
+  switch (act) {
+    KGCNN_PAIR(KGCNN_ACT_LINEAR)
+    KGCNN_PAIR(KGCNN_ACT_SHIFTED_SOFTPLUS)
+    KGCNN_PAIR(KGCNN_ACT_SOFTPLUS2)
+    KGCNN_PAIR(KGCNN_ACT_SWISH)
+    KGCNN_PAIR(KGCNN_ACT_TANH)
+    KGCNN_PAIR(KGCNN_ACT_RELU)
+    KGCNN_PAIR(KGCNN_ACT_SIGMOID)
+    KGCNN_PAIR(KGCNN_ACT_LEAKY_RELU)
+    default: return KGCNN_E_INVALID;
+  }
+#undef KGCNN_PAIR
 }
 
 size_t kgcnn_colsum_workspace_bytes(int64_t M, int U) {

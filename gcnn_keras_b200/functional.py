@@ -422,6 +422,22 @@ def raw_bias_act(pre, bias, g1, g2, act, order):
     return out
 
 
+BIAS_ACT_PAIR = True       # False: the two VJPs of an activation node as two launches (diagnostics, A/B timing)
+
+
+def raw_bias_act_pair(pre, bias, gy, g1, act, order):
+    """(gy * g1 * f^(order+1)(pre + bias), gy * f^(order)(pre + bias)) in one launch."""
+    _need_cuda(pre, bias, gy, g1)
+    pre, gy, g1 = _f32c(pre), _f32c(gy), _f32c(g1)
+    U = int(pre.shape[-1])
+    M = pre.numel() // U if U else 0
+    d_pre, d_g1 = torch.empty_like(pre), torch.empty_like(pre)
+    bias = None if bias is None else _f32c(bias)
+    check(_lib.lib().kgcnn_bias_act_pair(_ptr(pre), _ptr(bias), _ptr(gy), _ptr(g1), act, order, M, U, _ptr(d_pre),
+                                         _ptr(d_g1), _stream()), "kgcnn_bias_act_pair")
+    return d_pre, d_g1
+
+
 def raw_colsum(a2d):
     _need_cuda(a2d)
     a2d = _f32c(a2d)
@@ -464,6 +480,11 @@ class _BiasAct(torch.autograd.Function):
         act, k = ctx.act, ctx.order
         g_pre = g_bias = g_g1 = g_g2 = None
         want_bias = bias is not None and _want(ctx, 1, bias)
+        if (BIAS_ACT_PAIR and not torch.is_grad_enabled() and k <= 2 and ctx.needs_input_grad[0] and not want_bias
+                and g1 is not None and g2 is None and ctx.needs_input_grad[2]):
+            # last sweep (nothing differentiates through it again): both VJPs in one pass over (pre, gy, g1)
+            g_pre, g_g1 = raw_bias_act_pair(pre, bias, gy, g1, act, k)
+            return g_pre, None, g_g1, None, None, None
         if ctx.needs_input_grad[0] or want_bias:
             if k >= 3:
                 raise NotImplementedError("activation derivatives above order 3 are not instantiated")

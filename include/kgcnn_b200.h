@@ -151,6 +151,10 @@ int kgcnn_gather2_mul(const float* a, const int32_t* ia, int ia_stride, const fl
  * ------------------------------------------------------------------------------------------- */
 int kgcnn_bias_act(const float* pre, const float* bias, const float* g1, const float* g2, int act, int order,
                    int64_t M, int U, float* out, kgcnn_stream_t stream);
+/* both VJPs of out = g1 * f^(order)(pre + bias) for the cotangent gy in one pass (order 0..2):
+ *     d_pre = gy * g1 * f^(order+1)(pre + bias),  d_g1 = gy * f^(order)(pre + bias) */
+int kgcnn_bias_act_pair(const float* pre, const float* bias, const float* gy, const float* g1, int act, int order,
+                        int64_t M, int U, float* d_pre, float* d_g1, kgcnn_stream_t stream);
 size_t kgcnn_colsum_workspace_bytes(int64_t M, int U);
 int kgcnn_colsum(const float* a, int64_t M, int U, float* out, void* workspace, size_t workspace_bytes,
                  kgcnn_stream_t stream);

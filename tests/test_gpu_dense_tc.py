@@ -84,3 +84,40 @@ def test_dense_fused_activation_first_and_second_derivatives(act):
 
     for a, r in zip(run(True), run(False)):
         assert rel_err(a.cpu().numpy(), r.cpu().numpy()) < 1e-6
+
+
+@pytest.mark.parametrize("act", ACTS)
+@pytest.mark.parametrize("order", [0, 1, 2])
+@pytest.mark.parametrize("M,U,with_bias", [(18432, 128, False), (777, 35, True), (70, 5, True)])
+def test_bias_act_pair_matches_the_two_single_launches(act, order, M, U, with_bias):
+    from gcnn_keras_b200 import functional as F
+    rng = np.random.default_rng(M + U + order)
+    pre, gy, g1 = (torch.tensor(rng.standard_normal((M, U)).astype(np.float32)).cuda() for _ in range(3))
+    b = torch.tensor(rng.standard_normal((U,)).astype(np.float32)).cuda() if with_bias else None
+    code = F.act_code(act)
+    d_pre, d_g1 = F.raw_bias_act_pair(pre, b, gy, g1, code, order)
+    assert rel_err(d_pre.cpu().numpy(), F.raw_bias_act(pre, b, gy, g1, code, order + 1).cpu().numpy(), ) < 1e-6
+    assert rel_err(d_g1.cpu().numpy(), F.raw_bias_act(pre, b, gy, None, code, order).cpu().numpy()) < 1e-6
+
+
+def test_bias_act_pair_in_the_last_sweep_equals_two_launch_backward():
+    from gcnn_keras_b200 import functional as F
+    rng = np.random.default_rng(11)
+    M, K, U = 500, 32, 64
+    x0 = torch.tensor(rng.standard_normal((M, K)).astype(np.float32)).cuda()
+    w0 = torch.tensor((rng.standard_normal((K, U)) / np.sqrt(K)).astype(np.float32)).cuda()
+    b0 = torch.tensor(rng.standard_normal((U,)).astype(np.float32)).cuda()
+    c = torch.tensor(rng.standard_normal((M, K)).astype(np.float32)).cuda()
+
+    def run(pair):
+        F.BIAS_ACT_PAIR = pair
+        try:
+            x, w, b = (t.clone().requires_grad_(True) for t in (x0, w0, b0))
+            e = F.dense(x, w, b, "swish").sum()
+            (dx,) = torch.autograd.grad(e, x, create_graph=True)
+            return torch.autograd.grad((dx * c).sum(), (w, b))
+        finally:
+            F.BIAS_ACT_PAIR = True
+
+    for a, r in zip(run(True), run(False)):
+        assert rel_err(a.cpu().numpy(), r.cpu().numpy()) < 1e-6
