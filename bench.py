@@ -421,6 +421,10 @@ def gss_roofline(device, iters=10):
             "workload": "GSS-R (N=%d, E=%d uniform random senders, F=%d): gathered rows miss L2" % (n, e_r, feat),
             "algorithmic_bytes_per_launch": bytes_r, "ms_per_launch": ms_r, "peak_source": peak_src,
             "edges_per_s": e_r / (2 * ms_r * 1e-3),
+            "frac_on_traffic": 16.29e9 / (ms_r * 1e-3) / 1e9 / peak,
+            "note": "achieved = algorithmic bytes (every gathered row counted, SURVEY 8d) / launch time; the ncu DRAM "
+                    "traffic is 7 % below the algorithmic bytes (the 126 MB L2 serves part of the 1 GB of gathered "
+                    "rows), so frac can touch 1.0 while frac_on_traffic (real DRAM bytes / time / peak) is ~0.93",
             "cached_shape": {"workload": "GSS-L (N=%d, E=%d, F=64, C1 pattern x 65536 graphs)" % (N, E),
                              "achieved": ach_l, "frac": ach_l / peak, "ms_per_launch": ms_l,
                              "algorithmic_bytes_per_launch": bytes_l, "traffic": 752.2e6,
