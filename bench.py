@@ -478,8 +478,6 @@ def run_force(args, rank, world, device, kind):
     build, default_batch, metric, workload = FORCE_WORKLOADS[kind]
     batch = args.batch or default_batch
     model, train_step, data = build(device, batch, seed=rank)
-    if world > 1:
-        from gcnn_keras_b200.distributed import broadcast_parameters
     # C4: the 'kj' angle triples (278 MB per batch) are rebuilt on the device from the pair list in the e2e leg
     device_angles = "kj" if (kind == "hdnnp" and not args.host_angles) else None
     captured = CapturedForceTrainStep(train_step, data, device, device_angles=device_angles)

@@ -27,7 +27,9 @@ SIGNATURES = {
     "kgcnn_shift_index": (_i, [_p, _l, _i, _p, _p, _l, _p, _p, _p]),
     "kgcnn_value_rowids": (_i, [_p, _l, _l, _p, _p]),
     "kgcnn_cast_i64_i32": (_i, [_p, _l, _p, _p]),
-    "kgcnn_check_sorted": (_i, [_p, _i, _l, _l, _p, _p]),
+    "kgcnn_pad": (_i, [_p, _p, _l, _l, _l, ctypes.c_uint32, ctypes.c_uint32, _i, _p, _p, _i, _p]),
+    "kgcnn_unpad": (_i, [_p, _p, _l, _l, _l, _l, _p, _p]),
+    "kgcnn_check_sorted": (_i, [_p, _i, _l, _l, _p, _i, _p]),
     "kgcnn_plan_workspace_bytes": (_z, [_l, _l]),
     "kgcnn_plan_build": (_i, [_p, _i, _l, _l, _i, _p, _p, _p, _z, _p]),
     "kgcnn_permute_i32": (_i, [_p, _i, _p, _l, _p, _p]),
@@ -41,8 +43,6 @@ SIGNATURES = {
     "kgcnn_bias_act_pair": (_i, [_p, _p, _p, _p, _i, _i, _l, _i, _p, _p, _p]),
     "kgcnn_colsum_workspace_bytes": (_z, [_l, _i]),
     "kgcnn_colsum": (_i, [_p, _l, _i, _p, _p, _z, _p]),
-    "kgcnn_gemm_tn_workspace_bytes": (_z, [_l, _i, _i]),
-    "kgcnn_gemm_tn": (_i, [_p, _p, _l, _i, _i, _p, _p, _p, _z, _p]),
     "kgcnn_dense_tc_workspace_bytes": (_z, [_i, _l, _i, _i]),
     "kgcnn_dense_tc": (_i, [_i, _p, _p, _l, _i, _i, _p, _p, _p, _z, _p]),
     "kgcnn_dense_act": (_i, [_p, _p, _l, _i, _i, _p, _i, _p, _p, _p]),
@@ -61,7 +61,7 @@ SIGNATURES = {
     "kgcnn_range_count": (_i, [_p, _i, _p, _l, _l, _i, _i, _d, _i, _i, _i, _p, _p]),
     "kgcnn_range_emit": (_i, [_p, _i, _p, _l, _l, _i, _i, _d, _i, _i, _i, _p, _p, _p, _p, _p]),
     "kgcnn_segment_softmax": (_i, [_p, _p, _p, _l, _l, _i, _i, _p, _p]),
-    "kgcnn_adam_clipnorm": (_i, [_p, _p, _p, _p, _p, _p, _l, _f, _f, _f, _f, _f, _p, _p]),
+    "kgcnn_adam_clipnorm": (_i, [_p, _p, _p, _p, _p, _p, _l, _f, _f, _f, _f, _f, _p, _p, _p, _i, _p]),
 }
 
 OP_SUM, OP_MEAN, OP_MAX, OP_MIN = 0, 1, 2, 3

@@ -3,6 +3,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <mutex>
+
 #include "../../include/kgcnn_b200.h"
 
 namespace kgcnn {
@@ -20,6 +22,23 @@ inline int finish_launch(int n = 1) {
   }
   return KGCNN_OK;
 }
+
+// Function attributes (opt-in dynamic shared memory) are per device: one flag word per call site, one bit per
+// device ordinal, set under a lock so a second thread never launches before the attribute is in place.
+struct PerDeviceOnce {
+  std::mutex mu;
+  uint64_t done = 0;
+  template <typename Fn>
+  void run(Fn&& fn) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    const uint64_t bit = 1ull << (dev & 63);
+    std::lock_guard<std::mutex> lock(mu);
+    if (done & bit) return;
+    fn();
+    done |= bit;
+  }
+};
 
 inline cudaStream_t as_stream(kgcnn_stream_t s) { return reinterpret_cast<cudaStream_t>(s); }
 

@@ -616,16 +616,15 @@ static int dense_tc_launch(int op, const float* A, const float* B, int64_t M, in
   }
   if (!A || !B) return KGCNN_E_INVALID;
   auto al16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
-  static bool attr_set = false;
-  if (!attr_set) {
+  static PerDeviceOnce attr;
+  attr.run([] {
     cudaFuncSetAttribute(tc::dense_tc_kernel<tc::kNN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                          static_cast<int>(tc::kSmemBytes));
     cudaFuncSetAttribute(tc::dense_tc_kernel<tc::kNT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                          static_cast<int>(tc::kSmemBytes));
     cudaFuncSetAttribute(tc::dense_tc_kernel<tc::kTN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                          static_cast<int>(tc::kSmemBytes));
-    attr_set = true;
-  }
+  });
   if (op == tc::kNN) {
     dim3 grid(static_cast<unsigned>(ceil_div<int64_t>(M, tc::kBM)), ceil_div(U, tc::kMaxN));
     tc::dense_tc_kernel<tc::kNN><<<grid, tc::kCtaThreads, tc::kSmemBytes, st>>>(
@@ -686,23 +685,33 @@ int kgcnn_dense_tn_grouped(int n, const float* const* X, const float* const* G, 
   for (int i = 0; i < n; ++i)
     if (M[i] < 0 || K[i] <= 0 || U[i] <= 0 || !dW[i] || (M[i] > 0 && (!X[i] || !G[i]))) return KGCNN_E_INVALID;
   cudaStream_t st = as_stream(stream);
-  static bool attr_set = false;
-  if (!attr_set) {
+  static PerDeviceOnce attr;
+  attr.run([] {
     cudaFuncSetAttribute(tc::tn_grouped_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                          static_cast<int>(tc::kSmemBytes));
-    attr_set = true;
-  }
+  });
   const int64_t rps = tc::grouped_rows_per_split(n, M, K, U);
   float* ws = static_cast<float*>(workspace);
   int64_t ws_off = 0;
   int launches = 0;
-  for (int base = 0; base < n; base += tc::kMaxGroup) {
-    const int cnt = std::min(tc::kMaxGroup, n - base);
+  // Problems are packed into launches greedily.  Within one launch every dW (and its db) belongs to exactly ONE
+  // output run of adjacent problems -- the reduce kernel walks outputs, so a second run on the same dW would be a
+  // read-modify-write race; such a problem (same dW not adjacent, or a different non-null db) starts the next launch.
+  int i = 0;
+  while (i < n) {
     tc::TnGroup grp;
     grp.n_problems = 0; grp.n_outputs = 0; grp.total_ctas = 0; grp.pad = 0; grp.total_elems = 0;
-    for (int q = 0; q < cnt; ++q) {
-      const int i = base + q;
+    for (; i < n && grp.n_problems < tc::kMaxGroup; ++i) {
       if (M[i] == 0) continue;                                     // contributes nothing
+      int hit = -1;
+      for (int o = 0; o < grp.n_outputs; ++o)
+        if (grp.o[o].dW == dW[i]) hit = o;
+      bool merge = false;
+      if (hit >= 0) {
+        const tc::TnOutput& o = grp.o[hit];
+        merge = hit == grp.n_outputs - 1 && o.K == K[i] && o.U == U[i] && (o.db == db[i] || !db[i] || !o.db);
+        if (!merge) break;                                         // conflicting destination: next launch
+      }
       tc::TnProblem& pr = grp.p[grp.n_problems];
       pr.X = X[i]; pr.G = G[i]; pr.M = M[i]; pr.K = K[i]; pr.U = U[i];
       pr.splits = static_cast<int32_t>(std::max<int64_t>(1, ceil_div<int64_t>(M[i], rps)));
@@ -714,11 +723,7 @@ int kgcnn_dense_tn_grouped(int n, const float* const* X, const float* const* G, 
       grp.total_ctas += pr.tiles_k * pr.tiles_u * pr.splits;
       int64_t fl = static_cast<int64_t>(pr.splits) * (static_cast<int64_t>(K[i]) * U[i] + U[i]);
       ws_off += (fl + 63) / 64 * 64;
-      // same destination as the previous problem of this launch -> same output run
-      const bool same = grp.n_outputs > 0 && grp.o[grp.n_outputs - 1].dW == dW[i] &&
-                        grp.o[grp.n_outputs - 1].K == K[i] && grp.o[grp.n_outputs - 1].U == U[i] &&
-                        (grp.o[grp.n_outputs - 1].db == db[i] || !db[i] || !grp.o[grp.n_outputs - 1].db);
-      if (same) {
+      if (merge) {
         tc::TnOutput& o = grp.o[grp.n_outputs - 1];
         o.count += 1;
         if (!o.db && db[i]) { o.db = db[i]; grp.total_elems += U[i]; }   // it is the last output: no later shift

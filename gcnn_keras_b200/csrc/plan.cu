@@ -54,13 +54,17 @@ __global__ void cast_i64_i32_kernel(const int64_t* __restrict__ src, int64_t n, 
   if (i < n) dst[i] = static_cast<int32_t>(src[i]);
 }
 
+// `fixed` (nullable): a copy of the keys clamped into [0, N) for the consumers, so that a batch that violates
+// the range contract can never make a later kernel of an already enqueued (captured) step read out of bounds;
+// the flags still report the violation and the optimizer skips the update (kgcnn_adam_clipnorm's guard).
 __global__ void check_sorted_kernel(const int32_t* __restrict__ key, int stride, int64_t E, int64_t N,
-                                    int32_t* __restrict__ flags) {
+                                    int32_t* __restrict__ flags, int32_t* __restrict__ fixed) {
   int64_t e = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
   if (e >= E) return;
   int32_t k = key[e * stride];
   if (k < 0 || k >= N) flags[1] = 1;
   if (e > 0 && key[(e - 1) * stride] > k) flags[0] = 1;
+  if (fixed && (k < 0 || k >= N)) fixed[e * stride] = k < 0 ? 0 : static_cast<int32_t>(N - 1);
 }
 
 // Sorted keys: row pointer from segment boundaries, no atomics, no scan.
@@ -175,12 +179,13 @@ int kgcnn_cast_i64_i32(const int64_t* src, int64_t n, int32_t* dst, kgcnn_stream
   return finish_launch();
 }
 
-int kgcnn_check_sorted(const int32_t* key, int key_stride, int64_t E, int64_t N, int32_t* flags,
+int kgcnn_check_sorted(int32_t* key, int key_stride, int64_t E, int64_t N, int32_t* flags, int clamp_in_place,
                        kgcnn_stream_t stream) {
   if (E < 0 || N < 0 || key_stride <= 0 || !flags) return KGCNN_E_INVALID;
   if (E == 0) return KGCNN_OK;
-  if (!key) return KGCNN_E_INVALID;
-  check_sorted_kernel<<<blocks_for(E), kThreads, 0, as_stream(stream)>>>(key, key_stride, E, N, flags);
+  if (!key || (clamp_in_place && N == 0)) return KGCNN_E_INVALID;
+  check_sorted_kernel<<<blocks_for(E), kThreads, 0, as_stream(stream)>>>(key, key_stride, E, N, flags,
+                                                                         clamp_in_place ? key : nullptr);
   return finish_launch();
 }
 

@@ -72,3 +72,11 @@ def broadcast_parameters(module, src=0, group=None):
         return
     for p in module.parameters():
         dist.broadcast(p.data, src=src, group=group)
+
+
+def broadcast_flat(flat, src=0, group=None):
+    """One broadcast of a flat parameter buffer (FlatAdam.flat; the parameters are views of it)."""
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return
+    dist.broadcast(flat, src=src, group=group)

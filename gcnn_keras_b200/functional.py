@@ -83,11 +83,111 @@ def raw_cast_i32(t64):
     return out
 
 
-def raw_check_sorted(key, n_targets):
+def _elem_words(dtype):
+    if dtype in (torch.float32, torch.int32):
+        return 1
+    if dtype == torch.int64:
+        return 2
+    raise TypeError("ragged <-> padded conversion moves float32 / int32 / int64 values, got %s" % dtype)
+
+
+def raw_pad(values, row_splits, max_len, default_value=0, mask=None):
+    """a20: (padded [B, max_len, ...], mask | None).  mask: None, 'like' (ones_like of the values, same dtype and
+    shape as padded) or 'bool' (one flag per element).  One launch for both outputs."""
+    import struct
+    _need_cuda(values, row_splits)
+    words = _elem_words(values.dtype)
+    values = values.contiguous()
+    B = int(row_splits.shape[0]) - 1
+    tail = tuple(values.shape[1:])
+    n_tail = 1
+    for t in tail:
+        n_tail *= int(t)
+    out = torch.empty((B, int(max_len)) + tail, dtype=values.dtype, device=values.device)
+    m = None
+    if mask == "like":
+        m = torch.empty_like(out)
+    elif mask == "bool":
+        if words != 1:
+            raise TypeError("boolean masks are defined for 4-byte element types")
+        m = torch.empty(out.shape, dtype=torch.bool, device=values.device)
+    elif mask is not None:
+        raise ValueError("mask must be None, 'like' or 'bool'")
+    if values.dtype == torch.float32:
+        w0, w1 = struct.unpack("<I", struct.pack("<f", float(default_value)))[0], 0
+    else:
+        bits = int(default_value) & 0xFFFFFFFFFFFFFFFF
+        w0, w1 = bits & 0xFFFFFFFF, bits >> 32
+    if n_tail == 0:
+        return out, m
+    check(_lib.lib().kgcnn_pad(_ptr(values), _ptr(row_splits), B, int(max_len), n_tail * words, w0, w1, words,
+                               _ptr(out), _ptr(m), 1 if mask == "bool" else 0, _stream()), "kgcnn_pad")
+    return out, m
+
+
+def raw_unpad(padded, row_splits, n_values):
+    """values[n] = padded[graph_of(n), n - row_splits[graph_of(n)]] (force.py:204-211 without the mask tensor:
+    the row partition already says which slots are live)."""
+    _need_cuda(padded, row_splits)
+    words = _elem_words(padded.dtype)
+    padded = padded.contiguous()
+    B, max_len = int(padded.shape[0]), int(padded.shape[1])
+    tail = tuple(padded.shape[2:])
+    n_tail = 1
+    for t in tail:
+        n_tail *= int(t)
+    out = torch.empty((int(n_values),) + tail, dtype=padded.dtype, device=padded.device)
+    if n_tail and n_values:
+        check(_lib.lib().kgcnn_unpad(_ptr(padded), _ptr(row_splits), B, max_len, n_tail * words, int(n_values),
+                                     _ptr(out), _stream()), "kgcnn_unpad")
+    return out
+
+
+class _Pad(torch.autograd.Function):
+    """ragged values -> padded tensor; the VJP is the unpad kernel (padding slots carry no gradient)."""
+
+    @staticmethod
+    def forward(ctx, values, row_splits, max_len, default_value):
+        ctx.row_splits, ctx.n = row_splits, int(values.shape[0])
+        return raw_pad(values, row_splits, max_len, default_value)[0]
+
+    @staticmethod
+    def backward(ctx, g):
+        return _Unpad.apply(g.contiguous(), ctx.row_splits, ctx.n), None, None, None
+
+
+class _Unpad(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, padded, row_splits, n_values):
+        ctx.row_splits, ctx.max_len = row_splits, int(padded.shape[1])
+        return raw_unpad(padded, row_splits, n_values)
+
+    @staticmethod
+    def backward(ctx, g):
+        return _Pad.apply(g.contiguous(), ctx.row_splits, ctx.max_len, 0), None, None
+
+
+def pad(values, row_splits, max_len, default_value=0):
+    """RaggedTensor.to_tensor on the device (differentiable for floating values)."""
+    if values.is_floating_point() and values.requires_grad and torch.is_grad_enabled():
+        return _Pad.apply(values, row_splits, int(max_len), default_value)
+    return raw_pad(values, row_splits, max_len, default_value)[0]
+
+
+def unpad(padded, row_splits, n_values):
+    if padded.is_floating_point() and padded.requires_grad and torch.is_grad_enabled():
+        return _Unpad.apply(padded, row_splits, int(n_values))
+    return raw_unpad(padded, row_splits, n_values)
+
+
+def raw_check_sorted(key, n_targets, flags=None, clamp=False):
+    """flags int32[2] = (not ascending, out of range).  `flags`: a zeroed device slot to write into (the capture
+    mode's guard buffer); `clamp`: also rewrite out-of-range ids in place (see include/kgcnn_b200.h)."""
     _need_cuda(key)
-    flags = torch.zeros((2,), dtype=torch.int32, device=key.device)
-    check(_lib.lib().kgcnn_check_sorted(_ptr(key), 1, int(key.shape[0]), n_targets, _ptr(flags), _stream()),
-          "kgcnn_check_sorted")
+    if flags is None:
+        flags = torch.zeros((2,), dtype=torch.int32, device=key.device)
+    check(_lib.lib().kgcnn_check_sorted(_ptr(key), 1, int(key.shape[0]), n_targets, _ptr(flags),
+                                        1 if (clamp and n_targets > 0) else 0, _stream()), "kgcnn_check_sorted")
     return flags
 
 
@@ -511,20 +611,6 @@ def bias_act(pre, bias, activation):
     return _BiasAct.apply(pre, bias, None, None, code, 0)
 
 
-def raw_gemm_tn(x2d, g2d, want_colsum=False):
-    """dW = x^T g (and optionally db = colsum(g)) with the split-M deterministic kernel."""
-    _need_cuda(x2d, g2d)
-    x2d, g2d = _f32c(x2d), _f32c(g2d)
-    M, K1, K2 = int(x2d.shape[0]), int(x2d.shape[1]), int(g2d.shape[1])
-    dw = torch.empty((K1, K2), dtype=torch.float32, device=x2d.device)
-    db = torch.empty((K2,), dtype=torch.float32, device=x2d.device) if want_colsum else None
-    nbytes = int(_lib.lib().kgcnn_gemm_tn_workspace_bytes(M, K1, K2))
-    ws = torch.empty((max(nbytes, 4),), dtype=torch.uint8, device=x2d.device)
-    check(_lib.lib().kgcnn_gemm_tn(_ptr(x2d), _ptr(g2d), M, K1, K2, _ptr(dw), _ptr(db), _ptr(ws), nbytes, _stream()),
-          "kgcnn_gemm_tn")
-    return (dw, db) if want_colsum else dw
-
-
 class WeightGradSink:
     """Deferred, grouped weight gradients of one backward sweep.
 
@@ -646,8 +732,12 @@ def _sink():
     return _SINK if (_SINK is not None and not torch.is_grad_enabled()) else None
 
 
-_TN_MIN_ROWS = 512     # below this the reduction axis is short and a library GEMM is as good
-DENSE_LIBRARY = False  # diagnostics only (tools/diag_hdnnp.py): route Dense through the library GEMM instead of dense_tc
+def _dense_operands(*tensors):
+    """Dense contractions exist on the tcgen05 path only: CUDA float32 matrices, anything else raises."""
+    _need_cuda(*tensors)
+    for t in tensors:
+        if t is not None and t.dtype != torch.float32:
+            raise TypeError("kgcnn_b200 Dense kernels compute in float32, got %s" % t.dtype)
 
 
 class _MatMul(torch.autograd.Function):
@@ -658,13 +748,10 @@ class _MatMul(torch.autograd.Function):
     def forward(ctx, a, b, mode):
         ctx.mode = mode
         ctx.save_for_backward(a, b)
-        if a.is_cuda and a.dtype == torch.float32 and a.dim() == 2 and b.dim() == 2 and not DENSE_LIBRARY:
-            return raw_dense_tc(mode, a, b)          # tcgen05 tensor cores, 3xTF32
-        if mode == 0:
-            return a @ b
-        if mode == 1:
-            return a @ b.t()
-        return a.t() @ b
+        _dense_operands(a, b)
+        if a.dim() != 2 or b.dim() != 2:
+            raise ValueError("matmul operands must be matrices, got %s and %s" % (tuple(a.shape), tuple(b.shape)))
+        return raw_dense_tc(mode, a, b)              # tcgen05 tensor cores, 3xTF32
 
     @staticmethod
     def backward(ctx, g):
@@ -712,7 +799,7 @@ DENSE_FUSE_ACT = True      # False: Dense = GEMM launch + bias/activation launch
 
 
 class _Linear(torch.autograd.Function):
-    """pre = x @ W + b.  Backward: gx = g W^T (library GEMM); (gW, gb) in ONE pass over g by the split-M kernel."""
+    """pre = x @ W + b.  Backward: gx = g W^T (tcgen05 NT); (gW, gb) deferred to the grouped TN launch or _TNCol."""
 
     @staticmethod
     def forward(ctx, x, w, b):
@@ -720,9 +807,8 @@ class _Linear(torch.autograd.Function):
         ctx.has_bias = b is not None
         ctx.bias_ref = b.detach() if b is not None else None      # identity only (the sink's variable lookup)
         ctx.bias_leaf = b is not None and b.is_leaf
-        if x.is_cuda and x.dtype == torch.float32 and not DENSE_LIBRARY:
-            return raw_dense_tc(0, x, w, b)          # tcgen05 tensor cores, 3xTF32, bias in the epilogue
-        return torch.addmm(b, x, w) if b is not None else x @ w
+        _dense_operands(x, w, b)
+        return raw_dense_tc(0, x, w, b)              # tcgen05 tensor cores, 3xTF32, bias in the epilogue
 
     @staticmethod
     def backward(ctx, g):
@@ -781,9 +867,8 @@ class _TNCol(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, g):
         ctx.save_for_backward(x, g)
-        if x.is_cuda and x.dtype == torch.float32 and not DENSE_LIBRARY:
-            return raw_dense_tc(2, x, g), raw_colsum(g)
-        return x.t() @ g, g.sum(0)
+        _dense_operands(x, g)
+        return raw_dense_tc(2, x, g), raw_colsum(g)
 
     @staticmethod
     def backward(ctx, ggw, ggb):
@@ -803,8 +888,8 @@ def dense(x, kernel, bias, activation):
     code = activation if isinstance(activation, int) else act_code(activation)
     lead = x.shape[:-1]
     x2 = x.reshape(-1, x.shape[-1])
-    if code != _lib.ACT_CODES["linear"] and DENSE_FUSE_ACT and x2.is_cuda and x2.dtype == torch.float32 \
-            and not DENSE_LIBRARY:
+    _dense_operands(x2, kernel, bias)
+    if code != _lib.ACT_CODES["linear"] and DENSE_FUSE_ACT:
         _, out = _LinearAct.apply(x2, kernel, bias, code)
     else:
         pre = _Linear.apply(x2, kernel, bias)

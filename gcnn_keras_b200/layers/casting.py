@@ -26,12 +26,9 @@ class ChangeTensorType(GraphBaseLayer):
                 return inputs
             dv = 0 if self.default_value is None else self.default_value
             if self.output_tensor_type in self._str_type_tensor:
-                return inputs.to_tensor(default_value=dv)              # casting.py:78-79
-            if self.output_tensor_type in self._str_type_mask:         # casting.py:80-84
-                padded = inputs.to_tensor(default_value=dv)
-                ones = torch.ones_like(inputs.values, dtype=torch.bool if self.boolean_mask else inputs.values.dtype)
-                mask = inputs.with_values(ones).to_tensor()
-                return padded, mask
+                return inputs.to_tensor(default_value=dv, shape=self.shape)           # casting.py:78-79
+            if self.output_tensor_type in self._str_type_mask:         # casting.py:80-84 (padded + mask, one launch)
+                return inputs.to_tensor_and_mask(default_value=dv, boolean_mask=self.boolean_mask, shape=self.shape)
         raise NotImplementedError("Unsupported conversion from '%s' to '%s'."
                                   % (self.input_tensor_type, self.output_tensor_type))
 

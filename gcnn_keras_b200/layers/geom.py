@@ -230,7 +230,7 @@ class GaussBasisLayer(GraphBaseLayer):
         return config
 
 
-@register_keras_serializable(package="kgcnn", name="FourierBasisLayer")
+@register_keras_serializable(package="kgcnn", name="BesselBasisLayer")
 class BesselBasisLayer(GraphBaseLayer):
     """kgcnn/layers/geom.py:717-805: env(d/c) * sin(f_n d/c), trainable frequencies f_n = n pi."""
 

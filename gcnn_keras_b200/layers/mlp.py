@@ -53,9 +53,7 @@ class MLPBase(GraphBaseLayer):
 
 @register_keras_serializable(package="kgcnn", name="MLP")
 class MLP(MLPBase):
-    """kgcnn/layers/mlp.py:246-325: on dense tensors (graph-level embeddings)."""
+    """kgcnn/layers/mlp.py:246-322: Dense stack on dense tensors and, through map_values, on ragged embeddings."""
 
 
-@register_keras_serializable(package="kgcnn", name="GraphMLP")
-class GraphMLP(MLPBase):
-    """kgcnn/layers/mlp.py:329-416: on ragged node / edge embeddings."""
+GraphMLP = MLP      # kgcnn/layers/mlp.py:325 (an alias, registered once as 'kgcnn>MLP')

@@ -21,11 +21,33 @@ class PlanMode:
     'capture'       : no host sync (CUDA-graph capture): trust the recorded answers, write the device-side
                       check flags into `flags` so the host can validate the assumption after each replay."""
 
-    def __init__(self, kind, hints=None):
+    MAX_FLAGS = 64
+
+    def __init__(self, kind, hints=None, device=None):
         self.kind = kind
         self.hints = [] if hints is None else list(hints)
         self.cursor = 0
         self.flags = []          # (assumed_sorted, device int32[2]) per relation, capture mode
+        # capture mode: ONE guard buffer [MAX_FLAGS, 2] (zeroed at the start of every replay by the captured step)
+        # that the relations write their check flags into, and a mask of the words whose being non-zero violates
+        # the recorded assumptions; the optimizer kernel reads both and skips the update when they intersect.
+        self.flag_buf = self.mask_buf = None
+        if kind == "capture" and device is not None:
+            self.flag_buf = torch.zeros((self.MAX_FLAGS, 2), dtype=torch.int32, device=device)
+            self.mask_buf = torch.zeros((self.MAX_FLAGS, 2), dtype=torch.int32, device=device)
+
+    def next_flags(self):
+        if self.flag_buf is None:
+            return None
+        if len(self.flags) >= self.MAX_FLAGS:
+            raise RuntimeError("more than %d relations in one captured step" % self.MAX_FLAGS)
+        return self.flag_buf[len(self.flags)]
+
+    def finalize_mask(self):
+        """After the capture: which guard words mean 'violated' (unsorted only where sortedness was assumed)."""
+        if self.mask_buf is not None and self.flags:
+            m = torch.tensor([[1 if a else 0, 1] for a, _ in self.flags], dtype=torch.int32)
+            self.mask_buf[:len(self.flags)].copy_(m)
 
     def violated(self, host_flags):
         """host_flags: list of int32[2] tensors on the host, same order as self.flags."""
@@ -79,9 +101,11 @@ class Relation:
         if self._rowptr is not None:
             return
         if self._is_sorted is None:
-            flags = F.raw_check_sorted(self.ids, self.n_targets)
             mode = _MODE
-            if mode is not None and mode.kind == "capture":
+            capture = mode is not None and mode.kind == "capture"
+            flags = F.raw_check_sorted(self.ids, self.n_targets, flags=mode.next_flags() if capture else None,
+                                       clamp=capture)
+            if capture:
                 if mode.cursor >= len(mode.hints):
                     raise RuntimeError("CUDA-graph capture met a relation that the warm-up pass did not record")
                 self._is_sorted = bool(mode.hints[mode.cursor])
@@ -180,6 +204,7 @@ class IndexPlan:
         return self._relations[col]
 
 
+_MAX_PLANS_PER_TENSOR = 4   # distinct (node partition, index partition) wrappers kept per index tensor
 _PLAN_CACHE = {}   # id(index values tensor) -> (weakref to it, {key: (IndexPlan, partitions...)})
 
 
@@ -204,6 +229,8 @@ def get_plan(index_ragged, node_ragged):
     if entry is None:
         for k in [k for k in per_tensor if k[1] != vals._version]:
             del per_tensor[k]                # an in-place update of the index tensor invalidates its plans
+        while len(per_tensor) >= _MAX_PLANS_PER_TENSOR:
+            del per_tensor[next(iter(per_tensor))]   # callers that rebuild their partitions per call: oldest out
         # keep the partitions alive next to the plan so id() keys cannot be recycled
         entry = (IndexPlan(vals, index_ragged.partition, node_part), node_part, index_ragged.partition)
         per_tensor[key] = entry

@@ -167,18 +167,47 @@ class RaggedTensor:
         return RaggedTensor(self.values.to(device), RowPartition(self.partition.row_splits.to(device),
                                                                  nvals=int(self.values.shape[0])))
 
-    def to_tensor(self, default_value=0):
-        """Pad to [B, max_len, ...] (casting.py:80)."""
-        lengths = self.row_lengths()
+    def _max_len(self):
         if self.partition.max_len is not None:
-            nmax = int(self.partition.max_len)
-        else:
-            nmax = int(lengths.max().item()) if lengths.numel() else 0
+            return int(self.partition.max_len)
+        lengths = self.row_lengths()
+        return int(lengths.max().item()) if lengths.numel() else 0     # one sync; pass max_len to avoid it
+
+    def to_tensor(self, default_value=0, shape=None):
+        """Pad to [B, max_len, ...] (casting.py:78-80): kgcnn_pad on the device.  Host-resident ragged tensors
+        (data containers built by from_numpy_list) are padded with tensor indexing; no kernel math is involved."""
+        nmax = self._max_len() if shape is None or shape[1] is None else int(shape[1])
+        default_value = 0 if default_value is None else default_value
+        if self.values.is_cuda:
+            from . import functional as F
+            return F.pad(self.values, self.row_splits, nmax, default_value)
         out = self.values.new_full((self.partition.nrows, nmax) + tuple(self.values.shape[1:]), default_value)
         rowids = self.partition.value_rowids()
         pos = torch.arange(self.values.shape[0], device=self.values.device) - self.row_splits[rowids]
-        out[rowids, pos] = self.values
+        keep = pos < nmax
+        out[rowids[keep], pos[keep]] = self.values[keep]
         return out
+
+    def to_tensor_and_mask(self, default_value=0, boolean_mask=False, shape=None):
+        """(padded, mask) of ChangeTensorType 'mask' (casting.py:80-84), both from ONE launch on the device."""
+        nmax = self._max_len() if shape is None or shape[1] is None else int(shape[1])
+        default_value = 0 if default_value is None else default_value
+        if self.values.is_cuda and not (self.values.requires_grad and torch.is_grad_enabled()):
+            from . import functional as F
+            return F.raw_pad(self.values, self.row_splits, nmax, default_value, "bool" if boolean_mask else "like")
+        padded = self.to_tensor(default_value, shape=shape)
+        ones = torch.ones_like(self.values, dtype=torch.bool if boolean_mask else self.values.dtype)
+        return padded, self.with_values(ones).to_tensor(shape=shape)
+
+    @classmethod
+    def from_padded(cls, padded, partition):
+        """Inverse of to_tensor for a known row partition (force.py:204-211): kgcnn_unpad on the device."""
+        if padded.is_cuda:
+            from . import functional as F
+            return cls(F.unpad(padded, partition.row_splits, partition.nvals), partition)
+        rowids = partition.value_rowids()
+        pos = torch.arange(partition.nvals, device=padded.device) - partition.row_splits[rowids]
+        return cls(padded[rowids, pos], partition)
 
     def __getitem__(self, i):
         a, b = int(self.row_splits[i]), int(self.row_splits[i + 1])

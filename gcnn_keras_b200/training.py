@@ -67,10 +67,17 @@ class FlatAdam:
         g = allreduce_flat(self.gflat)                           # data parallel by graph: the step's only collective
         lr, b1, b2, eps, clip = self.hyper
         sumsq = F.raw_gms(g.unsqueeze(1), g.unsqueeze(1), self.rel, None) if clip > 0 else None
+        # inside a captured step the plan-validation flags guard the update: a replayed batch that breaks the
+        # recorded sortedness / index-range assumptions leaves parameters, moments and step counter untouched
+        from .plan import current_mode
+        mode = current_mode()
+        guard = mode.flag_buf if (mode is not None and mode.kind == "capture") else None
         _lib.check(_lib.lib().kgcnn_adam_clipnorm(
             self.flat.data_ptr(), g.data_ptr(), self.m.data_ptr(), self.v.data_ptr(), self.var_of.data_ptr(),
             None if sumsq is None else sumsq.data_ptr(), self.total, lr, b1, b2, eps, clip,
-            self.step_count.data_ptr(), torch.cuda.current_stream().cuda_stream), "kgcnn_adam_clipnorm")
+            self.step_count.data_ptr(), None if guard is None else guard.data_ptr(),
+            None if guard is None else mode.mask_buf.data_ptr(), 0 if guard is None else guard.numel(),
+            torch.cuda.current_stream().cuda_stream), "kgcnn_adam_clipnorm")
 
 
 class ForceTrainStep:
@@ -88,6 +95,10 @@ class ForceTrainStep:
         if self.optimizer is None:
             self.params = [p for p in self.model.parameters() if p.requires_grad]
             self.optimizer = FlatAdam(self.params, lr=self.lr, eps=self.eps, clipnorm=self.clipnorm)
+            # data parallel by graph: every replica starts from rank 0's weights (layers build lazily, so this
+            # is the first point at which all variables exist); one broadcast of the flat buffer
+            from .distributed import broadcast_flat
+            broadcast_flat(self.optimizer.flat)
 
     def loss(self, inputs, e_target, f_target):
         out = self.model(inputs, training=True)
@@ -210,28 +221,45 @@ class CapturedForceTrainStep:
         torch.cuda.current_stream(device).wait_stream(side)
         torch.cuda.synchronize(device)
         clear_plan_cache()
-        self.mode = PlanMode("capture", hints=record.hints)
+        self.mode = PlanMode("capture", hints=record.hints, device=device)
         self.graph = torch.cuda.CUDAGraph()
         _lib.launch_count_reset()
         with plan_mode(self.mode):
             with torch.cuda.graph(self.graph):
+                self.mode.flag_buf.zero_()                   # guard words are OR-accumulated per replay
                 inputs, e_t, f_t = self.make_inputs(self.static.dev, self.max_nodes)
                 self.loss = train_step.step(inputs, e_t, f_t)
-                self.flags = torch.stack([f for _, f in self.mode.flags]) if self.mode.flags else None
+        self.mode.finalize_mask()
+        self.flags = self.mode.flag_buf[:len(self.mode.flags)] if self.mode.flags else None
+        self._flags_event, self._flags_pending = torch.cuda.Event(), False
         self.kernels_per_step = _lib.launch_count()      # our kernels recorded in the graph
         self.loss_host = torch.zeros((), dtype=torch.float32).pin_memory()
         self.flags_host = None if self.flags is None else torch.zeros_like(self.flags, device="cpu").pin_memory()
 
     def run(self, batch=None, load=True):
         """H2D (if load) -> replay -> async D2H of the loss (+ validation flags).  Returns the pinned loss."""
-        if batch is not None and not self.static.signature_matches(molecule_batch_to_arrays(batch)):
-            raise ValueError("batch signature differs from the captured one; capture a new CapturedForceTrainStep")
+        if batch is not None:
+            if not self.static.signature_matches(molecule_batch_to_arrays(batch)):
+                raise ValueError("batch signature differs from the captured one; capture a new "
+                                 "CapturedForceTrainStep")
+            if int(batch["node_len"].max()) > self.max_nodes:
+                raise ValueError("batch has a molecule of %d atoms, the captured padded outputs hold %d"
+                                 % (int(batch["node_len"].max()), self.max_nodes))
+        # the previous replay's validation flags, if they have landed: a violated plan assumption raises here
+        # (the device-side guard already kept that step from touching the weights)
+        if self._flags_pending and self._flags_event.query():
+            self._flags_pending = False
+            if not self.check():
+                raise RuntimeError("a replayed batch violated the sortedness / index-range assumptions of the "
+                                   "captured plan; the optimizer update of that step was skipped")
         if load:
             self.static.load(None if batch is None else molecule_batch_to_arrays(batch))
         self.graph.replay()
         self.loss_host.copy_(self.loss.detach(), non_blocking=True)
         if self.flags is not None:
             self.flags_host.copy_(self.flags, non_blocking=True)
+            self._flags_event.record()
+            self._flags_pending = True
         return self.loss_host
 
     def check(self):

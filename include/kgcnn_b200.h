@@ -80,15 +80,34 @@ int kgcnn_value_rowids(const int64_t* row_splits, int64_t B, int64_t n_values, i
 int kgcnn_cast_i64_i32(const int64_t* src, int64_t n, int32_t* dst, kgcnn_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * a20  ragged <-> padded (+ mask)     kgcnn/layers/casting.py:78-84 (RaggedTensor.to_tensor and the ones_like
+ *      mask of ChangeTensorType 'mask'), kgcnn/model/force.py:204-211 (boolean-mask gather back to ragged).
+ *      Elements are moved as 32-bit words: words_per_row = trailing elements per value row x elem_words
+ *      (float32 / int32: elem_words 1, int64: 2).  out[b, j, :] = values[row_splits[b] + j, :] for
+ *      j < len(b), else the fill element (fill_word0 [, fill_word1]).  mask (nullable) has the shape of out
+ *      (1.0f / integer 1 where a value exists, 0 elsewhere) or, with mask_is_bool, one byte per 1-word element.
+ *      Rows longer than max_len are truncated (to_tensor(shape=...) semantics).  kgcnn_unpad is the inverse /
+ *      adjoint: values[n, :] = padded[graph_of(n), n - row_splits[graph_of(n)], :].
+ * ------------------------------------------------------------------------------------------- */
+int kgcnn_pad(const void* values, const int64_t* row_splits, int64_t B, int64_t max_len, int64_t words_per_row,
+              uint32_t fill_word0, uint32_t fill_word1, int elem_words, void* out, void* mask /*nullable*/,
+              int mask_is_bool, kgcnn_stream_t stream);
+int kgcnn_unpad(const void* padded, const int64_t* row_splits, int64_t B, int64_t max_len, int64_t words_per_row,
+                int64_t n_values, void* values, kgcnn_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
  * plan: replaces tf.argsort(stable) + permutation gathers of PoolingLocalEdges
  *       kgcnn/layers/pooling.py:63-68 (and :156-159), once per batch instead of once per layer.
  *  kgcnn_check_sorted : flags[0] = 1 if key is NOT ascending, flags[1] = 1 if any key outside [0,N)
- *                       (flags must be zeroed by the caller; OR-accumulated)
+ *                       (flags must be zeroed by the caller; OR-accumulated).  clamp_in_place != 0 also
+ *                       rewrites out-of-range keys to the nearest valid id, so that an already enqueued
+ *                       (CUDA-graph) step can never read out of bounds; the flags still report it and
+ *                       kgcnn_adam_clipnorm's guard skips the update.
  *  kgcnn_plan_build   : rowptr[N+1] = CSR row pointer of key (histogram + scan);
  *                       perm[E] = stable ascending argsort of key (identity when assume_sorted!=0).
  *                       key is read with stride `key_stride` (column of an [E,K] int32 tensor).
  * ------------------------------------------------------------------------------------------- */
-int kgcnn_check_sorted(const int32_t* key, int key_stride, int64_t E, int64_t N, int32_t* flags,
+int kgcnn_check_sorted(int32_t* key, int key_stride, int64_t E, int64_t N, int32_t* flags, int clamp_in_place,
                        kgcnn_stream_t stream);
 size_t kgcnn_plan_workspace_bytes(int64_t E, int64_t N);
 int kgcnn_plan_build(const int32_t* key, int key_stride, int64_t E, int64_t N, int assume_sorted,
@@ -158,15 +177,6 @@ int kgcnn_bias_act_pair(const float* pre, const float* bias, const float* gy, co
 size_t kgcnn_colsum_workspace_bytes(int64_t M, int U);
 int kgcnn_colsum(const float* a, int64_t M, int U, float* out, void* workspace, size_t workspace_bytes,
                  kgcnn_stream_t stream);
-
-/* ---------------------------------------------------------------------------------------------
- * a19  weight gradient of Dense on flat ragged values (backward of kgcnn/layers/modules.py:85):
- *     dW[K1,K2] = sum_m X[m,K1]^T G[m,K2],  db[K2] = sum_m G[m,K2] (db nullable)
- *     M (edges / atoms) is split over ~2 CTAs per SM; partial tiles are summed in fixed order.
- * ------------------------------------------------------------------------------------------- */
-size_t kgcnn_gemm_tn_workspace_bytes(int64_t M, int K1, int K2);
-int kgcnn_gemm_tn(const float* X, const float* G, int64_t M, int K1, int K2, float* dW, float* db,
-                  void* workspace, size_t workspace_bytes, kgcnn_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
  * a19  Dense contractions on the tcgen05 tensor cores (3xTF32 split, fp32 TMEM accumulators):
@@ -286,10 +296,14 @@ int kgcnn_painn_msg_edges(const float* gs, const float* gv, const float* phi, co
  * optimizer of the force_*.py drivers (force_schnet.py:196-203): Keras Adam with per-variable clipnorm on one
  * flat parameter buffer.  sumsq[var] = sum of squared gradients of variable var (from the segment kernel with
  * rowptr = variable offsets), var_of[i] = variable of element i, *step = device-resident step counter.
+ * guard (nullable): n_guard device words; if (guard[i] & guard_mask[i]) != 0 for any i the whole update is
+ * skipped (parameters, moments and the step counter stay untouched) -- the plan-validation flags of a replayed
+ * CUDA graph, so that a batch that breaks the recorded assumptions cannot corrupt the weights.
  * ------------------------------------------------------------------------------------------- */
 int kgcnn_adam_clipnorm(float* params, const float* grads, float* m, float* v, const int32_t* var_of,
                         const float* sumsq, int64_t n, float lr, float beta1, float beta2, float eps,
-                        float clipnorm, int32_t* step, kgcnn_stream_t stream);
+                        float clipnorm, int32_t* step, const int32_t* guard /*nullable*/,
+                        const int32_t* guard_mask /*nullable*/, int n_guard, kgcnn_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Batch graph construction (the step in front of the path).  Two-pass: count -> offsets ->

@@ -228,3 +228,32 @@ def dense(x, kernel, bias=None, activation=None):
         out = out + bias
     out = ops.activation(activation)(out)
     return x.with_values(out) if isinstance(x, R) else out
+
+
+def ragged_to_tensor(r, default_value=0, max_len=None):
+    """tf.RaggedTensor.to_tensor(shape, default_value) as ChangeTensorType uses it (kgcnn/layers/casting.py:78-80):
+    [B, max_len, ...], row b holds its values left-aligned, the rest is `default_value`; rows longer than a given
+    max_len are truncated.  NumPy-style loop over rows (integer/copy work, bit-exact comparand)."""
+    lengths = r.row_lengths()
+    nmax = int(lengths.max()) if max_len is None and len(lengths) else int(max_len or 0)
+    out = r.values.new_full((r.nrows(), nmax) + tuple(r.values.shape[1:]), default_value)
+    for b in range(r.nrows()):
+        n = min(int(lengths[b]), nmax)
+        out[b, :n] = r[b][:n]
+    return out
+
+
+def change_tensor_type_mask(r, default_value=0, boolean_mask=False, max_len=None):
+    """ChangeTensorType(ragged -> 'mask') (kgcnn/layers/casting.py:80-84): (padded, mask) with
+    mask = ones_like(flat_values) (or bool ones) padded with zeros."""
+    padded = ragged_to_tensor(r, default_value, max_len)
+    ones = torch.ones_like(r.values, dtype=torch.bool if boolean_mask else r.values.dtype)
+    return padded, ragged_to_tensor(r.with_values(ones), 0, max_len)
+
+
+def padded_to_ragged(x_pad, x_mask):
+    """EnergyForceModel._cast_coordinates_pad_to_ragged (kgcnn/model/force.py:204-211): boolean-mask gather of the
+    padded tensor by mask[:, :, 0], row lengths = number of live slots."""
+    from .ragged import R
+    live = x_mask[:, :, 0].to(torch.bool)
+    return R.from_row_lengths(x_pad[live], live.sum(dim=-1).numpy())

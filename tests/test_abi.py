@@ -63,3 +63,26 @@ def test_segment_name_dispatch_errors():
     assert F.op_code("mean") == 1 and F.op_code("segment_max") == 2 and F.op_code("reduce_min") == 3
     with pytest.raises(TypeError):
         F.op_code("softmax")
+
+
+def test_registered_layer_names_equal_the_reference_names():
+    """Every layer registered here carries the Keras registration name the reference gives the class of the same
+    name (tests/golden/registered_names.json, extracted from the reference's decorators by make_golden_names.py),
+    so a serialized reference model config resolves to the right class."""
+    import importlib
+    import json
+    import os
+    import pkgutil
+
+    import gcnn_keras_b200
+    from gcnn_keras_b200.layers.base import _REGISTRY, get_registered
+    for m in pkgutil.walk_packages(gcnn_keras_b200.__path__, "gcnn_keras_b200."):
+        if m.name.endswith((".build", ".libkgcnn_b200")):
+            continue
+        importlib.import_module(m.name)
+    with open(os.path.join(os.path.dirname(__file__), "golden", "registered_names.json")) as fh:
+        ref = json.load(fh)
+    assert len(_REGISTRY) >= 40
+    for key, cls in _REGISTRY.items():
+        assert ref.get(cls.__name__) == key, (key, cls.__name__, ref.get(cls.__name__))
+    assert get_registered("kgcnn>BesselBasisLayer").__name__ == "BesselBasisLayer"   # kgcnn/layers/geom.py:716

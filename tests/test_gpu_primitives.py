@@ -392,15 +392,15 @@ def test_many_long_rows_warp_per_row_mapping(feat):
 
 @pytest.mark.parametrize("M,K1,K2", [(18432, 128, 128), (5000, 25, 128), (700, 3, 1), (4097, 35, 50), (100, 64, 64),
                                        (40000, 384, 20)])
-def test_gemm_tn_weight_gradient(M, K1, K2):
+def test_weight_gradient_tn_and_colsum(M, K1, K2):
+    """(dW, db) = (x^T g, colsum g): tcgen05 TN contraction + deterministic column sum."""
     from gcnn_keras_b200 import functional as F
     rng = np.random.default_rng(15)
     x = rng.standard_normal((M, K1)).astype(np.float32)
     g = rng.standard_normal((M, K2)).astype(np.float32)
-    dw, db = F.raw_gemm_tn(torch.tensor(x).cuda(), torch.tensor(g).cuda(), want_colsum=True)
+    dw = F.raw_dense_tc(2, torch.tensor(x).cuda(), torch.tensor(g).cuda())
     assert rel_err(dw.cpu().numpy(), x.astype(np.float64).T @ g.astype(np.float64)) < RTOL
-    assert rel_err(db.cpu().numpy(), g.astype(np.float64).sum(0)) < RTOL
-    dw2 = F.raw_gemm_tn(torch.tensor(x).cuda(), torch.tensor(g).cuda())
+    dw2 = F.raw_dense_tc(2, torch.tensor(x).cuda(), torch.tensor(g).cuda())
     assert torch.equal(dw, dw2)                      # deterministic split-M reduction
     cs = F.raw_colsum(torch.tensor(g).cuda())
     assert rel_err(cs.cpu().numpy(), g.astype(np.float64).sum(0)) < RTOL

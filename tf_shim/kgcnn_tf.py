@@ -1,4 +1,4 @@
-"""TensorFlow-side binding of the shim (source only; needs TensorFlow + tf_shim/build.sh).
+"""UNCOMPILED / never run (no TensorFlow on either machine).  TensorFlow-side binding of the shim (source only; needs TensorFlow + tf_shim/build.sh).
 
 Registers the gradients so that the ops are closed under differentiation exactly like the PyTorch binding
 (gcnn_keras_b200/functional.py): gather <-> segment-sum, fused op <-> itself on the transposed relation + the

@@ -1,3 +1,4 @@
+// UNCOMPILED: this file has never met a compiler (no TensorFlow on either machine); it earns no coverage claim.
 // TensorFlow custom-op shim over the C-ABI of libkgcnn_b200.so (include/kgcnn_b200.h).
 // NOT built in this repository's environment: TensorFlow is not installable on the build or the GPU machine
 // (SURVEY.md F2).  Build on a machine with TensorFlow >= 2.9 (reference pin: setup.py:22) via tf_shim/build.sh.
