@@ -4,20 +4,29 @@
 //     TN : dW[K,U] = X[M,K]^T G[M,U]                weight gradient (split over M, fixed-order reduce)
 // M = edges / atoms of the batch (1e4 .. 1e6), K and U = layer widths (1 .. 640).
 //
-// Precision: the parity bar is 1e-5 of an fp64 oracle, single-pass TF32 (10-bit mantissa) is ~1e-3.  Every operand
-// tile is therefore split while it is staged into shared memory, x ~ hi + lo with hi = nearest TF32 value and
-// lo = nearest TF32 value of x - hi (|x - hi - lo| <= 2^-23 |x|), and three MMAs accumulate lo*hi + hi*lo + hi*hi
-// (3xTF32; lo*lo is 2^-22 relative, below the fp32 rounding of the result) in an fp32 TMEM accumulator that is
-// drained to fp32 registers every kFlush reduction elements.
+// Precision: the parity bar is 1e-5 of an fp64 oracle through six interaction blocks and two backward sweeps, so the
+// products must be fp32-grade.  Every operand element is split while it is staged into THREE bf16 pieces,
+// x = b1 + b2 + b3 (each the round-to-nearest bf16 of the running remainder; the remainders are exact in fp32, so
+// the three pieces carry 24 significant bits: the split is lossless up to 2^-25 |x|), and six kind::f16 MMAs per
+// 16 reduction elements accumulate every product of weight >= 2^-16,
+//     b3*b1' + b1*b3' + b2*b2'   (2^-16)      b2*b1' + b1*b2'   (2^-8)      b1*b1'   (1),
+// small terms first, in an fp32 TMEM accumulator (bf16 x bf16 products are exact in fp32).  The dropped terms are
+// 2^-24 relative.  (Round 1 used a 2-piece TF32 split: 22 bits, 3 MMAs per 8 elements = the same tensor time, but a
+// representation error of 2^-22 per element that showed up as 1.1-1.6e-5 on PaiNN weight gradients at depth 6,
+// profiles/parity_r2.json; the bf16 planes are also 25 % smaller: 6 instead of 8 bytes per element.)  The accumulator
+// is drained into fp32 registers after every chunk of 32 reduction elements: the tensor core's accumulate truncates
+// (measured ~2^-24 of the accumulator per MMA, one-sided), and with the small terms first only the two b1*b1' MMAs of
+// a chunk add at full magnitude (a 64-element flush group measured 4e-7 per Dense, 10 of its 24 MMAs adding small
+// terms into a full-size accumulator).
 //
-// Data path: these GEMMs are skinny (K, U <= 640) and sit where tensor time ~ memory time, and the split needs a
-// register pass anyway, so tiles go global -> registers -> (hi, lo) -> shared memory in the canonical no-swizzle
-// K-major UMMA layout (8 x 16 B core matrices); operands whose reduction index is the ROW of the global matrix (W in
-// NN, X and G in TN) are transposed on the way into shared memory, so every descriptor is K-major; no TMA descriptor
-// is needed.  The loop over 32-element reduction chunks is a 3-stage software pipeline: while one elected thread's
-// tcgen05.mma (kind::tf32, cta_group::1, M = 128) of chunk c run (tcgen05.commit -> one mbarrier per stage), the
-// CTA splits and stores chunk c+1, has the global loads of chunk c+2 in flight and drains the previous flush group
-// from the second TMEM accumulator with tcgen05.ld.
+// Data path: tiles go global -> registers -> split -> shared memory as 16-byte units of 8 bf16 in the canonical
+// NO-SWIZZLE UMMA layouts.  An operand whose reduction index runs along the global rows' feature axis (X in NN, G and
+// W in NT) is K-major: unit = 8 reduction elements of one row.  An operand whose reduction index is the global ROW
+// (W in NN, X and G in TN) is MN-major: unit = 8 features of one reduction row -- the instruction descriptor's
+// a_major / b_major bits tell the tensor core, so nothing is transposed on the way in and every shared-memory store
+// is a conflict-free 128-bit store.  kStages x 32 reduction elements are resident, i.e. for K <= 128 every global
+// load of a tile is issued up front; one warp issues the MMAs (tcgen05.commit -> one mbarrier per stage), 16 warps
+// stage and drain.
 #include <algorithm>
 
 #include "activation.cuh"
@@ -26,15 +35,22 @@
 namespace kgcnn {
 namespace tc {
 
-constexpr int kThreads = 512;   // 16 warps stage operands (4 per scheduler: the staging code is issue-latency bound);
+constexpr int kThreads = 512;   // 16 staging warps: one 8-element unit of A and one of B per thread and chunk;
                                 // warp w reads TMEM lanes 32*(w%4)..+31, columns 32*(w/4)..+31 in the drain / epilogue
-constexpr int kCtaThreads = kThreads + 32;   // + warp 8: waits for full stages and issues the MMAs, nothing else
+constexpr int kCtaThreads = kThreads + 32;   // + the MMA-issue warp
 constexpr int kBM = 128;        // MMA M
-constexpr int kKC = 32;         // reduction elements staged per chunk (4 MMA k-steps of 8)
-constexpr int kLd = 2;          // float4 per thread, operand and register set (= 128*8/512 = 32*32/512)
-constexpr int kStages = 3;      // shared-memory stages of (A hi/lo, B hi/lo) planes: 3 x 66 KB
+constexpr int kKC = 32;         // reduction elements staged per chunk (2 MMA k-steps of 16)
+constexpr int kStages = 4;      // shared-memory stages of (A b1,b2,b3, B b1,b2,b3) planes: 4 x 48.75 KB
 constexpr int kMaxN = 128;      // MMA N per CTA (TMEM columns)
-constexpr int kFlush = 64;      // reduction length accumulated inside the tensor core before an fp32 (RN) flush
+constexpr int kFlush = kKC;     // reduction length accumulated inside the tensor core before an fp32 (RN) flush
+constexpr int kTmemCols = 512;  // four accumulators of kMaxN columns (short reductions: one per chunk, drained at the end)
+// K-major plane: 16-byte unit (k8, mn) at slot k8 * kPitchK + mn.  130 = 2 mod 8: the 8 lanes of a quarter warp
+// (4 k8 columns x 2 rows) land in 8 different 16-byte bank groups.
+constexpr int kPitchK = kBM + 2;
+// MN-major plane: unit (mn8, k) at slot mn8 * kKC + k: 8 consecutive k are 128 contiguous bytes (one core matrix).
+constexpr int kPlaneUnits = (kKC / 8) * kPitchK;                       // 520 units >= 16 * kKC = 512
+static_assert(kPlaneUnits >= (kMaxN / 8) * kKC, "plane holds either layout");
+constexpr int kStageUnits = 6 * kPlaneUnits;
 
 enum { kNN = 0, kNT = 1, kTN = 2 };
 
@@ -42,26 +58,26 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
 
-// shared-memory matrix descriptor, SWIZZLE_NONE, version 1 (sm_100): start>>4 [0,14), LBO>>4 [16,30), SBO>>4 [32,46)
-__device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo16, uint32_t sbo16) {
-  return static_cast<uint64_t>((saddr >> 4) & 0x3FFF) | (static_cast<uint64_t>(lbo16 & 0x3FFF) << 16) |
-         (static_cast<uint64_t>(sbo16 & 0x3FFF) << 32) | (1ull << 46);
+// shared-memory matrix descriptor, SWIZZLE_NONE, version 1 (sm_100): start>>4 [0,14), LBO>>4 [16,30), SBO>>4 [32,46).
+// For both majors LBO is the byte offset between core matrices along K, SBO along M/N.
+__device__ __forceinline__ uint64_t desc_hi_bits(uint32_t lbo16, uint32_t sbo16) {
+  return (static_cast<uint64_t>(lbo16 & 0x3FFF) << 16) | (static_cast<uint64_t>(sbo16 & 0x3FFF) << 32) | (1ull << 46);
 }
 
-// instruction descriptor kind::tf32: D=F32 [4,6), A=TF32 [7,10), B=TF32 [10,13), a_major 15, b_major 16,
+// instruction descriptor kind::f16: D=F32 [4,6), A=BF16 [7,10), B=BF16 [10,13), a_major 15, b_major 16 (1 = MN-major),
 // N>>3 [17,23), M>>4 [24,29)
 __device__ __forceinline__ uint32_t make_idesc(int a_mn_major, int b_mn_major, int n) {
-  return (1u << 4) | (2u << 7) | (2u << 10) | (static_cast<uint32_t>(a_mn_major) << 15) |
+  return (1u << 4) | (1u << 7) | (1u << 10) | (static_cast<uint32_t>(a_mn_major) << 15) |
          (static_cast<uint32_t>(b_mn_major) << 16) | (static_cast<uint32_t>(n >> 3) << 17) |
          (static_cast<uint32_t>(kBM >> 4) << 24);
 }
 
-__device__ __forceinline__ void mma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+__device__ __forceinline__ void mma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
   asm volatile(
       "{\n\t"
       ".reg .pred p;\n\t"
       "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
       "}\n" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
       : "memory");
 }
@@ -83,99 +99,83 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   }
 }
 
-// K-major operand plane: element (mn, k) lives in float4 slot (k/4)*NRP + mn, component k%4, NRP = NR + 1
-// (odd pitch).  Descriptor: LBO = NRP (next 16 B k-chunk), SBO = 8 (next 8 mn), +2*NRP per MMA k-step of 8.
-__device__ __forceinline__ float4 load4(const float* __restrict__ g, int64_t row, int64_t row_end, int f, int f_end,
-                                        int ld, bool vec_ok) {
-  float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-  if (row < row_end) {
+// eight consecutive floats g[row, f .. f+7] (zero beyond row_end / f_end)
+struct F8 { float4 a, b; };
+__device__ __forceinline__ F8 load8(const float* __restrict__ g, int64_t row, int64_t row_end, int f, int f_end, int ld,
+                                    bool vec_ok, bool fast) {
+  F8 v;
+  if (fast) {
+    const float4* p = reinterpret_cast<const float4*>(g + row * ld + f);
+    v.a = __ldg(p);
+    v.b = __ldg(p + 1);
+    return v;
+  }
+  v.a = make_float4(0.f, 0.f, 0.f, 0.f);
+  v.b = v.a;
+  if (row < row_end && f < f_end) {
     const float* p = g + row * ld + f;
-    if (vec_ok && f + 3 < f_end) v = __ldg(reinterpret_cast<const float4*>(p));
-    else {
-      if (f + 0 < f_end) v.x = __ldg(p + 0);
-      if (f + 1 < f_end) v.y = __ldg(p + 1);
-      if (f + 2 < f_end) v.z = __ldg(p + 2);
-      if (f + 3 < f_end) v.w = __ldg(p + 3);
+    if (vec_ok && f + 7 < f_end) {
+      v.a = __ldg(reinterpret_cast<const float4*>(p));
+      v.b = __ldg(reinterpret_cast<const float4*>(p) + 1);
+    } else {
+      float t[8];
+#pragma unroll
+      for (int q = 0; q < 8; ++q) t[q] = (f + q < f_end) ? __ldg(p + q) : 0.f;
+      v.a = make_float4(t[0], t[1], t[2], t[3]);
+      v.b = make_float4(t[4], t[5], t[6], t[7]);
     }
   }
   return v;
 }
-// nearest TF32 value (round half away in magnitude): |x - hi| <= 2^-11 |x|, and x - hi is exact in fp32.  lo is
-// rounded the same way (the tensor core would truncate it, a one-sided 2^-22 |x| bias that adds up coherently over
-// a reduction); after RN the residual x - hi - lo is <= 2^-23 |x| and unbiased, i.e. fp32-like.
-__device__ __forceinline__ float tf32_hi(float x) {
-  return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xffffe000u);
+
+// (x0, x1) -> three packed bf16x2 words (x0 in the low half): b1 = rn(x), b2 = rn(x - b1), b3 = rn(x - b1 - b2);
+// both remainders are exact in fp32.
+__device__ __forceinline__ void split3(float x0, float x1, uint32_t& p1, uint32_t& p2, uint32_t& p3) {
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(p1) : "f"(x1), "f"(x0));
+  const float r0 = x0 - __uint_as_float(p1 << 16), r1 = x1 - __uint_as_float(p1 & 0xffff0000u);
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(p2) : "f"(r1), "f"(r0));
+  const float s0 = r0 - __uint_as_float(p2 << 16), s1 = r1 - __uint_as_float(p2 & 0xffff0000u);
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(p3) : "f"(s1), "f"(s0));
+}
+__device__ __forceinline__ void store_unit(const F8& v, uint4* __restrict__ planes, int slot) {
+  uint4 u1, u2, u3;
+  split3(v.a.x, v.a.y, u1.x, u2.x, u3.x);
+  split3(v.a.z, v.a.w, u1.y, u2.y, u3.y);
+  split3(v.b.x, v.b.y, u1.z, u2.z, u3.z);
+  split3(v.b.z, v.b.w, u1.w, u2.w, u3.w);
+  planes[slot] = u1;
+  planes[kPlaneUnits + slot] = u2;
+  planes[2 * kPlaneUnits + slot] = u3;
 }
 
-// mn = row of the global matrix, k = feature: rows [row0, row0+128), features [f0, f0+kKC).  Loads are issued as
-// one batch of kLd independent float4 per thread (registers), the split + shared-memory stores follow later, so
-// the next chunk's global latency overlaps the MMAs of the current one.
-// `fast` (CTA-uniform): the whole tile is in bounds and 16-byte aligned -> plain 128-bit loads, no predicates.
-__device__ __forceinline__ void load_direct(float4 (&v)[kLd], const float* __restrict__ g, int64_t row0,
-                                            int64_t row_end, int f0, int f_end, int ld, bool vec_ok, bool fast) {
-  constexpr int NCH = kKC / 4;
-#pragma unroll
-  for (int i = 0; i < kLd; ++i) {
-    const int it = threadIdx.x + i * kThreads;
-    const int c = it % NCH, r = it / NCH;                 // consecutive threads: consecutive 16 B of one row
-    if (fast) v[i] = __ldg(reinterpret_cast<const float4*>(g + (row0 + r) * ld + f0 + 4 * c));
-    else v[i] = load4(g, row0 + r, row_end, f0 + 4 * c, f_end, ld, vec_ok);
-  }
+// K-major tile: mn = global row (128 of them from row0), k = feature (kKC of them from f0).
+// thread -> (k8 = t % 4, mn = t / 4): a warp reads 8 rows x 128 contiguous bytes.
+__device__ __forceinline__ F8 load_kmajor(const float* __restrict__ g, int64_t row0, int64_t row_end, int f0, int f_end,
+                                          int ld, bool vec_ok, bool fast) {
+  const int k8 = threadIdx.x & 3, mn = threadIdx.x >> 2;
+  return load8(g, row0 + mn, row_end, f0 + 8 * k8, f_end, ld, vec_ok, fast);
 }
-__device__ __forceinline__ void store_direct(const float4 (&v)[kLd], float4* __restrict__ hi, float4* __restrict__ lo) {
-  constexpr int NRP = kBM + 1, NCH = kKC / 4;
-#pragma unroll
-  for (int i = 0; i < kLd; ++i) {
-    const int it = threadIdx.x + i * kThreads;
-    const int c = it % NCH, r = it / NCH;
-    const float4 h = make_float4(tf32_hi(v[i].x), tf32_hi(v[i].y), tf32_hi(v[i].z), tf32_hi(v[i].w));
-    hi[c * NRP + r] = h;
-    lo[c * NRP + r] = make_float4(tf32_hi(v[i].x - h.x), tf32_hi(v[i].y - h.y), tf32_hi(v[i].z - h.z),
-                                  tf32_hi(v[i].w - h.w));
-  }
+__device__ __forceinline__ void store_kmajor(const F8& v, uint4* __restrict__ planes) {
+  const int k8 = threadIdx.x & 3, mn = threadIdx.x >> 2;
+  store_unit(v, planes, k8 * kPitchK + mn);
 }
-
-// mn = feature, k = row of the global matrix (transposed on the way in): rows [row0, row0+kKC), features
-// [f0, f0+4*nchunks).  Thread -> (row k, 4-feature group j): within a warp 16 rows x 2 adjacent groups, so a load
-// instruction reads one full 32-byte sector per row and the scalar stores hit 32 different banks; register i is
-// the 16-row block, the warp selects the pair of feature groups.
-__device__ __forceinline__ void transposed_coords(int i, int& k, int& j) {
+// MN-major tile: k = global row (kKC of them from row0), mn = feature (128 of them from f0).
+// thread -> (k = 8 * (warp % 4) + lane % 8, mn8 = 4 * (warp / 4) + lane / 8): a quarter warp stores one core matrix.
+__device__ __forceinline__ void mn_coords(int& k, int& mn8) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  k = 16 * i + (lane & 15);
-  j = 2 * warp + (lane >> 4);
+  k = 8 * (warp & 3) + (lane & 7);
+  mn8 = 4 * (warp >> 2) + (lane >> 3);
 }
-static_assert(kLd * 16 == kKC && 2 * (kThreads / 32) == kBM / 4, "transposed staging map covers a 32 x 128 chunk");
-__device__ __forceinline__ void load_transposed(float4 (&v)[kLd], const float* __restrict__ g, int64_t row0,
-                                                int64_t row_end, int f0, int f_end, int ld, int nchunks, bool vec_ok,
-                                                bool fast) {
-#pragma unroll
-  for (int i = 0; i < kLd; ++i) {
-    int k, j;
-    transposed_coords(i, k, j);
-    if (fast) v[i] = __ldg(reinterpret_cast<const float4*>(g + (row0 + k) * ld + f0 + 4 * j));
-    else v[i] = (j < nchunks) ? load4(g, row0 + k, row_end, f0 + 4 * j, f_end, ld, vec_ok)
-                              : make_float4(0.f, 0.f, 0.f, 0.f);
-  }
+__device__ __forceinline__ F8 load_mnmajor(const float* __restrict__ g, int64_t row0, int64_t row_end, int f0, int f_end,
+                                           int ld, bool vec_ok, bool fast) {
+  int k, mn8;
+  mn_coords(k, mn8);
+  return load8(g, row0 + k, row_end, f0 + 8 * mn8, f_end, ld, vec_ok, fast);
 }
-__device__ __forceinline__ void store_transposed(const float4 (&v)[kLd], int nchunks, float4* __restrict__ hi,
-                                                 float4* __restrict__ lo) {
-  constexpr int NRP = kBM + 1;
-  float* hs = reinterpret_cast<float*>(hi);
-  float* ls = reinterpret_cast<float*>(lo);
-#pragma unroll
-  for (int i = 0; i < kLd; ++i) {
-    int k, j;
-    transposed_coords(i, k, j);
-    if (j >= nchunks) continue;
-    const float vv[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
-    const int base = ((k >> 2) * NRP + 4 * j) * 4 + (k & 3);
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      const float h = tf32_hi(vv[q]);
-      hs[base + 4 * q] = h;
-      ls[base + 4 * q] = tf32_hi(vv[q] - h);
-    }
-  }
+__device__ __forceinline__ void store_mnmajor(const F8& v, uint4* __restrict__ planes) {
+  int k, mn8;
+  mn_coords(k, mn8);
+  store_unit(v, planes, mn8 * kKC + k);
 }
 
 // One CTA = one 128-row output tile (NN / NT) or one (128-feature tile, split of the rows) (TN).
@@ -191,8 +191,8 @@ dense_tc_body(const float* __restrict__ A, const float* __restrict__ B, int64_t 
   __shared__ __align__(8) uint64_t mbar[kStages];
   __shared__ __align__(8) uint64_t full[kStages];
   __shared__ uint32_t tmem_base_s;
-  constexpr int PLANE = (kKC / 4) * (kBM + 1);     // float4 slots per plane: 8 k-chunks x (128 + 1) mn
-  float4* planes = reinterpret_cast<float4*>(smem_raw);          // [stage][a_hi, a_lo, b_hi, b_lo][PLANE]
+  __shared__ float csum_s[kThreads / 32][4][8];
+  uint4* planes = reinterpret_cast<uint4*>(smem_raw);            // [stage][a1, a2, a3, b1, b2, b3][kPlaneUnits]
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   // output-tile coordinates
@@ -208,9 +208,9 @@ dense_tc_body(const float* __restrict__ A, const float* __restrict__ B, int64_t 
   const int64_t row_end = (OP == kTN) ? min(M, row_beg + rows_per_split) : 0;
   const int64_t red_len = (OP == kNN) ? K : (OP == kNT ? U : (row_end > row_beg ? row_end - row_beg : 0));
 
-  if (warp == kThreads / 32) {                                   // two accumulators of kMaxN columns each
+  if (warp == kThreads / 32) {                                   // four accumulators of kMaxN columns each
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)),
-                 "r"(static_cast<uint32_t>(2 * kMaxN))
+                 "r"(static_cast<uint32_t>(kTmemCols))
                  : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
@@ -223,105 +223,137 @@ dense_tc_body(const float* __restrict__ A, const float* __restrict__ B, int64_t 
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
+
+  // which layout each operand takes (see the header comment)
+  constexpr bool kAMn = (OP == kTN);                 // A: X^T in TN
+  constexpr bool kBMn = (OP == kNN) || (OP == kTN);  // B: W in NN, G in TN
+  const uint32_t idesc = make_idesc(kAMn ? 1 : 0, kBMn ? 1 : 0, nt);
+
+  // interior tiles (every index in range, 16-byte aligned rows) take the unpredicated load path
+  const bool in_a = vec_a && ((OP == kTN) ? (a0 + kBM <= K) : (m0 + kBM <= M));
+  const bool in_b = vec_b && ((OP == kNT) ? (n0 + kMaxN <= K) : (n0 + kMaxN <= U)) && nt == kMaxN;
+  auto load_chunk = [&](int64_t k0, F8& va, F8& vb) {
+    const bool in_k = k0 + kKC <= red_len;
+    if (OP == kNN) {
+      va = load_kmajor(A, m0, M, static_cast<int>(k0), K, K, vec_a, in_a && in_k);             // X rows, K feats
+      vb = load_mnmajor(B, k0, K, n0, U, U, vec_b, in_b && in_k);                              // W rows = reduction
+    } else if (OP == kNT) {
+      va = load_kmajor(A, m0, M, static_cast<int>(k0), U, U, vec_a, in_a && in_k);             // G rows, U feats
+      vb = load_kmajor(B, n0, K, static_cast<int>(k0), U, U, vec_b, in_b && in_k);             // W rows n, U feats
+    } else {
+      va = load_mnmajor(A, row_beg + k0, row_end, a0, K, K, vec_a, in_a && in_k);              // X rows = reduction
+      vb = load_mnmajor(B, row_beg + k0, row_end, n0, U, U, vec_b, in_b && in_k);              // G rows = reduction
+    }
+  };
+  auto load_chunk_a = [&](int64_t k0, F8& va) {
+    const bool in_k = k0 + kKC <= red_len;
+    if (OP == kTN) va = load_mnmajor(A, row_beg + k0, row_end, a0, K, K, vec_a, in_a && in_k);
+    else va = load_kmajor(A, m0, M, static_cast<int>(k0), (OP == kNN) ? K : U, (OP == kNN) ? K : U, vec_a, in_a && in_k);
+  };
+  auto load_chunk_b = [&](int64_t k0, F8& vb) {
+    const bool in_k = k0 + kKC <= red_len;
+    if (OP == kNN) vb = load_mnmajor(B, k0, K, n0, U, U, vec_b, in_b && in_k);
+    else if (OP == kNT) vb = load_kmajor(B, n0, K, static_cast<int>(k0), U, U, vec_b, in_b && in_k);
+    else vb = load_mnmajor(B, row_beg + k0, row_end, n0, U, U, vec_b, in_b && in_k);
+  };
+  const int nchunk = static_cast<int>((red_len + kKC - 1) / kKC);
+  // Short reductions (nchunk <= kStages, i.e. K <= 128: every Dense of SchNet / PaiNN) issue the loads of their whole
+  // A tile and of the first two B chunks up front (B chunks 2, 3 follow as soon as a register set is free: B is the
+  // L2-resident operand) and drain their per-chunk accumulators once at the end, so no fp32 accumulator registers
+  // are live while the loads are in flight; long reductions run two register sets ahead of the stores.
+  static_assert(kStages == 4 && kStages * kMaxN == kTmemCols, "four named register sets / accumulators below");
+  const bool short_k = nchunk <= kStages;                // CTA-uniform
+  F8 va0, vb0, va1, vb1, va2, va3;
+  if (warp < kThreads / 32) {
+    if (nchunk > 0) load_chunk(0, va0, vb0);
+    if (nchunk > 1) load_chunk(kKC, va1, vb1);
+    if (short_k) {
+      if (nchunk > 2) load_chunk_a(2 * kKC, va2);
+      if (nchunk > 3) load_chunk_a(3 * kKC, va3);
+    }
+  }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem_d = tmem_base_s;
 
-  // every operand is K-major with 128 (+1) mn slots per k-chunk: LBO = 129, SBO = 8 (units of 16 B)
-  constexpr int NRP = kBM + 1;
-  static_assert(kMaxN == kBM, "A and B planes share one pitch");
-  constexpr uint32_t kstep = 2 * NRP;                          // descriptor advance per MMA k-step (8 elements)
-  const uint32_t idesc = make_idesc(0, 0, nt);
-
-  // two register sets: the global loads of chunk c+2 are issued as soon as chunk c has been stored, so every load
-  // has two full pipeline iterations to land (the kernel runs one CTA per SM; registers are not the limit)
-  float4 va0[kLd], vb0[kLd], va1[kLd], vb1[kLd];
-  // interior tiles (every mn index in range, 16-byte aligned rows) take the unpredicated load path
-  const bool in_a = vec_a && ((OP == kTN) ? (a0 + kBM <= K) : (m0 + kBM <= M));
-  const bool in_b = vec_b && ((OP == kNT) ? (n0 + kMaxN <= K) : (n0 + kMaxN <= U)) && nt == kMaxN;
-  auto load_chunk = [&](int64_t k0, float4 (&va)[kLd], float4 (&vb)[kLd]) {
-    const bool in_k = k0 + kKC <= red_len;
-    if (OP == kNN) {
-      load_direct(va, A, m0, M, static_cast<int>(k0), K, K, vec_a, in_a && in_k);          // X rows, K feats
-      load_transposed(vb, B, k0, K, n0, U, U, nt / 4, vec_b, in_b && in_k);                // W rows k -> K dim
-    } else if (OP == kNT) {
-      load_direct(va, A, m0, M, static_cast<int>(k0), U, U, vec_a, in_a && in_k);          // G rows, U feats
-      load_direct(vb, B, n0, K, static_cast<int>(k0), U, U, vec_b, in_b && in_k);          // W rows n, U feats
-    } else {
-      load_transposed(va, A, row_beg + k0, row_end, a0, K, K, kBM / 4, vec_a, in_a && in_k);   // X rows -> K dim
-      load_transposed(vb, B, row_beg + k0, row_end, n0, U, U, nt / 4, vec_b, in_b && in_k);    // G rows -> K dim
-    }
-  };
-  // The tensor core adds into the TMEM accumulator with truncation, which biases long reductions (measured:
-  // ~7e-9 relative per reduction element).  Every kFlush elements the accumulator is drained into fp32 registers
-  // (round-to-nearest adds) and the next MMAs start a fresh accumulation in the OTHER accumulator, so the drain of
-  // group g overlaps the MMAs of group g + 1.
+  // fp32 (round-to-nearest) running sum of the drained per-chunk accumulators
   float racc[32];
 #pragma unroll
   for (int i = 0; i < 32; ++i) racc[i] = 0.f;
   const int c0 = 32 * (warp >> 2);                       // this warp's 32 accumulator columns (staging warps only)
   auto drain = [&](uint32_t acc_col) {
     if (c0 < nt) {                                       // warp-uniform
-      uint32_t v[32];
       const uint32_t taddr = tmem_d + (static_cast<uint32_t>(32 * (warp & 3)) << 16) + acc_col +
                              static_cast<uint32_t>(c0);
-      asm volatile(
-          "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-          "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-          "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-          : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
-            "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
-            "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
-            "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
-          : "r"(taddr)
-          : "memory");
-      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 #pragma unroll
-      for (int i = 0; i < 32; ++i) racc[i] += __uint_as_float(v[i]);
+      for (int h = 0; h < 2; ++h) {                      // two 16-column halves: 16 temporaries instead of 32
+        uint32_t v[16];
+        asm volatile(
+            "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+            "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+            : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+              "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+            : "r"(taddr + 16u * h)
+            : "memory");
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+        for (int i = 0; i < 16; ++i) racc[16 * h + i] += __uint_as_float(v[i]);
+      }
     }
   };
   const bool do_colsum = (OP == kTN) && colsum_part != nullptr && a0 == 0;     // CTA-uniform
-  float4 csum4[kLd];                                     // bias gradient: this thread's (row lane, 4 features) sums
+  float csum[8];                                         // bias gradient: this thread's 8 features, its rows k
 #pragma unroll
-  for (int i = 0; i < kLd; ++i) csum4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-  // Warp-specialised software pipeline over chunks c of kKC reduction elements, kStages shared-memory stages:
-  //   warps 0-7 (staging):  [wait done(c - kStages)]  split+store(c)  load(c+2)  arrive full(c)  [drain group of c-1]
-  //   warp 8   (MMA issue): wait full(c)  tcgen05.mma x 3 x ksteps -> accumulator (group & 1)  commit -> done(c)
-  // No block-wide barrier inside the loop; two TMEM accumulators alternate per flush group so that the drain of
-  // group g (tcgen05.ld by the staging warps) overlaps the MMAs of group g + 1.
-  const int nchunk = static_cast<int>((red_len + kKC - 1) / kKC);
-  constexpr int kPerGroup = kFlush / kKC;
+  for (int i = 0; i < 8; ++i) csum[i] = 0.f;
+  // Warp-specialised pipeline over chunks c of kKC reduction elements, kStages shared-memory stages:
+  //   warps 0-15 (staging): [wait done(c - kStages)]  split+store(c)  load(c + kStages)  arrive full(c)  [drain]
+  //   warp 16   (MMA issue): wait full(c)  12 x tcgen05.mma -> accumulator (group & 1)  commit -> done(c)
+  // No block-wide barrier inside the loop; the drain of chunk c (tcgen05.ld by the staging warps) overlaps the MMAs
+  // of chunk c + 1, which accumulate in another TMEM accumulator.
+  static_assert(kFlush == kKC, "one accumulator per chunk");
   auto wait_chunk = [&](int c) { mbar_wait(smem_u32(&mbar[c % kStages]), static_cast<uint32_t>((c / kStages) & 1)); };
   if (warp == kThreads / 32) {
     // ------------------------------- MMA-issue warp -------------------------------
-    const uint64_t desc_hi = (static_cast<uint64_t>(NRP & 0x3FFF) << 16) | (static_cast<uint64_t>(8) << 32) | (1ull << 46);
+    // descriptors differ only in the 14-bit start-address field (16-byte units)
+    const uint64_t da_hi = kAMn ? desc_hi_bits(8, kKC) : desc_hi_bits(kPitchK, 8);
+    const uint64_t db_hi = kBMn ? desc_hi_bits(8, kKC) : desc_hi_bits(kPitchK, 8);
+    constexpr uint32_t a_step = kAMn ? 16 : 2 * kPitchK;       // start-address advance per MMA k-step (16 elements)
+    constexpr uint32_t b_step = kBMn ? 16 : 2 * kPitchK;
     for (int c = 0; c < nchunk; ++c) {
       const int st = c % kStages;
       mbar_wait(smem_u32(&full[st]), static_cast<uint32_t>((c / kStages) & 1));
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       if (lane == 0) {
-        const uint32_t base = smem_u32(planes + static_cast<size_t>(st) * 4 * PLANE);
-        // descriptors differ only in the 14-bit start-address field (16-byte units): + kstep per MMA k-step
-        const uint64_t dah0 = desc_hi | ((base >> 4) & 0x3FFF);
-        const uint64_t dal0 = dah0 + PLANE, dbh0 = dah0 + 2 * PLANE, dbl0 = dah0 + 3 * PLANE;
+        const uint32_t base = smem_u32(planes + static_cast<size_t>(st) * kStageUnits) >> 4;
+        const uint64_t a1 = da_hi | (base & 0x3FFF), a2 = a1 + kPlaneUnits, a3 = a2 + kPlaneUnits;
+        const uint64_t b1 = db_hi | ((base + 3 * kPlaneUnits) & 0x3FFF), b2 = b1 + kPlaneUnits, b3 = b2 + kPlaneUnits;
         const int64_t left = red_len - static_cast<int64_t>(c) * kKC;
-        const int ksteps = (static_cast<int>(left < kKC ? left : kKC) + 7) / 8;           // skip all-zero k-steps
-        const bool fresh = (c % kPerGroup) == 0;          // first chunk of a flush group overwrites the accumulator
-        const uint32_t acc = tmem_d + static_cast<uint32_t>(((c / kPerGroup) & 1) * kMaxN);
-        // small terms first: while they accumulate, the accumulator is ~2^-11 of its final size and so are the
-        // truncation errors of the tensor core's adds.  lo*lo (2^-22 relative) is below the fp32 rounding of the
-        // result and is left out (3xTF32).
+        const int ksteps = (static_cast<int>(left < kKC ? left : kKC) + 15) / 16;         // skip all-zero k-steps
+        constexpr bool fresh = true;                      // every chunk starts a new accumulation (kFlush == kKC)
+        const uint32_t acc = tmem_d + static_cast<uint32_t>((short_k ? c : (c & 1)) * kMaxN);
+        // small terms first: while they accumulate, the accumulator is 2^-16 .. 2^-8 of its final size and so are
+        // the truncation errors of the tensor core's adds
 #pragma unroll
-        for (int ks = 0; ks < kKC / 8; ++ks) {
+        for (int ks = 0; ks < kKC / 16; ++ks) {
           if (ks < ksteps) {
-            mma_tf32(acc, dal0 + ks * kstep, dbh0 + ks * kstep, idesc, (fresh && ks == 0) ? 0u : 1u);   // lo * hi
-            mma_tf32(acc, dah0 + ks * kstep, dbl0 + ks * kstep, idesc, 1u);                             // hi * lo
+            const uint32_t ao = ks * a_step, bo = ks * b_step;
+            mma_bf16(acc, a3 + ao, b1 + bo, idesc, (fresh && ks == 0) ? 0u : 1u);
+            mma_bf16(acc, a1 + ao, b3 + bo, idesc, 1u);
+            mma_bf16(acc, a2 + ao, b2 + bo, idesc, 1u);
           }
         }
 #pragma unroll
-        for (int ks = 0; ks < kKC / 8; ++ks)
-          if (ks < ksteps) mma_tf32(acc, dah0 + ks * kstep, dbh0 + ks * kstep, idesc, 1u);              // hi * hi
+        for (int ks = 0; ks < kKC / 16; ++ks) {
+          if (ks < ksteps) {
+            const uint32_t ao = ks * a_step, bo = ks * b_step;
+            mma_bf16(acc, a2 + ao, b1 + bo, idesc, 1u);
+            mma_bf16(acc, a1 + ao, b2 + bo, idesc, 1u);
+          }
+        }
+#pragma unroll
+        for (int ks = 0; ks < kKC / 16; ++ks)
+          if (ks < ksteps) mma_bf16(acc, a1 + ks * a_step, b1 + ks * b_step, idesc, 1u);
         asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
                          smem_u32(&mbar[st]))
                      : "memory");
@@ -330,46 +362,54 @@ dense_tc_body(const float* __restrict__ A, const float* __restrict__ B, int64_t 
     }
   } else {
     // ------------------------------- staging warps -------------------------------
-    if (nchunk > 0) load_chunk(0, va0, vb0);
-    if (nchunk > 1) load_chunk(kKC, va1, vb1);
-    auto step = [&](int c, float4 (&va)[kLd], float4 (&vb)[kLd]) {
+    auto stage = [&](int c, const F8& ra, const F8& rb) {         // split + store chunk c
       const int st = c % kStages;
-      float4* a_hi = planes + static_cast<size_t>(st) * 4 * PLANE;
-      float4* a_lo = a_hi + PLANE;
-      float4* b_hi = a_lo + PLANE;
-      float4* b_lo = b_hi + PLANE;
-      if (c >= kStages) wait_chunk(c - kStages);           // the MMAs that read this stage are done (long ago)
-      // ---- split (hi / lo) and store this chunk ----
-      if (OP == kNN) { store_direct(va, a_hi, a_lo); store_transposed(vb, nt / 4, b_hi, b_lo); }
-      else if (OP == kNT) { store_direct(va, a_hi, a_lo); store_direct(vb, b_hi, b_lo); }
-      else { store_transposed(va, kBM / 4, a_hi, a_lo); store_transposed(vb, nt / 4, b_hi, b_lo); }
+      uint4* pa = planes + static_cast<size_t>(st) * kStageUnits;
+      uint4* pb = pa + 3 * kPlaneUnits;
+      if (kAMn) store_mnmajor(ra, pa); else store_kmajor(ra, pa);
+      if (kBMn) store_mnmajor(rb, pb); else store_kmajor(rb, pb);
       if (OP == kTN && do_colsum) {
-#pragma unroll
-        for (int i = 0; i < kLd; ++i) {
-          csum4[i].x += vb[i].x; csum4[i].y += vb[i].y; csum4[i].z += vb[i].z; csum4[i].w += vb[i].w;
-        }
+        csum[0] += rb.a.x; csum[1] += rb.a.y; csum[2] += rb.a.z; csum[3] += rb.a.w;
+        csum[4] += rb.b.x; csum[5] += rb.b.y; csum[6] += rb.b.z; csum[7] += rb.b.w;
       }
-      if (c + 2 < nchunk) load_chunk(static_cast<int64_t>(c + 2) * kKC, va, vb);   // refill this register set
+    };
+    auto publish = [&](int c) {                                    // hand chunk c to the MMA warp
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // generic-proxy stores -> async proxy (MMA)
       asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
       __syncwarp();
       if (lane == 0)
-        asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&full[st])) : "memory");
-      // ---- drain the previous flush group while this chunk's MMAs run ----
-      if (c > 0 && (c % kPerGroup) == 0) {
-        wait_chunk(c - 1);
-        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        drain(static_cast<uint32_t>((((c - 1) / kPerGroup) & 1) * kMaxN));
-      }
+        asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&full[c % kStages])) : "memory");
     };
-    for (int c = 0; c < nchunk; c += 2) {
-      step(c, va0, vb0);
-      if (c + 1 < nchunk) step(c + 1, va1, vb1);
-    }
-    if (nchunk > 0) {
+    if (short_k) {
+      if (nchunk > 0) { stage(0, va0, vb0); if (nchunk > 2) load_chunk_b(2 * kKC, vb0); publish(0); }
+      if (nchunk > 1) { stage(1, va1, vb1); if (nchunk > 3) load_chunk_b(3 * kKC, vb1); publish(1); }
+      if (nchunk > 2) { stage(2, va2, vb0); publish(2); }
+      if (nchunk > 3) { stage(3, va3, vb1); publish(3); }
+      for (int c = 0; c < nchunk; ++c) {                   // accumulator c holds chunk c: fp32 (RN) sum in registers
+        wait_chunk(c);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        drain(static_cast<uint32_t>(c * kMaxN));
+      }
+    } else {
+      auto step = [&](int c, F8& ra, F8& rb) {
+        if (c >= kStages) wait_chunk(c - kStages);         // the MMAs that read this stage are done
+        stage(c, ra, rb);
+        if (c + 2 < nchunk) load_chunk(static_cast<int64_t>(c + 2) * kKC, ra, rb);   // refill this register set
+        publish(c);
+        // ---- drain the previous chunk's accumulator while this chunk's MMAs run ----
+        if (c > 0) {
+          wait_chunk(c - 1);
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          drain(static_cast<uint32_t>(((c - 1) & 1) * kMaxN));
+        }
+      };
+      for (int c = 0; c < nchunk; c += 2) {
+        step(c, va0, vb0);
+        if (c + 1 < nchunk) step(c + 1, va1, vb1);
+      }
       wait_chunk(nchunk - 1);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-      drain(static_cast<uint32_t>((((nchunk - 1) / kPerGroup) & 1) * kMaxN));
+      drain(static_cast<uint32_t>(((nchunk - 1) & 1) * kMaxN));
     }
   }
 
@@ -429,31 +469,28 @@ dense_tc_body(const float* __restrict__ A, const float* __restrict__ B, int64_t 
     }
   }
   if (OP == kTN && do_colsum && warp < kThreads / 32) {
-    // registers i = the two 16-row blocks of a chunk; lanes (l & 15) = rows; (2 warp + (l >> 4)) = 4-feature group:
-    // fixed order (i, then xor tree over 16 lanes) -> deterministic
-    float4 t = csum4[0];
+    // this thread summed 8 features (mn8 = 4 (warp / 4) + lane / 8) over its rows k = 8 (warp % 4) + lane % 8 of every
+    // chunk: fixed order = xor tree over the 8 row lanes, then the 4 row warps -> deterministic
 #pragma unroll
-    for (int i = 1; i < kLd; ++i) { t.x += csum4[i].x; t.y += csum4[i].y; t.z += csum4[i].z; t.w += csum4[i].w; }
-#pragma unroll
-    for (int o = 8; o > 0; o >>= 1) {
-      t.x += __shfl_xor_sync(0xffffffffu, t.x, o); t.y += __shfl_xor_sync(0xffffffffu, t.y, o);
-      t.z += __shfl_xor_sync(0xffffffffu, t.z, o); t.w += __shfl_xor_sync(0xffffffffu, t.w, o);
+    for (int i = 0; i < 8; ++i) {
+      float t = csum[i];
+      t += __shfl_xor_sync(0xffffffffu, t, 4);
+      t += __shfl_xor_sync(0xffffffffu, t, 2);
+      t += __shfl_xor_sync(0xffffffffu, t, 1);
+      if ((lane & 7) == 0) csum_s[warp][lane >> 3][i] = t;
     }
-    const int j = 2 * warp + (lane >> 4);
-    if ((lane & 15) == 0 && 4 * j < nt) {
-      const int col = n0 + 4 * j;
-      float* dst = colsum_part + static_cast<int64_t>(bz) * U;
-      if (col + 0 < U) dst[col + 0] = t.x;
-      if (col + 1 < U) dst[col + 1] = t.y;
-      if (col + 2 < U) dst[col + 2] = t.z;
-      if (col + 3 < U) dst[col + 3] = t.w;
+    asm volatile("bar.sync 1, %0;" ::"r"(kThreads) : "memory");
+    if (threadIdx.x < kMaxN) {
+      const int f = threadIdx.x, mn8 = f >> 3, j = f & 7, w0 = 4 * (mn8 >> 2), sub = mn8 & 3;
+      const float t = (csum_s[w0][sub][j] + csum_s[w0 + 1][sub][j]) + (csum_s[w0 + 2][sub][j] + csum_s[w0 + 3][sub][j]);
+      if (f < nt && n0 + f < U) colsum_part[static_cast<int64_t>(bz) * U + n0 + f] = t;
     }
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
   if (warp == kThreads / 32) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d),
-                 "r"(static_cast<uint32_t>(2 * kMaxN))
+                 "r"(static_cast<uint32_t>(kTmemCols))
                  : "memory");
   }
 }
@@ -571,7 +608,8 @@ tn_grouped_reduce_kernel(const __grid_constant__ TnGroup grp, const float* __res
   *dst = acc;
 }
 
-constexpr size_t kSmemBytes = kStages * 4 * (kKC / 4) * (kBM + 1) * sizeof(float4);   // 3 stages x 4 planes x 16.5 KB
+constexpr size_t kSmemBytes = static_cast<size_t>(kStages) * kStageUnits * sizeof(uint4);   // 4 stages x 6 planes x 8.1 KB
+static_assert(kSmemBytes >= static_cast<size_t>(kBM) * (kMaxN + 4) * sizeof(float), "epilogue tile fits in the stages");
 
 inline int tn_splits(int64_t M, int K, int U) {
   const int tiles = ceil_div(K, kBM) * ceil_div(U, kMaxN);
