@@ -1,0 +1,284 @@
+// Compact NN / NT Dense kernel for the shapes every SchNet / PaiNN layer has: reduction length 32 .. 128 (a multiple of
+// 32), 16-byte aligned rows, output width a multiple of 16.  Same arithmetic as dense_tc.cu (3-piece bf16 split, six
+// kind::f16 MMAs per 16 reduction elements, one TMEM accumulator per 32-element chunk, fp32 round-to-nearest sum of the
+// accumulators in registers), but straight-line code without any predicated edge path: a launch of the general kernel
+// runs every instruction exactly once per tile, and its ~10 k SASS instructions of edge handling cost more in
+// instruction-cache misses than in issue slots (tools/tc_timeline.cu: 3 900 cycles from entry to the first load).
+//   * rows past the end of the matrix are CLAMPED for the loads (their results are never stored);
+//   * columns past the layer width are clamped too (the MMA's N covers only the valid ones);
+//   * the reduction needs no zero fill because its length is a multiple of the chunk.
+// One CTA = one 128-row tile: 16 staging warps (one 8-element unit of A and of B per thread and chunk) + one warp that
+// issues the MMAs; all global loads of the A tile are in flight before the first split.  Epilogue: accumulators (+ bias,
+// + f(pre) beside it for the fused activation) -> shared memory -> one bulk asynchronous copy per 512-byte row.
+#include "dense_tc.cuh"
+
+namespace kgcnn {
+namespace tc {
+
+template <int OP, int ACT>   // ACT < 0: one output; otherwise out = pre, act_out = f_ACT(pre)
+__global__ void __launch_bounds__(kCtaThreads)
+dense_fast_kernel(const float* __restrict__ A, const float* __restrict__ B, int64_t M, int K, int U,
+                  const float* __restrict__ bias, float* __restrict__ out, float* __restrict__ act_out) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  __shared__ __align__(8) uint64_t mbar[kStages];
+  __shared__ __align__(8) uint64_t full[kStages];
+  __shared__ uint32_t tmem_base_s;
+  __shared__ __align__(16) float bias_s[kMaxN];
+  uint4* planes = reinterpret_cast<uint4*>(smem_raw);            // [stage][a1, a2, a3, b1, b2, b3][kPlaneUnits]
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  TL(0);
+  // Touch every kernel parameter first: the constant-bank misses of a freshly launched kernel (~700 cycles per access
+  // path, measured with tools/tc_timeline.cu) then overlap instead of queueing behind one another in the prologue.
+  asm volatile("" ::"l"(A), "l"(B), "l"(M), "r"(K), "r"(U), "l"(bias), "l"(out), "l"(act_out));
+  if (A == nullptr || B == nullptr || M <= 0 || K <= 0 || U <= 0 || out == nullptr) return;   // uniform-path reads
+  const int n_total = (OP == kNN) ? U : K;                       // output width
+  const int red = (OP == kNN) ? K : U;                           // reduction length = row length of A
+  const int n0 = blockIdx.y * kMaxN;
+  const int nt = min(kMaxN, n_total - n0);                       // MMA N (multiple of 16)
+  const int64_t m0 = static_cast<int64_t>(blockIdx.x) * kBM;
+  const int nchunk = red / kKC;                                  // 1 .. 4
+
+  if (warp == kThreads / 32) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)),
+                 "r"(static_cast<uint32_t>(kTmemCols))
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    TL(17);
+  }
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int st = 0; st < kStages; ++st) {
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&mbar[st])) : "memory");
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(&full[st])), "r"(kThreads / 32)
+                   : "memory");
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    TL(16);
+  }
+
+  // per-thread source pointers of its unit in chunk 0 (16-byte aligned by the launch conditions)
+  const float4* pa = nullptr;
+  const float4* pb = nullptr;
+  int64_t b_step = 0;                                            // float4 per chunk
+  if (warp < kThreads / 32) {
+    const int t = threadIdx.x;
+    const int64_t row = min(m0 + (t >> 2), M - 1);
+#ifdef KGCNN_TC_TIMELINE
+    asm volatile("" ::"l"(row));
+    TL(19);
+#endif
+    pa = reinterpret_cast<const float4*>(A + row * red + 8 * (t & 3));
+#ifdef KGCNN_TC_TIMELINE
+    asm volatile("" ::"l"(pa));
+    TL(30);
+#endif
+    if (OP == kNN) {                                             // W[k, u]: reduction along the rows, MN-major
+      int k, mn8;
+      mn_coords(k, mn8);
+      const int f = min(n0 + 8 * mn8, n_total - 8);
+      pb = reinterpret_cast<const float4*>(B + static_cast<int64_t>(k) * U + f);
+      b_step = static_cast<int64_t>(kKC) * U / 4;
+    } else {                                                     // W[n, u]: reduction along the features, K-major
+      const int n = min(n0 + (t >> 2), K - 1);
+      pb = reinterpret_cast<const float4*>(B + static_cast<int64_t>(n) * U + 8 * (t & 3));
+      b_step = kKC / 4;
+    }
+  }
+  auto ld_a = [&](int c) { F8 v; v.a = __ldg(pa + c * (kKC / 4)); v.b = __ldg(pa + c * (kKC / 4) + 1); return v; };
+  auto ld_b = [&](int c) { F8 v; v.a = __ldg(pb + c * b_step); v.b = __ldg(pb + c * b_step + 1); return v; };
+  F8 va0, va1, va2, vb0, vb1;
+  TL(18);
+  if (warp < kThreads / 32) {
+    va0 = ld_a(0);
+    vb0 = ld_b(0);
+    if (nchunk > 1) { va1 = ld_a(1); vb1 = ld_b(1); }
+    if (nchunk > 2) va2 = ld_a(2);
+    if (OP == kNN && threadIdx.x < kMaxN)                        // bias of this column tile -> shared (read in the epilogue)
+      bias_s[threadIdx.x] = (bias && threadIdx.x < nt) ? __ldg(bias + n0 + threadIdx.x) : 0.f;
+  }
+  TL(1);
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_d = tmem_base_s;
+  TL(2);
+
+  constexpr bool kBMn = (OP == kNN);
+  auto wait_chunk = [&](int c) { mbar_wait(smem_u32(&mbar[c]), 0u); };
+  float racc[32];
+  const int c0 = 32 * (warp >> 2);                       // this warp's 32 accumulator columns (staging warps only)
+  if (warp == kThreads / 32) {
+    // ------------------------------- MMA-issue warp -------------------------------
+    const uint32_t idesc = make_idesc(0, kBMn ? 1 : 0, nt);
+    const uint64_t da_hi = desc_hi_bits(kPitchK, 8);
+    const uint64_t db_hi = kBMn ? desc_hi_bits(8, kKC) : desc_hi_bits(kPitchK, 8);
+    constexpr uint32_t a_step = 2 * kPitchK;
+    constexpr uint32_t bk_step = kBMn ? 16 : 2 * kPitchK;
+    for (int c = 0; c < nchunk; ++c) {
+      mbar_wait(smem_u32(&full[c]), 0u);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      TL(20 + 2 * c);
+      if (lane == 0) {
+        const uint32_t base = smem_u32(planes + static_cast<size_t>(c) * kStageUnits) >> 4;
+        const uint64_t a1 = da_hi | (base & 0x3FFF), a2 = a1 + kPlaneUnits, a3 = a2 + kPlaneUnits;
+        const uint64_t b1 = db_hi | ((base + 3 * kPlaneUnits) & 0x3FFF), b2 = b1 + kPlaneUnits, b3 = b2 + kPlaneUnits;
+        const uint32_t acc = tmem_d + static_cast<uint32_t>(c * kMaxN);
+        // small terms first (see dense_tc.cu)
+        mma_bf16(acc, a3, b1, idesc, 0u);
+        mma_bf16(acc, a1, b3, idesc, 1u);
+        mma_bf16(acc, a2, b2, idesc, 1u);
+        mma_bf16(acc, a3 + a_step, b1 + bk_step, idesc, 1u);
+        mma_bf16(acc, a1 + a_step, b3 + bk_step, idesc, 1u);
+        mma_bf16(acc, a2 + a_step, b2 + bk_step, idesc, 1u);
+        mma_bf16(acc, a2, b1, idesc, 1u);
+        mma_bf16(acc, a1, b2, idesc, 1u);
+        mma_bf16(acc, a2 + a_step, b1 + bk_step, idesc, 1u);
+        mma_bf16(acc, a1 + a_step, b2 + bk_step, idesc, 1u);
+        mma_bf16(acc, a1, b1, idesc, 1u);
+        mma_bf16(acc, a1 + a_step, b1 + bk_step, idesc, 1u);
+        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
+                         smem_u32(&mbar[c]))
+                     : "memory");
+      }
+      TL(21 + 2 * c);
+      __syncwarp();
+    }
+  } else {
+    // ------------------------------- staging warps -------------------------------
+    auto stage = [&](int c, const F8& ra, const F8& rb) {
+      uint4* sa = planes + static_cast<size_t>(c) * kStageUnits;
+      store_kmajor(ra, sa);
+      if (kBMn) store_mnmajor(rb, sa + 3 * kPlaneUnits); else store_kmajor(rb, sa + 3 * kPlaneUnits);
+    };
+    auto publish = [&](int c) {
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // generic-proxy stores -> async proxy (MMA)
+      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+      __syncwarp();
+      if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&full[c])) : "memory");
+    };
+    stage(0, va0, vb0);
+    TL(3);
+    if (nchunk > 2) vb0 = ld_b(2);
+    if (nchunk > 3) va0 = ld_a(3);
+    publish(0);
+    TL(4);
+    if (nchunk > 1) { stage(1, va1, vb1); if (nchunk > 3) vb1 = ld_b(3); publish(1); TL(5); }
+    if (nchunk > 2) { stage(2, va2, vb0); publish(2); TL(6); }
+    if (nchunk > 3) { stage(3, va0, vb1); publish(3); TL(7); }
+    // accumulator c holds chunk c: fp32 (RN) sum in registers
+    for (int c = 0; c < nchunk; ++c) {
+      wait_chunk(c);
+      TL(8 + c);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      if (c0 < nt) {
+        const uint32_t taddr = tmem_d + (static_cast<uint32_t>(32 * (warp & 3)) << 16) + static_cast<uint32_t>(c * kMaxN + c0);
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          uint32_t v[16];
+          asm volatile(
+              "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+              "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+              : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+              : "r"(taddr + 16u * h)
+              : "memory");
+          asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+          for (int i = 0; i < 16; ++i)
+            racc[16 * h + i] = (c == 0) ? __uint_as_float(v[i]) : racc[16 * h + i] + __uint_as_float(v[i]);
+        }
+      }
+    }
+    TL(12);
+
+    // ---- epilogue: lane = output row 32 (warp % 4) + lane, columns c0 .. c0 + 31 ----
+    const int d_row = 32 * (warp & 3) + lane;
+    constexpr int OP_PITCH = kMaxN + 4;
+    float* otile = reinterpret_cast<float*>(smem_raw);             // the operand stages are free: every MMA has completed
+    float* atile = otile + kBM * OP_PITCH;
+    if (c0 < nt) {
+#pragma unroll
+      for (int i = 0; i < 32; i += 4) {
+        float4 v = make_float4(racc[i], racc[i + 1], racc[i + 2], racc[i + 3]);
+        if (OP == kNN) {
+          const float4 bv = *reinterpret_cast<const float4*>(bias_s + c0 + i);
+          v.x += bv.x; v.y += bv.y; v.z += bv.z; v.w += bv.w;
+        }
+        *reinterpret_cast<float4*>(otile + d_row * OP_PITCH + c0 + i) = v;
+        if (ACT >= 0)
+          *reinterpret_cast<float4*>(atile + d_row * OP_PITCH + c0 + i) =
+              make_float4(act_deriv<ACT < 0 ? 0 : ACT>(v.x, 0), act_deriv<ACT < 0 ? 0 : ACT>(v.y, 0),
+                          act_deriv<ACT < 0 ? 0 : ACT>(v.z, 0), act_deriv<ACT < 0 ? 0 : ACT>(v.w, 0));
+      }
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy stores -> async proxy (bulk copy)
+    asm volatile("bar.sync 1, %0;" ::"r"(kThreads) : "memory");    // staging warps only
+    TL(13);
+    if (threadIdx.x < kBM && m0 + threadIdx.x < M) {
+      const int r = threadIdx.x;
+      const uint32_t bytes = static_cast<uint32_t>(nt) * 4u;
+      asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(out + (m0 + r) * n_total + n0),
+                   "r"(smem_u32(otile + r * OP_PITCH)), "r"(bytes)
+                   : "memory");
+      if (ACT >= 0)
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(
+                         act_out + (m0 + r) * n_total + n0),
+                     "r"(smem_u32(atile + r * OP_PITCH)), "r"(bytes)
+                     : "memory");
+      asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+    }
+  }
+  TL(14);
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  TL(15);
+  if (warp == kThreads / 32) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d),
+                 "r"(static_cast<uint32_t>(kTmemCols))
+                 : "memory");
+  }
+}
+
+template <int OP, int ACT>
+static void launch_fast(const float* A, const float* B, int64_t M, int K, int U, const float* bias, float* out,
+                        float* act_out, cudaStream_t st) {
+  static PerDeviceOnce attr;
+  attr.run([] {
+    cudaFuncSetAttribute(dense_fast_kernel<OP, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         static_cast<int>(kSmemBytesDecl));
+  });
+  const int n_total = (OP == kNN) ? U : K;
+  dim3 grid(static_cast<unsigned>(ceil_div<int64_t>(M, kBM)), ceil_div(n_total, kMaxN));
+  dense_fast_kernel<OP, ACT><<<grid, kCtaThreads, kSmemBytesDecl, st>>>(A, B, M, K, U, bias, out, act_out);
+}
+
+bool dense_fast_try_launch(int op, const float* A, const float* B, int64_t M, int K, int U, const float* bias,
+                           float* out, float* act_out, int act, cudaStream_t st) {
+  if (op != kNN && op != kNT) return false;
+  const int red = (op == kNN) ? K : U, n_total = (op == kNN) ? U : K;
+  auto al16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
+  if (M < 1 || red % kKC != 0 || red > kStages * kKC || n_total % 16 != 0 || U % 4 != 0) return false;
+  if (!al16(A) || !al16(B) || !al16(out) || (bias && !al16(bias)) || (act_out && !al16(act_out))) return false;
+  if (op == kNT) {
+    launch_fast<kNT, -1>(A, B, M, K, U, nullptr, out, nullptr, st);
+    return true;
+  }
+  if (!act_out) {
+    launch_fast<kNN, -1>(A, B, M, K, U, bias, out, nullptr, st);
+    return true;
+  }
+  switch (act) {
+    case KGCNN_ACT_SHIFTED_SOFTPLUS: launch_fast<kNN, KGCNN_ACT_SHIFTED_SOFTPLUS>(A, B, M, K, U, bias, out, act_out, st); return true;
+    case KGCNN_ACT_SOFTPLUS2: launch_fast<kNN, KGCNN_ACT_SOFTPLUS2>(A, B, M, K, U, bias, out, act_out, st); return true;
+    case KGCNN_ACT_SWISH: launch_fast<kNN, KGCNN_ACT_SWISH>(A, B, M, K, U, bias, out, act_out, st); return true;
+    case KGCNN_ACT_TANH: launch_fast<kNN, KGCNN_ACT_TANH>(A, B, M, K, U, bias, out, act_out, st); return true;
+    case KGCNN_ACT_RELU: launch_fast<kNN, KGCNN_ACT_RELU>(A, B, M, K, U, bias, out, act_out, st); return true;
+    case KGCNN_ACT_SIGMOID: launch_fast<kNN, KGCNN_ACT_SIGMOID>(A, B, M, K, U, bias, out, act_out, st); return true;
+    case KGCNN_ACT_LEAKY_RELU: launch_fast<kNN, KGCNN_ACT_LEAKY_RELU>(A, B, M, K, U, bias, out, act_out, st); return true;
+    default: return false;
+  }
+}
+
+}  // namespace tc
+}  // namespace kgcnn

@@ -27,156 +27,10 @@
 // is a conflict-free 128-bit store.  kStages x 32 reduction elements are resident, i.e. for K <= 128 every global
 // load of a tile is issued up front; one warp issues the MMAs (tcgen05.commit -> one mbarrier per stage), 16 warps
 // stage and drain.
-#include <algorithm>
-
-#include "activation.cuh"
-#include "common.cuh"
+#include "dense_tc.cuh"
 
 namespace kgcnn {
 namespace tc {
-
-constexpr int kThreads = 512;   // 16 staging warps: one 8-element unit of A and one of B per thread and chunk;
-                                // warp w reads TMEM lanes 32*(w%4)..+31, columns 32*(w/4)..+31 in the drain / epilogue
-constexpr int kCtaThreads = kThreads + 32;   // + the MMA-issue warp
-constexpr int kBM = 128;        // MMA M
-constexpr int kKC = 32;         // reduction elements staged per chunk (2 MMA k-steps of 16)
-constexpr int kStages = 4;      // shared-memory stages of (A b1,b2,b3, B b1,b2,b3) planes: 4 x 48.75 KB
-constexpr int kMaxN = 128;      // MMA N per CTA (TMEM columns)
-constexpr int kFlush = kKC;     // reduction length accumulated inside the tensor core before an fp32 (RN) flush
-constexpr int kTmemCols = 512;  // four accumulators of kMaxN columns (short reductions: one per chunk, drained at the end)
-// K-major plane: 16-byte unit (k8, mn) at slot k8 * kPitchK + mn.  130 = 2 mod 8: the 8 lanes of a quarter warp
-// (4 k8 columns x 2 rows) land in 8 different 16-byte bank groups.
-constexpr int kPitchK = kBM + 2;
-// MN-major plane: unit (mn8, k) at slot mn8 * kKC + k: 8 consecutive k are 128 contiguous bytes (one core matrix).
-constexpr int kPlaneUnits = (kKC / 8) * kPitchK;                       // 520 units >= 16 * kKC = 512
-static_assert(kPlaneUnits >= (kMaxN / 8) * kKC, "plane holds either layout");
-constexpr int kStageUnits = 6 * kPlaneUnits;
-
-enum { kNN = 0, kNT = 1, kTN = 2 };
-
-__device__ __forceinline__ uint32_t smem_u32(const void* p) {
-  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
-}
-
-// shared-memory matrix descriptor, SWIZZLE_NONE, version 1 (sm_100): start>>4 [0,14), LBO>>4 [16,30), SBO>>4 [32,46).
-// For both majors LBO is the byte offset between core matrices along K, SBO along M/N.
-__device__ __forceinline__ uint64_t desc_hi_bits(uint32_t lbo16, uint32_t sbo16) {
-  return (static_cast<uint64_t>(lbo16 & 0x3FFF) << 16) | (static_cast<uint64_t>(sbo16 & 0x3FFF) << 32) | (1ull << 46);
-}
-
-// instruction descriptor kind::f16: D=F32 [4,6), A=BF16 [7,10), B=BF16 [10,13), a_major 15, b_major 16 (1 = MN-major),
-// N>>3 [17,23), M>>4 [24,29)
-__device__ __forceinline__ uint32_t make_idesc(int a_mn_major, int b_mn_major, int n) {
-  return (1u << 4) | (1u << 7) | (1u << 10) | (static_cast<uint32_t>(a_mn_major) << 15) |
-         (static_cast<uint32_t>(b_mn_major) << 16) | (static_cast<uint32_t>(n >> 3) << 17) |
-         (static_cast<uint32_t>(kBM >> 4) << 24);
-}
-
-__device__ __forceinline__ void mma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
-  asm volatile(
-      "{\n\t"
-      ".reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
-      "}\n" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
-      : "memory");
-}
-
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  uint32_t done = 0;
-  int spins = 0;
-  while (!done) {
-    asm volatile(
-        "{\n\t"
-        ".reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.b32 %0, 1, 0, p;\n\t"
-        "}\n"
-        : "=r"(done)
-        : "r"(bar), "r"(parity)
-        : "memory");
-    if (!done && ++spins > (1 << 22)) __trap();   // never hang the device on a lost arrival
-  }
-}
-
-// eight consecutive floats g[row, f .. f+7] (zero beyond row_end / f_end)
-struct F8 { float4 a, b; };
-__device__ __forceinline__ F8 load8(const float* __restrict__ g, int64_t row, int64_t row_end, int f, int f_end, int ld,
-                                    bool vec_ok, bool fast) {
-  F8 v;
-  if (fast) {
-    const float4* p = reinterpret_cast<const float4*>(g + row * ld + f);
-    v.a = __ldg(p);
-    v.b = __ldg(p + 1);
-    return v;
-  }
-  v.a = make_float4(0.f, 0.f, 0.f, 0.f);
-  v.b = v.a;
-  if (row < row_end && f < f_end) {
-    const float* p = g + row * ld + f;
-    if (vec_ok && f + 7 < f_end) {
-      v.a = __ldg(reinterpret_cast<const float4*>(p));
-      v.b = __ldg(reinterpret_cast<const float4*>(p) + 1);
-    } else {
-      float t[8];
-#pragma unroll
-      for (int q = 0; q < 8; ++q) t[q] = (f + q < f_end) ? __ldg(p + q) : 0.f;
-      v.a = make_float4(t[0], t[1], t[2], t[3]);
-      v.b = make_float4(t[4], t[5], t[6], t[7]);
-    }
-  }
-  return v;
-}
-
-// (x0, x1) -> three packed bf16x2 words (x0 in the low half): b1 = rn(x), b2 = rn(x - b1), b3 = rn(x - b1 - b2);
-// both remainders are exact in fp32.
-__device__ __forceinline__ void split3(float x0, float x1, uint32_t& p1, uint32_t& p2, uint32_t& p3) {
-  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(p1) : "f"(x1), "f"(x0));
-  const float r0 = x0 - __uint_as_float(p1 << 16), r1 = x1 - __uint_as_float(p1 & 0xffff0000u);
-  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(p2) : "f"(r1), "f"(r0));
-  const float s0 = r0 - __uint_as_float(p2 << 16), s1 = r1 - __uint_as_float(p2 & 0xffff0000u);
-  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(p3) : "f"(s1), "f"(s0));
-}
-__device__ __forceinline__ void store_unit(const F8& v, uint4* __restrict__ planes, int slot) {
-  uint4 u1, u2, u3;
-  split3(v.a.x, v.a.y, u1.x, u2.x, u3.x);
-  split3(v.a.z, v.a.w, u1.y, u2.y, u3.y);
-  split3(v.b.x, v.b.y, u1.z, u2.z, u3.z);
-  split3(v.b.z, v.b.w, u1.w, u2.w, u3.w);
-  planes[slot] = u1;
-  planes[kPlaneUnits + slot] = u2;
-  planes[2 * kPlaneUnits + slot] = u3;
-}
-
-// K-major tile: mn = global row (128 of them from row0), k = feature (kKC of them from f0).
-// thread -> (k8 = t % 4, mn = t / 4): a warp reads 8 rows x 128 contiguous bytes.
-__device__ __forceinline__ F8 load_kmajor(const float* __restrict__ g, int64_t row0, int64_t row_end, int f0, int f_end,
-                                          int ld, bool vec_ok, bool fast) {
-  const int k8 = threadIdx.x & 3, mn = threadIdx.x >> 2;
-  return load8(g, row0 + mn, row_end, f0 + 8 * k8, f_end, ld, vec_ok, fast);
-}
-__device__ __forceinline__ void store_kmajor(const F8& v, uint4* __restrict__ planes) {
-  const int k8 = threadIdx.x & 3, mn = threadIdx.x >> 2;
-  store_unit(v, planes, k8 * kPitchK + mn);
-}
-// MN-major tile: k = global row (kKC of them from row0), mn = feature (128 of them from f0).
-// thread -> (k = 8 * (warp % 4) + lane % 8, mn8 = 4 * (warp / 4) + lane / 8): a quarter warp stores one core matrix.
-__device__ __forceinline__ void mn_coords(int& k, int& mn8) {
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  k = 8 * (warp & 3) + (lane & 7);
-  mn8 = 4 * (warp >> 2) + (lane >> 3);
-}
-__device__ __forceinline__ F8 load_mnmajor(const float* __restrict__ g, int64_t row0, int64_t row_end, int f0, int f_end,
-                                           int ld, bool vec_ok, bool fast) {
-  int k, mn8;
-  mn_coords(k, mn8);
-  return load8(g, row0 + k, row_end, f0 + 8 * mn8, f_end, ld, vec_ok, fast);
-}
-__device__ __forceinline__ void store_mnmajor(const F8& v, uint4* __restrict__ planes) {
-  int k, mn8;
-  mn_coords(k, mn8);
-  store_unit(v, planes, mn8 * kKC + k);
-}
 
 // One CTA = one 128-row output tile (NN / NT) or one (128-feature tile, split of the rows) (TN).
 // (bx, by, bz) are the tile coordinates (blockIdx of the single-problem kernel; looked up per problem by the grouped
@@ -208,6 +62,7 @@ dense_tc_body(const float* __restrict__ A, const float* __restrict__ B, int64_t 
   const int64_t row_end = (OP == kTN) ? min(M, row_beg + rows_per_split) : 0;
   const int64_t red_len = (OP == kNN) ? K : (OP == kNT ? U : (row_end > row_beg ? row_end - row_beg : 0));
 
+  TL(0);
   if (warp == kThreads / 32) {                                   // four accumulators of kMaxN columns each
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)),
                  "r"(static_cast<uint32_t>(kTmemCols))
@@ -257,25 +112,25 @@ dense_tc_body(const float* __restrict__ A, const float* __restrict__ B, int64_t 
     else vb = load_mnmajor(B, row_beg + k0, row_end, n0, U, U, vec_b, in_b && in_k);
   };
   const int nchunk = static_cast<int>((red_len + kKC - 1) / kKC);
-  // Short reductions (nchunk <= kStages, i.e. K <= 128: every Dense of SchNet / PaiNN) issue the loads of their whole
-  // A tile and of the first two B chunks up front (B chunks 2, 3 follow as soon as a register set is free: B is the
-  // L2-resident operand) and drain their per-chunk accumulators once at the end, so no fp32 accumulator registers
-  // are live while the loads are in flight; long reductions run two register sets ahead of the stores.
+  // Short reductions (nchunk <= kStages, i.e. K <= 128: every Dense of SchNet / PaiNN) issue the loads of three A
+  // chunks and two B chunks up front (40 registers in flight; the 96-register budget of a 544-thread CTA spills
+  // beyond that) and the rest as soon as a register set is free, and drain their per-chunk accumulators once at the
+  // end, so no fp32 accumulator registers are live while the loads are in flight; long reductions run two register
+  // sets ahead of the stores.
   static_assert(kStages == 4 && kStages * kMaxN == kTmemCols, "four named register sets / accumulators below");
   const bool short_k = nchunk <= kStages;                // CTA-uniform
-  F8 va0, vb0, va1, vb1, va2, va3;
+  F8 va0, vb0, va1, vb1, va2;
   if (warp < kThreads / 32) {
     if (nchunk > 0) load_chunk(0, va0, vb0);
     if (nchunk > 1) load_chunk(kKC, va1, vb1);
-    if (short_k) {
-      if (nchunk > 2) load_chunk_a(2 * kKC, va2);
-      if (nchunk > 3) load_chunk_a(3 * kKC, va3);
-    }
+    if (short_k && nchunk > 2) load_chunk_a(2 * kKC, va2);
   }
+  TL(1);
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem_d = tmem_base_s;
+  TL(2);
 
   // fp32 (round-to-nearest) running sum of the drained per-chunk accumulators
   float racc[32];
@@ -324,6 +179,7 @@ dense_tc_body(const float* __restrict__ A, const float* __restrict__ B, int64_t 
       const int st = c % kStages;
       mbar_wait(smem_u32(&full[st]), static_cast<uint32_t>((c / kStages) & 1));
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      if (c < 4) TL(20 + 2 * c);
       if (lane == 0) {
         const uint32_t base = smem_u32(planes + static_cast<size_t>(st) * kStageUnits) >> 4;
         const uint64_t a1 = da_hi | (base & 0x3FFF), a2 = a1 + kPlaneUnits, a3 = a2 + kPlaneUnits;
@@ -358,6 +214,7 @@ dense_tc_body(const float* __restrict__ A, const float* __restrict__ B, int64_t 
                          smem_u32(&mbar[st]))
                      : "memory");
       }
+      if (c < 4) TL(21 + 2 * c);
       __syncwarp();
     }
   } else {
@@ -381,15 +238,24 @@ dense_tc_body(const float* __restrict__ A, const float* __restrict__ B, int64_t 
         asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&full[c % kStages])) : "memory");
     };
     if (short_k) {
-      if (nchunk > 0) { stage(0, va0, vb0); if (nchunk > 2) load_chunk_b(2 * kKC, vb0); publish(0); }
-      if (nchunk > 1) { stage(1, va1, vb1); if (nchunk > 3) load_chunk_b(3 * kKC, vb1); publish(1); }
-      if (nchunk > 2) { stage(2, va2, vb0); publish(2); }
-      if (nchunk > 3) { stage(3, va3, vb1); publish(3); }
+      if (nchunk > 0) {
+        stage(0, va0, vb0);
+        TL(3);
+        if (nchunk > 2) load_chunk_b(2 * kKC, vb0);
+        if (nchunk > 3) load_chunk_a(3 * kKC, va0);
+        publish(0);
+        TL(4);
+      }
+      if (nchunk > 1) { stage(1, va1, vb1); if (nchunk > 3) load_chunk_b(3 * kKC, vb1); publish(1); TL(5); }
+      if (nchunk > 2) { stage(2, va2, vb0); publish(2); TL(6); }
+      if (nchunk > 3) { stage(3, va0, vb1); publish(3); TL(7); }
       for (int c = 0; c < nchunk; ++c) {                   // accumulator c holds chunk c: fp32 (RN) sum in registers
         wait_chunk(c);
+        TL(8 + c);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         drain(static_cast<uint32_t>(c * kMaxN));
       }
+      TL(12);
     } else {
       auto step = [&](int c, F8& ra, F8& rb) {
         if (c >= kStages) wait_chunk(c - kStages);         // the MMAs that read this stage are done
@@ -413,53 +279,74 @@ dense_tc_body(const float* __restrict__ A, const float* __restrict__ B, int64_t 
     }
   }
 
-  // ---- epilogue: TMEM lane 32*(warp%4) + lane = output row; warps 0-3 take the even 32-column groups, 4-7 the odd ----
+  // ---- epilogue: TMEM lane 32*(warp%4) + lane = output row; warp w holds columns 32*(w/4)..+31 of its 32 rows ----
   // The accumulator registers hold one output ROW per lane (TMEM lane = row).  Writing them straight out would make
-  // every store instruction touch 32 different rows with 16 bytes each; instead the tile goes through shared memory
-  // (the operand stages are free: the last MMAs have completed) and leaves as full 512-byte row segments.
+  // every store instruction touch 32 different rows with 16 bytes each; instead the tile (+ bias, and f(pre) beside
+  // it for the fused activation) goes through shared memory (the operand stages are free: the last MMAs have
+  // completed) and leaves as one bulk asynchronous copy (TMA engine) per 512-byte row.
   const int d_row = 32 * (warp & 3) + lane;
-  constexpr int OP_PITCH = kMaxN + 4;                              // floats; +4 keeps float4 alignment, spreads banks
+  constexpr int OP_PITCH = kMaxN + 4;                              // floats; +4 keeps 16-byte alignment, spreads banks
   float* otile = reinterpret_cast<float*>(smem_raw);               // [kBM][OP_PITCH] = 67.6 KB
+  float* atile = otile + kBM * OP_PITCH;                           // f(pre) tile of the fused activation
+  static_assert(kSmemBytesDecl >= 2 * kBM * OP_PITCH * sizeof(float), "two epilogue tiles fit in the stages");
   if (warp < kThreads / 32) {
+    const bool with_act = (OP == kNN) && act_out != nullptr;
     if (c0 < nt) {
 #pragma unroll
-      for (int i = 0; i < 32; i += 4)
-        *reinterpret_cast<float4*>(otile + d_row * OP_PITCH + c0 + i) =
-            make_float4(racc[i], racc[i + 1], racc[i + 2], racc[i + 3]);
+      for (int i = 0; i < 32; i += 4) {
+        float4 v = make_float4(racc[i], racc[i + 1], racc[i + 2], racc[i + 3]);
+        if (OP == kNN && bias) {                                   // scalar loads: the bias may be an unaligned view
+          const int col = n0 + c0 + i;
+          if (col + 0 < n_total) v.x += __ldg(bias + col + 0);
+          if (col + 1 < n_total) v.y += __ldg(bias + col + 1);
+          if (col + 2 < n_total) v.z += __ldg(bias + col + 2);
+          if (col + 3 < n_total) v.w += __ldg(bias + col + 3);
+        }
+        *reinterpret_cast<float4*>(otile + d_row * OP_PITCH + c0 + i) = v;
+        if (with_act)       // Dense + activation in one pass: pre (kept for the derivatives) and f(pre)
+          *reinterpret_cast<float4*>(atile + d_row * OP_PITCH + c0 + i) =
+              make_float4(act_value(act, v.x), act_value(act, v.y), act_value(act, v.z), act_value(act, v.w));
+      }
     }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy stores -> async proxy (bulk copy)
     asm volatile("bar.sync 1, %0;" ::"r"(kThreads) : "memory");    // staging warps only
+    TL(13);
     const int64_t out_rows = (OP == kTN) ? K : M;                  // rows of the output matrix this tile maps to
     const int64_t row_base = (OP == kTN) ? a0 : m0;
     float* obase = (OP == kTN) ? out + static_cast<int64_t>(bz) * K * U : out;
-    const bool vec_out = (n_total % 4 == 0) && ((reinterpret_cast<uintptr_t>(out) & 15) == 0);
-    const int col = n0 + 4 * lane;                                 // this lane's 4 columns of every row
-    float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (OP == kNN && bias) {                                       // scalar loads: the bias may be an unaligned view
-      if (col + 0 < n_total) bv.x = __ldg(bias + col + 0);
-      if (col + 1 < n_total) bv.y = __ldg(bias + col + 1);
-      if (col + 2 < n_total) bv.z = __ldg(bias + col + 2);
-      if (col + 3 < n_total) bv.w = __ldg(bias + col + 3);
-    }
-    for (int r = warp; r < kBM; r += kThreads / 32) {              // one full row segment per warp instruction
-      const int64_t row = row_base + r;
-      if (row >= out_rows || 4 * lane >= nt) continue;
-      float4 v = *reinterpret_cast<const float4*>(otile + r * OP_PITCH + 4 * lane);
-      v.x += bv.x; v.y += bv.y; v.z += bv.z; v.w += bv.w;
-      float* o = obase + row * n_total + col;
-      if (vec_out && col + 3 < n_total) *reinterpret_cast<float4*>(o) = v;
-      else {
+    const int ncols = min(nt, n_total - n0);                       // valid columns of this tile
+    const bool bulk_ok = (n_total % 4 == 0) && (ncols % 4 == 0) && ((reinterpret_cast<uintptr_t>(obase) & 15) == 0) &&
+                         (!with_act || (reinterpret_cast<uintptr_t>(act_out) & 15) == 0);
+    if (bulk_ok) {
+      if (threadIdx.x < kBM && row_base + threadIdx.x < out_rows) {
+        const int r = threadIdx.x;
+        const uint32_t bytes = static_cast<uint32_t>(ncols) * 4u;
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(
+                         obase + (row_base + r) * n_total + n0),
+                     "r"(smem_u32(otile + r * OP_PITCH)), "r"(bytes)
+                     : "memory");
+        if (with_act)
+          asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(
+                           act_out + (row_base + r) * n_total + n0),
+                       "r"(smem_u32(atile + r * OP_PITCH)), "r"(bytes)
+                       : "memory");
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");     // shared memory is released below
+      }
+    } else {                                                       // unaligned / ragged widths: per-element stores
+      const int col = n0 + 4 * lane;                               // this lane's 4 columns of every row
+      for (int r = warp; r < kBM; r += kThreads / 32) {
+        const int64_t row = row_base + r;
+        if (row >= out_rows || 4 * lane >= nt) continue;
+        const float4 v = *reinterpret_cast<const float4*>(otile + r * OP_PITCH + 4 * lane);
+        float* o = obase + row * n_total + col;
         if (col + 0 < n_total) o[0] = v.x;
         if (col + 1 < n_total) o[1] = v.y;
         if (col + 2 < n_total) o[2] = v.z;
         if (col + 3 < n_total) o[3] = v.w;
-      }
-      if (OP == kNN && act_out) {          // Dense + activation in one pass: pre (kept for the derivatives) and f(pre)
-        const float4 f = make_float4(act_value(act, v.x), act_value(act, v.y), act_value(act, v.z),
-                                     act_value(act, v.w));
-        float* q = act_out + row * n_total + col;
-        if (vec_out && ((reinterpret_cast<uintptr_t>(act_out) & 15) == 0) && col + 3 < n_total)
-          *reinterpret_cast<float4*>(q) = f;
-        else {
+        if (with_act) {
+          const float4 f = *reinterpret_cast<const float4*>(atile + r * OP_PITCH + 4 * lane);
+          float* q = act_out + row * n_total + col;
           if (col + 0 < n_total) q[0] = f.x;
           if (col + 1 < n_total) q[1] = f.y;
           if (col + 2 < n_total) q[2] = f.z;
@@ -486,8 +373,10 @@ dense_tc_body(const float* __restrict__ A, const float* __restrict__ B, int64_t 
       if (f < nt && n0 + f < U) colsum_part[static_cast<int64_t>(bz) * U + n0 + f] = t;
     }
   }
+  TL(14);
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
+  TL(15);
   if (warp == kThreads / 32) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d),
                  "r"(static_cast<uint32_t>(kTmemCols))
@@ -608,8 +497,7 @@ tn_grouped_reduce_kernel(const __grid_constant__ TnGroup grp, const float* __res
   *dst = acc;
 }
 
-constexpr size_t kSmemBytes = static_cast<size_t>(kStages) * kStageUnits * sizeof(uint4);   // 4 stages x 6 planes x 8.1 KB
-static_assert(kSmemBytes >= static_cast<size_t>(kBM) * (kMaxN + 4) * sizeof(float), "epilogue tile fits in the stages");
+constexpr size_t kSmemBytes = kSmemBytesDecl;
 
 inline int tn_splits(int64_t M, int K, int U) {
   const int tiles = ceil_div(K, kBM) * ceil_div(U, kMaxN);
@@ -653,6 +541,8 @@ static int dense_tc_launch(int op, const float* A, const float* B, int64_t M, in
     return KGCNN_OK;
   }
   if (!A || !B) return KGCNN_E_INVALID;
+  // every Dense of SchNet / PaiNN: the compact aligned kernel (dense_fast.cu); everything else: the general one
+  if (op != tc::kTN && tc::dense_fast_try_launch(op, A, B, M, K, U, bias, out, act_out, act, st)) return finish_launch();
   auto al16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
   static PerDeviceOnce attr;
   attr.run([] {

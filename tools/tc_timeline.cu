@@ -1,0 +1,35 @@
+// Timeline probe of one Dense tile (diagnostics): clock64 stamps of CTA 0 of dense_tc_kernel.
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 --expt-relaxed-constexpr -o tools/tc_timeline tools/tc_timeline.cu
+#define KGCNN_TC_TIMELINE 1
+#include <cstdio>
+#include <vector>
+namespace kgcnn { void count_launch(int) {} }
+#include "../gcnn_keras_b200/csrc/dense_tc.cu"
+#include "../gcnn_keras_b200/csrc/dense_fast.cu"
+extern "C" const char* kgcnn_error_string(int) { return ""; }
+
+int main(int argc, char** argv) {
+  const int64_t M = argc > 1 ? atoll(argv[1]) : 18432;
+  const int K = 128, U = 128;
+  float *x, *w, *b, *y, *y2;
+  cudaMalloc(&x, M * K * 4); cudaMalloc(&w, K * U * 4); cudaMalloc(&b, U * 4); cudaMalloc(&y, M * U * 4); cudaMalloc(&y2, M * U * 4);
+  cudaMemset(x, 0, M * K * 4); cudaMemset(w, 0, K * U * 4); cudaMemset(b, 0, U * 4);
+  const char* names[3] = {"NN", "NT", "NN+act"};
+  for (int mode = 0; mode < 3; ++mode) {
+    for (int rep = 0; rep < 5; ++rep) {
+      if (mode == 0) kgcnn_dense_tc(0, x, w, M, K, U, b, y, nullptr, 0, nullptr);
+      if (mode == 1) kgcnn_dense_tc(1, x, w, M, K, U, nullptr, y, nullptr, 0, nullptr);
+      if (mode == 2) kgcnn_dense_act(x, w, M, K, U, b, 1, y, y2, nullptr);
+    }
+    cudaError_t e = cudaDeviceSynchronize();
+    long long t[64];
+    cudaMemcpyFromSymbol(t, kgcnn::tc::g_timeline, sizeof(t));
+    printf("%s M=%lld (%s): cycles since kernel entry (staging thread 0 / MMA lane 0)\n", names[mode], (long long)M, cudaGetErrorString(e));
+    const char* lab[] = {"entry", "loads issued", "after sync (tmem)", "stage0 stored", "publish0", "publish1", "publish2", "publish3",
+                         "mma0 done", "mma1 done", "mma2 done", "mma3 done", "drained", "epi tile sync", "stores done", "end sync"};
+    for (int i = 0; i < 16; ++i) printf("  %-20s %7lld\n", lab[i], t[i] - t[0]);
+    printf("  barrier init done %7lld   tmem alloc done (mma warp) %7lld   pointers ready %7lld  row known %7lld  pa known %7lld\n", t[16] - t[0], t[17] - t[0], t[18] - t[0], t[19] - t[0], t[30] - t[0]);
+    for (int c = 0; c < 4; ++c) printf("  mma warp chunk %d: full seen %7lld  issued %7lld\n", c, t[20 + 2 * c] - t[0], t[21 + 2 * c] - t[0]);
+  }
+  return 0;
+}
