@@ -255,13 +255,12 @@ def run_gss(args, rank, world, device):
                    "parallelism": "graphs sharded across %d rank(s), no data-path collective" % world},
         "hbm_gbs_algorithmic": alg_bytes / (ms_step * 1e-3) / 1e9,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": 747.6e6,   # ncu --set full: dram read 0.446 GB + write 0.301 GB per launch (profiles/r1_gms_full_v5.csv)
+                     "traffic": profile_traffic(GMS_PROFILE, "gms_kernel", 6, 2),
                      "kernel": "gms_kernel<float4,8,2,SumW0,gather>",
                      "algorithmic_bytes_per_launch": alg_bytes / n_kernel_launches, "peak_source": peak_src,
                      "note": "algorithmic bytes count every gathered row (no cache credit, SURVEY 8d); E/N = 20, so "
-                             "19 of 20 row reads hit L1/L2 and the real DRAM traffic is 0.75 GB per launch: frac > 1 "
-                             "is cache reuse, not skipped work. The HBM-bound shapes are GSS-R (default bench "
-                             "line's roofline) and --workload gcn"},
+                             "19 of 20 row reads hit L1/L2: frac > 1 is cache reuse (on-chip gather throughput), not an "
+                             "HBM number. The HBM-bound shapes are in the default bench line's roofline block"},
         "e2e": {"value": total_edges / (ms_e2e * 1e-3), "unit": "edges/s", "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e},
         "gpu_launches": launches_per_step * args.steps,
@@ -365,32 +364,51 @@ def timed_steps_with_l2_flush(step_fn, steps, warmup, world, device):
     return max_over_ranks(ms, world, device) / steps, clocks.summary()
 
 
-def _time_gms_pair(x, dy, recv, send, iters):
-    from gcnn_keras_b200 import functional as F
+def _time(fn, iters):
     for _ in range(3):
-        F.raw_gms(x, None, recv, send)
-        F.raw_gms(dy, None, send, recv)
+        fn()
     torch.cuda.synchronize()
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     a.record()
     for _ in range(iters):
-        F.raw_gms(x, None, recv, send)        # forward  (receiver CSR)
-        F.raw_gms(dy, None, send, recv)       # backward (same kernel on the sender CSC)
+        fn()
     b.record()
     torch.cuda.synchronize()
-    return a.elapsed_time(b) / (2 * iters)
+    return a.elapsed_time(b) / iters
 
 
-def gss_roofline(device, iters=10):
-    """The north-star kernel (fused gather -> CSR segment-sum) timed alone, forward + backward launches, on
-      GSS-R: N = 2 M nodes, 16 uniformly random senders per receiver, F = 128 (1 GB of features, every gathered row
-             comes from DRAM: algorithmic bytes ~ real traffic) -> the HBM roofline fraction;
-      GSS-L: C1 pattern x 65 536 graphs, F = 64 (gathered rows hit in L1/L2) -> reported beside it."""
+def profile_traffic(csv_name, kernel_substr, skip=0, count=None):
+    """DRAM bytes per launch (read + write, mean over the matching rows) of a COMMITTED ncu summary under profiles/
+    (written by profiles/summarize.py from an `ncu --set full` capture of tools/ncu_gms.py).  None if absent."""
+    import csv
+    path = os.path.join(ROOT, "profiles", csv_name)
+    if not os.path.exists(path):
+        return None
+    with open(path) as fh:
+        rows = list(csv.reader(fh))
+    hdr = rows[0]
+    try:
+        i_r = next(i for i, h in enumerate(hdr) if h.startswith("dram__bytes_read.sum"))
+        i_w = next(i for i, h in enumerate(hdr) if h.startswith("dram__bytes_write.sum"))
+    except StopIteration:
+        return None
+    scale = lambda h: {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}.get(h.split("[")[-1].rstrip("]"), 1.0)
+    sel = [r for r in rows[1:] if kernel_substr in r[0]][skip:]
+    sel = sel[:count] if count else sel
+    if not sel:
+        return None
+    return sum(float(r[i_r]) * scale(hdr[i_r]) + float(r[i_w]) * scale(hdr[i_w]) for r in sel) / len(sel)
+
+
+def roofline_shapes(device):
+    """Generator over the measured shapes of the north-star kernel family: (key, workload text, kernel text,
+    algorithmic bytes, edges, [launch callables]).  Used by gss_roofline (timing) and tools/ncu_gms.py (one launch of
+    each callable, in this order, under ncu -> profiles/r2_gms_full.csv)."""
     from gcnn_keras_b200 import RaggedTensor
+    from gcnn_keras_b200 import functional as F
     from gcnn_keras_b200.plan import Relation, get_plan
-    peak, peak_src = measured_peaks()
-    # ---- GSS-R ----
     rng = np.random.default_rng(0)
+    # ---- plain, GSS-R ----
     n, deg, feat = 2_000_000, 16, 128
     recv_r = torch.from_numpy(np.repeat(np.arange(n, dtype=np.int32), deg)).to(device)
     send_r = torch.from_numpy(rng.integers(0, n, size=n * deg, dtype=np.int32)).to(device)
@@ -398,12 +416,46 @@ def gss_roofline(device, iters=10):
     r_recv.rowptr, r_send.rowptr, r_send.permuted_ids(r_recv)
     x = torch.randn(n, feat, device=device)
     dy = torch.randn(n, feat, device=device)
-    ms_r = _time_gms_pair(x, dy, r_recv, r_send, iters)
-    e_r = n * deg
-    bytes_r = gss_bytes(e_r, n, feat) / 2
-    ach_r = bytes_r / (ms_r * 1e-3) / 1e9
+    yield ("plain", "GSS-R (N=%d, E=%d uniform random senders, F=%d): gathered rows miss L2" % (n, n * deg, feat),
+           "gms_kernel (gather -> CSR segment-sum), forward + backward launch", gss_bytes(n * deg, n, feat), n * deg,
+           [lambda: F.raw_gms(x, None, r_recv, r_send), lambda: F.raw_gms(dy, None, r_send, r_recv)])
     del x, dy, r_recv, r_send, recv_r, send_r
-    # ---- GSS-L ----
+    # ---- weighted (cfconv) ----
+    n, deg, feat = 1_000_000, 16, 128
+    e_w = n * deg
+    recv_w = torch.from_numpy(np.repeat(np.arange(n, dtype=np.int32), deg)).to(device)
+    send_w = torch.from_numpy(rng.integers(0, n, size=e_w, dtype=np.int32)).to(device)
+    w_recv, w_send = Relation(recv_w, n, is_sorted=True), Relation(send_w, n)
+    w_recv.rowptr, w_send.rowptr, w_send.permuted_ids(w_recv)
+    x = torch.randn(n, feat, device=device)
+    dy = torch.randn(n, feat, device=device)
+    w = torch.randn(e_w, feat, device=device)
+    yield ("weighted", "cfconv variant (N=%d, E=%d, F=%d, w [E,F]): y = sum w*x[s], dx, dw" % (n, e_w, feat),
+           "gms_kernel (w [E,F]) forward + transposed, gather2_mul_kernel (dw)",
+           20 * e_w * feat + 12 * n * feat + 12 * e_w + 8 * n, e_w,
+           [lambda: F.raw_gms(x, w, w_recv, w_send), lambda: F.raw_gms(dy, w, w_send, w_recv),
+            lambda: F.raw_g2m(x, w_send.ids, dy, w_recv.ids, e_w, False)])
+    del x, dy, w, w_recv, w_send, recv_w, send_w
+    # ---- GSS-G: one C5 shard ----
+    n_src, n_dst, e_g, feat = 2_000_000, 250_000, 7_500_000, 128
+    deg_g = e_g // n_dst
+    recv_g = torch.from_numpy(np.repeat(np.arange(n_dst, dtype=np.int32), deg_g)).to(device)
+    base = np.repeat(np.arange(n_dst, dtype=np.int64), deg_g)
+    local = rng.random(e_g) < 0.8
+    send_np = np.where(local, np.mod(base + rng.integers(-50000, 50001, size=e_g), n_src),
+                       rng.integers(0, n_src, size=e_g))
+    send_g = torch.from_numpy(send_np.astype(np.int32)).to(device)
+    g_recv, g_send = Relation(recv_g, n_dst, is_sorted=True), Relation(send_g, n_src)
+    g_recv.rowptr, g_send.rowptr, g_send.permuted_ids(g_recv)
+    x = torch.randn(n_src, feat, device=device)
+    dy = torch.randn(n_dst, feat, device=device)
+    w1 = torch.rand(e_g, 1, device=device)
+    yield ("gss_g", "GSS-G, one C5 shard (N_src=%d, N_dst=%d, E=%d, F=%d, w [E,1])" % (n_src, n_dst, e_g, feat),
+           "gms_kernel (w [E,1]) forward on the receiver CSR + backward on the sender CSC",
+           8 * e_g * feat + 4 * (n_src + n_dst) * feat + 16 * e_g + 4 * (n_src + n_dst), e_g,
+           [lambda: F.raw_gms(x, w1, g_recv, g_send), lambda: F.raw_gms(dy, w1, g_send, g_recv)])
+    del x, dy, w1, g_recv, g_send, recv_g, send_g
+    # ---- GSS-L: served by L1/L2 ----
     x_h, idx_h, ns_h, es_h = gss_inputs(65536, feat=64, seed=0)
     N, E = x_h.shape[0], idx_h.shape[0]
     x = torch.from_numpy(x_h).to(device)
@@ -412,26 +464,54 @@ def gss_roofline(device, iters=10):
     plan = get_plan(index, nodes)
     recv, send = plan.relation(0), plan.relation(1)
     recv.rowptr, send.rowptr, send.permuted_ids(recv)
-    ms_l = _time_gms_pair(x, torch.randn(N, 64, device=device), recv, send, iters)
-    bytes_l = gss_bytes(E, N, 64) / 2
-    ach_l = bytes_l / (ms_l * 1e-3) / 1e9
-    return {"bound": "hbm", "achieved": ach_r, "peak": peak, "unit": "GB/s", "frac": ach_r / peak,
-            "traffic": 16.29e9,   # ncu --set full: dram read 15.27 GB + write 1.02 GB per launch (profiles/r1_gms_full_v3.csv)
-            "kernel": "gms_kernel (fused gather*w -> CSR segment-sum), mean of the fwd and bwd launch",
-            "workload": "GSS-R (N=%d, E=%d uniform random senders, F=%d): gathered rows miss L2" % (n, e_r, feat),
-            "algorithmic_bytes_per_launch": bytes_r, "ms_per_launch": ms_r, "peak_source": peak_src,
-            "edges_per_s": e_r / (2 * ms_r * 1e-3),
-            "frac_on_traffic": 16.29e9 / (ms_r * 1e-3) / 1e9 / peak,
-            "note": "achieved = algorithmic bytes (every gathered row counted, SURVEY 8d) / launch time; the ncu DRAM "
-                    "traffic is 7 % below the algorithmic bytes (the 126 MB L2 serves part of the 1 GB of gathered "
-                    "rows), so frac can touch 1.0 while frac_on_traffic (real DRAM bytes / time / peak) is ~0.93",
-            "cached_shape": {"workload": "GSS-L (N=%d, E=%d, F=64, C1 pattern x 65536 graphs)" % (N, E),
-                             "achieved": ach_l, "frac": ach_l / peak, "ms_per_launch": ms_l,
-                             "algorithmic_bytes_per_launch": bytes_l, "traffic": 752.2e6,
-                             "edges_per_s": E / (2 * ms_l * 1e-3),
-                             "note": "algorithmic bytes count every gathered row (no cache credit, SURVEY 8d); ncu "
-                                     "DRAM traffic is 0.75 GB per launch because the rows hit in L1/L2, so frac > 1 "
-                                     "here is cache reuse, not skipped work"}}
+    dyl = torch.randn(N, 64, device=device)
+    yield ("cached_shape", "GSS-L (N=%d, E=%d, F=64, C1 pattern x 65536 graphs)" % (N, E),
+           "gms_kernel, forward + backward launch", gss_bytes(E, N, 64), E,
+           [lambda: F.raw_gms(x, None, recv, send), lambda: F.raw_gms(dyl, None, send, recv)])
+
+
+GMS_PROFILE = "r2_gms_full.csv"     # ncu --set full of tools/ncu_gms.py on the final build (rows in launch order)
+_PROFILE_ROWS = {"plain": [("gms_kernel", 0, 2)], "weighted": [("gms_kernel", 2, 2), ("gather2_mul", 0, 1)],
+                 "gss_g": [("gms_kernel", 4, 2)], "cached_shape": [("gms_kernel", 6, 2)]}
+
+
+def gss_roofline(device, iters=10):
+    """The north-star kernel family (fused gather [* w] -> CSR segment-sum and its two VJPs) timed alone against the
+    measured HBM copy peak, on the three HBM-bound shapes of SURVEY.md 8(d) (plain GSS-R; the cfconv variant with
+    w [E, F]: forward, dx, dw = B_cfconv; GSS-G = one C5 shard, B_gcn) and on GSS-L, whose gathered rows are served by
+    L1/L2 and which is therefore reported as on-chip throughput, not as an HBM fraction.  `traffic` = DRAM bytes of
+    the same launches from the committed ncu capture (profiles/r2_gms_full.csv), summed over the launches."""
+    peak, peak_src = measured_peaks()
+    out = {}
+    for key, workload, kernel, alg_bytes, edges, fns in roofline_shapes(device):
+        ms = _time(lambda: [f() for f in fns], iters if key != "weighted" else max(3, iters // 2))
+        parts = [profile_traffic(GMS_PROFILE, k, sk, cnt) for k, sk, cnt in _PROFILE_ROWS[key]]
+        traffic = None if any(p is None for p in parts) else sum(
+            p * cnt for p, (_, _, cnt) in zip(parts, _PROFILE_ROWS[key]))
+        ach = alg_bytes / (ms * 1e-3) / 1e9
+        if key == "cached_shape":
+            out[key] = {"bound": "l2", "workload": workload, "kernel": kernel, "on_chip_throughput_GBps": ach,
+                        "ms": ms, "launches": len(fns), "edges_per_s": edges / (ms * 1e-3),
+                        "algorithmic_bytes": alg_bytes, "traffic": traffic,
+                        "note": "E/N = 20 and the 20 senders of a receiver sit in its own graph: 19 of 20 row reads "
+                                "hit L1/L2, so this shape measures on-chip gather throughput, not an HBM fraction"}
+            continue
+        e = {"bound": "hbm", "workload": workload, "kernel": kernel, "achieved": ach, "peak": peak, "unit": "GB/s",
+             "frac": ach / peak, "algorithmic_bytes": alg_bytes, "ms": ms, "launches": len(fns),
+             "edges_per_s": edges / (ms * 1e-3), "traffic": traffic,
+             "frac_on_traffic": None if traffic is None else traffic / (ms * 1e-3) / 1e9 / peak,
+             "traffic_source": ("profiles/" + GMS_PROFILE) if traffic is not None else None, "peak_source": peak_src,
+             "algorithmic_bytes_per_launch": alg_bytes / len(fns), "ms_per_launch": ms / len(fns),
+             "traffic_per_launch": None if traffic is None else traffic / len(fns)}
+        if key == "plain":
+            out.update(e)
+        else:
+            out[key] = e
+    out["kernel_family"] = "gms_kernel / gather2_mul_kernel (csrc/segment_impl.cuh, csrc/gather.cu)"
+    out["note"] = ("achieved = algorithmic bytes of SURVEY 8(d) (every gathered row counted, no cache credit) / time of "
+                   "the launches; traffic = measured DRAM bytes of the same launches (ncu), so frac_on_traffic is the "
+                   "fraction of the HBM peak the kernels actually drive")
+    return out
 
 
 def build_painn(device, batch, seed):
@@ -513,6 +593,30 @@ def run_force(args, rank, world, device, kind):
     if rank == 0 and not args.no_roofline:
         line["roofline"] = gss_roofline(device)
     return line
+
+
+def other_workloads(args, rank, world, device):
+    """The other BASELINE configurations at this GPU count, a few steps each, so that the driver's BENCH / SCALE
+    records carry them too: C3 PaiNN and C4 HDNNP2nd training steps (molecules/s) and the C5 GCN layer (ms/step)."""
+    import argparse as _ap
+    import gc
+    out = {}
+    for kind in ("painn", "hdnnp", "gcn"):
+        sub = _ap.Namespace(**vars(args))
+        sub.steps, sub.warmup, sub.batch, sub.no_roofline, sub.workload = 3, 3, 0, True, kind
+        try:
+            res = run_gcn(sub, rank, world, device) if kind == "gcn" else run_force(sub, rank, world, device, kind)
+            keep = {k: res[k] for k in ("metric", "value", "unit", "ms_per_step", "scaling", "steps", "warmup") if k in res}
+            keep["workload"] = res["config"]["workload"]
+            keep["e2e"] = {k: res["e2e"][k] for k in ("value", "unit", "ms_per_step") if k in res["e2e"]}
+            if kind == "gcn":
+                keep["roofline_frac_algorithmic"] = res["roofline"]["frac"]
+            out[kind] = keep
+        except Exception as exc:                                    # a failure here must not lose the headline line
+            out[kind] = {"error": "%s: %s" % (type(exc).__name__, str(exc)[:200])}
+        gc.collect()
+        torch.cuda.empty_cache()
+    return out
 
 
 # ----------------------------------------------------------------------------------------------------
@@ -690,6 +794,8 @@ def main():
     ap.add_argument("--gcn-feat", type=int, default=128)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
+    ap.add_argument("--no-other-workloads", action="store_true",
+                    help="default schnet line only: skip the short C3 / C4 / C5 runs reported under other_workloads")
     ap.add_argument("--batch", type=int, default=0, help="molecules per GPU (0 = the config's batch size)")
     ap.add_argument("--host-angles", action="store_true",
                     help="hdnnp e2e leg: copy the angle triples from the host instead of building them on the device")
@@ -718,6 +824,11 @@ def main():
         line = run_force(args, rank, world, device, args.workload)
     else:
         line = {"gss": run_gss, "gcn": run_gcn}[args.workload](args, rank, world, device)
+    if args.workload == "schnet" and not args.no_other_workloads:
+        import gc
+        gc.collect()
+        torch.cuda.empty_cache()
+        line["other_workloads"] = other_workloads(args, rank, world, device)
     if rank == 0:
         if world == 1 and not args.no_cpu_baseline:
             cb = {"gss": cpu_baseline_gss, "schnet": cpu_baseline_schnet}.get(args.workload)

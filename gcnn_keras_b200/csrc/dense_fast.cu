@@ -15,7 +15,10 @@
 namespace kgcnn {
 namespace tc {
 
-template <int OP, int ACT>   // ACT < 0: one output; otherwise out = pre, act_out = f_ACT(pre)
+// RAG 0: everything aligned.  RAG 1 (NN): reduction length K arbitrary <= 128, rows of A unaligned (the [E, 20..25]
+// radial-basis inputs of the filter networks): element-wise predicated loads of A, rows of W past K read as zero.
+// RAG 2 (NT): output width K arbitrary (the gradient with respect to that basis): element-wise stores.
+template <int OP, int ACT, int RAG>   // ACT < 0: one output; otherwise out = pre, act_out = f_ACT(pre)
 __global__ void __launch_bounds__(kCtaThreads)
 dense_fast_kernel(const float* __restrict__ A, const float* __restrict__ B, int64_t M, int K, int U,
                   const float* __restrict__ bias, float* __restrict__ out, float* __restrict__ act_out) {
@@ -34,9 +37,9 @@ dense_fast_kernel(const float* __restrict__ A, const float* __restrict__ B, int6
   const int n_total = (OP == kNN) ? U : K;                       // output width
   const int red = (OP == kNN) ? K : U;                           // reduction length = row length of A
   const int n0 = blockIdx.y * kMaxN;
-  const int nt = min(kMaxN, n_total - n0);                       // MMA N (multiple of 16)
+  const int nt = min(kMaxN, (n_total - n0 + 15) / 16 * 16);      // MMA N (multiple of 16; RAG 2: rounded up)
   const int64_t m0 = static_cast<int64_t>(blockIdx.x) * kBM;
-  const int nchunk = red / kKC;                                  // 1 .. 4
+  const int nchunk = (red + kKC - 1) / kKC;                      // 1 .. 4
 
   if (warp == kThreads / 32) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)),
@@ -84,8 +87,33 @@ dense_fast_kernel(const float* __restrict__ A, const float* __restrict__ B, int6
       b_step = kKC / 4;
     }
   }
-  auto ld_a = [&](int c) { F8 v; v.a = __ldg(pa + c * (kKC / 4)); v.b = __ldg(pa + c * (kKC / 4) + 1); return v; };
-  auto ld_b = [&](int c) { F8 v; v.a = __ldg(pb + c * b_step); v.b = __ldg(pb + c * b_step + 1); return v; };
+  auto ld_a = [&](int c) {
+    F8 v;
+    if (RAG == 1) {                                              // unaligned rows, ragged reduction length
+      const float* p = reinterpret_cast<const float*>(pa) + c * kKC;
+      const int f = c * kKC + 8 * (threadIdx.x & 3);
+      float t[8];
+#pragma unroll
+      for (int q = 0; q < 8; ++q) t[q] = (f + q < red) ? __ldg(p + q) : 0.f;
+      v.a = make_float4(t[0], t[1], t[2], t[3]);
+      v.b = make_float4(t[4], t[5], t[6], t[7]);
+    } else {
+      v.a = __ldg(pa + c * (kKC / 4));
+      v.b = __ldg(pa + c * (kKC / 4) + 1);
+    }
+    return v;
+  };
+  auto ld_b = [&](int c) {
+    F8 v;
+    if (RAG == 1 && c * kKC + 8 * (warp & 3) + (lane & 7) >= red) {   // row of W past the reduction length
+      v.a = make_float4(0.f, 0.f, 0.f, 0.f);
+      v.b = v.a;
+    } else {
+      v.a = __ldg(pb + c * b_step);
+      v.b = __ldg(pb + c * b_step + 1);
+    }
+    return v;
+  };
   F8 va0, va1, va2, vb0, vb1;
   TL(18);
   if (warp < kThreads / 32) {
@@ -214,7 +242,14 @@ dense_fast_kernel(const float* __restrict__ A, const float* __restrict__ B, int6
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy stores -> async proxy (bulk copy)
     asm volatile("bar.sync 1, %0;" ::"r"(kThreads) : "memory");    // staging warps only
     TL(13);
-    if (threadIdx.x < kBM && m0 + threadIdx.x < M) {
+    if (RAG == 2) {                                               // ragged output width: element-wise stores
+      const int ncols = min(nt, n_total - n0);
+      for (int r = warp; r < kBM; r += kThreads / 32) {
+        if (m0 + r >= M) break;
+        for (int cidx = lane; cidx < ncols; cidx += 32)
+          out[(m0 + r) * n_total + n0 + cidx] = otile[r * OP_PITCH + cidx];
+      }
+    } else if (threadIdx.x < kBM && m0 + threadIdx.x < M) {
       const int r = threadIdx.x;
       const uint32_t bytes = static_cast<uint32_t>(nt) * 4u;
       asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(out + (m0 + r) * n_total + n0),
@@ -240,17 +275,17 @@ dense_fast_kernel(const float* __restrict__ A, const float* __restrict__ B, int6
   }
 }
 
-template <int OP, int ACT>
+template <int OP, int ACT, int RAG = 0>
 static void launch_fast(const float* A, const float* B, int64_t M, int K, int U, const float* bias, float* out,
                         float* act_out, cudaStream_t st) {
   static PerDeviceOnce attr;
   attr.run([] {
-    cudaFuncSetAttribute(dense_fast_kernel<OP, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaFuncSetAttribute(dense_fast_kernel<OP, ACT, RAG>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                          static_cast<int>(kSmemBytesDecl));
   });
   const int n_total = (OP == kNN) ? U : K;
   dim3 grid(static_cast<unsigned>(ceil_div<int64_t>(M, kBM)), ceil_div(n_total, kMaxN));
-  dense_fast_kernel<OP, ACT><<<grid, kCtaThreads, kSmemBytesDecl, st>>>(A, B, M, K, U, bias, out, act_out);
+  dense_fast_kernel<OP, ACT, RAG><<<grid, kCtaThreads, kSmemBytesDecl, st>>>(A, B, M, K, U, bias, out, act_out);
 }
 
 bool dense_fast_try_launch(int op, const float* A, const float* B, int64_t M, int K, int U, const float* bias,
@@ -258,8 +293,19 @@ bool dense_fast_try_launch(int op, const float* A, const float* B, int64_t M, in
   if (op != kNN && op != kNT) return false;
   const int red = (op == kNN) ? K : U, n_total = (op == kNN) ? U : K;
   auto al16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
-  if (M < 1 || red % kKC != 0 || red > kStages * kKC || n_total % 16 != 0 || U % 4 != 0) return false;
-  if (!al16(A) || !al16(B) || !al16(out) || (bias && !al16(bias)) || (act_out && !al16(act_out))) return false;
+  if (M < 1 || red > kStages * kKC || U % 4 != 0 || !al16(B)) return false;
+  if (op == kNN && (red % kKC != 0 || !al16(A))) {          // ragged reduction (radial-basis inputs, K = 20 .. 25)
+    if (n_total % 16 != 0 || !al16(out) || act_out) return false;
+    launch_fast<kNN, -1, 1>(A, B, M, K, U, bias, out, nullptr, st);
+    return true;
+  }
+  if (op == kNT && (n_total % 16 != 0 || !al16(out))) {     // ragged output width (gradient of those inputs)
+    if (red % kKC != 0 || !al16(A)) return false;
+    launch_fast<kNT, -1, 2>(A, B, M, K, U, nullptr, out, nullptr, st);
+    return true;
+  }
+  if (red % kKC != 0 || n_total % 16 != 0) return false;
+  if (!al16(A) || !al16(out) || (bias && !al16(bias)) || (act_out && !al16(act_out))) return false;
   if (op == kNT) {
     launch_fast<kNT, -1>(A, B, M, K, U, nullptr, out, nullptr, st);
     return true;

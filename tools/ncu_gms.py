@@ -1,6 +1,8 @@
-"""Runs the north-star kernel (fused gather -> CSR segment-sum) a few times on GSS-R and GSS-L for an
-`ncu --set full -k regex:gms` capture (profiling helper, never a bench number).
-    ncu --set full --clock-control none --import-source on -k regex:gms -c 4 -o gpurun_out/gms python tools/ncu_gms.py
+"""One launch of every kernel of the roofline block (bench.roofline_shapes: plain GSS-R, cfconv variant, GSS-G, GSS-L), in
+that order, for an `ncu --set full` capture (profiling helper, never a bench number):
+    ncu --set full --clock-control none --import-source on -k regex:"gms_kernel|gather2_mul" -f -o gpurun_out/gms_full \\
+        python tools/ncu_gms.py
+    python profiles/summarize.py gpurun_out/gms_full.ncu-rep profiles/r2_gms_full.csv      # read by bench.py
 """
 import os
 import sys
@@ -12,4 +14,8 @@ sys.path.insert(0, ROOT)
 import bench  # noqa: E402
 
 if __name__ == "__main__":
-    print(bench.gss_roofline(torch.device("cuda", 0), iters=1))
+    for key, workload, kernel, alg_bytes, edges, fns in bench.roofline_shapes(torch.device("cuda", 0)):
+        for f in fns:
+            f()
+        torch.cuda.synchronize()
+        print(key, workload, alg_bytes)
