@@ -497,6 +497,86 @@ tn_grouped_reduce_kernel(const __grid_constant__ TnGroup grp, const float* __res
   *dst = acc;
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Relational Dense (kgcnn/layers/relational.py:232-234: out[n] = x[n] @ kernel[relation[n]]): the rows arrive
+// SORTED by relation and `offs` (device, int32 [R + 1]) holds where each relation's rows begin, so one launch runs
+// R independent Dense problems, each against its own [K, U] kernel.  The group sizes are read on the DEVICE: the
+// launch shape depends only on (M, R), a CUDA graph replays on batches with another element composition.
+// ---------------------------------------------------------------------------------------------------------
+constexpr int kRelSplits = 8;     // row splits per relation of the relational weight gradient
+
+// tile -> (relation, tile inside the relation's row range): warp-parallel prefix over the tile counts
+__device__ __forceinline__ void rel_find_tile(const int32_t* __restrict__ offs, int R, int t, int* group, int* tile) {
+  const int lane = threadIdx.x & 31;
+  int base_tiles = 0, found_g = R, found_t = 0;
+  for (int g0 = 0; g0 < R && found_g == R; g0 += 32) {
+    const int g = g0 + lane;
+    const int tiles = (g < R) ? (__ldg(offs + g + 1) - __ldg(offs + g) + kBM - 1) / kBM : 0;
+    int incl = tiles;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int v = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= d) incl += v;
+    }
+    const int excl = base_tiles + incl - tiles;
+    const unsigned hit = __ballot_sync(0xffffffffu, g < R && t >= excl && t < excl + tiles);
+    if (hit) {
+      const int src = __ffs(hit) - 1;
+      found_g = g0 + src;
+      found_t = t - __shfl_sync(0xffffffffu, excl, src);
+    }
+    base_tiles += __shfl_sync(0xffffffffu, incl, 31);
+  }
+  *group = found_g;
+  *tile = found_t;
+}
+
+template <int OP>
+__global__ void __launch_bounds__(kCtaThreads)
+dense_rel_kernel(const float* __restrict__ A, const float* __restrict__ W, const int32_t* __restrict__ offs, int R,
+                 int K, int U, const float* __restrict__ bias, float* __restrict__ out, int vec_a, int vec_b) {
+  __shared__ int s_group, s_tile;
+  if (threadIdx.x < 32) {
+    int g, t;
+    rel_find_tile(offs, R, static_cast<int>(blockIdx.x), &g, &t);
+    if (threadIdx.x == 0) { s_group = g; s_tile = t; }
+  }
+  __syncthreads();
+  const int g = s_group;
+  if (g >= R) return;                                           // the grid is an upper bound on the tile count
+  const int64_t row0 = __ldg(offs + g), cnt = __ldg(offs + g + 1) - row0;
+  const int wa = (OP == kNN) ? K : U, wo = (OP == kNN) ? U : K;
+  dense_tc_body<OP>(A + row0 * wa, W + static_cast<int64_t>(g) * K * U, cnt, K, U, bias, out + row0 * wo, 0, vec_a,
+                    vec_b, s_tile, blockIdx.y, 0, nullptr);
+}
+
+// dW[g] = X_g^T G_g: grid (feature tiles, column tiles, R * kRelSplits); partials [R][kRelSplits][K*U]
+__global__ void __launch_bounds__(kCtaThreads)
+dense_rel_tn_kernel(const float* __restrict__ X, const float* __restrict__ G, const int32_t* __restrict__ offs,
+                    int K, int U, float* __restrict__ partial, int vec_a, int vec_b) {
+  const int g = blockIdx.z / kRelSplits, s = blockIdx.z % kRelSplits;
+  const int64_t row0 = __ldg(offs + g), cnt = __ldg(offs + g + 1) - row0;
+  const int64_t rps = ceil_div<int64_t>(ceil_div<int64_t>(cnt, kRelSplits), kKC) * kKC;
+  if (rps * s >= cnt) return;                                   // empty split (CTA-uniform): the reduce skips it
+  dense_tc_body<kTN>(X + row0 * K, G + row0 * U, cnt, K, U, nullptr,
+                     partial + static_cast<int64_t>(g) * kRelSplits * K * U, rps, vec_a, vec_b, blockIdx.x, blockIdx.y,
+                     s, nullptr);
+}
+
+__global__ void __launch_bounds__(256)
+dense_rel_tn_reduce_kernel(const float* __restrict__ partial, const int32_t* __restrict__ offs, int64_t n,
+                           float* __restrict__ out) {
+  const int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
+  if (i >= n) return;
+  const int g = blockIdx.y;
+  const int64_t cnt = __ldg(offs + g + 1) - __ldg(offs + g);
+  const int64_t rps = ceil_div<int64_t>(ceil_div<int64_t>(cnt, kRelSplits), kKC) * kKC;
+  float acc = 0.f;
+  for (int s = 0; s < kRelSplits && rps * s < cnt; ++s)         // fixed order; relations without rows give 0
+    acc += partial[(static_cast<int64_t>(g) * kRelSplits + s) * n + i];
+  out[static_cast<int64_t>(g) * n + i] = acc;
+}
+
 constexpr size_t kSmemBytes = kSmemBytesDecl;
 
 inline int tn_splits(int64_t M, int K, int U) {
@@ -669,6 +749,58 @@ int kgcnn_dense_tn_grouped(int n, const float* const* X, const float* const* G, 
     launches += 2;
   }
   return launches ? finish_launch(launches) : KGCNN_OK;
+}
+
+
+size_t kgcnn_dense_rel_workspace_bytes(int op, int R, int K, int U) {
+  if (op != tc::kTN || R <= 0 || K <= 0 || U <= 0) return 0;
+  return static_cast<size_t>(R) * tc::kRelSplits * K * U * sizeof(float) + 256;
+}
+
+int kgcnn_dense_rel(int op, const float* A, const float* B, const int32_t* offs, int R, int64_t M, int K, int U,
+                    const float* bias, float* out, void* workspace, size_t workspace_bytes, kgcnn_stream_t stream) {
+  if (op < tc::kNN || op > tc::kTN || R <= 0 || M < 0 || K <= 0 || U <= 0 || !out || !offs) return KGCNN_E_INVALID;
+  if (M > (int64_t{1} << 31) - 1) return KGCNN_E_INVALID;       // offsets are int32
+  cudaStream_t st = as_stream(stream);
+  if (op != tc::kTN && M == 0) return KGCNN_OK;
+  if (M > 0 && (!A || !B)) return KGCNN_E_INVALID;
+  auto al16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
+  static PerDeviceOnce attr;
+  attr.run([] {
+    cudaFuncSetAttribute(tc::dense_rel_kernel<tc::kNN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         static_cast<int>(tc::kSmemBytes));
+    cudaFuncSetAttribute(tc::dense_rel_kernel<tc::kNT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         static_cast<int>(tc::kSmemBytes));
+    cudaFuncSetAttribute(tc::dense_rel_tn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         static_cast<int>(tc::kSmemBytes));
+  });
+  if (op == tc::kTN) {                                          // A = X [M, K], B = G [M, U], out = dW [R, K, U]
+    if (!workspace || workspace_bytes < kgcnn_dense_rel_workspace_bytes(op, R, K, U)) return KGCNN_E_WORKSPACE;
+    if (!al16(workspace)) return KGCNN_E_INVALID;
+    float* partial = static_cast<float*>(workspace);
+    const int64_t n = static_cast<int64_t>(K) * U;
+    if (M > 0) {
+      dim3 grid(ceil_div(K, tc::kBM), ceil_div(U, tc::kMaxN), static_cast<unsigned>(R) * tc::kRelSplits);
+      tc::dense_rel_tn_kernel<<<grid, tc::kCtaThreads, tc::kSmemBytes, st>>>(
+          A, B, offs, K, U, partial, (K % 4 == 0 && al16(A)) ? 1 : 0, (U % 4 == 0 && al16(B)) ? 1 : 0);
+    }
+    dim3 rgrid(static_cast<unsigned>(ceil_div<int64_t>(n, 256)), static_cast<unsigned>(R));
+    tc::dense_rel_tn_reduce_kernel<<<rgrid, 256, 0, st>>>(partial, offs, n, out);
+    return finish_launch(2);
+  }
+  // sum over relations of ceil(rows / 128) <= M / 128 + R
+  const unsigned tiles = static_cast<unsigned>(M / tc::kBM + R);
+  if (op == tc::kNN) {                                          // A = X [M, K], B = kernels [R, K, U], out [M, U]
+    dim3 grid(tiles, ceil_div(U, tc::kMaxN));
+    tc::dense_rel_kernel<tc::kNN><<<grid, tc::kCtaThreads, tc::kSmemBytes, st>>>(
+        A, B, offs, R, K, U, bias, out, (K % 4 == 0 && al16(A)) ? 1 : 0, (U % 4 == 0 && al16(B)) ? 1 : 0);
+  } else {                                                      // A = G [M, U], B = kernels [R, K, U], out [M, K]
+    dim3 grid(tiles, ceil_div(K, tc::kMaxN));
+    tc::dense_rel_kernel<tc::kNT><<<grid, tc::kCtaThreads, tc::kSmemBytes, st>>>(
+        A, B, offs, R, K, U, nullptr, out, (U % 4 == 0 && al16(A)) ? 1 : 0,
+        (U % 4 == 0 && al16(B) && (static_cast<int64_t>(K) * U) % 4 == 0) ? 1 : 0);
+  }
+  return finish_launch();
 }
 
 }  // extern "C"

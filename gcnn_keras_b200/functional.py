@@ -742,7 +742,7 @@ def _dense_operands(*tensors):
 
 class _MatMul(torch.autograd.Function):
     """Bilinear products closed under differentiation.  mode 0: a @ b, 1: a @ b^T, 2: a^T @ b, all three on the
-    tcgen05 tensor cores (3xTF32 split, fp32 TMEM accumulation; dense_tc.cu)."""
+    tcgen05 tensor cores (three-piece bf16 split, fp32 TMEM accumulation; dense_tc.cu)."""
 
     @staticmethod
     def forward(ctx, a, b, mode):
@@ -751,7 +751,7 @@ class _MatMul(torch.autograd.Function):
         _dense_operands(a, b)
         if a.dim() != 2 or b.dim() != 2:
             raise ValueError("matmul operands must be matrices, got %s and %s" % (tuple(a.shape), tuple(b.shape)))
-        return raw_dense_tc(mode, a, b)              # tcgen05 tensor cores, 3xTF32
+        return raw_dense_tc(mode, a, b)              # tcgen05 tensor cores, bf16x3 split
 
     @staticmethod
     def backward(ctx, g):
@@ -808,7 +808,7 @@ class _Linear(torch.autograd.Function):
         ctx.bias_ref = b.detach() if b is not None else None      # identity only (the sink's variable lookup)
         ctx.bias_leaf = b is not None and b.is_leaf
         _dense_operands(x, w, b)
-        return raw_dense_tc(0, x, w, b)              # tcgen05 tensor cores, 3xTF32, bias in the epilogue
+        return raw_dense_tc(0, x, w, b)              # tcgen05 tensor cores, bf16x3 split, bias in the epilogue
 
     @staticmethod
     def backward(ctx, g):
@@ -883,7 +883,7 @@ class _TNCol(torch.autograd.Function):
 
 def dense(x, kernel, bias, activation):
     """DenseEmbedding on flat values (kgcnn/layers/modules.py:85): activation(x @ kernel + bias).
-    x @ W (+ b), g @ W^T and x^T g run on the tcgen05 tensor cores (3xTF32); the activation and all its derivatives
+    x @ W (+ b), g @ W^T and x^T g run on the tcgen05 tensor cores (bf16x3 split); the activation and all its derivatives
     in the fused bias/activation kernel family."""
     code = activation if isinstance(activation, int) else act_code(activation)
     lead = x.shape[:-1]
@@ -1068,7 +1068,7 @@ def acsf(xyz, spec):
 
 
 # ------------------------------------------------------------------------------------------------
-# Dense contractions on tcgen05 tensor cores (3xTF32)
+# Dense contractions on tcgen05 tensor cores (bf16x3 split)
 # ------------------------------------------------------------------------------------------------
 def raw_dense_tc(op, a, b, bias=None):
     """op 0: a[M,K] @ b[K,U] (+bias); op 1: a[M,U] @ b[K,U]^T; op 2: a[M,K]^T @ b[M,U]."""
@@ -1103,6 +1103,90 @@ def raw_dense_act(x, w, bias, act):
     check(_lib.lib().kgcnn_dense_act(_ptr(x), _ptr(w), M, K, U, _ptr(bias), int(act), _ptr(pre), _ptr(y), _stream()),
           "kgcnn_dense_act")
     return pre, y
+
+
+# ------------------------------------------------------------------------------------------------
+# relational Dense (f1): rows sorted by relation, one grouped launch per product
+# ------------------------------------------------------------------------------------------------
+def raw_dense_rel(op, a, b, offs, n_rel, bias=None):
+    """Rows of `a` (and of `b` for op 2) are sorted by relation, offs = int32 [R + 1] device row offsets.
+    op 0: a[M,K] @ b[R,K,U][rel] (+bias) -> [M,U]; op 1: a[M,U] @ b[R,K,U][rel]^T -> [M,K];
+    op 2: per relation a[M,K]^T @ b[M,U] -> [R,K,U]."""
+    _need_cuda(a, b, offs, bias)
+    a, b = _f32c(a), _f32c(b)
+    M, R = int(a.shape[0]), int(n_rel)
+    if offs.dtype != torch.int32 or int(offs.shape[0]) != R + 1:
+        raise ValueError("offs must be int32 [num_relations + 1]")
+    if op == 2:
+        K, U = int(a.shape[1]), int(b.shape[1])
+        out = torch.empty((R, K, U), dtype=torch.float32, device=a.device)
+    else:
+        K, U = int(b.shape[1]), int(b.shape[2])
+        out = torch.empty((M, U if op == 0 else K), dtype=torch.float32, device=a.device)
+    nbytes = int(_lib.lib().kgcnn_dense_rel_workspace_bytes(op, R, K, U))
+    ws = torch.empty((max(nbytes, 16),), dtype=torch.uint8, device=a.device) if nbytes else None
+    bias = None if bias is None else _f32c(bias)
+    check(_lib.lib().kgcnn_dense_rel(op, _ptr(a), _ptr(b), _ptr(offs), R, M, K, U, _ptr(bias), _ptr(out), _ptr(ws),
+                                     nbytes, _stream()), "kgcnn_dense_rel")
+    return out
+
+
+class _RelMatMul(torch.autograd.Function):
+    """The three relational products, closed under differentiation like _MatMul (mode = op of raw_dense_rel)."""
+
+    @staticmethod
+    def forward(ctx, a, b, offs, n_rel, mode):
+        ctx.mode, ctx.n_rel = mode, n_rel
+        ctx.save_for_backward(a, b, offs)
+        _dense_operands(a, b)
+        return raw_dense_rel(mode, a, b, offs, n_rel)
+
+    @staticmethod
+    def backward(ctx, g):
+        a, b, offs = ctx.saved_tensors
+        R, mode = ctx.n_rel, ctx.mode
+        g = g.contiguous()
+        ga = gb = None
+        if mode == 0:       # y = a kernel[rel]
+            if _want(ctx, 0, a):
+                ga = _RelMatMul.apply(g, b, offs, R, 1)
+            if _want(ctx, 1, b):
+                gb = _RelMatMul.apply(a, g, offs, R, 2)
+        elif mode == 1:     # y = a kernel[rel]^T
+            if _want(ctx, 0, a):
+                ga = _RelMatMul.apply(g, b, offs, R, 0)
+            if _want(ctx, 1, b):
+                gb = _RelMatMul.apply(g, a, offs, R, 2)
+        else:               # y[rel] = a^T b
+            if _want(ctx, 0, a):
+                ga = _RelMatMul.apply(b, g, offs, R, 1)
+            if _want(ctx, 1, b):
+                gb = _RelMatMul.apply(a, g, offs, R, 0)
+        return ga, gb, None, None, None
+
+
+def dense_rel(x_sorted, kernels, offs):
+    """x_sorted[M,K] @ kernels[R,K,U][relation of the row]; rows sorted by relation (see RelationalDense)."""
+    return _RelMatMul.apply(x_sorted, kernels, offs, int(kernels.shape[0]), 0)
+
+
+class _PermuteRows(torch.autograd.Function):
+    """out[i] = x[perm[i]] for a PERMUTATION perm (inv = its inverse): the gradient is the inverse gather, so no
+    scatter is needed in either direction."""
+
+    @staticmethod
+    def forward(ctx, x, perm, inv):
+        ctx.save_for_backward(perm, inv)
+        return raw_gather_rows(_f32c(x), perm)
+
+    @staticmethod
+    def backward(ctx, g):
+        perm, inv = ctx.saved_tensors
+        return _PermuteRows.apply(g.contiguous(), inv, perm), None, None
+
+
+def permute_rows(x, perm, inv):
+    return _PermuteRows.apply(x, perm, inv)
 
 
 # ------------------------------------------------------------------------------------------------

@@ -1,8 +1,11 @@
 """RelationalDense / RelationalMLP of kgcnn/layers/relational.py:204-238 and kgcnn/layers/mlp.py:329-416.
 
 out[n] = activation(x[n] @ kernel[relation[n]] + bias): one weight matrix per relation (atomic number in HDNNP).
-The per-atom kernel gather runs through the row-gather kernel so that the kernel gradient is the deterministic
-CSR segment-sum over relation (the reference gathers with tf.gather, whose gradient scatters atomically).
+The reference gathers a full (F_in, units) kernel per atom (relational.py:233) and batch_dots.  Here the atoms are
+sorted by relation once per batch (the stable CSR plan of the relation tensor), every relation's rows then form
+one contiguous Dense problem against its own kernel, and all relations run in ONE grouped tcgen05 launch
+(kgcnn_dense_rel: forward, input gradient and per-relation kernel gradient, closed under differentiation).
+A RelationalMLP sorts on entry and un-sorts on exit, not per layer.
 """
 import math
 
@@ -13,6 +16,44 @@ from ..plan import Relation
 from ..ragged import RaggedTensor
 from .base import GraphBaseLayer, register_keras_serializable
 from .mlp import _per_layer
+
+
+class RelationGroups:
+    """Rows sorted by relation: `offs` int32 [R + 1] (device) row offsets, `perm` / `inv` the stable sort and its
+    inverse (None when the relation tensor is already ascending).  A relation outside [0, R) raises IndexError
+    (the reference's tf.gather fails on CPU and returns zeros on GPU); inside a captured step it sets the step's
+    guard flag instead, and the optimizer update of that replay is skipped (see plan.PlanMode)."""
+
+    def __init__(self, relation_values, n_rel):
+        ids = relation_values.reshape(-1)
+        if ids.dtype != torch.int32:
+            ids = F.raw_cast_i32(ids.to(torch.int64).contiguous()) if ids.is_cuda else ids.to(torch.int32)
+        rel = Relation(ids.contiguous(), int(n_rel))
+        self.n_rel = int(n_rel)
+        self.offs = rel.rowptr
+        self.perm = rel.perm
+        self.inv = None
+        if self.perm is not None:
+            self.inv = torch.empty_like(self.perm)
+            self.inv[self.perm.long()] = torch.arange(self.perm.shape[0], dtype=torch.int32, device=self.perm.device)
+
+    @classmethod
+    def of(cls, relation_values, n_rel):
+        """Cached on the relation tensor (identity + version), like the index plans."""
+        from ..plan import _cache_slot
+        slot = _cache_slot(relation_values)
+        key = ("relation_groups", relation_values._version, int(n_rel))
+        if key not in slot:
+            for k in [k for k in slot if k[0] == "relation_groups" and k != key]:
+                del slot[k]
+            slot[key] = cls(relation_values, n_rel)
+        return slot[key]
+
+    def sort(self, x):
+        return x if self.perm is None else F.permute_rows(x, self.perm, self.inv)
+
+    def unsort(self, y):
+        return y if self.perm is None else F.permute_rows(y, self.inv, self.perm)
 
 
 @register_keras_serializable(package="kgcnn", name="RelationalDense")
@@ -49,21 +90,19 @@ class RelationalDense(GraphBaseLayer):
 
     def call(self, inputs, **kwargs):
         features, relations = self.assert_ragged_input_rank(inputs, ragged_rank=1)
-        x = features.values
-        r, fi, fo = self.kernel.shape
-        # The reference gathers a full (F_in, units) kernel per atom (relational.py:233: a 1.47 GB temporary at
-        # config 4) and batch_dots.  Equivalent without the temporary: ONE Dense against all relation kernels side
-        # by side, [N, F_in] @ [F_in, R*units], then pick each atom's own block; the kernel gradient becomes the
-        # split-M weight-gradient GEMM instead of a per-atom scatter.
-        wcat = self.kernel.permute(1, 0, 2).reshape(fi, r * fo)
-        y = F._Linear.apply(x, wcat, None).reshape(-1, r, fo)
-        sel = relations.values.reshape(-1).to(torch.int64).clamp(0, r - 1)
-        new = torch.gather(y, 1, sel.view(-1, 1, 1).expand(-1, 1, fo)).squeeze(1)                 # :233-234
+        group = kwargs.get("relation_groups")
+        if group is None:                                   # a layer used on its own sorts and un-sorts itself
+            group = RelationGroups.of(relations.values, self.num_relations)
+            return features.with_values(group.unsort(self._call_sorted(group.sort(features.values), group)))
+        return features.with_values(self._call_sorted(features.values, group))
+
+    def _call_sorted(self, x, group):
+        if group.n_rel != self.num_relations:
+            raise ValueError("relation groups built for %d relations, layer has %d" % (group.n_rel, self.num_relations))
+        new = F.dense_rel(x, self.kernel, group.offs)                                              # :233-234
         if self._act_code is None:
-            new = self.activation(new + self.bias if self.use_bias else new)
-        else:
-            new = F.bias_act(new, self.bias if self.use_bias else None, self._act_code)           # :235-237
-        return features.with_values(new)
+            return self.activation(new + self.bias if self.use_bias else new)
+        return F.bias_act(new, self.bias if self.use_bias else None, self._act_code)               # :235-237
 
     def get_config(self):
         config = super().get_config()
@@ -97,9 +136,15 @@ class RelationalMLP(GraphBaseLayer):
 
     def call(self, inputs, **kwargs):
         x, relations = inputs
+        if len(set(self._conf_num_relations)) != 1:         # layers with different relation counts: each sorts itself
+            for layer in self.mlp_dense_layer_list:
+                x = layer([x, relations])
+            return x
+        group = RelationGroups.of(relations.values, self._conf_num_relations[0])
+        x = x.with_values(group.sort(x.values))
         for layer in self.mlp_dense_layer_list:
-            x = layer([x, relations])
-        return x
+            x = layer([x, relations], relation_groups=group)
+        return x.with_values(group.unsort(x.values))
 
     def get_config(self):
         config = super().get_config()

@@ -179,7 +179,7 @@ int kgcnn_colsum(const float* a, int64_t M, int U, float* out, void* workspace, 
                  kgcnn_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
- * a19  Dense contractions on the tcgen05 tensor cores (3xTF32 split, fp32 TMEM accumulators):
+ * a19  Dense contractions on the tcgen05 tensor cores (three-piece bf16 split, fp32 TMEM accumulators):
  *   op 0 (NN): out[M,U] = A[M,K] B[K,U] + bias[U] (bias nullable)      forward, kgcnn/layers/modules.py:85
  *   op 1 (NT): out[M,K] = A[M,U] B[K,U]^T                              input gradient
  *   op 2 (TN): out[K,U] = A[M,K]^T B[M,U]                              weight gradient (needs the workspace)
@@ -196,7 +196,7 @@ int kgcnn_dense_act(const float* X, const float* W, int64_t M, int K, int U, con
 
 /* ---------------------------------------------------------------------------------------------
  * a19  grouped weight gradients: every  dW_i[K_i,U_i] += X_i[M_i,K_i]^T G_i[M_i,U_i],  db_i[U_i] += colsum(G_i)
- *   of one backward sweep in two launches (tcgen05 3xTF32 + fixed-order reduce).  The products are leaves of the
+ *   of one backward sweep in two launches (tcgen05 bf16x3 + fixed-order reduce).  The products are leaves of the
  *   backward graph (backward of kgcnn/layers/modules.py:85 for every Dense, once through the energy and once
  *   through the force), so the host defers them and submits the list.  X, G, M, K, U, dW, db are HOST arrays of
  *   length n (device pointers inside); db[i] nullable.  Results are ACCUMULATED into dW / db (zero them first);
@@ -206,6 +206,20 @@ size_t kgcnn_dense_tn_grouped_workspace_bytes(int n, const int64_t* M, const int
 int kgcnn_dense_tn_grouped(int n, const float* const* X, const float* const* G, const int64_t* M, const int32_t* K,
                            const int32_t* U, float* const* dW, float* const* db, void* workspace,
                            size_t workspace_bytes, kgcnn_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * f1  RelationalDense (kgcnn/layers/relational.py:232-234: kernel_per_feature = gather(kernel, relation);
+ *   out = batch_dot(x, kernel_per_feature)) as R grouped Dense problems in one launch.  The M rows are SORTED by
+ *   relation; offs (DEVICE, int32 [R + 1], offs[0] = 0, offs[R] = M) gives each relation's row range and is read on
+ *   the device, so the launch shape depends on (M, R) only.  kernels = [R, K, U] row-major.
+ *     op 0 (NN): out[M,U] rows of relation r = A[M,K] rows of r  @ kernels[r]   (+ bias[U], nullable)
+ *     op 1 (NT): out[M,K] rows of relation r = A[M,U] rows of r  @ kernels[r]^T         (input gradient)
+ *     op 2 (TN): out[R,K,U]; out[r] = A[M,K] rows of r ^T  @ B[M,U] rows of r           (kernel gradient, B = G;
+ *                relations without rows give zeros; fixed-order split reduce, needs the workspace)
+ * ------------------------------------------------------------------------------------------- */
+size_t kgcnn_dense_rel_workspace_bytes(int op, int R, int K, int U);
+int kgcnn_dense_rel(int op, const float* A, const float* B, const int32_t* offs, int R, int64_t M, int K, int U,
+                    const float* bias, float* out, void* workspace, size_t workspace_bytes, kgcnn_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
  * a9-a12  fused edge geometry: coordinates + index pair -> distance, unit direction, radial basis, cosine cutoff
