@@ -55,7 +55,7 @@ SIGNATURES = {
     "kgcnn_acsf_g4": (_i, [_p, _p, _p, _p, _i, _p, _p, _p, _p, _p, _i, _i, _f, _f, _i, _l, _p, _p, _p, _p, _l, _i, _p, _p, _p, _p]),
     "kgcnn_painn_msg_nodes": (_i, [_p, _p, _p, _p, _p, _p, _p, _i, _l, _l, _i, _i, _p, _p, _p]),
     "kgcnn_painn_msg_senders": (_i, [_p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _l, _l, _i, _i, _p, _p, _p]),
-    "kgcnn_painn_msg_edges": (_i, [_p, _p, _p, _p, _p, _p, _p, _p, _l, _i, _i, _p, _p, _p]),
+    "kgcnn_painn_msg_edges": (_i, [_p, _p, _p, _p, _p, _p, _p, _p, _l, _i, _i, _p, _p, _p, _p]),
     "kgcnn_offsets_workspace_bytes": (_z, [_l]),
     "kgcnn_offsets_from_counts": (_i, [_p, _l, _p, _p, _z, _p]),
     "kgcnn_angle_count": (_i, [_p, _l, _l, _p, _p, _i, _i, _i, _i, _i, _p, _p]),

@@ -10,6 +10,10 @@
 // One CTA = one 128-row tile: 16 staging warps (one 8-element unit of A and of B per thread and chunk) + one warp that
 // issues the MMAs; all global loads of the A tile are in flight before the first split.  Epilogue: accumulators (+ bias,
 // + f(pre) beside it for the fused activation) -> shared memory -> one bulk asynchronous copy per 512-byte row.
+// Large M with a short reduction (<= 64: the [E, 20] -> [E, 384] filter Dense of PaiNN on 4e5 edges) runs PERSISTENT:
+// one CTA per SM walks over row tiles, so TMEM allocation, barrier set-up, the parameter fetch and the staging of W
+// happen once; the next tile's rows are loaded while the current tile drains, and its bulk stores leave while the next
+// tile is staged (the output tile then has its own shared memory instead of aliasing the operand stages).
 #include "dense_tc.cuh"
 
 namespace kgcnn {
@@ -38,8 +42,11 @@ dense_fast_kernel(const float* __restrict__ A, const float* __restrict__ B, int6
   const int red = (OP == kNN) ? K : U;                           // reduction length = row length of A
   const int n0 = blockIdx.y * kMaxN;
   const int nt = min(kMaxN, (n_total - n0 + 15) / 16 * 16);      // MMA N (multiple of 16; RAG 2: rounded up)
-  const int64_t m0 = static_cast<int64_t>(blockIdx.x) * kBM;
+  int64_t m0 = static_cast<int64_t>(blockIdx.x) * kBM;
   const int nchunk = (red + kKC - 1) / kKC;                      // 1 .. 4
+  const int64_t ntiles = (M + kBM - 1) / kBM;
+  const bool persistent = gridDim.x < ntiles;                    // the launcher guarantees nchunk <= 2 and the smem
+  const int my_tiles = static_cast<int>((ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x);
 
   if (warp == kThreads / 32) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)),
@@ -66,15 +73,7 @@ dense_fast_kernel(const float* __restrict__ A, const float* __restrict__ B, int6
   if (warp < kThreads / 32) {
     const int t = threadIdx.x;
     const int64_t row = min(m0 + (t >> 2), M - 1);
-#ifdef KGCNN_TC_TIMELINE
-    asm volatile("" ::"l"(row));
-    TL(19);
-#endif
     pa = reinterpret_cast<const float4*>(A + row * red + 8 * (t & 3));
-#ifdef KGCNN_TC_TIMELINE
-    asm volatile("" ::"l"(pa));
-    TL(30);
-#endif
     if (OP == kNN) {                                             // W[k, u]: reduction along the rows, MN-major
       int k, mn8;
       mn_coords(k, mn8);
@@ -132,7 +131,7 @@ dense_fast_kernel(const float* __restrict__ A, const float* __restrict__ B, int6
   TL(2);
 
   constexpr bool kBMn = (OP == kNN);
-  auto wait_chunk = [&](int c) { mbar_wait(smem_u32(&mbar[c]), 0u); };
+  auto wait_chunk = [&](int c, int it) { mbar_wait(smem_u32(&mbar[c]), static_cast<uint32_t>(it & 1)); };
   float racc[32];
   const int c0 = 32 * (warp >> 2);                       // this warp's 32 accumulator columns (staging warps only)
   if (warp == kThreads / 32) {
@@ -142,8 +141,9 @@ dense_fast_kernel(const float* __restrict__ A, const float* __restrict__ B, int6
     const uint64_t db_hi = kBMn ? desc_hi_bits(8, kKC) : desc_hi_bits(kPitchK, 8);
     constexpr uint32_t a_step = 2 * kPitchK;
     constexpr uint32_t bk_step = kBMn ? 16 : 2 * kPitchK;
+    for (int it = 0; it < my_tiles; ++it)
     for (int c = 0; c < nchunk; ++c) {
-      mbar_wait(smem_u32(&full[c]), 0u);
+      mbar_wait(smem_u32(&full[c]), static_cast<uint32_t>(it & 1));
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       TL(20 + 2 * c);
       if (lane == 0) {
@@ -184,84 +184,113 @@ dense_fast_kernel(const float* __restrict__ A, const float* __restrict__ B, int6
       __syncwarp();
       if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&full[c])) : "memory");
     };
-    stage(0, va0, vb0);
-    TL(3);
-    if (nchunk > 2) vb0 = ld_b(2);
-    if (nchunk > 3) va0 = ld_a(3);
-    publish(0);
-    TL(4);
-    if (nchunk > 1) { stage(1, va1, vb1); if (nchunk > 3) vb1 = ld_b(3); publish(1); TL(5); }
-    if (nchunk > 2) { stage(2, va2, vb0); publish(2); TL(6); }
-    if (nchunk > 3) { stage(3, va0, vb1); publish(3); TL(7); }
-    // accumulator c holds chunk c: fp32 (RN) sum in registers
-    for (int c = 0; c < nchunk; ++c) {
-      wait_chunk(c);
-      TL(8 + c);
-      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-      if (c0 < nt) {
-        const uint32_t taddr = tmem_d + (static_cast<uint32_t>(32 * (warp & 3)) << 16) + static_cast<uint32_t>(c * kMaxN + c0);
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-          uint32_t v[16];
-          asm volatile(
-              "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
-              "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-              : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
-                "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
-              : "r"(taddr + 16u * h)
-              : "memory");
-          asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-          for (int i = 0; i < 16; ++i)
-            racc[16 * h + i] = (c == 0) ? __uint_as_float(v[i]) : racc[16 * h + i] + __uint_as_float(v[i]);
-        }
-      }
-    }
-    TL(12);
-
-    // ---- epilogue: lane = output row 32 (warp % 4) + lane, columns c0 .. c0 + 31 ----
-    const int d_row = 32 * (warp & 3) + lane;
+    auto stage_a = [&](int c, const F8& ra) { store_kmajor(ra, planes + static_cast<size_t>(c) * kStageUnits); };
+    const int d_row = 32 * (warp & 3) + lane;                      // epilogue: lane = output row, columns c0 .. c0 + 31
     constexpr int OP_PITCH = kMaxN + 4;
-    float* otile = reinterpret_cast<float*>(smem_raw);             // the operand stages are free: every MMA has completed
+    // one-tile launches alias the output tile onto the operand stages (free once every MMA has completed); the
+    // persistent loop keeps W staged and the next tile's stores in flight, so its output tile lies behind the stages
+    float* otile = reinterpret_cast<float*>(smem_raw + (persistent ? static_cast<size_t>(nchunk) * kStageUnits * 16 : 0));
     float* atile = otile + kBM * OP_PITCH;
-    if (c0 < nt) {
+    for (int it = 0; it < my_tiles; ++it) {
+      TL(31);
+      if (it == 0) {
+        stage(0, va0, vb0);
+        TL(3);
+        if (nchunk > 2) vb0 = ld_b(2);
+        if (nchunk > 3) va0 = ld_a(3);
+        publish(0);
+        TL(4);
+        if (nchunk > 1) { stage(1, va1, vb1); if (nchunk > 3) vb1 = ld_b(3); publish(1); TL(5); }
+        if (nchunk > 2) { stage(2, va2, vb0); publish(2); TL(6); }
+        if (nchunk > 3) { stage(3, va0, vb1); publish(3); TL(7); }
+      } else {                                                     // persistent: W stays staged, nchunk <= 2
+        stage_a(0, va0);
+        publish(0);
+        if (nchunk > 1) { stage_a(1, va1); publish(1); }
+      }
+      TL(32);
+      if (it + 1 < my_tiles) {                                     // next tile's rows: in flight during drain + epilogue
+        const int64_t row = min(m0 + static_cast<int64_t>(gridDim.x) * kBM + (threadIdx.x >> 2), M - 1);
+        pa = reinterpret_cast<const float4*>(A + row * red + 8 * (threadIdx.x & 3));
+        va0 = ld_a(0);
+        if (nchunk > 1) va1 = ld_a(1);
+      }
+      // accumulator c holds chunk c: fp32 (RN) sum in registers
+      for (int c = 0; c < nchunk; ++c) {
+        wait_chunk(c, it);
+        TL(8 + c);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        if (c0 < nt) {
+          const uint32_t taddr = tmem_d + (static_cast<uint32_t>(32 * (warp & 3)) << 16) + static_cast<uint32_t>(c * kMaxN + c0);
 #pragma unroll
-      for (int i = 0; i < 32; i += 4) {
-        float4 v = make_float4(racc[i], racc[i + 1], racc[i + 2], racc[i + 3]);
-        if (OP == kNN) {
-          const float4 bv = *reinterpret_cast<const float4*>(bias_s + c0 + i);
-          v.x += bv.x; v.y += bv.y; v.z += bv.z; v.w += bv.w;
+          for (int h = 0; h < 2; ++h) {
+            uint32_t v[16];
+            asm volatile(
+                "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+                "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                  "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+                : "r"(taddr + 16u * h)
+                : "memory");
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+            for (int i = 0; i < 16; ++i)
+              racc[16 * h + i] = (c == 0) ? __uint_as_float(v[i]) : racc[16 * h + i] + __uint_as_float(v[i]);
+          }
         }
-        *reinterpret_cast<float4*>(otile + d_row * OP_PITCH + c0 + i) = v;
-        if (ACT >= 0)
-          *reinterpret_cast<float4*>(atile + d_row * OP_PITCH + c0 + i) =
-              make_float4(act_deriv<ACT < 0 ? 0 : ACT>(v.x, 0), act_deriv<ACT < 0 ? 0 : ACT>(v.y, 0),
-                          act_deriv<ACT < 0 ? 0 : ACT>(v.z, 0), act_deriv<ACT < 0 ? 0 : ACT>(v.w, 0));
       }
-    }
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy stores -> async proxy (bulk copy)
-    asm volatile("bar.sync 1, %0;" ::"r"(kThreads) : "memory");    // staging warps only
-    TL(13);
-    if (RAG == 2) {                                               // ragged output width: element-wise stores
-      const int ncols = min(nt, n_total - n0);
-      for (int r = warp; r < kBM; r += kThreads / 32) {
-        if (m0 + r >= M) break;
-        for (int cidx = lane; cidx < ncols; cidx += 32)
-          out[(m0 + r) * n_total + n0 + cidx] = otile[r * OP_PITCH + cidx];
+      TL(12);
+
+      if (it > 0) {                                                // the previous tile's bulk stores have read otile
+        if (threadIdx.x < kBM) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        TL(33);
+        asm volatile("bar.sync 1, %0;" ::"r"(kThreads) : "memory");
       }
-    } else if (threadIdx.x < kBM && m0 + threadIdx.x < M) {
-      const int r = threadIdx.x;
-      const uint32_t bytes = static_cast<uint32_t>(nt) * 4u;
-      asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(out + (m0 + r) * n_total + n0),
-                   "r"(smem_u32(otile + r * OP_PITCH)), "r"(bytes)
-                   : "memory");
-      if (ACT >= 0)
-        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(
-                         act_out + (m0 + r) * n_total + n0),
-                     "r"(smem_u32(atile + r * OP_PITCH)), "r"(bytes)
-                     : "memory");
-      asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-      asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+      TL(34);
+      if (c0 < nt) {
+#pragma unroll
+        for (int i = 0; i < 32; i += 4) {
+          float4 v = make_float4(racc[i], racc[i + 1], racc[i + 2], racc[i + 3]);
+          if (OP == kNN) {
+            const float4 bv = *reinterpret_cast<const float4*>(bias_s + c0 + i);
+            v.x += bv.x; v.y += bv.y; v.z += bv.z; v.w += bv.w;
+          }
+          *reinterpret_cast<float4*>(otile + d_row * OP_PITCH + c0 + i) = v;
+          if (ACT >= 0)
+            *reinterpret_cast<float4*>(atile + d_row * OP_PITCH + c0 + i) =
+                make_float4(act_deriv<ACT < 0 ? 0 : ACT>(v.x, 0), act_deriv<ACT < 0 ? 0 : ACT>(v.y, 0),
+                            act_deriv<ACT < 0 ? 0 : ACT>(v.z, 0), act_deriv<ACT < 0 ? 0 : ACT>(v.w, 0));
+        }
+      }
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy stores -> async proxy (bulk copy)
+      asm volatile("bar.sync 1, %0;" ::"r"(kThreads) : "memory");    // staging warps only
+      TL(13);
+      if (RAG == 2) {                                               // ragged output width: element-wise stores
+        const int ncols = min(nt, n_total - n0);
+        for (int r = warp; r < kBM; r += kThreads / 32) {
+          if (m0 + r >= M) break;
+          for (int cidx = lane; cidx < ncols; cidx += 32)
+            out[(m0 + r) * n_total + n0 + cidx] = otile[r * OP_PITCH + cidx];
+        }
+      } else if (threadIdx.x < kBM) {
+        if (m0 + threadIdx.x < M) {
+          const int r = threadIdx.x;
+          const uint32_t bytes = static_cast<uint32_t>(nt) * 4u;
+          asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(
+                           out + (m0 + r) * n_total + n0),
+                       "r"(smem_u32(otile + r * OP_PITCH)), "r"(bytes)
+                       : "memory");
+          if (ACT >= 0)
+            asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(
+                             act_out + (m0 + r) * n_total + n0),
+                         "r"(smem_u32(atile + r * OP_PITCH)), "r"(bytes)
+                         : "memory");
+        }
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        if (it + 1 == my_tiles) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+      }
+      m0 += static_cast<int64_t>(gridDim.x) * kBM;
+      TL(35);
     }
   }
   TL(14);
@@ -283,8 +312,15 @@ static void launch_fast(const float* A, const float* B, int64_t M, int K, int U,
     cudaFuncSetAttribute(dense_fast_kernel<OP, ACT, RAG>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                          static_cast<int>(kSmemBytesDecl));
   });
-  const int n_total = (OP == kNN) ? U : K;
-  dim3 grid(static_cast<unsigned>(ceil_div<int64_t>(M, kBM)), ceil_div(n_total, kMaxN));
+  const int n_total = (OP == kNN) ? U : K, red = (OP == kNN) ? K : U;
+  const int nchunk = ceil_div(red, kKC), col_tiles = ceil_div(n_total, kMaxN);
+  int64_t row_ctas = ceil_div<int64_t>(M, kBM);
+  // persistent walk over the row tiles: short reductions only (stages + separate output tile(s) must fit), and only
+  // when there are more than two waves of tiles to amortise over
+  const size_t need = static_cast<size_t>(nchunk) * kStageUnits * 16 + (ACT >= 0 ? 2 : 1) * kBM * (kMaxN + 4) * sizeof(float);
+  if (nchunk <= 2 && need <= kSmemBytesDecl && row_ctas * col_tiles > 2 * kNumSM)
+    row_ctas = std::max(1, kNumSM / col_tiles);
+  dim3 grid(static_cast<unsigned>(row_ctas), col_tiles);
   dense_fast_kernel<OP, ACT, RAG><<<grid, kCtaThreads, kSmemBytesDecl, st>>>(A, B, M, K, U, bias, out, act_out);
 }
 

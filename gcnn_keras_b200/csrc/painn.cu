@@ -154,11 +154,12 @@ senders_kernel(const float* __restrict__ gs, const float* __restrict__ gv, const
 // edges: gw[e] = ( P1[j] Gs[i],  P2[j] sum_c Gv[i,c] V[j,c],  P3[j] sum_c R[e,c] Gv[i,c] )     [E,3F]
 //        gr[e,c] = sum_f P3[j,f] W3[e,f] Gv[i,c,f]                                              [E,3]
 // ---------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kWarps * 32)
-edges_kernel(const float* __restrict__ gs, const float* __restrict__ gv, const float* __restrict__ phi,
+template <bool ACC>
+__device__ __forceinline__ void
+edges_body(const float* __restrict__ gs, const float* __restrict__ gv, const float* __restrict__ phi,
              const float* __restrict__ v, const float* __restrict__ w, const float* __restrict__ r,
              const int32_t* __restrict__ recv, const int32_t* __restrict__ send, int64_t E, int F, int mask,
-             float* __restrict__ gw, float* __restrict__ gr) {
+             const float* __restrict__ gw_acc, float* __restrict__ gw, float* __restrict__ gr) {
   const int lane = threadIdx.x & 31;
   const int64_t e = static_cast<int64_t>(blockIdx.x) * kWarps + (threadIdx.x >> 5);
   if (e >= E) return;
@@ -199,6 +200,13 @@ edges_kernel(const float* __restrict__ gs, const float* __restrict__ gv, const f
       }
     }
     if (gw) {
+      if (ACC) {             // sum of two substitutions of one backward node: the second call adds onto the first
+        const float* ap = gw_acc + e * F3 + f0;
+        const float4 a1 = ld4s(ap), a2 = ld4s(ap + F), a3 = ld4s(ap + 2 * F);
+        o1.x += a1.x; o1.y += a1.y; o1.z += a1.z; o1.w += a1.w;
+        o2.x += a2.x; o2.y += a2.y; o2.z += a2.z; o2.w += a2.w;
+        o3.x += a3.x; o3.y += a3.y; o3.z += a3.z; o3.w += a3.w;
+      }
       st4(gw + e * F3 + f0, o1);
       st4(gw + e * F3 + F + f0, o2);
       st4(gw + e * F3 + 2 * F + f0, o3);
@@ -209,6 +217,19 @@ edges_kernel(const float* __restrict__ gs, const float* __restrict__ gv, const f
     if (lane == 0) { gr[3 * e] = q0; gr[3 * e + 1] = q1; gr[3 * e + 2] = q2; }
   }
 }
+
+#define KGCNN_EDGES_PARAMS                                                                                       \
+  const float *__restrict__ gs, const float *__restrict__ gv, const float *__restrict__ phi,                     \
+      const float *__restrict__ v, const float *__restrict__ w, const float *__restrict__ r,                      \
+      const int32_t *__restrict__ recv, const int32_t *__restrict__ send, int64_t E, int F, int mask,             \
+      const float *__restrict__ gw_acc, float *__restrict__ gw, float *__restrict__ gr
+__global__ void __launch_bounds__(kWarps * 32) edges_kernel(KGCNN_EDGES_PARAMS) {
+  edges_body<false>(gs, gv, phi, v, w, r, recv, send, E, F, mask, nullptr, gw, gr);
+}
+__global__ void __launch_bounds__(kWarps * 32, 3) edges_acc_kernel(KGCNN_EDGES_PARAMS) {   // 3 CTAs / SM like the plain one
+  edges_body<true>(gs, gv, phi, v, w, r, recv, send, E, F, mask, gw_acc, gw, gr);
+}
+#undef KGCNN_EDGES_PARAMS
 
 }  // namespace painn
 }  // namespace kgcnn
@@ -255,7 +276,7 @@ int kgcnn_painn_msg_senders(const float* gs, const float* gv, const float* phi, 
 
 int kgcnn_painn_msg_edges(const float* gs, const float* gv, const float* phi, const float* v, const float* w,
                           const float* r, const int32_t* recv, const int32_t* send, int64_t E, int F, int mask,
-                          float* gw, float* gr, kgcnn_stream_t stream) {
+                          const float* gw_acc, float* gw, float* gr, kgcnn_stream_t stream) {
   if (E < 0 || F <= 0 || (F & 3) || (mask & ~7)) return KGCNN_E_INVALID;
   if (E == 0 || (!gw && !gr)) return KGCNN_OK;
   if (!recv || !send || !phi) return KGCNN_E_INVALID;
@@ -263,10 +284,15 @@ int kgcnn_painn_msg_edges(const float* gs, const float* gv, const float* phi, co
   if ((mask & 6) && !gv) return KGCNN_E_INVALID;
   if ((mask & 2) && gw && !v) return KGCNN_E_INVALID;
   if ((mask & 4) && ((gw && !r) || (gr && !w))) return KGCNN_E_INVALID;
-  if (!ok16(gs) || !ok16(gv) || !ok16(phi) || !ok16(v) || !ok16(w) || !ok16(gw)) return KGCNN_E_INVALID;
+  if (!ok16(gs) || !ok16(gv) || !ok16(phi) || !ok16(v) || !ok16(w) || !ok16(gw) || !ok16(gw_acc)) return KGCNN_E_INVALID;
+  if (gw_acc && (!gw || gw_acc == gw)) return KGCNN_E_INVALID;
   const unsigned grid = static_cast<unsigned>(ceil_div<int64_t>(E, painn::kWarps));
-  painn::edges_kernel<<<grid, painn::kWarps * 32, 0, as_stream(stream)>>>(gs, gv, phi, v, w, r, recv, send, E, F, mask,
-                                                                          gw, gr);
+  if (gw_acc)
+    painn::edges_acc_kernel<<<grid, painn::kWarps * 32, 0, as_stream(stream)>>>(gs, gv, phi, v, w, r, recv, send, E,
+                                                                                  F, mask, gw_acc, gw, gr);
+  else
+    painn::edges_kernel<<<grid, painn::kWarps * 32, 0, as_stream(stream)>>>(gs, gv, phi, v, w, r, recv, send, E,
+                                                                                   F, mask, nullptr, gw, gr);
   return finish_launch();
 }
 

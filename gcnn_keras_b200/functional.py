@@ -1197,8 +1197,9 @@ _PM_TERMS = {"gs": 1, "gv": 6, "phi": 7, "v": 2, "w": 7, "r": 4}        # terms 
 _PM_SLOTS = {"G": ("gs", "gv"), "J": ("phi", "v"), "E": ("w", "r")}     # kernel -> the two derivatives it writes
 
 
-def raw_painn_msg(slot, mask, want_a, want_b, ops, recv, send, F_dim):
-    """(dM/dXa, dM/dXb) for the operand pair of `slot` (csrc/painn.cu); None for an output that is not wanted."""
+def raw_painn_msg(slot, mask, want_a, want_b, ops, recv, send, F_dim, acc_a=None):
+    """(dM/dXa, dM/dXb) for the operand pair of `slot` (csrc/painn.cu); None for an output that is not wanted.
+    acc_a (slot 'E' only): the first output is acc_a + dM/dW (sum of two substitutions without an add pass)."""
     t = {k: (None if x is None else _f32c(x)) for k, x in ops.items()}
     _need_cuda(*[x for x in t.values() if x is not None])
     dev = recv.ids.device
@@ -1227,7 +1228,8 @@ def raw_painn_msg(slot, mask, want_a, want_b, ops, recv, send, F_dim):
     else:
         a, b = new(E, 3 * F_dim, want_a), new(E, 3, want_b)        # gr of an inactive term 3 is written as zeros
         check(L.kgcnn_painn_msg_edges(_ptr(t["gs"]), _ptr(t["gv"]), _ptr(t["phi"]), _ptr(t["v"]), _ptr(t["w"]),
-                                      _ptr(t["r"]), _ptr(recv.ids), _ptr(send.ids), E, F_dim, mask, _ptr(a), _ptr(b),
+                                      _ptr(t["r"]), _ptr(recv.ids), _ptr(send.ids), E, F_dim, mask,
+                                      _ptr(None if acc_a is None or a is None else _f32c(acc_a)), _ptr(a), _ptr(b),
                                       _stream()), "kgcnn_painn_msg_edges")
     return a, b
 
@@ -1239,11 +1241,11 @@ class _PainnMsg(torch.autograd.Function):
     cotangent substituted for the differentiated operand: the class is closed under differentiation."""
 
     @staticmethod
-    def forward(ctx, slot, mask, want_a, want_b, gs, gv, phi, v, w, r, recv, send, F_dim):
+    def forward(ctx, slot, mask, want_a, want_b, gs, gv, phi, v, w, r, recv, send, F_dim, acc_a=None):
         ctx.slot, ctx.mask, ctx.recv, ctx.send, ctx.F_dim = slot, mask, recv, send, F_dim
         ctx.save_for_backward(gs, gv, phi, v, w, r)
         ops = dict(zip(_PM_ORDER, (gs, gv, phi, v, w, r)))
-        a, b = raw_painn_msg(slot, mask, want_a, want_b, ops, recv, send, F_dim)
+        a, b = raw_painn_msg(slot, mask, want_a, want_b, ops, recv, send, F_dim, acc_a)
         return a, b
 
     @staticmethod
@@ -1278,19 +1280,26 @@ class _PainnMsg(torch.autograd.Function):
                 wb = yb not in replaced and needs[yb] and bool(_PM_TERMS[yb] & m)
                 if not (wa or wb):
                     continue
+                # the [E, 3F] filter gradient of a second substitution is summed inside the kernel
+                acc = grads["w"] if (slot == "E" and wa and grads["w"] is not None) else None
                 ra, rb = _PainnMsg.apply(slot, m, wa, wb, o["gs"], o["gv"], o["phi"], o["v"], o["w"], o["r"],
-                                         ctx.recv, ctx.send, ctx.F_dim)
+                                         ctx.recv, ctx.send, ctx.F_dim, acc)
                 for y, res, wanted in ((ya, ra, wa), (yb, rb, wb)):
                     if wanted:
                         res = res.reshape(ops[y].shape)
-                        grads[y] = res if grads[y] is None else grads[y] + res
-        return (None, None, None, None) + tuple(grads[k] for k in _PM_ORDER) + (None, None, None)
+                        if y == "w" and acc is not None:
+                            grads[y] = res
+                        else:
+                            grads[y] = res if grads[y] is None else grads[y] + res
+        # the accumulate operand enters its output with derivative 1
+        g_acc = ca if (ctx.slot == "E" and ctx.needs_input_grad[-1]) else None
+        return (None, None, None, None) + tuple(grads[k] for k in _PM_ORDER) + (None, None, None, g_acc)
 
 
 def painn_message(phi, v, w, r, recv, send):
     """(ds [N,F], dv [N,3,F]) of PAiNNconv (painn_conv.py:104-114) for phi [N,3F], v [N,3,F], w [E,3F], r [E,3]."""
     F_dim = int(phi.shape[1]) // 3
-    return _PainnMsg.apply("G", 7, True, True, None, None, phi, v, w, r, recv, send, F_dim)
+    return _PainnMsg.apply("G", 7, True, True, None, None, phi, v, w, r, recv, send, F_dim, None)
 
 
 # ------------------------------------------------------------------------------------------------

@@ -304,6 +304,7 @@ int kgcnn_painn_msg_senders(const float* gs, const float* gv, const float* phi, 
                             float* gphi /*nullable*/, float* gvv /*nullable*/, kgcnn_stream_t stream);
 int kgcnn_painn_msg_edges(const float* gs, const float* gv, const float* phi, const float* v, const float* w,
                           const float* r, const int32_t* recv, const int32_t* send, int64_t E, int F, int mask,
+                          const float* gw_acc /*nullable: gw = gw_acc + dM/dW, may not alias gw*/,
                           float* gw /*nullable*/, float* gr /*nullable*/, kgcnn_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------

@@ -10,7 +10,7 @@ extern "C" const char* kgcnn_error_string(int) { return ""; }
 
 int main(int argc, char** argv) {
   const int64_t M = argc > 1 ? atoll(argv[1]) : 18432;
-  const int K = 128, U = 128;
+  const int K = argc > 2 ? atoi(argv[2]) : 128, U = argc > 3 ? atoi(argv[3]) : 128;
   float *x, *w, *b, *y, *y2;
   cudaMalloc(&x, M * K * 4); cudaMalloc(&w, K * U * 4); cudaMalloc(&b, U * 4); cudaMalloc(&y, M * U * 4); cudaMalloc(&y2, M * U * 4);
   cudaMemset(x, 0, M * K * 4); cudaMemset(w, 0, K * U * 4); cudaMemset(b, 0, U * 4);
@@ -29,6 +29,8 @@ int main(int argc, char** argv) {
                          "mma0 done", "mma1 done", "mma2 done", "mma3 done", "drained", "epi tile sync", "stores done", "end sync"};
     for (int i = 0; i < 16; ++i) printf("  %-20s %7lld\n", lab[i], t[i] - t[0]);
     printf("  barrier init done %7lld   tmem alloc done (mma warp) %7lld   pointers ready %7lld  row known %7lld  pa known %7lld\n", t[16] - t[0], t[17] - t[0], t[18] - t[0], t[19] - t[0], t[30] - t[0]);
+    printf("  LAST ITERATION (relative to its start): staged+published %lld  mma0 done %lld  mma1 done %lld  drained %lld  prev stores read %lld  bar %lld  tile written+sync %lld  end %lld   | mma warp: full0 seen %lld issued %lld\n",
+           t[32] - t[31], t[8] - t[31], t[9] - t[31], t[12] - t[31], t[33] - t[31], t[34] - t[31], t[13] - t[31], t[35] - t[31], t[20] - t[31], t[21] - t[31]);
     for (int c = 0; c < 4; ++c) printf("  mma warp chunk %d: full seen %7lld  issued %7lld\n", c, t[20 + 2 * c] - t[0], t[21 + 2 * c] - t[0]);
   }
   return 0;
