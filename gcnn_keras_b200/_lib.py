@@ -63,7 +63,7 @@ SIGNATURES = {
     "kgcnn_range_count": (_i, [_p, _i, _p, _l, _l, _i, _i, _d, _i, _i, _i, _p, _p]),
     "kgcnn_range_emit": (_i, [_p, _i, _p, _l, _l, _i, _i, _d, _i, _i, _i, _p, _p, _p, _p, _p]),
     "kgcnn_segment_softmax": (_i, [_p, _p, _p, _l, _l, _i, _i, _p, _p]),
-    "kgcnn_adam_clipnorm": (_i, [_p, _p, _p, _p, _p, _p, _l, _f, _f, _f, _f, _f, _p, _p, _p, _i, _p]),
+    "kgcnn_adam_clipnorm": (_i, [_p, _p, _p, _p, _p, _p, _l, _f, _p, _f, _f, _f, _f, _p, _p, _p, _i, _p]),
 }
 
 OP_SUM, OP_MEAN, OP_MAX, OP_MIN = 0, 1, 2, 3

@@ -18,12 +18,14 @@ __device__ __forceinline__ bool guard_tripped(const int32_t* __restrict__ guard,
 __global__ void __launch_bounds__(256)
 adam_clipnorm_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
                      const int32_t* __restrict__ var_of, const float* __restrict__ sumsq, int64_t n, float lr,
-                     float b1, float b2, float eps, float clipnorm, const int32_t* __restrict__ step,
+                     const float* __restrict__ lr_device, float b1, float b2, float eps, float clipnorm,
+                     const int32_t* __restrict__ step,
                      const int32_t* __restrict__ guard, const int32_t* __restrict__ guard_mask, int n_guard) {
   if (guard_tripped(guard, guard_mask, n_guard)) return;
   const int t = *step + 1;
   const float c1 = 1.f - powf(b1, static_cast<float>(t));
   const float c2 = sqrtf(1.f - powf(b2, static_cast<float>(t)));
+  if (lr_device) lr = *lr_device;                    // a learning-rate schedule under a captured graph
   const float lr_t = lr * c2 / c1;
   for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < n;
        i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
@@ -51,8 +53,8 @@ __global__ void bump_step_kernel(int32_t* step, const int32_t* __restrict__ guar
 using namespace kgcnn;
 
 extern "C" int kgcnn_adam_clipnorm(float* params, const float* grads, float* m, float* v, const int32_t* var_of,
-                                   const float* sumsq, int64_t n, float lr, float beta1, float beta2, float eps,
-                                   float clipnorm, int32_t* step, const int32_t* guard,
+                                   const float* sumsq, int64_t n, float lr, const float* lr_device, float beta1,
+                                   float beta2, float eps, float clipnorm, int32_t* step, const int32_t* guard,
                                    const int32_t* guard_mask, int n_guard, kgcnn_stream_t stream) {
   if (n < 0 || !step || n_guard < 0 || (n_guard > 0 && (!guard || !guard_mask))) return KGCNN_E_INVALID;
   if (!guard) n_guard = 0;
@@ -61,7 +63,8 @@ extern "C" int kgcnn_adam_clipnorm(float* params, const float* grads, float* m, 
   cudaStream_t st = as_stream(stream);
   const unsigned grid = static_cast<unsigned>(ceil_div<int64_t>(n, 256) < kNumSM * 8 ? ceil_div<int64_t>(n, 256)
                                                                                      : kNumSM * 8);
-  adam_clipnorm_kernel<<<grid, 256, 0, st>>>(params, grads, m, v, var_of, sumsq, n, lr, beta1, beta2, eps, clipnorm,
+  adam_clipnorm_kernel<<<grid, 256, 0, st>>>(params, grads, m, v, var_of, sumsq, n, lr, lr_device, beta1, beta2, eps,
+                                             clipnorm,
                                              step, guard, guard_mask, n_guard);
   bump_step_kernel<<<1, 1, 0, st>>>(step, guard, guard_mask, n_guard);
   return finish_launch(2);

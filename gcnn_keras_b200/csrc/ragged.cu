@@ -54,7 +54,7 @@ unpad_kernel(const V* __restrict__ padded, const int64_t* __restrict__ splits, i
     const int64_t c = i % Wv, n = i / Wv;
     const int64_t b = graph_of(splits, B, n);
     const int64_t j = n - __ldg(splits + b);
-    values[i] = __ldg(padded + (b * max_len + j) * Wv + c);
+    values[i] = j < max_len ? __ldg(padded + (b * max_len + j) * Wv + c) : V{};   // rows cut by the pad read as 0
   }
 }
 

@@ -316,8 +316,10 @@ int kgcnn_painn_msg_edges(const float* gs, const float* gv, const float* phi, co
  * CUDA graph, so that a batch that breaks the recorded assumptions cannot corrupt the weights.
  * ------------------------------------------------------------------------------------------- */
 int kgcnn_adam_clipnorm(float* params, const float* grads, float* m, float* v, const int32_t* var_of,
-                        const float* sumsq, int64_t n, float lr, float beta1, float beta2, float eps,
-                        float clipnorm, int32_t* step, const int32_t* guard /*nullable*/,
+                        const float* sumsq, int64_t n, float lr,
+                        const float* lr_device /*nullable; DEVICE scalar that overrides lr (schedules under a graph)*/,
+                        float beta1, float beta2, float eps, float clipnorm, int32_t* step,
+                        const int32_t* guard /*nullable*/,
                         const int32_t* guard_mask /*nullable*/, int n_guard, kgcnn_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
