@@ -650,26 +650,38 @@ def run_gcn(args, rank, world, device):
     per, bounds = partition_bounds(n_nodes, world)
     lo, hi = bounds[rank]
     recv, send, w = gcn_c5_shard(n_nodes, lo, hi, seed=0)
-    # PartitionedGraph slices a global receiver-sorted list; hand it this rank's slice with global ids
-    graph = PartitionedGraph.__new__(PartitionedGraph)
-    graph.n_nodes, graph.rank, graph.world, graph.per, graph.lo, graph.hi = n_nodes, rank, world, per, lo, hi
+    # every rank generates only its own in-edges (receiver ids local to its block, sender ids global); the halo plan
+    # (which rows cross the cut) is host-side preprocessing done once per graph, like the reference's adjacency set-up
+    graph = PartitionedGraph.from_shard(n_nodes, recv - rank * per, send, w, rank, world, device,
+                                        exchange=args.gcn_exchange)
     from gcnn_keras_b200.plan import Relation
-    pin = lambda a: torch.from_numpy(a).pin_memory()
-    recv_p, send_p, w_p = pin((recv - rank * per).astype(np.int32)), pin(send.astype(np.int32)), pin(w.reshape(-1, 1))
     x_p = torch.randn(per, feat).pin_memory()
     E = len(recv)
+    # e2e: the index columns, edge weights and features of the step come from pinned host memory
+    if graph.halo is None:
+        names = [("rel_recv", per, True), ("rel_send", per * world, False)]
+        w_names = ["weights"]
+    else:
+        names = [("recv_loc", per, True), ("send_loc", per, False), ("recv_rem", per, True),
+                 ("send_rem", max(graph.halo.n_halo, 1), False)]
+        w_names = ["w_loc", "w_rem"]
+    pinned_ids = {n: getattr(graph, n).ids.cpu().pin_memory() for n, _, _ in names}
+    pinned_w = {n: getattr(graph, n).cpu().pin_memory() for n in w_names}
+    h2d_bytes = sum(t.numel() * t.element_size() for t in list(pinned_ids.values()) + list(pinned_w.values())) \
+        + x_p.numel() * 4
 
     def load():
-        graph.rel_recv = Relation(recv_p.to(device, non_blocking=True), per, is_sorted=True)
-        graph.rel_send = Relation(send_p.to(device, non_blocking=True), per * world)
-        graph.weights = w_p.to(device, non_blocking=True)
+        for n, targets, is_sorted in names:
+            setattr(graph, n, Relation(pinned_ids[n].to(device, non_blocking=True), targets, is_sorted=is_sorted))
+        for n in w_names:
+            setattr(graph, n, pinned_w[n].to(device, non_blocking=True))
         return x_p.to(device, non_blocking=True).requires_grad_(True)
 
     torch.manual_seed(0)
     kernel = (torch.randn(feat, feat, device=device) / feat ** 0.5).requires_grad_(True)
     bias = torch.zeros(feat, device=device, requires_grad=True)
     x_d = load()
-    graph.rel_recv.rowptr, graph.rel_send.rowptr, graph.rel_send.permuted_ids(graph.rel_recv)
+    graph.warm()
     dy = torch.randn(per, feat, device=device)
 
     def step(x=None):
@@ -702,12 +714,17 @@ def run_gcn(args, rank, world, device):
                                % (n_nodes, feat, world),
                    "nodes": n_nodes, "edges_this_rank": E, "features": feat,
                    "l2_policy": "inputs larger than L2 (node features %.0f MB)" % (n_nodes * feat * 4 / 1e6),
-                   "parallelism": "halo all-gather fwd / reduce-scatter bwd per layer (NCCL), weights replicated"},
+                   "parallelism": ("halo exchange: only the rows referenced across the cut travel (row gather -> NCCL "
+                                   "all-to-all, %d of %d remote rows per rank), overlapped with the local edges; "
+                                   "transpose on the way back; weights replicated"
+                                   % (graph.halo.n_halo, per * (world - 1))) if graph.halo is not None else
+                                  "all-gather of the whole feature matrix fwd / reduce-scatter bwd (NCCL)",
+                   "exchange": args.gcn_exchange},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": None, "kernel": "whole layer step (gms fwd + gms^T bwd dominate)",
                      "algorithmic_bytes_per_step": alg, "peak_source": peak_src},
         "e2e": {"value": total_edges / (ms_e2e * 1e-3), "unit": "edges/s",
-                "h2d_bytes_per_step": recv_p.numel() * 4 + send_p.numel() * 4 + w_p.numel() * 4 + x_p.numel() * 4,
+                "h2d_bytes_per_step": h2d_bytes,
                 "d2h_bytes_per_step": per * feat * 4, "ms_per_step": ms_e2e},
         "gpu_launches": launches * args.steps, "clocks": clocks,
     }
@@ -791,6 +808,8 @@ def main():
     ap.add_argument("--gss-graphs", type=int, default=65536)
     ap.add_argument("--gss-feat", type=int, default=64)
     ap.add_argument("--gcn-nodes", type=int, default=2000000)
+    ap.add_argument("--gcn-exchange", default="halo", choices=["halo", "allgather"],
+                    help="C5 multi-GPU exchange: referenced rows only + overlap (default) or the whole feature matrix")
     ap.add_argument("--gcn-feat", type=int, default=128)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")

@@ -87,3 +87,53 @@ def test_halo_all_gather_and_reduce_scatter_adjoint_world2():
         p.join(120)
         assert p.exitcode == 0
     assert all(ret[r] for r in range(world))
+
+
+def _halo_plan_worker(rank, world, port, ret):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    from gcnn_keras_b200.partition import HaloPlan, _all_to_all_rows, partition_bounds
+    n_nodes, feat = 23, 3
+    per, bounds = partition_bounds(n_nodes, world)
+    rng = np.random.default_rng(11)                       # the same graph on both ranks; each keeps its receivers
+    recv_all = np.sort(rng.integers(0, n_nodes, size=90))
+    send_all = rng.integers(0, n_nodes, size=90)
+    mine = (recv_all // per) == rank
+    send = send_all[mine]
+    plan = HaloPlan(send, rank, world, per, torch.device("cpu"))
+    ok = True
+    # what the OTHER rank reads from this rank's block, from the global edge list
+    for q in range(world):
+        theirs = np.unique(send_all[((recv_all // per) == q) & ((send_all // per) == rank)]) if q != rank else []
+        got = plan.send_ids.numpy()[sum(plan.send_counts[:q]):sum(plan.send_counts[:q + 1])]
+        ok = ok and np.array_equal(got, np.asarray(theirs, dtype=np.int64) - rank * per)
+    ok = ok and plan.n_halo == len(np.unique(send[(send // per) != rank])) and sum(plan.need_counts) == plan.n_halo
+    # forward exchange: the halo buffer holds exactly the remote rows, in ascending global id order
+    table = torch.arange(per * world * feat, dtype=torch.float32).reshape(per * world, feat)
+    local = table[rank * per:(rank + 1) * per]
+    _, halo = _all_to_all_rows(local[plan.send_ids.long()], plan.send_counts, plan.need_counts)
+    ok = ok and torch.equal(halo, table[torch.as_tensor(plan.halo_ids)])
+    # transpose: <halo(h), g> summed over the ranks == <h, back(g)> summed over the ranks
+    g_halo = torch.from_numpy(np.random.default_rng(rank).normal(size=(plan.n_halo, feat)).astype(np.float32))
+    _, back = _all_to_all_rows(g_halo, plan.need_counts, plan.send_counts)
+    dlocal = torch.zeros(per, feat).index_add_(0, plan.send_ids.long(), back)
+    sums = torch.tensor([float((halo * g_halo).sum()), float((local * dlocal).sum())], dtype=torch.float64)
+    dist.all_reduce(sums)
+    ok = ok and abs(float(sums[0] - sums[1])) <= 1e-6 * abs(float(sums[0]))
+    ret[rank] = bool(ok)
+    dist.destroy_process_group()
+
+
+def test_halo_plan_exchanges_only_referenced_rows_and_is_adjoint_world2():
+    world, port = 2, 33500 + (os.getpid() % 2000)
+    ctx = mp.get_context("spawn")
+    ret = ctx.Manager().dict()
+    procs = [ctx.Process(target=_halo_plan_worker, args=(r, world, port, ret)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(120)
+        assert p.exitcode == 0
+    assert all(ret[r] for r in range(world))

@@ -1,0 +1,61 @@
+"""Two-GPU NCCL checks of the partitioned-graph path (skipped on a one-GPU box; run with `gpurun --gpus 2`)."""
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+pytestmark = pytest.mark.gpu
+
+
+def _worker(rank, world, port, ret):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    from gcnn_keras_b200.partition import PartitionedGraph, gcn_layer_partitioned, partition_bounds
+    dev = torch.device("cuda", rank)
+    n_nodes, feat = 5000, 64
+    rng = np.random.default_rng(3)                         # the same graph on every rank
+    recv = np.sort(rng.integers(0, n_nodes, size=60000))
+    send = rng.integers(0, n_nodes, size=60000)
+    w = rng.random(60000).astype(np.float32)
+    per, bounds = partition_bounds(n_nodes, world)
+    torch.manual_seed(0)
+    x_full = torch.randn(per * world, feat, device=dev)
+    kernel = (torch.randn(feat, feat, device=dev) / 8).requires_grad_(True)
+    bias = torch.zeros(feat, device=dev, requires_grad=True)
+    dy = torch.randn(per * world, feat, device=dev)[rank * per:(rank + 1) * per]
+    outs = {}
+    for mode in ("halo", "allgather"):
+        graph = PartitionedGraph(n_nodes, recv, send, w, rank, world, dev, exchange=mode)
+        x = x_full[rank * per:(rank + 1) * per].clone().requires_grad_(True)
+        y = gcn_layer_partitioned(graph, x, kernel, bias, "relu")
+        gx, gk, gb = torch.autograd.grad(y, [x, kernel, bias], dy)
+        outs[mode] = (y.detach(), gx, gk, gb)
+        if mode == "halo":
+            n_halo = graph.halo.n_halo
+    ok = n_halo < per * (world - 1)                        # fewer rows travel than the all-gather moves
+    for a, b in zip(outs["halo"], outs["allgather"]):
+        scale = float(b.abs().max()) + 1e-30
+        ok = ok and float((a - b).abs().max()) <= 2e-6 * scale
+    ret[rank] = bool(ok)
+    dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_halo_exchange_equals_all_gather_scheme_on_two_gpus():
+    world, port = 2, 35500 + (os.getpid() % 2000)
+    ctx = mp.get_context("spawn")
+    ret = ctx.Manager().dict()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, ret)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(300)
+        assert p.exitcode == 0
+    assert all(ret[r] for r in range(world))
