@@ -19,10 +19,22 @@
 namespace kgcnn {
 namespace tc {
 
+// persistent walk: W planes (4 chunks) + X planes (4 chunks) or two dense 64 KB output tiles behind the W planes
+constexpr size_t kSmemBytesPersistent = static_cast<size_t>(kStages) * 3 * kPlaneUnits * 16 + 2 * kBM * kMaxN * 4;
+static_assert(kSmemBytesPersistent >= kSmemBytesDecl && kSmemBytesPersistent + 1024 <= 232448, "fits one SM");
+
 // RAG 0: everything aligned.  RAG 1 (NN): reduction length K arbitrary <= 128, rows of A unaligned (the [E, 20..25]
 // radial-basis inputs of the filter networks): element-wise predicated loads of A, rows of W past K read as zero.
 // RAG 2 (NT): output width K arbitrary (the gradient with respect to that basis): element-wise stores.
-template <int OP, int ACT, int RAG>   // ACT < 0: one output; otherwise out = pre, act_out = f_ACT(pre)
+//
+// TR (output width a multiple of 128): the MMA computes the TRANSPOSED tile, D^T = W^T X^T -- the operand roles are
+// swapped in the instruction (the shared-memory planes and descriptors are the same), so a TMEM lane is an output
+// COLUMN and the 32 lanes of a warp write 32 consecutive floats of one output row.  The output tile can then be
+// dense in shared memory (pitch 512 B, conflict-free) and a [rows, 128] matrix leaves as ONE bulk copy of up to 64 KB
+// instead of 128 copies of one padded row each (measured with tools/tc_timeline.cu: issuing the 128 row copies took
+// ~2 400 cycles of a ~6 000-cycle tile).
+template <int OP, int ACT, int RAG, bool TR, bool PS>   // ACT < 0: one output; else out = pre, act_out = f_ACT(pre)
+                                                          // PS: persistent walk over row tiles (grid.x < tiles)
 __global__ void __launch_bounds__(kCtaThreads)
 dense_fast_kernel(const float* __restrict__ A, const float* __restrict__ B, int64_t M, int K, int U,
                   const float* __restrict__ bias, float* __restrict__ out, float* __restrict__ act_out) {
@@ -31,7 +43,12 @@ dense_fast_kernel(const float* __restrict__ A, const float* __restrict__ B, int6
   __shared__ __align__(8) uint64_t full[kStages];
   __shared__ uint32_t tmem_base_s;
   __shared__ __align__(16) float bias_s[kMaxN];
-  uint4* planes = reinterpret_cast<uint4*>(smem_raw);            // [stage][a1, a2, a3, b1, b2, b3][kPlaneUnits]
+  // shared memory: [W planes: chunk][b1, b2, b3] then [X planes: chunk][a1, a2, a3], kPlaneUnits 16-byte units each.
+  // The persistent walk keeps the W region for the whole kernel and reuses the X region (and what lies behind it)
+  // for the output tile.
+  uint4* planes = reinterpret_cast<uint4*>(smem_raw);
+  auto b_planes = [&](int c) { return planes + static_cast<size_t>(c) * 3 * kPlaneUnits; };
+  auto a_planes = [&](int c) { return planes + static_cast<size_t>(kStages + c) * 3 * kPlaneUnits; };
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   TL(0);
   // Touch every kernel parameter first: the constant-bank misses of a freshly launched kernel (~700 cycles per access
@@ -45,8 +62,8 @@ dense_fast_kernel(const float* __restrict__ A, const float* __restrict__ B, int6
   int64_t m0 = static_cast<int64_t>(blockIdx.x) * kBM;
   const int nchunk = (red + kKC - 1) / kKC;                      // 1 .. 4
   const int64_t ntiles = (M + kBM - 1) / kBM;
-  const bool persistent = gridDim.x < ntiles;                    // the launcher guarantees nchunk <= 2 and the smem
-  const int my_tiles = static_cast<int>((ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x);
+  constexpr bool persistent = PS;                                // the launcher guarantees nchunk <= 2 and the smem
+  const int my_tiles = PS ? static_cast<int>((ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x) : 1;
 
   if (warp == kThreads / 32) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)),
@@ -136,7 +153,10 @@ dense_fast_kernel(const float* __restrict__ A, const float* __restrict__ B, int6
   const int c0 = 32 * (warp >> 2);                       // this warp's 32 accumulator columns (staging warps only)
   if (warp == kThreads / 32) {
     // ------------------------------- MMA-issue warp -------------------------------
-    const uint32_t idesc = make_idesc(0, kBMn ? 1 : 0, nt);
+    const uint32_t idesc = TR ? make_idesc(kBMn ? 1 : 0, 0, kBM) : make_idesc(0, kBMn ? 1 : 0, nt);
+    auto mm = [&](uint32_t acc, uint64_t xd, uint64_t wd, uint32_t flag) {
+      if (TR) mma_bf16(acc, wd, xd, idesc, flag); else mma_bf16(acc, xd, wd, idesc, flag);
+    };
     const uint64_t da_hi = desc_hi_bits(kPitchK, 8);
     const uint64_t db_hi = kBMn ? desc_hi_bits(8, kKC) : desc_hi_bits(kPitchK, 8);
     constexpr uint32_t a_step = 2 * kPitchK;
@@ -147,23 +167,23 @@ dense_fast_kernel(const float* __restrict__ A, const float* __restrict__ B, int6
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       TL(20 + 2 * c);
       if (lane == 0) {
-        const uint32_t base = smem_u32(planes + static_cast<size_t>(c) * kStageUnits) >> 4;
-        const uint64_t a1 = da_hi | (base & 0x3FFF), a2 = a1 + kPlaneUnits, a3 = a2 + kPlaneUnits;
-        const uint64_t b1 = db_hi | ((base + 3 * kPlaneUnits) & 0x3FFF), b2 = b1 + kPlaneUnits, b3 = b2 + kPlaneUnits;
+        const uint32_t base_a = smem_u32(a_planes(c)) >> 4, base_b = smem_u32(b_planes(c)) >> 4;
+        const uint64_t a1 = da_hi | (base_a & 0x3FFF), a2 = a1 + kPlaneUnits, a3 = a2 + kPlaneUnits;
+        const uint64_t b1 = db_hi | (base_b & 0x3FFF), b2 = b1 + kPlaneUnits, b3 = b2 + kPlaneUnits;
         const uint32_t acc = tmem_d + static_cast<uint32_t>(c * kMaxN);
         // small terms first (see dense_tc.cu)
-        mma_bf16(acc, a3, b1, idesc, 0u);
-        mma_bf16(acc, a1, b3, idesc, 1u);
-        mma_bf16(acc, a2, b2, idesc, 1u);
-        mma_bf16(acc, a3 + a_step, b1 + bk_step, idesc, 1u);
-        mma_bf16(acc, a1 + a_step, b3 + bk_step, idesc, 1u);
-        mma_bf16(acc, a2 + a_step, b2 + bk_step, idesc, 1u);
-        mma_bf16(acc, a2, b1, idesc, 1u);
-        mma_bf16(acc, a1, b2, idesc, 1u);
-        mma_bf16(acc, a2 + a_step, b1 + bk_step, idesc, 1u);
-        mma_bf16(acc, a1 + a_step, b2 + bk_step, idesc, 1u);
-        mma_bf16(acc, a1, b1, idesc, 1u);
-        mma_bf16(acc, a1 + a_step, b1 + bk_step, idesc, 1u);
+        mm(acc, a3, b1, 0u);
+        mm(acc, a1, b3, 1u);
+        mm(acc, a2, b2, 1u);
+        mm(acc, a3 + a_step, b1 + bk_step, 1u);
+        mm(acc, a1 + a_step, b3 + bk_step, 1u);
+        mm(acc, a2 + a_step, b2 + bk_step, 1u);
+        mm(acc, a2, b1, 1u);
+        mm(acc, a1, b2, 1u);
+        mm(acc, a2 + a_step, b1 + bk_step, 1u);
+        mm(acc, a1 + a_step, b2 + bk_step, 1u);
+        mm(acc, a1, b1, 1u);
+        mm(acc, a1 + a_step, b1 + bk_step, 1u);
         asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
                          smem_u32(&mbar[c]))
                      : "memory");
@@ -174,9 +194,8 @@ dense_fast_kernel(const float* __restrict__ A, const float* __restrict__ B, int6
   } else {
     // ------------------------------- staging warps -------------------------------
     auto stage = [&](int c, const F8& ra, const F8& rb) {
-      uint4* sa = planes + static_cast<size_t>(c) * kStageUnits;
-      store_kmajor(ra, sa);
-      if (kBMn) store_mnmajor(rb, sa + 3 * kPlaneUnits); else store_kmajor(rb, sa + 3 * kPlaneUnits);
+      store_kmajor(ra, a_planes(c));
+      if (kBMn) store_mnmajor(rb, b_planes(c)); else store_kmajor(rb, b_planes(c));
     };
     auto publish = [&](int c) {
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // generic-proxy stores -> async proxy (MMA)
@@ -184,16 +203,31 @@ dense_fast_kernel(const float* __restrict__ A, const float* __restrict__ B, int6
       __syncwarp();
       if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&full[c])) : "memory");
     };
-    auto stage_a = [&](int c, const F8& ra) { store_kmajor(ra, planes + static_cast<size_t>(c) * kStageUnits); };
+    auto stage_a = [&](int c, const F8& ra) { store_kmajor(ra, a_planes(c)); };
     const int d_row = 32 * (warp & 3) + lane;                      // epilogue: lane = output row, columns c0 .. c0 + 31
     constexpr int OP_PITCH = kMaxN + 4;
-    // one-tile launches alias the output tile onto the operand stages (free once every MMA has completed); the
-    // persistent loop keeps W staged and the next tile's stores in flight, so its output tile lies behind the stages
-    float* otile = reinterpret_cast<float*>(smem_raw + (persistent ? static_cast<size_t>(nchunk) * kStageUnits * 16 : 0));
-    float* atile = otile + kBM * OP_PITCH;
+    // One-tile launches alias the output tile(s) onto the operand planes from the start of shared memory (free once
+    // every MMA has completed).  The persistent walk keeps W staged: its output tile(s) lie behind the X planes of
+    // this reduction length when that fits (the bulk stores of a tile then overlap the staging of the next), else ON
+    // the X planes (staging waits until the stores have read them).
+    constexpr size_t kTileBytes = static_cast<size_t>(kBM) * (TR ? kMaxN : OP_PITCH) * sizeof(float) * (ACT >= 0 ? 2 : 1);
+    const size_t x_end = static_cast<size_t>(kStages + nchunk) * 3 * kPlaneUnits * 16;
+    const bool alias_x = PS && (x_end + kTileBytes > kSmemBytesPersistent);                  // CTA-uniform
+    float* otile = reinterpret_cast<float*>(
+        smem_raw + (!PS ? 0 : (alias_x ? static_cast<size_t>(kStages) * 3 * kPlaneUnits * 16 : x_end)));
+    float* atile = otile + kBM * (TR ? kMaxN : OP_PITCH);
+    auto stage_b = [&](int c, const F8& rb) {
+      if (kBMn) store_mnmajor(rb, b_planes(c)); else store_kmajor(rb, b_planes(c));
+    };
+    if (PS) {                                                      // W is staged once for all tiles
+      stage_b(0, vb0);
+      if (nchunk > 1) stage_b(1, vb1);
+      if (nchunk > 2) { vb0 = ld_b(2); if (nchunk > 3) vb1 = ld_b(3); stage_b(2, vb0); }
+      if (nchunk > 3) stage_b(3, vb1);
+    }
     for (int it = 0; it < my_tiles; ++it) {
       TL(31);
-      if (it == 0) {
+      if (!PS) {
         stage(0, va0, vb0);
         TL(3);
         if (nchunk > 2) vb0 = ld_b(2);
@@ -203,24 +237,27 @@ dense_fast_kernel(const float* __restrict__ A, const float* __restrict__ B, int6
         if (nchunk > 1) { stage(1, va1, vb1); if (nchunk > 3) vb1 = ld_b(3); publish(1); TL(5); }
         if (nchunk > 2) { stage(2, va2, vb0); publish(2); TL(6); }
         if (nchunk > 3) { stage(3, va0, vb1); publish(3); TL(7); }
-      } else {                                                     // persistent: W stays staged, nchunk <= 2
+      } else {
+        if (it > 0 && alias_x) {                                   // the previous tile's bulk stores have read the X planes
+          if (threadIdx.x < kBM) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+          asm volatile("bar.sync 1, %0;" ::"r"(kThreads) : "memory");
+        }
+        TL(36);
         stage_a(0, va0);
+        if (nchunk > 3) va0 = ld_a(3);                             // pa already points at this tile's rows
         publish(0);
         if (nchunk > 1) { stage_a(1, va1); publish(1); }
+        if (nchunk > 2) { stage_a(2, va2); publish(2); }
+        TL(37);
+        if (nchunk > 3) { stage_a(3, va0); publish(3); }
       }
       TL(32);
-      if (it + 1 < my_tiles) {                                     // next tile's rows: in flight during drain + epilogue
-        const int64_t row = min(m0 + static_cast<int64_t>(gridDim.x) * kBM + (threadIdx.x >> 2), M - 1);
-        pa = reinterpret_cast<const float4*>(A + row * red + 8 * (threadIdx.x & 3));
-        va0 = ld_a(0);
-        if (nchunk > 1) va1 = ld_a(1);
-      }
       // accumulator c holds chunk c: fp32 (RN) sum in registers
       for (int c = 0; c < nchunk; ++c) {
         wait_chunk(c, it);
         TL(8 + c);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        if (c0 < nt) {
+        if (TR || c0 < nt) {
           const uint32_t taddr = tmem_d + (static_cast<uint32_t>(32 * (warp & 3)) << 16) + static_cast<uint32_t>(c * kMaxN + c0);
 #pragma unroll
           for (int h = 0; h < 2; ++h) {
@@ -240,14 +277,30 @@ dense_fast_kernel(const float* __restrict__ A, const float* __restrict__ B, int6
         }
       }
       TL(12);
+      if (it + 1 < my_tiles) {                                     // next tile's rows: in flight during the epilogue
+        const int64_t row = min(m0 + static_cast<int64_t>(gridDim.x) * kBM + (threadIdx.x >> 2), M - 1);
+        pa = reinterpret_cast<const float4*>(A + row * red + 8 * (threadIdx.x & 3));
+        va0 = ld_a(0);
+        if (nchunk > 1) va1 = ld_a(1);
+        if (nchunk > 2) va2 = ld_a(2);
+      }
 
-      if (it > 0) {                                                // the previous tile's bulk stores have read otile
-        if (threadIdx.x < kBM) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+      if (it > 0 && !alias_x) {                                    // the previous tile's bulk stores have read otile
+        if (threadIdx.x < kBM) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // the issuing threads
         TL(33);
         asm volatile("bar.sync 1, %0;" ::"r"(kThreads) : "memory");
       }
       TL(34);
-      if (c0 < nt) {
+      if (TR) {                                                    // lane = output column, registers = 32 rows
+        const int col = 32 * (warp & 3) + lane;
+        const float bv = (OP == kNN) ? bias_s[col] : 0.f;
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          const float v = racc[i] + bv;
+          otile[(c0 + i) * kMaxN + col] = v;
+          if (ACT >= 0) atile[(c0 + i) * kMaxN + col] = act_deriv<ACT < 0 ? 0 : ACT>(v, 0);
+        }
+      } else if (c0 < nt) {
 #pragma unroll
         for (int i = 0; i < 32; i += 4) {
           float4 v = make_float4(racc[i], racc[i + 1], racc[i + 2], racc[i + 3]);
@@ -272,18 +325,33 @@ dense_fast_kernel(const float* __restrict__ A, const float* __restrict__ B, int6
           for (int cidx = lane; cidx < ncols; cidx += 32)
             out[(m0 + r) * n_total + n0 + cidx] = otile[r * OP_PITCH + cidx];
         }
+      } else if (TR && n_total == kMaxN) {                           // the tile is one contiguous range of the output
+        if (threadIdx.x == 0) {
+          const int64_t rows = min(static_cast<int64_t>(kBM), M - m0);
+          const uint32_t bytes = static_cast<uint32_t>(rows) * kMaxN * 4u;
+          asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(out + m0 * kMaxN),
+                       "r"(smem_u32(otile)), "r"(bytes)
+                       : "memory");
+          if (ACT >= 0)
+            asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(act_out + m0 * kMaxN),
+                         "r"(smem_u32(atile)), "r"(bytes)
+                         : "memory");
+          asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+          if (it + 1 == my_tiles) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        }
       } else if (threadIdx.x < kBM) {
         if (m0 + threadIdx.x < M) {
           const int r = threadIdx.x;
           const uint32_t bytes = static_cast<uint32_t>(nt) * 4u;
+          const int pitch = TR ? kMaxN : OP_PITCH;
           asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(
                            out + (m0 + r) * n_total + n0),
-                       "r"(smem_u32(otile + r * OP_PITCH)), "r"(bytes)
+                       "r"(smem_u32(otile + r * pitch)), "r"(bytes)
                        : "memory");
           if (ACT >= 0)
             asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(
                              act_out + (m0 + r) * n_total + n0),
-                         "r"(smem_u32(atile + r * OP_PITCH)), "r"(bytes)
+                         "r"(smem_u32(atile + r * pitch)), "r"(bytes)
                          : "memory");
         }
         asm volatile("cp.async.bulk.commit_group;" ::: "memory");
@@ -304,24 +372,37 @@ dense_fast_kernel(const float* __restrict__ A, const float* __restrict__ B, int6
   }
 }
 
-template <int OP, int ACT, int RAG = 0>
-static void launch_fast(const float* A, const float* B, int64_t M, int K, int U, const float* bias, float* out,
+template <int OP, int ACT, int RAG, bool TR>
+static void launch_fast_tr(const float* A, const float* B, int64_t M, int K, int U, const float* bias, float* out,
                         float* act_out, cudaStream_t st) {
   static PerDeviceOnce attr;
   attr.run([] {
-    cudaFuncSetAttribute(dense_fast_kernel<OP, ACT, RAG>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaFuncSetAttribute(dense_fast_kernel<OP, ACT, RAG, TR, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                          static_cast<int>(kSmemBytesDecl));
+    cudaFuncSetAttribute(dense_fast_kernel<OP, ACT, RAG, TR, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         static_cast<int>(kSmemBytesPersistent));
   });
-  const int n_total = (OP == kNN) ? U : K, red = (OP == kNN) ? K : U;
-  const int nchunk = ceil_div(red, kKC), col_tiles = ceil_div(n_total, kMaxN);
+  const int n_total = (OP == kNN) ? U : K;
+  const int col_tiles = ceil_div(n_total, kMaxN);
   int64_t row_ctas = ceil_div<int64_t>(M, kBM);
-  // persistent walk over the row tiles: short reductions only (stages + separate output tile(s) must fit), and only
-  // when there are more than two waves of tiles to amortise over
-  const size_t need = static_cast<size_t>(nchunk) * kStageUnits * 16 + (ACT >= 0 ? 2 : 1) * kBM * (kMaxN + 4) * sizeof(float);
-  if (nchunk <= 2 && need <= kSmemBytesDecl && row_ctas * col_tiles > 2 * kNumSM)
-    row_ctas = std::max(1, kNumSM / col_tiles);
+  // persistent walk over the row tiles when there are more than two waves of them to amortise the set-up over
+  if (row_ctas * col_tiles > 2 * kNumSM && (ACT < 0 || TR)) {     // (two PADDED tiles do not fit behind W)
+    dim3 grid(static_cast<unsigned>(std::max(1, kNumSM / col_tiles)), col_tiles);
+    dense_fast_kernel<OP, ACT, RAG, TR, true><<<grid, kCtaThreads, kSmemBytesPersistent, st>>>(A, B, M, K, U, bias, out,
+                                                                                               act_out);
+    return;
+  }
   dim3 grid(static_cast<unsigned>(row_ctas), col_tiles);
-  dense_fast_kernel<OP, ACT, RAG><<<grid, kCtaThreads, kSmemBytesDecl, st>>>(A, B, M, K, U, bias, out, act_out);
+  dense_fast_kernel<OP, ACT, RAG, TR, false><<<grid, kCtaThreads, kSmemBytesDecl, st>>>(A, B, M, K, U, bias, out,
+                                                                                        act_out);
+}
+
+template <int OP, int ACT, int RAG = 0>
+static void launch_fast(const float* A, const float* B, int64_t M, int K, int U, const float* bias, float* out,
+                        float* act_out, cudaStream_t st) {
+  const int n_total = (OP == kNN) ? U : K;
+  if (RAG != 2 && n_total % kMaxN == 0) launch_fast_tr<OP, ACT, RAG, (RAG != 2)>(A, B, M, K, U, bias, out, act_out, st);
+  else launch_fast_tr<OP, ACT, RAG, false>(A, B, M, K, U, bias, out, act_out, st);
 }
 
 bool dense_fast_try_launch(int op, const float* A, const float* B, int64_t M, int K, int U, const float* bias,

@@ -40,7 +40,7 @@ def err(a, b):
 print("%-22s %9s %9s %9s   %9s %9s %9s   (us per launch in a graph, back to back; rel err vs fp64)" %
       ("shape M,K,U", "NN", "NT", "TN", "errNN", "errNT", "errTN"))
 for M, K, U in [(18432, 128, 128), (2304, 128, 128), (18432, 25, 128), (2304, 128, 64), (256, 64, 1), (404544, 128, 128),
-                (404544, 20, 384), (404544, 64, 128), (404544, 32, 128), (50000, 20, 384), (15360, 128, 384), (16384, 640, 35), (16384, 35, 35)]:
+                (404544, 20, 384), (404544, 64, 128), (404544, 32, 128), (2000000, 128, 128), (50000, 20, 384), (15360, 128, 384), (16384, 640, 35), (16384, 35, 35)]:
     x = torch.randn(M, K, device="cuda"); w = torch.randn(K, U, device="cuda") / K ** 0.5
     g = torch.randn(M, U, device="cuda"); bias = torch.randn(U, device="cuda")
     r = [t(lambda: F.raw_dense_tc(0, x, w, bias)), t(lambda: F.raw_dense_tc(1, g, w)), t(lambda: F.raw_dense_tc(2, x, g))]

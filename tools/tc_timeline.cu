@@ -18,7 +18,7 @@ int main(int argc, char** argv) {
   for (int mode = 0; mode < 3; ++mode) {
     for (int rep = 0; rep < 5; ++rep) {
       if (mode == 0) kgcnn_dense_tc(0, x, w, M, K, U, b, y, nullptr, 0, nullptr);
-      if (mode == 1) kgcnn_dense_tc(1, x, w, M, K, U, nullptr, y, nullptr, 0, nullptr);
+      if (mode == 1 && K == U) kgcnn_dense_tc(1, x, w, M, K, U, nullptr, y, nullptr, 0, nullptr);
       if (mode == 2) kgcnn_dense_act(x, w, M, K, U, b, 1, y, y2, nullptr);
     }
     cudaError_t e = cudaDeviceSynchronize();
@@ -31,6 +31,9 @@ int main(int argc, char** argv) {
     printf("  barrier init done %7lld   tmem alloc done (mma warp) %7lld   pointers ready %7lld  row known %7lld  pa known %7lld\n", t[16] - t[0], t[17] - t[0], t[18] - t[0], t[19] - t[0], t[30] - t[0]);
     printf("  LAST ITERATION (relative to its start): staged+published %lld  mma0 done %lld  mma1 done %lld  drained %lld  prev stores read %lld  bar %lld  tile written+sync %lld  end %lld   | mma warp: full0 seen %lld issued %lld\n",
            t[32] - t[31], t[8] - t[31], t[9] - t[31], t[12] - t[31], t[33] - t[31], t[34] - t[31], t[13] - t[31], t[35] - t[31], t[20] - t[31], t[21] - t[31]);
+    printf("  LAST ITERATION 2: alias wait done %lld  chunks 0-2 published %lld  all published %lld  mma0..3 done %lld %lld %lld %lld  drained %lld  tile written+sync %lld  end %lld | mma warp full seen/issued: %lld/%lld %lld/%lld %lld/%lld %lld/%lld\n",
+           t[36] - t[31], t[37] - t[31], t[32] - t[31], t[8] - t[31], t[9] - t[31], t[10] - t[31], t[11] - t[31], t[12] - t[31], t[13] - t[31], t[35] - t[31],
+           t[20] - t[31], t[21] - t[31], t[22] - t[31], t[23] - t[31], t[24] - t[31], t[25] - t[31], t[26] - t[31], t[27] - t[31]);
     for (int c = 0; c < 4; ++c) printf("  mma warp chunk %d: full seen %7lld  issued %7lld\n", c, t[20 + 2 * c] - t[0], t[21 + 2 * c] - t[0]);
   }
   return 0;
