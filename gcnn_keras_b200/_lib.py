@@ -51,6 +51,8 @@ SIGNATURES = {
     "kgcnn_dense_rel_workspace_bytes": (_z, [_i, _i, _i, _i]),
     "kgcnn_dense_rel": (_i, [_i, _p, _p, _p, _i, _l, _i, _i, _p, _p, _p, _z, _p]),
     "kgcnn_edge_geometry": (_i, [_p, _p, _p, _l, _i, _i, _i, _p, _p, _f, _i, _f, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
+    "kgcnn_bessel_frequency_grad_workspace_bytes": (_z, [_i]),
+    "kgcnn_bessel_frequency_grad": (_i, [_p, _p, _p, _l, _i, _p, _p, _f, _p, _p, _p, _p, _z, _p]),
     "kgcnn_acsf_g2": (_i, [_p, _p, _p, _p, _p, _p, _i, _p, _i, _i, _f, _l, _p, _i, _p, _p, _p, _p]),
     "kgcnn_acsf_g4": (_i, [_p, _p, _p, _p, _i, _p, _p, _p, _p, _p, _i, _i, _f, _f, _i, _l, _p, _p, _p, _p, _l, _i, _p, _p, _p, _p]),
     "kgcnn_painn_msg_nodes": (_i, [_p, _p, _p, _p, _p, _p, _p, _i, _l, _l, _i, _i, _p, _p, _p]),

@@ -142,6 +142,73 @@ edge_geometry_kernel(const float* __restrict__ xyz, const int32_t* __restrict__ 
   }
 }
 
+
+// ---------------------------------------------------------------------------------------------------------
+// Gradient of a scalar with respect to the TRAINABLE Bessel frequencies f_n (kgcnn/layers/geom.py:766-770):
+//   tangent_xyz == nullptr :  g_f[n] = sum_e c[e,n] d rbf_n / d f_n              (through the energy)
+//   tangent_xyz != nullptr :  g_f[n] = sum_e c[e,n] t_d[e] d2 rbf_n / (d d  d f_n)   (through the forces: c is the
+//                              cotangent that entered the coordinate VJP, t_d = (d d / d x) . tangent)
+// with  d rbf / d f = env x cos(f x),   d2 rbf / (d d d f) = (env' x cos + env cos - env f x sin) / c,   x = d / c.
+// One lane per frequency, one edge per warp and iteration; block partials, then a fixed-order sum: deterministic.
+// ---------------------------------------------------------------------------------------------------------
+constexpr int kFreqBlocks = 2 * kNumSM;
+constexpr int kFreqWarps = 8;
+
+__global__ void __launch_bounds__(kFreqWarps * 32)
+bessel_freq_partial_kernel(const float* __restrict__ xyz, const int32_t* __restrict__ idx_i,
+                           const int32_t* __restrict__ idx_j, int64_t E, GeoParams prm, const float* __restrict__ freq,
+                           const float* __restrict__ cot, const float* __restrict__ h, float* __restrict__ partial) {
+  __shared__ float red[kFreqWarps][kMaxBasis];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int R = prm.R;
+  const float f0 = lane < R ? __ldg(freq + lane) : 0.f, f1 = lane + 32 < R ? __ldg(freq + lane + 32) : 0.f;
+  float acc0 = 0.f, acc1 = 0.f;
+  const int64_t per = (E + gridDim.x - 1) / gridDim.x;
+  const int64_t e_beg = blockIdx.x * per, e_end = min(E, e_beg + per);
+  for (int64_t e = e_beg + warp; e < e_end; e += kFreqWarps) {
+    const int i = __ldg(idx_i + e), j = __ldg(idx_j + e);
+    const float vx = __ldg(xyz + 3 * i) - __ldg(xyz + 3 * j);
+    const float vy = __ldg(xyz + 3 * i + 1) - __ldg(xyz + 3 * j + 1);
+    const float vz = __ldg(xyz + 3 * i + 2) - __ldg(xyz + 3 * j + 2);
+    const float d = sqrtf(fmaxf(vx * vx + vy * vy + vz * vz, 0.f) + prm.eps);
+    const float x = d * prm.inv_cutoff;
+    float env, denv;
+    bessel_env(x, prm.p, env, denv);
+    float t_d = 1.f;
+    if (h) {
+      const float hx = __ldg(h + 3 * i) - __ldg(h + 3 * j), hy = __ldg(h + 3 * i + 1) - __ldg(h + 3 * j + 1),
+                  hz = __ldg(h + 3 * i + 2) - __ldg(h + 3 * j + 2);
+      t_d = (d > 0.f) ? (vx * hx + vy * hy + vz * hz) / d : 0.f;
+    }
+    auto term = [&](float f) {
+      float sn, cs;
+      sincosf(f * x, &sn, &cs);
+      return h ? t_d * (denv * x * cs + env * cs - env * f * x * sn) * prm.inv_cutoff : env * x * cs;
+    };
+    if (lane < R) acc0 += __ldg(cot + e * R + lane) * term(f0);
+    if (lane + 32 < R) acc1 += __ldg(cot + e * R + lane + 32) * term(f1);
+  }
+  red[warp][lane] = acc0;
+  red[warp][lane + 32] = acc1;
+  __syncthreads();
+  if (threadIdx.x < kMaxBasis) {
+    float s = 0.f;
+#pragma unroll
+    for (int w = 0; w < kFreqWarps; ++w) s += red[w][threadIdx.x];
+    if (threadIdx.x < R) partial[static_cast<int64_t>(blockIdx.x) * R + threadIdx.x] = s;
+  }
+}
+
+__global__ void bessel_freq_reduce_kernel(const float* __restrict__ partial, int blocks, int R, float* __restrict__ out) {
+  const int n = threadIdx.x;
+  if (n >= R) return;
+  float s0 = 0.f, s1 = 0.f;
+  int b = 0;
+  for (; b + 1 < blocks; b += 2) { s0 += partial[b * R + n]; s1 += partial[(b + 1) * R + n]; }
+  if (b < blocks) s0 += partial[b * R + n];
+  out[n] = s0 + s1;
+}
+
 }  // namespace
 }  // namespace kgcnn
 
@@ -177,6 +244,33 @@ int kgcnn_edge_geometry(const float* xyz, const int32_t* idx_i, const int32_t* i
   if (mode == kGeoFwd) KGCNN_GEO(kGeoFwd); else if (mode == kGeoVjp) KGCNN_GEO(kGeoVjp); else KGCNN_GEO(kGeoJvp);
 #undef KGCNN_GEO
   return finish_launch();
+}
+
+size_t kgcnn_bessel_frequency_grad_workspace_bytes(int R) {
+  return R > 0 ? static_cast<size_t>(kFreqBlocks) * R * sizeof(float) : 0;
+}
+
+int kgcnn_bessel_frequency_grad(const float* xyz, const int32_t* idx_i, const int32_t* idx_j, int64_t E, int R,
+                                const float* basis_params, const float* frequencies, float eps, const float* cot_rbf,
+                                const float* tangent_xyz, float* out, void* workspace, size_t workspace_bytes,
+                                kgcnn_stream_t stream) {
+  static_assert(kMaxBasis == 64, "two frequencies per lane");
+  if (E < 0 || R <= 0 || R > kMaxBasis || !basis_params || !frequencies || !out) return KGCNN_E_INVALID;
+  cudaStream_t st = as_stream(stream);
+  if (E == 0) return cudaMemsetAsync(out, 0, sizeof(float) * R, st) == cudaSuccess ? KGCNN_OK : KGCNN_E_CUDA;
+  if (!xyz || !idx_i || !idx_j || !cot_rbf) return KGCNN_E_INVALID;
+  if (!workspace || workspace_bytes < kgcnn_bessel_frequency_grad_workspace_bytes(R)) return KGCNN_E_WORKSPACE;
+  GeoParams prm;
+  prm.basis = kBasisBessel; prm.R = R; prm.eps = eps; prm.no_nan = 1; prm.cos_cutoff = 0.f;
+  prm.gamma = prm.offset = prm.step = 0.f;
+  prm.inv_cutoff = basis_params[0]; prm.p = static_cast<int>(basis_params[1]);
+  if (prm.p < 1) return KGCNN_E_INVALID;
+  const int blocks = static_cast<int>(std::min<int64_t>(kFreqBlocks, ceil_div<int64_t>(E, kFreqWarps)));
+  float* partial = static_cast<float*>(workspace);
+  bessel_freq_partial_kernel<<<blocks, kFreqWarps * 32, 0, st>>>(xyz, idx_i, idx_j, E, prm, frequencies, cot_rbf,
+                                                                 tangent_xyz, partial);
+  bessel_freq_reduce_kernel<<<1, kMaxBasis, 0, st>>>(partial, blocks, R, out);
+  return finish_launch(2);
 }
 
 }  // extern "C"

@@ -1397,43 +1397,79 @@ def _geom_vjp_raw(xyz, cots, spec):
     return raw_gms(gv, None, spec.rel_i, None) - raw_gms(gv, None, spec.rel_j, None)
 
 
+def raw_bessel_frequency_grad(xyz, spec, cot_rbf, tangent=None):
+    """d(scalar)/d(frequencies) [R] of the Bessel basis: through the basis values (tangent None) or through their
+    coordinate VJP contracted with `tangent` [N,3] (include/kgcnn_b200.h, kgcnn_bessel_frequency_grad)."""
+    import ctypes
+    _need_cuda(xyz, cot_rbf)
+    xyz, cot_rbf = _f32c(xyz), _f32c(cot_rbf)
+    tangent = None if tangent is None else _f32c(tangent)
+    out = torch.empty((spec.R,), dtype=torch.float32, device=xyz.device)
+    nbytes = int(_lib.lib().kgcnn_bessel_frequency_grad_workspace_bytes(spec.R))
+    ws = torch.empty((max(nbytes, 16),), dtype=torch.uint8, device=xyz.device)
+    bp = (ctypes.c_float * 3)(*spec.basis_params)
+    check(_lib.lib().kgcnn_bessel_frequency_grad(
+        _ptr(xyz), _ptr(spec.rel_i.ids), _ptr(spec.rel_j.ids), spec.rel_i.n_elements, spec.R,
+        ctypes.cast(bp, ctypes.c_void_p), _ptr(spec.frequencies), spec.eps, _ptr(cot_rbf), _ptr(tangent), _ptr(out),
+        _ptr(ws), nbytes, _stream()), "kgcnn_bessel_frequency_grad")
+    return out
+
+
+def _rbf_cotangent(spec, cots):
+    return dict(zip(spec.want, cots)).get("rbf")
+
+
 class _EdgeGeom(torch.autograd.Function):
+    """freq: the trainable Bessel frequencies (a leaf Parameter whose storage spec.frequencies views) or None."""
+
     @staticmethod
-    def forward(ctx, xyz, spec):
+    def forward(ctx, xyz, spec, freq=None):
         ctx.spec = spec
         ctx.set_materialize_grads(False)
-        ctx.save_for_backward(xyz)
+        ctx.save_for_backward(xyz, freq)
         return raw_edge_geometry(xyz, spec, 0)
 
     @staticmethod
     def backward(ctx, *cots):
-        (xyz,) = ctx.saved_tensors
-        return _EdgeGeomVjp.apply(xyz, ctx.spec, *[None if c is None else c.contiguous() for c in cots]), None
+        xyz, freq = ctx.saved_tensors
+        cots = [None if c is None else c.contiguous() for c in cots]
+        g_xyz = g_f = None
+        # inside the weight sweep of a training step (no_coordinate_hessian) nobody reads d/d(coordinates)
+        if ctx.needs_input_grad[0] and (COORDINATE_HESSIAN or _INPUT_ONLY is not None or torch.is_grad_enabled()):
+            g_xyz = _EdgeGeomVjp.apply(xyz, ctx.spec, freq, *cots)
+        c_rbf = _rbf_cotangent(ctx.spec, cots)
+        if freq is not None and c_rbf is not None and _want(ctx, 2, freq):
+            g_f = raw_bessel_frequency_grad(xyz.detach(), ctx.spec, c_rbf.detach())
+        return g_xyz, None, g_f
 
 
 class _EdgeGeomVjp(torch.autograd.Function):
     """J^T (cotangents): linear in the cotangents, so its VJP with respect to them is the JVP kernel."""
 
     @staticmethod
-    def forward(ctx, xyz, spec, *cots):
+    def forward(ctx, xyz, spec, freq, *cots):
         ctx.spec = spec
         ctx.present = [c is not None for c in cots]
-        ctx.save_for_backward(xyz, *[c for c in cots if c is not None])
+        ctx.save_for_backward(xyz, freq, *[c for c in cots if c is not None])
         return _geom_vjp_raw(xyz, cots, spec)
 
     @staticmethod
     def backward(ctx, hvec):
-        xyz, saved = ctx.saved_tensors[0], list(ctx.saved_tensors[1:])
-        g_xyz = None
+        xyz, freq, saved = ctx.saved_tensors[0], ctx.saved_tensors[1], list(ctx.saved_tensors[2:])
+        cots = [saved.pop(0) if p else None for p in ctx.present]
+        g_xyz = g_f = None
         if hvec is not None and ctx.needs_input_grad[0] and COORDINATE_HESSIAN:
-            cots = [saved.pop(0) if p else None for p in ctx.present]
             g_xyz = _geom_hessian_term(xyz, ctx.spec, [None if c is None else c.detach() for c in cots],
                                        hvec.detach())
+        c_rbf = _rbf_cotangent(ctx.spec, cots)
+        if hvec is not None and freq is not None and c_rbf is not None and _want(ctx, 2, freq):
+            # the force depends on the frequencies through d rbf / d d: mixed second derivative, summed over the edges
+            g_f = raw_bessel_frequency_grad(xyz.detach(), ctx.spec, c_rbf.detach(), tangent=hvec.detach())
         g_cots = [None] * len(ctx.present)
-        if any(ctx.needs_input_grad[2:]):
+        if hvec is not None and any(ctx.needs_input_grad[3:]):
             tang = _EdgeGeomJvp.apply(xyz, ctx.spec, hvec.contiguous())
-            g_cots = [t if (p and n) else None for t, p, n in zip(tang, ctx.present, ctx.needs_input_grad[2:])]
-        return (g_xyz, None) + tuple(g_cots)
+            g_cots = [t if (p and n) else None for t, p, n in zip(tang, ctx.present, ctx.needs_input_grad[3:])]
+        return (g_xyz, None, g_f) + tuple(g_cots)
 
 
 class _EdgeGeomJvp(torch.autograd.Function):
@@ -1452,10 +1488,12 @@ class _EdgeGeomJvp(torch.autograd.Function):
         g_xyz = _no_hessian("edge geometry (third order)") if ctx.needs_input_grad[0] else None
         g_h = None
         if ctx.needs_input_grad[2]:
-            g_h = _EdgeGeomVjp.apply(xyz, ctx.spec, *[None if c is None else c.contiguous() for c in cots])
+            g_h = _EdgeGeomVjp.apply(xyz, ctx.spec, None, *[None if c is None else c.contiguous() for c in cots])
         return g_xyz, None, g_h
 
 
-def edge_geometry(xyz, spec):
-    """Tuple of tensors for spec.want, differentiable to the order force training needs."""
-    return _EdgeGeom.apply(xyz, spec)
+def edge_geometry(xyz, spec, trainable_frequencies=None):
+    """Tuple of tensors for spec.want, differentiable to the order force training needs.  trainable_frequencies: the
+    Bessel layer's frequency Parameter (spec.frequencies must be its detached view); it then receives its gradient
+    through the energy AND through the forces."""
+    return _EdgeGeom.apply(xyz, spec, trainable_frequencies)

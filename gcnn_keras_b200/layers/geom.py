@@ -264,15 +264,17 @@ class BesselBasisLayer(GraphBaseLayer):
     def call(self, inputs, **kwargs):
         fused = _distance_source(inputs) if isinstance(inputs, RaggedTensor) else None
         trainable = self.frequencies.requires_grad and torch.is_grad_enabled()
-        if fused is not None and not trainable and self.num_radial <= 64:
+        if fused is not None and self.num_radial <= 64:
             src, ri, rj, eps = fused
             if self.frequencies.device != src.values.device:
                 self.to(src.values.device)
             spec = F.GeometrySpec(ri, rj, ("rbf",), basis=2, R=self.num_radial, eps=eps,
                                   basis_params=(self.inv_cutoff, self.envelope_exponent + 1, 0.0),
-                                  frequencies=self.frequencies.detach().contiguous())
-            return inputs.with_values(F.edge_geometry(src.values, spec)[0])
-        return self.map_values(self.expand_bessel_basis, inputs)   # trainable frequencies: differentiable in f_n
+                                  frequencies=self.frequencies.detach())
+            # trainable frequencies (geom.py:766-770): d/d f_n through the energy and through the forces comes from
+            # kgcnn_bessel_frequency_grad (edge reduction inside the kernel), not from an eager sin / cos graph
+            return inputs.with_values(F.edge_geometry(src.values, spec, self.frequencies if trainable else None)[0])
+        return self.map_values(self.expand_bessel_basis, inputs)   # distances not produced by the fused geometry
 
     def get_config(self):
         config = super().get_config()

@@ -243,6 +243,17 @@ int kgcnn_edge_geometry(const float* xyz, const int32_t* idx_i, const int32_t* i
                         const float* cot_fc, const float* tangent_xyz, float* out_d, float* out_u, float* out_rbf,
                         float* out_fc, float* out_gv, kgcnn_stream_t stream);
 
+/* a10  gradient with respect to the TRAINABLE Bessel frequencies f_n (kgcnn/layers/geom.py:766-770, tf.Variable):
+ *   tangent_xyz null : out[n] = sum_e cot_rbf[e,n] * d rbf_n / d f_n                    (loss -> energy -> basis)
+ *   tangent_xyz given: out[n] = sum_e cot_rbf[e,n] * t_d[e] * d2 rbf_n / (d d  d f_n),  t_d = (d d_e / d x) . tangent
+ *                      (loss -> force = coordinate VJP of the basis; cot_rbf is the cotangent that entered that VJP)
+ *   basis_params as for basis 2 of kgcnn_edge_geometry.  Block partials + fixed-order sum (deterministic). */
+size_t kgcnn_bessel_frequency_grad_workspace_bytes(int R);
+int kgcnn_bessel_frequency_grad(const float* xyz, const int32_t* idx_i, const int32_t* idx_j, int64_t E, int R,
+                                const float* basis_params, const float* frequencies, float eps, const float* cot_rbf,
+                                const float* tangent_xyz /*nullable*/, float* out, void* workspace,
+                                size_t workspace_bytes, kgcnn_stream_t stream);
+
 /* ---------------------------------------------------------------------------------------------
  * a15/a16  fused ACSF symmetry functions (kgcnn/layers/conv/acsf_conv.py:199-211 and :473-494)
  *   mode 0: G[N, R*m]                  (out)

@@ -138,3 +138,49 @@ def test_coordinate_hessian_term_through_the_fused_geometry_matches_op_chain():
     finally:
         G.FUSED = True
     assert rel_err(res[0], res[1]) < 1e-4          # both fp32
+
+
+def test_trainable_bessel_frequencies_get_their_gradient_from_the_kernel():
+    """kgcnn/layers/geom.py:766-770: the frequencies are a trainable variable.  A force-training loss reaches them
+    through the energy (d rbf / d f) and through the forces (d2 rbf / d d d f); both come from
+    kgcnn_bessel_frequency_grad while the basis itself stays on the fused geometry kernel."""
+    from gcnn_keras_b200 import RaggedTensor, _lib
+    from gcnn_keras_b200.functional import no_coordinate_hessian
+    from gcnn_keras_b200.layers import geom as G
+    x_np, idx, nl, el = _mol_batch(seed=4, n_graphs=6, n_atoms=9)
+    rng = np.random.default_rng(9)
+    w_e = rng.normal(size=(len(idx), 20))                    # a fixed "network": energy = sum(rbf * w_e)
+    w_f = rng.normal(size=x_np.shape)                        # force loss direction
+
+    def loss_and_grad(rbf_of, x, freq, dt):
+        rbf = rbf_of(x)
+        energy = (rbf * torch.as_tensor(w_e, dtype=dt, device=x.device)).sum()
+        (force,) = torch.autograd.grad(energy, x, create_graph=True)
+        loss = 0.3 * energy + (force * torch.as_tensor(w_f, dtype=dt, device=x.device)).sum()
+        with no_coordinate_hessian():
+            (g,) = torch.autograd.grad(loss, freq)
+        return float(loss), g
+
+    lay = G.BesselBasisLayer(num_radial=20, cutoff=5.0, envelope_exponent=5).cuda()
+    x_dev = torch.tensor(x_np, device="cuda", requires_grad=True)
+
+    def device_rbf(x):
+        xyz = RaggedTensor.from_row_lengths(x, torch.as_tensor(nl).cuda())
+        p1, p2 = G.NodePosition()([xyz, device_ragged(idx, el)])
+        return lay(G.NodeDistanceEuclidean()([p1, p2])).values
+
+    _lib.launch_count_reset()
+    loss_d, g_d = loss_and_grad(device_rbf, x_dev, lay.frequencies, torch.float32)
+    assert _lib.launch_count() > 0
+
+    f64 = lay.frequencies.detach().double().cpu().requires_grad_(True)
+    x64 = torch.tensor(x_np, dtype=torch.float64, requires_grad=True)
+
+    def oracle_rbf(x):
+        xyz = oracle_ragged(np.zeros((len(x_np), 3)), nl, torch.float64).with_values(x)
+        p1, p2 = OL.node_position(xyz, oracle_ragged(idx, el))
+        return OL.bessel_basis(OL.node_distance_euclidean(p1, p2), 20, 5.0, 5, frequencies=f64).values
+
+    loss_o, g_o = loss_and_grad(oracle_rbf, x64, f64, torch.float64)
+    assert abs(loss_d - loss_o) <= RTOL * abs(loss_o)
+    assert rel_err(g_d.cpu().numpy(), g_o.numpy()) < RTOL
