@@ -898,6 +898,181 @@ def dense(x, kernel, bias, activation):
 
 
 # ------------------------------------------------------------------------------------------------
+# fused continuous-filter convolution (a13): filter network inside the gather-scale-scatter
+# ------------------------------------------------------------------------------------------------
+CFCONV_FUSED = True     # False: Dense -> Dense -> fused gather-multiply-pool (filter [E, units] through HBM)
+
+
+class CfconvSpec:
+    """Static part of one fused cfconv call (kgcnn/layers/conv/schnet_conv.py:73-79 behind GaussBasisLayer,
+    kgcnn/layers/geom.py:567-570): receiver / sender relations, Gaussian basis, activation of the first Dense."""
+
+    def __init__(self, recv, send, bins, gamma, offset, step, act):
+        self.recv, self.send = recv, send
+        self.R, self.gamma, self.offset, self.step, self.act = int(bins), float(gamma), float(offset), float(step), int(act)
+
+    @staticmethod
+    def supported(units, bins, act, w1, w2):
+        return (CFCONV_FUSED and units == 128 and 1 <= bins <= 32
+                and act in (_lib.ACT_CODES["shifted_softplus"], _lib.ACT_CODES["softplus2"])
+                and tuple(w1.shape) == (bins, 128) and tuple(w2.shape) == (128, 128)
+                and w1.is_cuda and w1.dtype == torch.float32 and w2.dtype == torch.float32)
+
+
+def raw_cfconv(mode, spec, d, w1, b1, w2, b2, rel_out, rel_other, a, b=None, c=None, tang=None, want_wg=False):
+    """One launch of kgcnn_cfconv_fused (+ its fix-up): (out [n_out,128], edge_out [E] | None, wg | None).
+    want_wg (modes 1, 3): also the operand pairs of the filter network's weight gradients, as a dict
+    {"w2": [(x, g, with_bias), ...], "w1": [...]} of [E, *] tensors (rows in the CSR order of this call)."""
+    import ctypes
+    _need_cuda(d, w1, w2, a)
+    E = rel_out.n_elements
+    dev = a.device
+    d = _f32c(d.reshape(-1))
+    if int(d.shape[0]) != E:
+        raise ValueError("cfconv: %d distances for %d edges" % (int(d.shape[0]), E))
+    a = _f32c(a)
+    b = None if b is None else _f32c(b)
+    c = None if c is None else _f32c(c)
+    tang = None if tang is None else _f32c(tang.reshape(-1))
+    w1, w2 = _f32c(w1), _f32c(w2)
+    b1 = None if b1 is None else _f32c(b1)
+    b2 = None if b2 is None else _f32c(b2)
+    out = torch.empty((rel_out.n_targets, 128), dtype=torch.float32, device=dev)
+    edge_out = torch.empty((E,), dtype=torch.float32, device=dev) if mode in (1, 3) else None
+    nbytes = int(_lib.lib().kgcnn_cfconv_fused_workspace_bytes(E))
+    ws = torch.empty((nbytes,), dtype=torch.uint8, device=dev)
+    wg = wg_arr = None
+    if want_wg:
+        new = lambda cols: torch.empty((E, cols), dtype=torch.float32, device=dev)
+        t = [new(spec.R), new(128), new(128), new(128)]
+        if mode == 3:
+            t += [new(spec.R), new(128), new(128), new(128)]
+        wg_arr = (ctypes.c_void_p * 8)(*([x.data_ptr() for x in t] + [None] * (8 - len(t))))
+        wg = {"w2": [(t[1], t[2], True)], "w1": [(t[0], t[3], True)]}
+        if mode == 3:
+            wg["w2"].append((t[5], t[6], False))
+            wg["w1"].append((t[4], t[7], False))
+    check(_lib.lib().kgcnn_cfconv_fused(
+        mode, _ptr(d), E, spec.R, spec.gamma, spec.offset, spec.step, _ptr(w1), _ptr(b1), _ptr(w2), _ptr(b2), 128,
+        spec.act, _ptr(rel_out.rowptr), _ptr(rel_out.permuted_ids(rel_out)), _ptr(rel_out.permuted_ids(rel_other)),
+        _ptr(rel_out.perm), rel_out.n_targets, _ptr(a), _ptr(b), _ptr(c), _ptr(tang), _ptr(out), _ptr(edge_out),
+        wg_arr, _ptr(ws), nbytes, _stream()), "kgcnn_cfconv_fused")
+    return out, edge_out, wg
+
+
+def raw_gauss_basis(d, spec, order, scale=None):
+    d = _f32c(d.reshape(-1))
+    E = int(d.shape[0])
+    out = torch.empty((E, spec.R), dtype=torch.float32, device=d.device)
+    scale = None if scale is None else _f32c(scale.reshape(-1))
+    check(_lib.lib().kgcnn_gauss_basis(_ptr(d), E, spec.R, spec.gamma, spec.offset, spec.step, order, _ptr(scale),
+                                       _ptr(out), _stream()), "kgcnn_gauss_basis")
+    return out
+
+
+def _cfconv_weight_grads(wg, w1, b1, w2, b2):
+    """Hand the operand pairs a WG launch produced to the grouped weight-gradient launch (active sink) or contract
+    them here.  Returns (gW1, gb1, gW2, gb2); entries that went to the sink are None."""
+    sink = _sink()
+    direct = {}
+    for w, bias, key in ((w2, b2, "w2"), (w1, b1, "w1")):
+        for x, g, with_bias in wg[key]:
+            bb = bias if with_bias else None
+            if sink is not None and sink.add(w, x, g, bb):
+                continue
+            direct[id(w)] = direct.get(id(w), 0) + raw_dense_tc(2, x, g)
+            if bb is not None:
+                direct[id(bb)] = direct.get(id(bb), 0) + raw_colsum(g)
+    return tuple(direct.get(id(t)) if t is not None else None for t in (w1, b1, w2, b2))
+
+
+def _cfconv_unfused(x, d, w1, b1, w2, b2, spec):
+    """The same layer op by op (basis, Dense, Dense, fused gather-multiply-pool) with the closed primitives."""
+    k = torch.arange(spec.R, dtype=d.dtype, device=d.device)
+    t = d.reshape(-1, 1) - spec.offset - spec.step * k
+    rbf = torch.exp(-spec.gamma * t * t)
+    filt = dense(dense(rbf, w1, b1, spec.act), w2, b2, _lib.ACT_CODES["linear"])
+    return gather_mul_segment_sum(x, filt, spec.recv, spec.send)
+
+
+class _CfConv(torch.autograd.Function):
+    """y[i] = sum_{e->i} x[s_e] * phi(d_e),  phi = Dense2(ssp(Dense1(gauss(d))))  -- one fused launch, nothing of size
+    [E, units] in HBM (csrc/cfconv.cu mode 0).  Backward = _CfConvVjp (differentiable once more)."""
+
+    @staticmethod
+    def forward(ctx, x, d, w1, b1, w2, b2, spec):
+        ctx.spec = spec
+        ctx.save_for_backward(x, d, w1, b1, w2, b2)
+        return raw_cfconv(0, spec, d, w1, b1, w2, b2, spec.recv, spec.send, x)[0]
+
+    @staticmethod
+    def backward(ctx, gy):
+        x, d, w1, b1, w2, b2 = ctx.saved_tensors
+        spec = ctx.spec
+        gy = gy.contiguous()
+        wanted_w = [t is not None and _want(ctx, i, t) for i, t in ((2, w1), (3, b1), (4, w2), (5, b2))]
+        if any(wanted_w) and torch.is_grad_enabled():
+            # weight gradients that are themselves differentiated again (not a training step): record them through
+            # the unfused chain of closed primitives
+            ins = [x, d, w1, b1, w2, b2]
+            want = [_want(ctx, 0, x), _want(ctx, 1, d)] + wanted_w
+            with torch.enable_grad():
+                y2 = _cfconv_unfused(x, d, w1, b1, w2, b2, spec)
+                gs = torch.autograd.grad(y2, [t for t, w in zip(ins, want) if w], gy, create_graph=True,
+                                         allow_unused=True)
+            it = iter(gs)
+            return tuple(next(it) if w else None for w in want) + (None,)
+        if any(wanted_w):      # weight-gradient sweep: the VJP kernel also emits the operands of dW1, db1, dW2, db2
+            gx, gd, wg = raw_cfconv(1, spec, d, w1, b1, w2, b2, spec.send, spec.recv, gy, b=x, want_wg=True)
+            gw = _cfconv_weight_grads(wg, w1, b1, w2, b2)
+            return (gx, gd.reshape(d.shape)) + gw + (None,)
+        gx = gd = None
+        if _want(ctx, 0, x) or _want(ctx, 1, d):
+            gx, gd = _CfConvVjp.apply(gy, x, d, w1, b1, w2, b2, spec)
+            gd = gd.reshape(d.shape)
+        return (gx, gd, None, None, None, None, None)
+
+
+class _CfConvVjp(torch.autograd.Function):
+    """(gx[s], gd[e]) = (sum_{e: s_e = s} gy[r_e] * phi(d_e),  <gy[r_e] * x[s_e], phi'(d_e)>)  (csrc/cfconv.cu mode 1).
+    Its own VJP (the weight-gradient sweep of force training) is the JVP of the layer (mode 2) for gy, mode 3 for x
+    and d, and the reverse sweep through the filter network for the weights."""
+
+    @staticmethod
+    def forward(ctx, gy, x, d, w1, b1, w2, b2, spec):
+        ctx.spec = spec
+        ctx.save_for_backward(gy, x, d, w1, b1, w2, b2)
+        gx, gd, _ = raw_cfconv(1, spec, d, w1, b1, w2, b2, spec.send, spec.recv, gy, b=x)
+        return gx, gd
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, ggx, ggd):
+        gy, x, d, w1, b1, w2, b2 = ctx.saved_tensors
+        spec = ctx.spec
+        ggx = torch.zeros_like(x) if ggx is None else ggx.contiguous()
+        ggd = torch.zeros((spec.recv.n_elements,), dtype=torch.float32, device=x.device) if ggd is None \
+            else ggd.contiguous().reshape(-1)
+        ggy = g2x = g2d = None
+        if ctx.needs_input_grad[0]:
+            ggy = raw_cfconv(2, spec, d, w1, b1, w2, b2, spec.recv, spec.send, ggx, b=x, tang=ggd)[0]
+        want_w = any(t is not None and _want(ctx, i, t) for i, t in ((3, w1), (4, b1), (5, w2), (6, b2)))
+        gw = (None,) * 4
+        if want_w or _want(ctx, 1, x) or _want(ctx, 2, d):
+            g2x, g2d, wg = raw_cfconv(3, spec, d, w1, b1, w2, b2, spec.send, spec.recv, gy, b=x, c=ggx, tang=ggd,
+                                      want_wg=want_w)
+            g2d = g2d.reshape(d.shape)
+            if want_w:
+                gw = _cfconv_weight_grads(wg, w1, b1, w2, b2)
+        return (ggy, g2x, g2d) + gw + (None,)
+
+
+def cfconv_fused(x, d, w1, b1, w2, b2, spec):
+    """SchNet cfconv from the distances: x [N,128], d [E] or [E,1] -> [N,128]."""
+    return _CfConv.apply(x, d, w1, b1, w2, b2, spec)
+
+
+# ------------------------------------------------------------------------------------------------
 # fused ACSF G2 / G4 (a15, a16): G, J^T v, J u
 # ------------------------------------------------------------------------------------------------
 COORDINATE_HESSIAN = True     # False inside a training step: coordinates are not trained, d2/dx2 is never needed

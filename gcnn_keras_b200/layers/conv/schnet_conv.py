@@ -5,6 +5,8 @@ The reference cfconv is Dense -> Dense -> GatherNodesOutgoing -> LazyMultiply ->
 is ONE kernel over the cached receiver CSR, and its VJPs are the same kernel on the sender CSC plus the
 two-sided gather-product (closed under differentiation for force training).
 """
+import torch
+
 from ... import functional as F
 from ...plan import get_plan
 from ..base import GraphBaseLayer, register_keras_serializable
@@ -41,9 +43,20 @@ class SchNetCFconv(GraphBaseLayer):
 
     def call(self, inputs, **kwargs):
         node, edge, indexlist = inputs
+        code = F.op_code(self.cfconv_pool)
+        fused = self._fused_source(node, edge) if code in (F.OP_SUM, F.OP_MEAN) else None
+        if fused is not None:        # :74-78 in ONE kernel: the filter [E, units] never reaches HBM (csrc/cfconv.cu)
+            dist, gamma, offset, step, bins = fused
+            plan = get_plan(indexlist, node)
+            recv, send = plan.relation(self.lay_sum.pooling_index), plan.relation(self.gather_n.selection_index[0])
+            spec = F.CfconvSpec(recv, send, bins, gamma, offset, step, self.lay_dense1._act_code)
+            out = F.cfconv_fused(node.values, dist.values, self.lay_dense1.kernel, self.lay_dense1.bias,
+                                 self.lay_dense2.kernel, self.lay_dense2.bias, spec)
+            if code == F.OP_MEAN:
+                out = out * recv.inv_count()
+            return node.with_values(out)
         x = self.lay_dense1(edge, **kwargs)                                   # schnet_conv.py:74
         x = self.lay_dense2(x, **kwargs)                                      # :75
-        code = F.op_code(self.cfconv_pool)
         if code in (F.OP_SUM, F.OP_MEAN):
             plan = get_plan(indexlist, node)
             recv, send = plan.relation(self.lay_sum.pooling_index), plan.relation(self.gather_n.selection_index[0])
@@ -54,6 +67,26 @@ class SchNetCFconv(GraphBaseLayer):
         node2exp = self.gather_n([node, indexlist], **kwargs)                 # max / min: unfused chain
         x = self.lay_mult([node2exp, x], **kwargs)
         return self.lay_sum([node, x, indexlist], **kwargs)
+
+    def _fused_source(self, node, edge):
+        """(distance ragged, gamma, offset, step, bins) when `edge` is the untouched output of GaussBasisLayer and the
+        shapes are the ones csrc/cfconv.cu is instantiated for (units 128, <= 32 bins, shifted softplus)."""
+        p = getattr(edge, "provenance", None)
+        if p is None or p[0] != "gauss" or self.lay_dense1._act_code is None:
+            return None
+        dist, gamma, offset, step, bins = p[1:]
+        v, dv = node.values, dist.values
+        if not (v.is_cuda and v.dtype == torch.float32 and v.dim() == 2 and int(v.shape[1]) == self.units
+                and dv.dtype == torch.float32 and dv.numel() == edge.values.shape[0]):
+            return None
+        for lay, in_dim in ((self.lay_dense1, bins), (self.lay_dense2, self.units)):
+            if not lay.built:
+                lay.build((None, in_dim))
+                lay.to(v.device)
+        if not F.CfconvSpec.supported(self.units, bins, self.lay_dense1._act_code, self.lay_dense1.kernel,
+                                      self.lay_dense2.kernel):
+            return None
+        return dist, gamma, offset, step, bins
 
     def get_config(self):
         config = super().get_config()

@@ -220,9 +220,14 @@ class GaussBasisLayer(GraphBaseLayer):
             src, ri, rj, eps = fused
             spec = F.GeometrySpec(ri, rj, ("rbf",), basis=1, R=self.bins, eps=eps,
                                   basis_params=(self.gamma, self.offset, self.distance / float(self.bins)))
-            return inputs.with_values(F.edge_geometry(src.values, spec)[0])
-        return self.map_values(self._compute_gauss_basis, inputs, offset=self.offset, gamma=self.gamma,
-                               bins=self.bins, distance=self.distance)
+            out = inputs.with_values(F.edge_geometry(src.values, spec)[0])
+        else:
+            out = self.map_values(self._compute_gauss_basis, inputs, offset=self.offset, gamma=self.gamma,
+                                  bins=self.bins, distance=self.distance)
+        if isinstance(inputs, RaggedTensor) and isinstance(out, RaggedTensor):
+            # lets SchNetCFconv evaluate its filter network from the distances inside the fused kernel (schnet_conv.py)
+            out.provenance = ("gauss", inputs, self.gamma, self.offset, self.distance / float(self.bins), self.bins)
+        return out
 
     def get_config(self):
         config = super().get_config()

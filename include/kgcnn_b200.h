@@ -384,6 +384,42 @@ int kgcnn_range_emit(const void* xyz, int is_f64, const int64_t* node_row_splits
 int kgcnn_segment_softmax(const float* a, const int32_t* rowptr, const int32_t* perm /*nullable*/, int64_t n_out,
                           int64_t n_elements, int H, int normalize, float* out, kgcnn_stream_t stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * a13  SchNet continuous-filter convolution with the filter network inside the gather-scale-scatter
+ *   (kgcnn/layers/conv/schnet_conv.py:73-79 fed by GaussBasisLayer, kgcnn/layers/geom.py:567-570):
+ *       rbf_k(d) = exp(-gamma (d - offset - k step)^2),  k < R <= 32
+ *       phi(d)   = ssp(rbf(d) W1 + b1) W2 + b2           W1[R,128], W2[128,128]   (units = 128)
+ *   No [E, units] tensor is read or written: the basis, both Dense layers (tcgen05, three-piece bf16 split) and the
+ *   multiply / segment sum run per tile of 128 edges.  The filter depends on one scalar per edge, so the derivatives
+ *   of the layer are forward-mode chains phi', phi'' through the same network; the four modes are closed under the
+ *   two differentiations of force training (i = output row of an edge, o = its other end; a, b, c: [*,128]):
+ *     mode 0  out[i] = sum a[o] phi                                                   value (CSR of the receivers)
+ *     mode 1  out[i] = sum a[o] phi;            edge_out[e] = <a[o] b[i], phi'>          VJP   (CSR of the senders)
+ *     mode 2  out[i] = sum a[o] phi + t b[o] phi'                                       JVP   (CSR of the receivers)
+ *     mode 3  out[i] = sum t a[o] phi';  edge_out[e] = <a[o] c[i], phi'> + t <a[o] b[i], phi''>   VJP of mode 1
+ *   (rowptr, rows, other, eperm): CSR of the output rows; rows[p] / other[p] = output / gathered row of CSR position
+ *   p, eperm[p] = original edge id (NULL: identity).  dist, tang (t), edge_out are in the ORIGINAL edge order.
+ *   Rows without edges are written as 0.  Summation inside a row is in CSR order (deterministic, no atomics).
+ *   KGCNN_E_UNSUPPORTED: units != 128, R > 32, activation other than shifted softplus.
+ * ------------------------------------------------------------------------------------------- */
+size_t kgcnn_cfconv_fused_workspace_bytes(int64_t E);
+/* out[e,k] = scale[e] * (d/dd)^order exp(-gamma (dist[e] - offset - k step)^2), order 0..2, scale nullable: the
+ * basis operands of the filter network's weight gradients (kgcnn/layers/geom.py:567-570 and its derivatives). */
+int kgcnn_gauss_basis(const float* dist, int64_t E, int R, float gamma, float offset, float step, int order,
+                      const float* scale /*nullable*/, float* out, kgcnn_stream_t stream);
+int kgcnn_cfconv_fused(int mode, const float* dist, int64_t E, int R, float gamma, float offset, float step,
+                       const float* W1, const float* b1 /*nullable*/, const float* W2, const float* b2 /*nullable*/,
+                       int units, int act, const int32_t* rowptr, const int32_t* rows, const int32_t* other,
+                       const int32_t* eperm /*nullable*/, int64_t n_out, const float* a, const float* b,
+                       const float* c, const float* tang, float* out, float* edge_out,
+                       float* const* wg /*nullable; HOST array of 8 device pointers*/, void* workspace,
+                       size_t workspace_bytes, kgcnn_stream_t stream);
+/* wg (modes 1 and 3 only): the operands of the filter network's weight gradients, produced in the same pass, rows in
+ * CSR order of this call:   dW2 += h^T A (+ hd^T Bt),  db2 += colsum A,  dW1 += rbf^T gp (+ rbf1^T gpd),  db1 += colsum gp
+ *   wg[0] rbf [E,R]   wg[1] h [E,128]   wg[2] A [E,128] = a[o] b[i] (mode 1) | a[o] c[i] (mode 3)   wg[3] gp [E,128]
+ *   mode 3 also:  wg[4] rbf1 [E,R] = t rbf'   wg[5] hd [E,128]   wg[6] Bt [E,128] = a[o] b[i]   wg[7] gpd [E,128]
+ * (reverse sweep of kgcnn/layers/conv/schnet_conv.py:74-75 on the edge rows; the pairs go to kgcnn_dense_tn_grouped). */
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,148 @@
+"""Fused continuous-filter convolution (csrc/cfconv.cu; kgcnn/layers/conv/schnet_conv.py:73-79 behind GaussBasisLayer,
+kgcnn/layers/geom.py:567-570) against an fp64 restatement of the reference op chain: value, first derivatives, and
+the second-order sweep of force training (cotangents on gx and gd -> gradients of x, d, gy and the four weights)."""
+import numpy as np
+import pytest
+import torch
+
+from helpers import RTOL, device_ragged, rel_err
+
+pytestmark = pytest.mark.gpu
+
+GAUSS = dict(bins=25, distance=5.0, offset=0.0, sigma=0.4)
+
+
+def _graph(rng, kind):
+    """node counts, edge counts, [E,2] (receiver, sender) in sample indexing."""
+    if kind == "c2":                     # 9 atoms, all 72 ordered pairs, receiver-sorted (config C2)
+        n_graphs, n = 12, 9
+        pairs = np.array([(i, j) for i in range(n) for j in range(n) if i != j], dtype=np.int64)
+        return np.full(n_graphs, n), np.full(n_graphs, len(pairs)), np.concatenate([pairs] * n_graphs)
+    node_len, edge_len, idx = [], [], []
+    for g in range(7):
+        n = int(rng.integers(3, 40))
+        if kind == "hub" and g == 3:
+            n = 6
+        deg = rng.integers(0, 12, size=n)
+        if kind == "hub" and g == 3:
+            deg = np.array([0, 300, 2, 0, 45, 1])       # rows across several 32-edge groups and 128-edge tiles, empty rows
+        recv = np.repeat(np.arange(n), deg)
+        send = rng.integers(0, n, size=recv.shape[0])
+        ii = np.stack([recv, send], 1)
+        if kind == "unsorted":
+            ii = ii[rng.permutation(len(ii))]
+        node_len.append(n)
+        edge_len.append(len(ii))
+        idx.append(ii)
+    return np.array(node_len), np.array(edge_len), np.concatenate(idx).astype(np.int64)
+
+
+def _oracle_phi(d, w1, b1, w2, b2):
+    k = torch.arange(GAUSS["bins"], dtype=d.dtype)
+    gamma = 1.0 / (2 * GAUSS["sigma"] ** 2)
+    rbf = torch.exp(-gamma * (d[:, None] - GAUSS["offset"] - k * GAUSS["distance"] / GAUSS["bins"]) ** 2)
+    p = rbf @ w1 + b1
+    h = torch.nn.functional.softplus(p) - np.log(2.0)
+    return h @ w2 + b2
+
+
+def _oracle_cfconv(x, d, w1, b1, w2, b2, recv, send, n):
+    msg = x[send] * _oracle_phi(d, w1, b1, w2, b2)
+    return torch.zeros((n, x.shape[1]), dtype=x.dtype).index_add(0, recv, msg)
+
+
+def _case(kind, seed=0):
+    from gcnn_keras_b200 import functional as F
+    from gcnn_keras_b200.plan import get_plan
+    rng = np.random.default_rng(seed)
+    node_len, edge_len, idx = _graph(rng, kind)
+    N, E = int(node_len.sum()), int(edge_len.sum())
+    x = rng.standard_normal((N, 128))
+    d = rng.uniform(0.8, 4.8, size=E)
+    w1 = rng.standard_normal((GAUSS["bins"], 128)) * 0.4
+    b1 = rng.standard_normal(128) * 0.3
+    w2 = rng.standard_normal((128, 128)) * 0.15
+    b2 = rng.standard_normal(128) * 0.3
+    cot = [rng.standard_normal((N, 128)), rng.standard_normal((N, 128)), rng.standard_normal(E)]
+    nodes = device_ragged(x.astype(np.float32), node_len)
+    index = device_ragged(idx, edge_len)
+    plan = get_plan(index, nodes)
+    recv, send = plan.relation(0), plan.relation(1)
+    gamma = 1.0 / (2 * GAUSS["sigma"] ** 2)
+    spec = F.CfconvSpec(recv, send, GAUSS["bins"], gamma, GAUSS["offset"], GAUSS["distance"] / GAUSS["bins"],
+                        F.act_code("kgcnn>shifted_softplus"))
+    off = np.repeat(np.concatenate([[0], np.cumsum(node_len)[:-1]]), edge_len)
+    return dict(N=N, E=E, arrays=[x, d, w1, b1, w2, b2], cot=cot, spec=spec,
+                recv=torch.tensor(idx[:, 0] + off), send=torch.tensor(idx[:, 1] + off))
+
+
+def _run_fused(c, data_only=True):
+    from gcnn_keras_b200 import functional as F
+    t = [torch.tensor(a, dtype=torch.float32, device="cuda", requires_grad=True) for a in c["arrays"]]
+    cy, cgx, cgd = [torch.tensor(a, dtype=torch.float32, device="cuda") for a in c["cot"]]
+    cy.requires_grad_(True)
+    y = F.cfconv_fused(*t, c["spec"])
+    if data_only:      # the inner dE/dx sweep of EnergyForceModel: data gradients only -> the fused VJP kernel
+        with F.input_gradients_only(t[0], t[1]):
+            gx, gd = torch.autograd.grad(y, [t[0], t[1]], cy, create_graph=True)
+    else:              # weight gradients recorded for a further derivative: the unfused composite
+        gx, gd = torch.autograd.grad(y, [t[0], t[1]], cy, create_graph=True)
+    second = torch.autograd.grad((gx * cgx).sum() + (gd * cgd).sum() + 0.5 * (y * y).sum(), t + [cy])
+    return [v.detach().cpu().double().numpy() for v in (y, gx, gd) + tuple(second)]
+
+
+def _run_oracle(c):
+    t = [torch.tensor(a, dtype=torch.float64, requires_grad=True) for a in c["arrays"]]
+    cy, cgx, cgd = [torch.tensor(a, dtype=torch.float64) for a in c["cot"]]
+    cy.requires_grad_(True)
+    y = _oracle_cfconv(*t, c["recv"], c["send"], c["N"])
+    gx, gd = torch.autograd.grad(y, [t[0], t[1]], cy, create_graph=True)
+    second = torch.autograd.grad((gx * cgx).sum() + (gd * cgd).sum() + 0.5 * (y * y).sum(), t + [cy])
+    return [v.detach().numpy() for v in (y, gx, gd) + tuple(second)]
+
+
+NAMES = ["y", "gx", "gd", "L_x", "L_d", "L_W1", "L_b1", "L_W2", "L_b2", "L_gy"]
+
+
+@pytest.mark.parametrize("kind", ["c2", "sorted", "unsorted", "hub"])
+def test_fused_cfconv_matches_fp64_restatement(kind):
+    c = _case(kind)
+    got, want = _run_fused(c), _run_oracle(c)
+    errs = {n: rel_err(g, w) for n, g, w in zip(NAMES, got, want)}
+    assert all(e < RTOL for e in errs.values()), errs
+
+
+def test_fused_cfconv_backward_without_the_data_only_context():
+    c = _case("sorted", seed=5)
+    got, want = _run_fused(c, data_only=False), _run_oracle(c)
+    errs = {n: rel_err(g, w) for n, g, w in zip(NAMES, got, want)}
+    assert all(e < RTOL for e in errs.values()), errs
+
+
+def test_fused_cfconv_is_deterministic_and_equals_the_unfused_layer():
+    """Run-to-run bitwise equality, and the SchNetCFconv layer gives the same values with and without the fusion."""
+    from gcnn_keras_b200 import functional as F
+    c = _case("unsorted", seed=3)
+    a, b = _run_fused(c), _run_fused(c)
+    for n, u, v in zip(NAMES, a, b):
+        assert np.array_equal(u, v), n
+    t = [torch.tensor(v, dtype=torch.float32, device="cuda") for v in c["arrays"]]
+    spec = c["spec"]
+    y = F.cfconv_fused(*t, spec)
+    rbf = F.raw_gauss_basis(t[1], spec, 0)
+    filt = F.dense(F.dense(rbf, t[2], t[3], spec.act), t[4], t[5], "linear")
+    y_unfused = F.gather_mul_segment_sum(t[0], filt, spec.recv, spec.send)
+    assert rel_err(y.cpu().numpy(), y_unfused.cpu().numpy()) < 2e-6
+
+
+def test_fused_cfconv_empty_edge_set():
+    from gcnn_keras_b200 import functional as F
+    from gcnn_keras_b200.plan import get_plan
+    nodes = device_ragged(np.ones((5, 128), dtype=np.float32), np.array([2, 3]))
+    index = device_ragged(np.zeros((0, 2), dtype=np.int64), np.array([0, 0]))
+    plan = get_plan(index, nodes)
+    spec = F.CfconvSpec(plan.relation(0), plan.relation(1), 25, 3.125, 0.0, 0.2, F.act_code("kgcnn>shifted_softplus"))
+    w1 = torch.zeros((25, 128), device="cuda")
+    w2 = torch.zeros((128, 128), device="cuda")
+    y = F.cfconv_fused(nodes.values, torch.zeros((0,), device="cuda"), w1, None, w2, None, spec)
+    assert y.shape == (5, 128) and float(y.abs().max()) == 0.0
