@@ -8,7 +8,12 @@
 //     fc = 0.5 (cos(pi clip(d, -c, c) / c) + 1)        CosCutOffEnvelope                geom.py:834-835
 // Three maps, like the ACSF kernels (forces are trained on; coordinates are not):
 //     mode 0  values;   mode 1  VJP: cotangents of (d, u, rbf, fc) -> g_v[E,3] (scattered +i / -j by the CSR kernel);
-//     mode 2  JVP: tangent h[N,3] of the coordinates -> tangents of (d, u, rbf, fc).
+//     mode 2  JVP: tangent h[N,3] of the coordinates -> tangents of (d, u, rbf, fc);
+//     mode 3  VJP of the VJP with respect to the coordinates (the coordinate-Hessian term): cotangents c of
+//             (d, u, rbf, fc) that entered mode 1 and the cotangent h[N,3] of its result ->
+//             g_v[E,3] = d/dv sum_out <c_out, D out(v)[eta]>,  eta = h_i - h_j:
+//                 scalar outputs g(d):  A2 (u.eta) u + A1 (eta - u (u.eta)) / d,   A1 = sum c g'(d), A2 = sum c g''(d)
+//                 direction u = v / d:  (3 (c.u)(u.eta) u - (c.eta) u - (u.eta) c - (c.u) eta) / d^2
 // One thread per edge; the [E,R] rows of consecutive edges are contiguous, so the per-k strided accesses of a warp
 // stay inside one 32*R*4-byte window that L1 serves after the first touch.
 #include "common.cuh"
@@ -19,7 +24,7 @@ namespace {
 constexpr float kPiF = 3.14159265358979323846f;
 constexpr int kMaxBasis = 64;
 
-enum { kGeoFwd = 0, kGeoVjp = 1, kGeoJvp = 2 };
+enum { kGeoFwd = 0, kGeoVjp = 1, kGeoJvp = 2, kGeoVjpVjp = 3 };
 enum { kBasisNone = 0, kBasisGauss = 1, kBasisBessel = 2 };
 
 struct GeoParams {
@@ -46,6 +51,18 @@ __device__ __forceinline__ void bessel_env(float x, int p, float& e, float& de) 
   de = -1.f / (x * x) + a * (p - 1) * xp2 + b * p * xp1 + c * (p + 1) * xp;
 }
 
+// second derivative of the envelope (x < 1, else 0)
+__device__ __forceinline__ float bessel_env2(float x, int p) {
+  if (!(x < 1.f)) return 0.f;
+  const float a = -0.5f * (p + 1) * (p + 2), b = static_cast<float>(p) * (p + 2), c = -0.5f * p * (p + 1);
+  float xp3 = 1.f;                                   // x^(p-3), built from x^(p-1) / x^2 (p >= 1)
+  float xp1 = 1.f;
+  for (int q = 0; q < p - 1; ++q) xp1 *= x;
+  xp3 = xp1 / (x * x);
+  const float xp2 = xp1 / x;
+  return 2.f / (x * x * x) + a * (p - 1) * (p - 2) * xp3 + b * p * (p - 1) * xp2 + c * (p + 1) * p * xp1;
+}
+
 template <int MODE>
 __global__ void __launch_bounds__(256)
 edge_geometry_kernel(const float* __restrict__ xyz, const int32_t* __restrict__ idx_i,
@@ -70,28 +87,35 @@ edge_geometry_kernel(const float* __restrict__ xyz, const int32_t* __restrict__ 
   const float gdx = (d > 0.f) ? vx / d : 0.f, gdy = (d > 0.f) ? vy / d : 0.f, gdz = (d > 0.f) ? vz / d : 0.f;
 
   float t_d = 0.f, hx = 0.f, hy = 0.f, hz = 0.f;
-  if (MODE == kGeoJvp) {
+  if (MODE == kGeoJvp || MODE == kGeoVjpVjp) {
     hx = __ldg(h + 3 * i) - __ldg(h + 3 * j);
     hy = __ldg(h + 3 * i + 1) - __ldg(h + 3 * j + 1);
     hz = __ldg(h + 3 * i + 2) - __ldg(h + 3 * j + 2);
     t_d = gdx * hx + gdy * hy + gdz * hz;
   }
-  float a_d = 0.f;                                    // VJP: total cotangent arriving at d
-  if (MODE == kGeoVjp && c_d) a_d += __ldg(c_d + e);
+  float a_d = 0.f;                                    // VJP: total cotangent arriving at d (sum c g'(d))
+  float a_dd = 0.f;                                   // mode 3: sum c g''(d)
+  constexpr bool kCot = (MODE == kGeoVjp || MODE == kGeoVjpVjp);
+  if (kCot && c_d) a_d += __ldg(c_d + e);
 
   // ---- cosine cutoff envelope ----
-  if (prm.cos_cutoff > 0.f && (MODE == kGeoVjp ? c_fc != nullptr : o_fc != nullptr)) {
+  if (prm.cos_cutoff > 0.f && (kCot ? c_fc != nullptr : o_fc != nullptr)) {
     const float rc = prm.cos_cutoff;
     const float dc = fminf(fmaxf(d, -rc), rc);
     float sn, cs;
     sincosf(dc * kPiF / rc, &sn, &cs);
-    const float dfc = (d > -rc && d < rc) ? -0.5f * kPiF / rc * sn : 0.f;
+    const bool inside = (d > -rc && d < rc);
+    const float dfc = inside ? -0.5f * kPiF / rc * sn : 0.f;
     if (MODE == kGeoFwd) o_fc[e] = 0.5f * (cs + 1.f);
     else if (MODE == kGeoJvp) o_fc[e] = dfc * t_d;
-    else a_d += __ldg(c_fc + e) * dfc;
+    else {
+      const float c = __ldg(c_fc + e);
+      a_d += c * dfc;
+      if (MODE == kGeoVjpVjp && inside) a_dd += c * (-0.5f * (kPiF / rc) * (kPiF / rc) * cs);
+    }
   }
   // ---- radial basis ----
-  if (prm.basis != kBasisNone && (MODE == kGeoVjp ? c_rbf != nullptr : o_rbf != nullptr)) {
+  if (prm.basis != kBasisNone && (kCot ? c_rbf != nullptr : o_rbf != nullptr)) {
     const int R = prm.R;
     if (prm.basis == kBasisGauss) {
       const float t0 = d - prm.offset;
@@ -102,13 +126,18 @@ edge_geometry_kernel(const float* __restrict__ xyz, const int32_t* __restrict__ 
         else {
           const float dg = -2.f * prm.gamma * t * g;
           if (MODE == kGeoJvp) o_rbf[e * R + k] = dg * t_d;
-          else a_d += __ldg(c_rbf + e * R + k) * dg;
+          else {
+            const float c = __ldg(c_rbf + e * R + k);
+            a_d += c * dg;
+            if (MODE == kGeoVjpVjp) a_dd += c * (4.f * prm.gamma * prm.gamma * t * t - 2.f * prm.gamma) * g;
+          }
         }
       }
     } else {
       const float x = d * prm.inv_cutoff;
       float env, denv;
       bessel_env(x, prm.p, env, denv);
+      const float ddenv = (MODE == kGeoVjpVjp) ? bessel_env2(x, prm.p) : 0.f;
       for (int k = 0; k < R; ++k) {
         const float f = __ldg(freq + k);
         float sn, cs;
@@ -117,7 +146,12 @@ edge_geometry_kernel(const float* __restrict__ xyz, const int32_t* __restrict__ 
         else {
           const float dr = (denv * sn + env * f * cs) * prm.inv_cutoff;        // d rbf / d d
           if (MODE == kGeoJvp) o_rbf[e * R + k] = dr * t_d;
-          else a_d += __ldg(c_rbf + e * R + k) * dr;
+          else {
+            const float c = __ldg(c_rbf + e * R + k);
+            a_d += c * dr;
+            if (MODE == kGeoVjpVjp)
+              a_dd += c * (ddenv * sn + 2.f * denv * f * cs - env * f * f * sn) * prm.inv_cutoff * prm.inv_cutoff;
+          }
         }
       }
     }
@@ -131,6 +165,23 @@ edge_geometry_kernel(const float* __restrict__ xyz, const int32_t* __restrict__ 
       const float uh = ux * hx + uy * hy + uz * hz;
       o_u[3 * e] = (hx - uh * ux) * inv; o_u[3 * e + 1] = (hy - uh * uy) * inv; o_u[3 * e + 2] = (hz - uh * uz) * inv;
     }
+  } else if (MODE == kGeoVjpVjp) {
+    float gx = 0.f, gy = 0.f, gz = 0.f;
+    if (d > 0.f) {
+      const float wx = vx / d, wy = vy / d, wz = vz / d;           // v / d (= u unless d == 0)
+      const float we = wx * hx + wy * hy + wz * hz;                // u . eta
+      const float k1 = a_dd * we - a_d * we / d, k2 = a_d / d;     // A2 (u.eta) u + A1 (eta - u (u.eta)) / d
+      gx = k1 * wx + k2 * hx; gy = k1 * wy + k2 * hy; gz = k1 * wz + k2 * hz;
+      if (c_u) {
+        const float cx = __ldg(c_u + 3 * e), cy = __ldg(c_u + 3 * e + 1), cz = __ldg(c_u + 3 * e + 2);
+        const float al = cx * wx + cy * wy + cz * wz, ga = cx * hx + cy * hy + cz * hz, id2 = 1.f / (d * d);
+        const float ku = (3.f * al * we - ga) * id2;
+        gx += ku * wx - (we * cx + al * hx) * id2;
+        gy += ku * wy - (we * cy + al * hy) * id2;
+        gz += ku * wz - (we * cz + al * hz) * id2;
+      }
+    }
+    o_gv[3 * e] = gx; o_gv[3 * e + 1] = gy; o_gv[3 * e + 2] = gz;
   } else {
     float gx = a_d * gdx, gy = a_d * gdy, gz = a_d * gdz;
     if (c_u) {                                         // (c_u - (c_u.u) u) / d
@@ -221,12 +272,12 @@ int kgcnn_edge_geometry(const float* xyz, const int32_t* idx_i, const int32_t* i
                         int no_nan, float cos_cutoff, const float* cot_d, const float* cot_u, const float* cot_rbf,
                         const float* cot_fc, const float* tangent_xyz, float* out_d, float* out_u, float* out_rbf,
                         float* out_fc, float* out_gv, kgcnn_stream_t stream) {
-  if (E < 0 || mode < kGeoFwd || mode > kGeoJvp || basis < kBasisNone || basis > kBasisBessel) return KGCNN_E_INVALID;
+  if (E < 0 || mode < kGeoFwd || mode > kGeoVjpVjp || basis < kBasisNone || basis > kBasisBessel) return KGCNN_E_INVALID;
   if (basis != kBasisNone && (R <= 0 || R > kMaxBasis || !basis_params)) return KGCNN_E_INVALID;
   if (E == 0) return KGCNN_OK;
   if (!xyz || !idx_i || !idx_j) return KGCNN_E_INVALID;
-  if (mode == kGeoVjp && !out_gv) return KGCNN_E_INVALID;
-  if (mode == kGeoJvp && !tangent_xyz) return KGCNN_E_INVALID;
+  if ((mode == kGeoVjp || mode == kGeoVjpVjp) && !out_gv) return KGCNN_E_INVALID;
+  if ((mode == kGeoJvp || mode == kGeoVjpVjp) && !tangent_xyz) return KGCNN_E_INVALID;
   if (basis == kBasisBessel && !frequencies) return KGCNN_E_INVALID;
   GeoParams prm;
   prm.basis = basis; prm.R = R; prm.eps = eps; prm.no_nan = no_nan; prm.cos_cutoff = cos_cutoff;
@@ -241,7 +292,10 @@ int kgcnn_edge_geometry(const float* xyz, const int32_t* idx_i, const int32_t* i
   cudaStream_t st = as_stream(stream);
 #define KGCNN_GEO(M) edge_geometry_kernel<M><<<grid, 256, 0, st>>>(xyz, idx_i, idx_j, E, prm, frequencies, cot_d, \
     cot_u, cot_rbf, cot_fc, tangent_xyz, out_d, out_u, out_rbf, out_fc, out_gv)
-  if (mode == kGeoFwd) KGCNN_GEO(kGeoFwd); else if (mode == kGeoVjp) KGCNN_GEO(kGeoVjp); else KGCNN_GEO(kGeoJvp);
+  if (mode == kGeoFwd) KGCNN_GEO(kGeoFwd);
+  else if (mode == kGeoVjp) KGCNN_GEO(kGeoVjp);
+  else if (mode == kGeoJvp) KGCNN_GEO(kGeoJvp);
+  else KGCNN_GEO(kGeoVjpVjp);
 #undef KGCNN_GEO
   return finish_launch();
 }

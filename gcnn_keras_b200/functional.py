@@ -1506,7 +1506,7 @@ def raw_edge_geometry(xyz, spec, mode, cots=None, tangent=None):
     bp = (ctypes.c_float * 3)(*spec.basis_params)
     outs = {k: None for k in ("d", "u", "rbf", "fc")}
     gv = None
-    if mode == 1:
+    if mode in (1, 3):
         gv = torch.empty((E, 3), dtype=torch.float32, device=dev)
         cots = {k: (None if v is None else _f32c(v)) for k, v in cots.items()}
     else:
@@ -1521,7 +1521,7 @@ def raw_edge_geometry(xyz, spec, mode, cots=None, tangent=None):
         _ptr(cots.get("d")), _ptr(cots.get("u")), _ptr(cots.get("rbf")), _ptr(cots.get("fc")), _ptr(tangent),
         _ptr(outs["d"]), _ptr(outs["u"]), _ptr(outs["rbf"]), _ptr(outs["fc"]), _ptr(gv), _stream()),
         "kgcnn_edge_geometry")
-    return gv if mode == 1 else tuple(outs[k] for k in spec.want)
+    return gv if mode in (1, 3) else tuple(outs[k] for k in spec.want)
 
 
 def _geom_composite(xyz, spec):
@@ -1555,9 +1555,16 @@ def _geom_composite(xyz, spec):
     return tuple(out[k] for k in spec.want)
 
 
+GEOMETRY_HESSIAN_KERNEL = True    # False: the coordinate-Hessian term through the op-by-op composite (tests, A/B)
+
+
 def _geom_hessian_term(xyz, spec, cots, hvec):
-    """d/dxyz <J(xyz)^T cots, hvec> through the composite (only when the caller really differentiates the
-    force with respect to the coordinates; force TRAINING never does)."""
+    """d/dxyz <J(xyz)^T cots, hvec>: the coordinate-Hessian term (only when the caller really differentiates the
+    force with respect to the coordinates; force TRAINING never does).  One launch of the geometry kernel in mode 3
+    + the two deterministic segment sums; Bessel bases with trainable frequencies included (frequencies constant)."""
+    if GEOMETRY_HESSIAN_KERNEL:
+        gv = raw_edge_geometry(xyz, spec, 3, cots=dict(zip(spec.want, cots)), tangent=hvec)
+        return raw_gms(gv, None, spec.rel_i, None) - raw_gms(gv, None, spec.rel_j, None)
     with torch.enable_grad():
         x = xyz.detach().requires_grad_(True)
         outs = _geom_composite(x, spec)

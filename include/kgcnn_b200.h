@@ -234,6 +234,10 @@ int kgcnn_dense_rel(int op, const float* A, const float* B, const int32_t* offs,
  *   mode 1: VJP; cot_d / cot_u / cot_rbf / cot_fc (each nullable) -> out_gv[E,3] = cotangent of v; the caller adds
  *           it to x_i and subtracts it from x_j with the deterministic segment kernel
  *   mode 2: JVP; tangent_xyz[N,3] -> tangents of (d, u, rbf, fc) into the mode-0 outputs
+ *   mode 3: VJP of mode 1 with respect to the coordinates (_vjp_vjp, the coordinate-Hessian term of
+ *           kgcnn/layers/geom.py:181-190 under two tapes): the cotangents cot_* that entered mode 1 and the cotangent
+ *           tangent_xyz[N,3] of its result -> out_gv[E,3] = d/dv sum <cot, D out(v)[h_i - h_j]>  (scattered +i / -j
+ *           by the caller like mode 1)
  *   idx_i / idx_j: batch-indexed int32 columns in the ORIGINAL edge order.  Frequencies are constants here (a
  *   trainable Bessel basis keeps its own differentiable path on top of out_d).
  * ------------------------------------------------------------------------------------------- */

@@ -184,3 +184,27 @@ def test_trainable_bessel_frequencies_get_their_gradient_from_the_kernel():
     loss_o, g_o = loss_and_grad(oracle_rbf, x64, f64, torch.float64)
     assert abs(loss_d - loss_o) <= RTOL * abs(loss_o)
     assert rel_err(g_d.cpu().numpy(), g_o.numpy()) < RTOL
+
+
+@pytest.mark.parametrize("kind", ["distance", "direction", "gauss", "bessel", "cos"])
+@pytest.mark.parametrize("add_eps", [False, True])
+def test_coordinate_hessian_kernel_matches_fp64_oracle(kind, add_eps):
+    """kgcnn_edge_geometry mode 3 (the VJP of the coordinate VJP, kgcnn/layers/geom.py:181-190 under two tapes):
+    d/dx <J(x)^T c, h> against the fp64 restatement, for every output the fused geometry produces."""
+    from gcnn_keras_b200 import functional as F
+    assert F.GEOMETRY_HESSIAN_KERNEL
+    x_np, idx, nl, el = _mol_batch(seed=4)
+    x = torch.tensor(x_np, device="cuda", requires_grad=True)
+    ox = torch.tensor(x_np, dtype=torch.float64, requires_grad=True)
+    out = _device_outputs(kind, x, nl, idx, el, add_eps)
+    o_out = _oracle_outputs(kind, ox, nl, idx, el, add_eps)
+    rng = np.random.default_rng(7)
+    cot = rng.standard_normal(tuple(o_out.shape))
+    h = rng.standard_normal(x_np.shape)
+    launches = F._lib.launch_count()
+    (vjp,) = torch.autograd.grad(out, x, torch.tensor(cot, dtype=torch.float32, device="cuda"), create_graph=True)
+    (hess,) = torch.autograd.grad(vjp, x, torch.tensor(h, dtype=torch.float32, device="cuda"))
+    assert F._lib.launch_count() > launches
+    (o_vjp,) = torch.autograd.grad(o_out, ox, torch.tensor(cot), create_graph=True)
+    (o_hess,) = torch.autograd.grad(o_vjp, ox, torch.tensor(h))
+    assert rel_err(hess.cpu().numpy(), o_hess.numpy()) < RTOL
