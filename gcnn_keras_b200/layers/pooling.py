@@ -151,6 +151,123 @@ class PoolingLocalEdgesAttention(GraphBaseLayer):
 PoolingLocalMessagesAttention = PoolingLocalEdgesAttention
 
 
+@register_keras_serializable(package="kgcnn", name="PoolingLocalEdgesLSTM")
+class PoolingLocalEdgesLSTM(GraphBaseLayer):
+    """kgcnn/layers/pooling.py:288-460.  call([nodes, edges, tensor_index]) -> the LAST hidden state of an LSTM run
+    over the edges of every node in (stable) receiver order; nodes without edges keep the zero initial state.
+
+    The reference sorts the edges, builds a ragged [N, (deg), F] tensor and hands it to ``ks.layers.LSTM``
+    (pooling.py:417-437), whose cell is  z = x W + h U + b,  (i, f, g, o) = split(z),
+    c' = sigma(f) c + sigma(i) tanh(g),  h' = sigma(o) tanh(c')  (Keras LSTMCell, gate order i, f, c, o), with the
+    state frozen once a sequence has ended.  Here the input projection of ALL edges is one tcgen05 Dense, the rows are
+    brought into CSR order by the permutation kernel and padded to [N, max_deg, 4 units] by ``kgcnn_pad``; each time
+    step is then one recurrent Dense [N, units] x [units, 4 units] plus the gate arithmetic on the rows still active.
+    Supported: the configuration the reference's models use (return_sequences / return_state / stateful False, no
+    dropout); anything else raises at construction."""
+
+    def __init__(self, units, pooling_method="LSTM", pooling_index=0, activation="tanh",
+                 recurrent_activation="sigmoid", use_bias=True, kernel_initializer="glorot_uniform",
+                 recurrent_initializer="orthogonal", bias_initializer="zeros", unit_forget_bias=True,
+                 kernel_regularizer=None, recurrent_regularizer=None, bias_regularizer=None,
+                 activity_regularizer=None, kernel_constraint=None, recurrent_constraint=None, bias_constraint=None,
+                 dropout=0.0, recurrent_dropout=0.0, return_sequences=False, return_state=False, go_backwards=False,
+                 stateful=False, time_major=False, unroll=False, **kwargs):
+        super().__init__(**kwargs)
+        if return_sequences or return_state or stateful:
+            raise ValueError("PoolingLocalEdgesLSTM: return_sequences / return_state / stateful are not supported "
+                             "(the pooled output is the last hidden state per node)")
+        if dropout or recurrent_dropout:
+            raise ValueError("PoolingLocalEdgesLSTM: dropout inside the recurrence is not supported")
+        self.units = int(units)
+        self.pooling_method = pooling_method
+        self.pooling_index = pooling_index
+        self.use_bias, self.unit_forget_bias, self.go_backwards = use_bias, unit_forget_bias, go_backwards
+        self._cfg = {"activation": activation, "recurrent_activation": recurrent_activation, "use_bias": use_bias,
+                     "kernel_initializer": kernel_initializer, "recurrent_initializer": recurrent_initializer,
+                     "bias_initializer": bias_initializer, "unit_forget_bias": unit_forget_bias,
+                     "kernel_regularizer": kernel_regularizer, "recurrent_regularizer": recurrent_regularizer,
+                     "bias_regularizer": bias_regularizer, "activity_regularizer": activity_regularizer,
+                     "kernel_constraint": kernel_constraint, "recurrent_constraint": recurrent_constraint,
+                     "bias_constraint": bias_constraint, "dropout": dropout, "recurrent_dropout": recurrent_dropout,
+                     "implementation": 2, "return_sequences": return_sequences, "return_state": return_state,
+                     "go_backwards": go_backwards, "stateful": stateful, "time_major": time_major, "unroll": unroll}
+        self._act, self._rec_act = self._activation(activation), self._activation(recurrent_activation)
+        self.kernel = self.recurrent_kernel = self.bias = None
+        if self.pooling_method not in ["LSTM", "lstm"]:
+            print("Warning: Pooling method does not match with layer, expected 'LSTM' but got", self.pooling_method)
+
+    @staticmethod
+    def _activation(name):
+        table = {"tanh": torch.tanh, "sigmoid": torch.sigmoid, "relu": torch.relu, "linear": lambda x: x,
+                 None: lambda x: x, "hard_sigmoid": lambda x: torch.clamp(0.2 * x + 0.5, 0.0, 1.0)}
+        if name not in table:
+            raise ValueError("PoolingLocalEdgesLSTM: unsupported activation %r" % (name,))
+        return table[name]
+
+    def build(self, input_shape):
+        super().build(input_shape)
+        from .modules import _glorot_uniform_
+        in_dim, u = int(input_shape[-1]), self.units
+        self.kernel = torch.nn.Parameter(_glorot_uniform_(torch.empty(in_dim, 4 * u)))
+        self.recurrent_kernel = torch.nn.Parameter(torch.cat(
+            [torch.nn.init.orthogonal_(torch.empty(u, u)) for _ in range(4)], dim=1))
+        if self.use_bias:
+            b = torch.zeros(4 * u)
+            if self.unit_forget_bias:
+                b[u:2 * u] = 1.0
+            self.bias = torch.nn.Parameter(b)
+
+    def forward(self, inputs, **kwargs):
+        if not self.built:
+            v = inputs[1].values
+            self.build(tuple(v.shape))
+            self.to(v.device)
+        return self.call(inputs, **kwargs)
+
+    def call(self, inputs, **kwargs):
+        nodes, edges, index = self.assert_ragged_input_rank(inputs)
+        rel = get_plan(index, nodes).relation(self.pooling_index)
+        u, n = self.units, rel.n_targets
+        dev = edges.values.device
+        h = torch.zeros((n, u), dtype=torch.float32, device=dev)
+        if rel.n_elements == 0 or n == 0:
+            return nodes.with_values(h)
+        zx = F.dense(edges.values, self.kernel, self.bias, "linear")            # [E, 4u]: x W + b for every edge
+        perm = rel.perm
+        if perm is not None:                                                   # stable receiver order (pooling.py:419-423)
+            inv = torch.empty_like(perm)
+            inv[perm.long()] = torch.arange(perm.shape[0], dtype=perm.dtype, device=dev)
+            zx = F.permute_rows(zx, perm, inv)
+        rowptr = rel.rowptr.to(torch.int64)
+        deg = rowptr[1:] - rowptr[:-1]
+        max_len = int(deg.max())                                               # one host sync per call
+        zp = F.pad(zx, rowptr, max_len)                                        # [N, max_len, 4u]
+        c = torch.zeros_like(h)
+        for step in range(max_len):
+            active = (deg > step).unsqueeze(1)
+            if self.go_backwards:                                              # position deg - 1 - step of every row
+                pos = (deg - 1 - step).clamp_min(0).view(n, 1, 1).expand(n, 1, 4 * u)
+                z_in = torch.gather(zp, 1, pos).squeeze(1)
+            else:
+                z_in = zp[:, step]
+            z = z_in + F.matmul(h, self.recurrent_kernel)
+            zi, zf, zg, zo = z[:, :u], z[:, u:2 * u], z[:, 2 * u:3 * u], z[:, 3 * u:]
+            c_new = self._rec_act(zf) * c + self._rec_act(zi) * self._act(zg)
+            h_new = self._rec_act(zo) * self._act(c_new)
+            c = torch.where(active, c_new, c)
+            h = torch.where(active, h_new, h)
+        return nodes.with_values(h)
+
+    def get_config(self):
+        config = super().get_config()
+        config.update({"pooling_method": self.pooling_method, "pooling_index": self.pooling_index, "units": self.units})
+        config.update(self._cfg)
+        return config
+
+
+PoolingLocalMessagesLSTM = PoolingLocalEdgesLSTM
+
+
 @register_keras_serializable(package="kgcnn", name="PoolingEmbeddingAttention")
 class PoolingEmbeddingAttention(GraphBaseLayer):
     """kgcnn/layers/pooling.py:550-599.  call([nodes, attention]) -> dense [B, F]: s = sum_i softmax_i(a_i) n_i."""

@@ -113,6 +113,38 @@ def pooling_local_edges_attention(nodes, edges, attention, index, pooling_index=
     return nodes.with_values(get)
 
 
+def pooling_local_edges_lstm(nodes, edges, index, kernel, recurrent_kernel, bias=None, pooling_index=0,
+                             is_sorted=False, go_backwards=False):
+    """PoolingLocalEdgesLSTM.call, pooling.py:398-446: stable sort by receiver (:419-423), ragged [N, (deg), F]
+    (:427), ks.layers.LSTM -> last hidden state (:428), zero rows for nodes without edges (:430-434).
+    The cell is Keras' LSTMCell (third party, TensorFlow 2.12 keras/layers/rnn/lstm.py): z = x W + h U + b,
+    gate order (i, f, c, o), c' = sigmoid(f) c + sigmoid(i) tanh(g), h' = sigmoid(o) tanh(c').  PARITY UNPINNED:
+    the reference holds no numeric test for this layer.  Plain loop per node: small cases only."""
+    shiftind = _batch_index(index, nodes)
+    nodind = shiftind[:, pooling_index]
+    dens = edges.values
+    if not is_sorted:
+        node_order = torch.argsort(nodind, stable=True)
+        nodind, dens = nodind[node_order], dens[node_order]
+    n, u = nodes.values.shape[0], recurrent_kernel.shape[0]
+    rows = []
+    for i in range(n):
+        seq = dens[nodind == i]
+        if go_backwards:
+            seq = torch.flip(seq, dims=[0])
+        h = torch.zeros(u, dtype=dens.dtype)
+        c = torch.zeros(u, dtype=dens.dtype)
+        for x in seq:
+            z = x @ kernel + h @ recurrent_kernel
+            if bias is not None:
+                z = z + bias
+            zi, zf, zg, zo = z[:u], z[u:2 * u], z[2 * u:3 * u], z[3 * u:]
+            c = torch.sigmoid(zf) * c + torch.sigmoid(zi) * torch.tanh(zg)
+            h = torch.sigmoid(zo) * torch.tanh(c)
+        rows.append(h)
+    return nodes.with_values(torch.stack(rows) if rows else torch.zeros((0, u), dtype=dens.dtype))
+
+
 def pooling_embedding_attention(nodes, attention):
     """PoolingEmbeddingAttention.call (= PoolingNodesAttention), pooling.py:583-589: dense [B, F]."""
     batchi = nodes.value_rowids()

@@ -165,3 +165,28 @@ def test_attention_pooling_oracle_properties():
     a = att.values.clone().requires_grad_(True)
     fn = lambda e_, a_: OL.pooling_local_edges_attention(nodes, ones.with_values(e_), att.with_values(a_), o_idx).values
     assert torch.autograd.gradcheck(fn, (e, a))
+
+
+def test_oracle_lstm_pooling_agrees_with_an_independent_lstm():
+    """The LSTM restatement (oracle/layers.py, Keras gate order i, f, c, o) against torch.nn.LSTM (same gate order,
+    weights transposed) on every node's edge sequence."""
+    import numpy as np
+    import torch
+    from oracle import R
+    from oracle import layers as OL
+    rng = np.random.default_rng(0)
+    n, feat, u = 5, 6, 4
+    recv = np.array([0, 0, 0, 2, 2, 3, 4, 4, 4, 4])
+    idx = np.stack([recv, rng.integers(0, n, size=recv.shape)], 1)
+    edges = torch.tensor(rng.standard_normal((len(recv), feat)))
+    w, uu, b = (torch.tensor(rng.standard_normal(s)) for s in ((feat, 4 * u), (u, 4 * u), (4 * u,)))
+    nodes = R.from_row_lengths(torch.zeros((n, 1), dtype=torch.float64), [n])
+    got = OL.pooling_local_edges_lstm(nodes, R.from_row_lengths(edges, [len(recv)]),
+                                      R.from_row_lengths(torch.tensor(idx), [len(recv)]), w, uu, b).values
+    lstm = torch.nn.LSTM(feat, u, batch_first=True).double()
+    with torch.no_grad():
+        lstm.weight_ih_l0.copy_(w.t()), lstm.weight_hh_l0.copy_(uu.t()), lstm.bias_ih_l0.copy_(b), lstm.bias_hh_l0.zero_()
+    for i in range(n):
+        seq = edges[torch.tensor(recv == i)]
+        want = torch.zeros(u, dtype=torch.float64) if len(seq) == 0 else lstm(seq[None])[1][0][0, 0]
+        assert torch.allclose(got[i], want.detach(), atol=1e-12)
