@@ -470,6 +470,72 @@ def roofline_shapes(device):
            [lambda: F.raw_gms(x, None, recv, send), lambda: F.raw_gms(dyl, None, send, recv)])
 
 
+CFCONV_PROFILE = "r2_cfconv_full.csv"   # ncu --set full of tools/ncu_cfconv.py (mode 0 and mode 1 launch, same shape)
+
+
+def cfconv_roofline(device, iters=5):
+    """The fused SchNet cfconv (csrc/cfconv.cu: basis -> Dense(ssp) -> Dense -> gather * filter -> segment sum in ONE
+    kernel, kgcnn/layers/conv/schnet_conv.py:73-79) at an HBM-sized graph, forward (mode 0) and input-gradient (mode 1)
+    launch, beside the unfused chain on the same inputs.  The kernel is TENSOR-bound, not HBM-bound: its DRAM traffic
+    is the node rows and the indices only (ncu: profiles/r2_cfconv_full.csv).  `achieved` counts the ALGORITHMIC
+    flops of the two Dense layers (2 (R + 128) 128 per edge and derivative order); `issued` the bf16 MMA flops the
+    three-piece split really executes (6 MMAs per product, R padded to 32)."""
+    from gcnn_keras_b200 import RaggedTensor
+    from gcnn_keras_b200 import functional as F
+    from gcnn_keras_b200.plan import get_plan
+    rng = np.random.default_rng(0)
+    n, deg, R = 262144, 32, 25
+    recv = np.repeat(np.arange(n), deg)
+    send = (recv + rng.integers(1, 4096, size=recv.shape)) % n
+    E = recv.shape[0]
+    nodes = RaggedTensor.from_row_lengths(torch.randn(n, 128, device=device), torch.tensor([n], device=device))
+    index = RaggedTensor.from_row_lengths(torch.tensor(np.stack([recv, send], 1), device=device),
+                                          torch.tensor([E], device=device))
+    plan = get_plan(index, nodes)
+    spec = F.CfconvSpec(plan.relation(0), plan.relation(1), R, 3.125, 0.0, 0.2, F.act_code("kgcnn>shifted_softplus"))
+    x, d = nodes.values, torch.rand(E, device=device) * 4 + 0.8
+    w1, b1 = torch.randn(R, 128, device=device) * 0.4, torch.zeros(128, device=device)
+    w2, b2 = torch.randn(128, 128, device=device) * 0.15, torch.zeros(128, device=device)
+    gy = torch.randn(n, 128, device=device)
+    spec.recv.rowptr, spec.send.rowptr, spec.send.permuted_ids(spec.recv), spec.send.permuted_ids(spec.send)
+    fwd = lambda: F.raw_cfconv(0, spec, d, w1, b1, w2, b2, spec.recv, spec.send, x)
+    vjp = lambda: F.raw_cfconv(1, spec, d, w1, b1, w2, b2, spec.send, spec.recv, gy, b=x)
+    with torch.no_grad():
+        ms_f, ms_b = _time(fwd, iters), _time(vjp, iters)
+        ms_unf = _time(lambda: F._cfconv_unfused(x, d, w1, b1, w2, b2, spec), iters)
+    tensor_peak = None
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
+            tensor_peak = float(json.load(fh)["bf16_tflops"])
+    except Exception:
+        pass
+    tensor_peak = tensor_peak or 1633.0
+    alg = 2.0 * (R + 128) * 128 * E                      # forward; the VJP evaluates phi and phi': twice that
+    issued = 60 * 2.0 * 128 * 128 * 16 * ((E + 127) // 128)
+    t_f = profile_traffic(CFCONV_PROFILE, "cfconv_kernel<0", 0, 1)
+    t_b = profile_traffic(CFCONV_PROFILE, "cfconv_kernel<1", 0, 1)
+    alg_bytes_f = 8 * n * 128 + 12 * E                    # node rows in, node rows out, (row, other, distance) per edge
+    hbm_peak, _ = measured_peaks()
+    return {"bound": "tensor", "workload": "fused cfconv, N=%d, E=%d, F=128, %d Gaussians" % (n, E, R),
+            "kernel": "cf::cfconv_kernel<0> (value) and <1> (input gradients), csrc/cfconv.cu",
+            "unit": "TFLOP/s", "peak": tensor_peak, "peak_source": "MEASURED_PEAKS.json bf16_tflops (burst)",
+            "achieved": alg / (ms_f * 1e-3) / 1e12, "frac": alg / (ms_f * 1e-3) / 1e12 / tensor_peak,
+            "issued_TFLOPs": issued / (ms_f * 1e-3) / 1e12, "frac_issued": issued / (ms_f * 1e-3) / 1e12 / tensor_peak,
+            "ms_forward": ms_f, "ms_input_gradients": ms_b, "edges_per_s_forward": E / (ms_f * 1e-3),
+            "achieved_input_gradients": 2 * alg / (ms_b * 1e-3) / 1e12,
+            "frac_issued_input_gradients": 2 * issued / (ms_b * 1e-3) / 1e12 / tensor_peak,
+            "unfused_forward_ms": ms_unf, "speedup_over_unfused_forward": ms_unf / ms_f,
+            "algorithmic_bytes_forward": alg_bytes_f, "traffic": t_f, "traffic_input_gradients": t_b,
+            "traffic_over_algorithmic_bytes": None if t_f is None else t_f / alg_bytes_f,
+            "unfused_algorithmic_bytes_forward": 4 * E * (2 * R + 5 * 128) + 8 * n * 128 + 8 * E,
+            "hbm_floor_ms_of_unfused_forward": (4 * E * (2 * R + 5 * 128) + 8 * n * 128 + 8 * E) / hbm_peak / 1e6,
+            "traffic_source": "profiles/" + CFCONV_PROFILE,
+            "note": "the fused kernel moves 0.35 GB where the unfused chain moves >= 5.7 GB (rbf, two [E,128] "
+                    "activations written and re-read, the filter read by the pooling kernel); what bounds it is the "
+                    "serial per-tile chain basis -> MMA -> activation -> MMA -> epilogue (ncu: tensor pipe 25-31 % "
+                    "active, issue slots 32-34 %)"}
+
+
 GMS_PROFILE = "r2_gms_full.csv"     # ncu --set full of tools/ncu_gms.py on the final build (rows in launch order)
 _PROFILE_ROWS = {"plain": [("gms_kernel", 0, 2)], "weighted": [("gms_kernel", 2, 2), ("gather2_mul", 0, 1)],
                  "gss_g": [("gms_kernel", 4, 2)], "cached_shape": [("gms_kernel", 6, 2)]}
@@ -507,6 +573,7 @@ def gss_roofline(device, iters=10):
             out.update(e)
         else:
             out[key] = e
+    out["cfconv_fused"] = cfconv_roofline(device, max(3, iters // 2))
     out["kernel_family"] = "gms_kernel / gather2_mul_kernel (csrc/segment_impl.cuh, csrc/gather.cu)"
     out["note"] = ("achieved = algorithmic bytes of SURVEY 8(d) (every gathered row counted, no cache credit) / time of "
                    "the launches; traffic = measured DRAM bytes of the same launches (ncu), so frac_on_traffic is the "

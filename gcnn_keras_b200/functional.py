@@ -395,6 +395,41 @@ class _GMS_edge(torch.autograd.Function):
         return gv, gw, None
 
 
+class _GatherConcat(torch.autograd.Function):
+    """y[e] = concat_k x[rel_k.ids[e]]  (kgcnn/layers/gather.py:83-90: tf.gather [E,K,F] + K slices + tf.concat):
+    K launches of the strided-output row gather into ONE [E, K F] buffer, no concat pass.  Backward: the segment sum
+    of each column block along its relation."""
+
+    @staticmethod
+    def forward(ctx, x, *rels):
+        ctx.rels = rels
+        x2 = _f32c(_flat2d(x))
+        ctx.tail = tuple(x.shape[1:])
+        Fd = int(x2.shape[1])
+        out = torch.empty((rels[0].n_elements, Fd * len(rels)), dtype=torch.float32, device=x2.device)
+        for k, rel in enumerate(rels):
+            raw_gather_rows(x2, rel.ids, out=out, col_offset=k * Fd)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        Fd = g.shape[1] // len(ctx.rels)
+        total = None
+        for k, rel in enumerate(ctx.rels):
+            part = _SegmentSum.apply(g[:, k * Fd:(k + 1) * Fd].contiguous(), rel)
+            total = part if total is None else total + part
+        return (total.reshape((total.shape[0],) + ctx.tail),) + (None,) * len(ctx.rels)
+
+
+def gather_concat(x, rels):
+    """Concatenated row gathers along several relations of the same element set (GatherEmbedding, concat_axis=2)."""
+    if len(rels) == 1:
+        return gather(x, rels[0])
+    if not torch.is_floating_point(x) or x.dim() != 2:
+        return torch.cat([gather(x, r) for r in rels], dim=1)
+    return _GatherConcat.apply(x, *rels)
+
+
 def gather(x, rel):
     """Row gather along a relation (any trailing feature shape)."""
     if x.dtype == torch.int64 or not torch.is_floating_point(x):

@@ -40,8 +40,7 @@ class GatherEmbedding(GraphBaseLayer):
         x = nodes.values
         if self.concat_axis == 2:                                 # gather.py:85-90
             cols = list(self.concat_indices) if self.concat_indices else list(range(plan.K))
-            parts = [F.gather(x, plan.relation(c)) for c in cols]
-            return index.with_values(torch.cat(parts, dim=1) if len(parts) > 1 else parts[0])
+            return index.with_values(F.gather_concat(x, [plan.relation(c) for c in cols]))   # strided gathers, no cat
         if self.split_axis == 2:                                  # gather.py:92-97
             cols = list(self.split_indices) if self.split_indices else list(range(plan.K))
             return [index.with_values(F.gather(x, plan.relation(c))) for c in cols]
