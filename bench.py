@@ -530,7 +530,7 @@ def cfconv_roofline(device, iters=5):
             "unfused_algorithmic_bytes_forward": 4 * E * (2 * R + 5 * 128) + 8 * n * 128 + 8 * E,
             "hbm_floor_ms_of_unfused_forward": (4 * E * (2 * R + 5 * 128) + 8 * n * 128 + 8 * E) / hbm_peak / 1e6,
             "traffic_source": "profiles/" + CFCONV_PROFILE,
-            "note": "the fused kernel moves 0.35 GB where the unfused chain moves >= 5.7 GB (rbf, two [E,128] "
+            "note": "the fused kernel moves 0.35 GB where the unfused chain moves >= 23 GB (rbf, two [E,128] "
                     "activations written and re-read, the filter read by the pooling kernel); what bounds it is the "
                     "serial per-tile chain basis -> MMA -> activation -> MMA -> epilogue (ncu: tensor pipe 25-31 % "
                     "active, issue slots 32-34 %)"}
