@@ -417,7 +417,7 @@ tn_split_reduce_kernel(const float* __restrict__ partial, int S, int64_t n, floa
 // fixed order (deterministic); several problems may target the same dW (a weight used by the forward Linear and by
 // the force's g W^T): the reduce kernel walks outputs, not problems, so there is no write race.
 // ---------------------------------------------------------------------------------------------------------
-constexpr int kMaxGroup = 64;
+constexpr int kMaxGroup = 128;     // problems per launch (the table travels as a 13 KB kernel parameter)
 
 struct TnProblem {          // 64 bytes
   const float* X;           // [M, K]
@@ -586,16 +586,23 @@ inline int tn_splits(int64_t M, int K, int U) {
   return static_cast<int>(s);
 }
 
-// rows per split for a grouped launch: ~2 waves of one resident CTA per SM (the kernel needs ~230 registers per
-// thread) over all problems, at least 2 chunks each
+// rows per split for one grouped launch: the finest split whose CTA count still fits TWO FULL WAVES of one resident
+// CTA per SM (a launch of 2.1 waves runs three rounds: ncu of the C2 step, 314 CTAs), at least 4 chunks per CTA.
 inline int64_t grouped_rows_per_split(int n, const int64_t* M, const int32_t* K, const int32_t* U) {
   int64_t chunk_tiles = 0;
   for (int i = 0; i < n; ++i)
     chunk_tiles += ceil_div<int64_t>(std::max<int64_t>(M[i], 1), kKC) * ceil_div(K[i], kBM) * ceil_div(U[i], kMaxN);
   const int64_t target = 2LL * kNumSM;
-  // (a search that grows the split until the launch fits two full waves was measured: PaiNN C3 -0.5 %, SchNet C2
-  //  +14 % on this kernel because its many small problems then share fewer, longer CTAs -- not kept)
-  const int64_t per_cta = std::max<int64_t>(4, ceil_div<int64_t>(chunk_tiles, target));
+  int64_t per_cta = std::max<int64_t>(4, ceil_div<int64_t>(chunk_tiles, target));
+  for (int iter = 0; iter < 4096; ++iter) {
+    int64_t ctas = 0;
+    for (int i = 0; i < n; ++i) {
+      if (M[i] <= 0) continue;
+      ctas += ceil_div<int64_t>(ceil_div<int64_t>(M[i], kKC), per_cta) * ceil_div(K[i], kBM) * ceil_div(U[i], kMaxN);
+    }
+    if (ctas <= target) break;
+    per_cta += std::max<int64_t>(1, per_cta / 64);
+  }
   return per_cta * kKC;
 }
 
@@ -672,14 +679,18 @@ int kgcnn_dense_act(const float* X, const float* W, int64_t M, int K, int U, con
 
 size_t kgcnn_dense_tn_grouped_workspace_bytes(int n, const int64_t* M, const int32_t* K, const int32_t* U) {
   if (n <= 0 || !M || !K || !U) return 0;
-  const int64_t rps = tc::grouped_rows_per_split(n, M, K, U);
   size_t floats = 0;
-  for (int i = 0; i < n; ++i) {
-    const int64_t splits = std::max<int64_t>(1, ceil_div<int64_t>(M[i], rps));
-    floats += static_cast<size_t>(splits) * (static_cast<size_t>(K[i]) * U[i] + U[i]);
-    floats = (floats + 63) / 64 * 64;
+  for (int g0 = 0; g0 < n; g0 += tc::kMaxGroup) {            // the launcher packs kMaxGroup problems per launch
+    const int cnt = std::min(tc::kMaxGroup, n - g0);
+    const int64_t rps = tc::grouped_rows_per_split(cnt, M + g0, K + g0, U + g0);
+    for (int i = g0; i < g0 + cnt; ++i) {
+      const int64_t splits = std::max<int64_t>(1, ceil_div<int64_t>(M[i], rps));
+      floats += static_cast<size_t>(splits) * (static_cast<size_t>(K[i]) * U[i] + U[i]);
+      floats = (floats + 63) / 64 * 64;
+    }
   }
-  return floats * sizeof(float) + 256;
+  // x2: a destination conflict or an empty problem shifts the launch boundaries, and with them the split sizes
+  return 2 * floats * sizeof(float) + 256;
 }
 
 int kgcnn_dense_tn_grouped(int n, const float* const* X, const float* const* G, const int64_t* M, const int32_t* K,
@@ -698,7 +709,6 @@ int kgcnn_dense_tn_grouped(int n, const float* const* X, const float* const* G, 
     cudaFuncSetAttribute(tc::tn_grouped_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                          static_cast<int>(tc::kSmemBytes));
   });
-  const int64_t rps = tc::grouped_rows_per_split(n, M, K, U);
   float* ws = static_cast<float*>(workspace);
   int64_t ws_off = 0;
   int launches = 0;
@@ -709,6 +719,9 @@ int kgcnn_dense_tn_grouped(int n, const float* const* X, const float* const* G, 
   while (i < n) {
     tc::TnGroup grp;
     grp.n_problems = 0; grp.n_outputs = 0; grp.total_ctas = 0; grp.pad = 0; grp.total_elems = 0;
+    // split size of this launch: from the problems it can hold at most (a destination conflict may end it earlier,
+    // which only leaves the launch below two waves)
+    const int64_t rps = tc::grouped_rows_per_split(std::min(tc::kMaxGroup, n - i), M + i, K + i, U + i);
     for (; i < n && grp.n_problems < tc::kMaxGroup; ++i) {
       if (M[i] == 0) continue;                                     // contributes nothing
       int hit = -1;
@@ -731,6 +744,7 @@ int kgcnn_dense_tn_grouped(int n, const float* const* X, const float* const* G, 
       grp.total_ctas += pr.tiles_k * pr.tiles_u * pr.splits;
       int64_t fl = static_cast<int64_t>(pr.splits) * (static_cast<int64_t>(K[i]) * U[i] + U[i]);
       ws_off += (fl + 63) / 64 * 64;
+      if (static_cast<size_t>(ws_off) * sizeof(float) > workspace_bytes) return KGCNN_E_WORKSPACE;
       if (merge) {
         tc::TnOutput& o = grp.o[grp.n_outputs - 1];
         o.count += 1;
