@@ -17,6 +17,8 @@ template <int ACT, bool VEC>
 __global__ void __launch_bounds__(256)
 bias_act_kernel(const float* __restrict__ pre, const float* __restrict__ bias, const float* __restrict__ g1,
                 const float* __restrict__ g2, int order, int64_t total, int U, float* __restrict__ out) {
+  pdl_trigger();
+  pdl_wait();
   const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
   if (VEC) {
     const int64_t nv = total >> 2;
@@ -52,8 +54,8 @@ int launch_act(const float* pre, const float* bias, const float* g1, const float
   const bool vec = (U % 4 == 0) && al(pre) && al(bias) && al(g1) && al(g2) && al(out);
   const int64_t work = vec ? (total >> 2) : total;
   const unsigned grid = static_cast<unsigned>(std::min<int64_t>(ceil_div<int64_t>(work, 256), kNumSM * 16));
-  if (vec) bias_act_kernel<ACT, true><<<grid, 256, 0, st>>>(pre, bias, g1, g2, order, total, U, out);
-  else bias_act_kernel<ACT, false><<<grid, 256, 0, st>>>(pre, bias, g1, g2, order, total, U, out);
+  if (vec) launch_pdl(bias_act_kernel<ACT, true>, dim3(grid), dim3(256), 0, st, pre, bias, g1, g2, order, total, U, out);
+  else launch_pdl(bias_act_kernel<ACT, false>, dim3(grid), dim3(256), 0, st, pre, bias, g1, g2, order, total, U, out);
   return finish_launch();
 }
 
@@ -65,6 +67,8 @@ __global__ void __launch_bounds__(256)
 bias_act_pair_kernel(const float* __restrict__ pre, const float* __restrict__ bias, const float* __restrict__ gy,
                      const float* __restrict__ g1, int order, int64_t total, int U, float* __restrict__ d_pre,
                      float* __restrict__ d_g1) {
+  pdl_trigger();
+  pdl_wait();
   const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
   if (VEC) {
     const int64_t nv = total >> 2;
@@ -101,8 +105,8 @@ int launch_act_pair(const float* pre, const float* bias, const float* gy, const 
   const bool vec = (U % 4 == 0) && al(pre) && al(bias) && al(gy) && al(g1) && al(d_pre) && al(d_g1);
   const int64_t work = vec ? (total >> 2) : total;
   const unsigned grid = static_cast<unsigned>(std::min<int64_t>(ceil_div<int64_t>(work, 256), kNumSM * 16));
-  if (vec) bias_act_pair_kernel<ACT, true><<<grid, 256, 0, st>>>(pre, bias, gy, g1, order, total, U, d_pre, d_g1);
-  else bias_act_pair_kernel<ACT, false><<<grid, 256, 0, st>>>(pre, bias, gy, g1, order, total, U, d_pre, d_g1);
+  if (vec) launch_pdl(bias_act_pair_kernel<ACT, true>, dim3(grid), dim3(256), 0, st, pre, bias, gy, g1, order, total, U, d_pre, d_g1);
+  else launch_pdl(bias_act_pair_kernel<ACT, false>, dim3(grid), dim3(256), 0, st, pre, bias, gy, g1, order, total, U, d_pre, d_g1);
   return finish_launch();
 }
 

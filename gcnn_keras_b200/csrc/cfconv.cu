@@ -195,6 +195,7 @@ cfconv_kernel(const Params P) {
   uint4* hplanes = w2planes + 3 * kBigPlane;                    // [piece][kBigPlane]
   uint4* rplanes = hplanes;                                     // [q][piece][kKPlane]   (alias: dead before h is staged)
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  pdl_trigger();
   CTL(0);
   // touch every parameter line first: the constant-bank misses of a freshly launched kernel then overlap
   asm volatile("" ::"l"(P.dist), "l"(P.rows), "l"(P.a), "l"(P.out), "l"(P.wg_h), "l"(P.E), "r"(P.R));
@@ -242,6 +243,7 @@ cfconv_kernel(const Params P) {
       row_s[kBM + 1] = (e0 + kBM < E) ? __ldg(P.rows + e0 + kBM) : -2;
     }
   };
+  pdl_wait();                                                    // first global access below
   // weights -> operand planes, once per CTA; every global load is in flight before the first split
   if (warp < kWorkers / 32) {
     const int kk = 8 * (warp & 3) + (lane & 7), mn8 = 4 * (warp >> 2) + (lane >> 3);
@@ -653,6 +655,8 @@ cfconv_kernel(const Params P) {
 __global__ void __launch_bounds__(256)
 cfconv_fixup_kernel(const int32_t* __restrict__ rowptr, int64_t n_out, const float* __restrict__ ws,
                     float* __restrict__ out) {
+  pdl_trigger();
+  pdl_wait();
   const int64_t r = (blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (r >= n_out) return;
@@ -702,11 +706,12 @@ static int launch(const Params& P, const int32_t* rowptr, int64_t n_out, cudaStr
   int launches = 0;
   if (ntiles > 0) {
     const unsigned grid = static_cast<unsigned>(std::min<int64_t>(ntiles, kNumSM));
-    cfconv_kernel<MODE, WG><<<grid, kCtaThreads, kSmemBytes, st>>>(P);
+    launch_pdl(cfconv_kernel<MODE, WG>, dim3(grid), dim3(kCtaThreads), kSmemBytes, st, P);
     ++launches;
   }
   const int64_t threads = n_out * 32;
-  cfconv_fixup_kernel<<<static_cast<unsigned>((threads + 255) / 256), 256, 0, st>>>(rowptr, n_out, P.ws, P.out);
+  launch_pdl(cfconv_fixup_kernel, dim3(static_cast<unsigned>((threads + 255) / 256)), dim3(256), 0, st, rowptr, n_out,
+             static_cast<const float*>(P.ws), P.out);
   return finish_launch(launches + 1);
 }
 

@@ -42,6 +42,33 @@ struct PerDeviceOnce {
 
 inline cudaStream_t as_stream(kgcnn_stream_t s) { return reinterpret_cast<cudaStream_t>(s); }
 
+// Programmatic dependent launch (PDL).  The captured training steps are chains of hundreds of DEPENDENT kernels of
+// 2-15 us; with the launch attribute below the next kernel's CTAs are scheduled as soon as every CTA of the current one
+// has executed pdl_trigger() (the first instruction of each converted kernel), run their prologue (parameter fetch,
+// TMEM allocation, barrier set-up, address arithmetic) under the current kernel's tail and block in pdl_wait() until
+// the current grid has completed and its writes are visible.  Rule for every converted kernel: NO global-memory access
+// before pdl_wait().  Kernels launched with plain <<<>>> neither wait nor trigger and stay fully serialised on both
+// sides, so the two kinds mix freely.  KGCNN_PDL=0 in the environment turns the attribute off.
+bool pdl_enabled();
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+template <typename... Params, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(Params...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                              Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<Params>(args)...);
+}
+
 template <typename T>
 __host__ __device__ inline T ceil_div(T a, T b) {
   return (a + b - 1) / b;

@@ -50,6 +50,7 @@ dense_fast_kernel(const float* __restrict__ A, const float* __restrict__ B, int6
   auto b_planes = [&](int c) { return planes + static_cast<size_t>(c) * 3 * kPlaneUnits; };
   auto a_planes = [&](int c) { return planes + static_cast<size_t>(kStages + c) * 3 * kPlaneUnits; };
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  pdl_trigger();
   TL(0);
   // Touch every kernel parameter first: the constant-bank misses of a freshly launched kernel (~700 cycles per access
   // path, measured with tools/tc_timeline.cu) then overlap instead of queueing behind one another in the prologue.
@@ -132,6 +133,7 @@ dense_fast_kernel(const float* __restrict__ A, const float* __restrict__ B, int6
   };
   F8 va0, va1, va2, vb0, vb1;
   TL(18);
+  pdl_wait();                                                    // first global access below
   if (warp < kThreads / 32) {
     va0 = ld_a(0);
     vb0 = ld_b(0);
@@ -388,13 +390,13 @@ static void launch_fast_tr(const float* A, const float* B, int64_t M, int K, int
   // persistent walk over the row tiles when there are more than two waves of them to amortise the set-up over
   if (row_ctas * col_tiles > 2 * kNumSM && (ACT < 0 || TR)) {     // (two PADDED tiles do not fit behind W)
     dim3 grid(static_cast<unsigned>(std::max(1, kNumSM / col_tiles)), col_tiles);
-    dense_fast_kernel<OP, ACT, RAG, TR, true><<<grid, kCtaThreads, kSmemBytesPersistent, st>>>(A, B, M, K, U, bias, out,
-                                                                                               act_out);
+    launch_pdl(dense_fast_kernel<OP, ACT, RAG, TR, true>, grid, dim3(kCtaThreads), kSmemBytesPersistent, st, A, B, M, K,
+               U, bias, out, act_out);
     return;
   }
   dim3 grid(static_cast<unsigned>(row_ctas), col_tiles);
-  dense_fast_kernel<OP, ACT, RAG, TR, false><<<grid, kCtaThreads, kSmemBytesDecl, st>>>(A, B, M, K, U, bias, out,
-                                                                                        act_out);
+  launch_pdl(dense_fast_kernel<OP, ACT, RAG, TR, false>, grid, dim3(kCtaThreads), kSmemBytesDecl, st, A, B, M, K, U, bias,
+             out, act_out);
 }
 
 template <int OP, int ACT, int RAG = 0>

@@ -62,6 +62,7 @@ dense_tc_body(const float* __restrict__ A, const float* __restrict__ B, int64_t 
   const int64_t row_end = (OP == kTN) ? min(M, row_beg + rows_per_split) : 0;
   const int64_t red_len = (OP == kNN) ? K : (OP == kNT ? U : (row_end > row_beg ? row_end - row_beg : 0));
 
+  pdl_trigger();
   TL(0);
   if (warp == kThreads / 32) {                                   // four accumulators of kMaxN columns each
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)),
@@ -120,6 +121,7 @@ dense_tc_body(const float* __restrict__ A, const float* __restrict__ B, int64_t 
   static_assert(kStages == 4 && kStages * kMaxN == kTmemCols, "four named register sets / accumulators below");
   const bool short_k = nchunk <= kStages;                // CTA-uniform
   F8 va0, vb0, va1, vb1, va2;
+  pdl_wait();                                            // first global access below
   if (warp < kThreads / 32) {
     if (nchunk > 0) load_chunk(0, va0, vb0);
     if (nchunk > 1) load_chunk(kKC, va1, vb1);
@@ -471,6 +473,8 @@ tn_grouped_kernel(const __grid_constant__ TnGroup grp, float* __restrict__ ws) {
 
 __global__ void __launch_bounds__(256)
 tn_grouped_reduce_kernel(const __grid_constant__ TnGroup grp, const float* __restrict__ ws) {
+  pdl_trigger();
+  pdl_wait();
   const int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
   if (i >= grp.total_elems) return;
   int lo = 0, hi = grp.n_outputs - 1;
@@ -642,15 +646,15 @@ static int dense_tc_launch(int op, const float* A, const float* B, int64_t M, in
   });
   if (op == tc::kNN) {
     dim3 grid(static_cast<unsigned>(ceil_div<int64_t>(M, tc::kBM)), ceil_div(U, tc::kMaxN));
-    tc::dense_tc_kernel<tc::kNN><<<grid, tc::kCtaThreads, tc::kSmemBytes, st>>>(
-        A, B, M, K, U, bias, out, 0, (K % 4 == 0 && al16(A)) ? 1 : 0, (U % 4 == 0 && al16(B)) ? 1 : 0, act_out, act);
+    launch_pdl(tc::dense_tc_kernel<tc::kNN>, grid, dim3(tc::kCtaThreads), tc::kSmemBytes, st,
+               A, B, M, K, U, bias, out, 0, (K % 4 == 0 && al16(A)) ? 1 : 0, (U % 4 == 0 && al16(B)) ? 1 : 0, act_out, act);
     return finish_launch();
   }
   if (op == tc::kNT) {
     dim3 grid(static_cast<unsigned>(ceil_div<int64_t>(M, tc::kBM)), ceil_div(K, tc::kMaxN));
-    tc::dense_tc_kernel<tc::kNT><<<grid, tc::kCtaThreads, tc::kSmemBytes, st>>>(
-        A, B, M, K, U, nullptr, out, 0, (U % 4 == 0 && al16(A)) ? 1 : 0, (U % 4 == 0 && al16(B)) ? 1 : 0, nullptr,
-        0);
+    launch_pdl(tc::dense_tc_kernel<tc::kNT>, grid, dim3(tc::kCtaThreads), tc::kSmemBytes, st,
+               A, B, M, K, U, nullptr, out, 0, (U % 4 == 0 && al16(A)) ? 1 : 0, (U % 4 == 0 && al16(B)) ? 1 : 0, nullptr,
+               0);
     return finish_launch();
   }
   const int S = tc::tn_splits(M, K, U);
@@ -758,8 +762,10 @@ int kgcnn_dense_tn_grouped(int n, const float* const* X, const float* const* G, 
       grp.n_problems += 1;
     }
     if (grp.n_problems == 0) continue;
-    tc::tn_grouped_kernel<<<static_cast<unsigned>(grp.total_ctas), tc::kCtaThreads, tc::kSmemBytes, st>>>(grp, ws);
-    tc::tn_grouped_reduce_kernel<<<static_cast<unsigned>(ceil_div<int64_t>(grp.total_elems, 256)), 256, 0, st>>>(grp, ws);
+    launch_pdl(tc::tn_grouped_kernel, dim3(static_cast<unsigned>(grp.total_ctas)), dim3(tc::kCtaThreads), tc::kSmemBytes,
+               st, grp, ws);
+    launch_pdl(tc::tn_grouped_reduce_kernel, dim3(static_cast<unsigned>(ceil_div<int64_t>(grp.total_elems, 256))),
+               dim3(256), 0, st, grp, static_cast<const float*>(ws));
     launches += 2;
   }
   return launches ? finish_launch(launches) : KGCNN_OK;

@@ -72,6 +72,8 @@ template <typename V, int LPR, bool REDUCE>
 __global__ void __launch_bounds__(kThreads)
 gather2_mul_kernel(const V* __restrict__ a, const int32_t* __restrict__ ia, int ia_stride, const V* __restrict__ b,
                    const int32_t* __restrict__ ib, int ib_stride, int64_t E, int nvec, float* __restrict__ z) {
+  pdl_trigger();
+  pdl_wait();
   constexpr int kGroups = kThreads / LPR;
   const int gid = threadIdx.x / LPR, sub = threadIdx.x % LPR;
   const int64_t base = static_cast<int64_t>(blockIdx.x) * (kGroups * kRows);
@@ -151,7 +153,7 @@ int launch_gather2(const V* a, const int32_t* ia, int ias, const V* b, const int
 #define KGCNN_G2_CASE(L)                                                                             \
   case L: {                                                                                          \
     unsigned grid = static_cast<unsigned>(ceil_div<int64_t>(E, (kThreads / L) * kRows));             \
-    gather2_mul_kernel<V, L, REDUCE><<<grid, kThreads, 0, st>>>(a, ia, ias, b, ib, ibs, E, nvec, z); \
+    launch_pdl(gather2_mul_kernel<V, L, REDUCE>, dim3(grid), dim3(kThreads), 0, st, a, ia, ias, b, ib, ibs, E, nvec, z); \
     break;                                                                                           \
   }
   switch (lpr) {

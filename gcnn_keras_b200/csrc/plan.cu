@@ -3,6 +3,7 @@
 //   kgcnn/ops/partition.py:97-161   (partition_row_indexing)
 //   kgcnn/layers/pooling.py:63-68   (argsort(stable) + permutation gathers)
 // Integer work only; results are bit-exact against the oracle.
+#include <cstdlib>
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
 
@@ -14,6 +15,14 @@ namespace kgcnn {
 
 static std::atomic<long long> g_launches{0};
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+bool pdl_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("KGCNN_PDL");
+    return !(e && e[0] == '0');
+  }();
+  return on;
+}
 
 namespace {
 

@@ -79,6 +79,8 @@ gms_kernel(const V* __restrict__ x, const V* __restrict__ wv, const float* __res
            const int32_t* __restrict__ rowptr, const int32_t* __restrict__ perm, const int32_t* __restrict__ gidx,
            int gidx_stride, int gidx_permuted, int64_t n_out, int nvec, int mean, V* __restrict__ y,
            int long_thresh) {
+  pdl_trigger();
+  pdl_wait();
   constexpr int G = 32 / LPR;
   constexpr int U = (VPL >= 3) ? 2 : 4;  // gathered rows in flight per lane group
   using T = Vec<V>;
@@ -205,6 +207,8 @@ gms_block_kernel(const V* __restrict__ x, const V* __restrict__ wv, const float*
                  const int32_t* __restrict__ gidx, int gidx_stride, int gidx_permuted, int64_t n_out, int nvec,
                  int mean, V* __restrict__ y, const int32_t* __restrict__ row_map,
                  const int32_t* __restrict__ n_rows_dev) {
+  pdl_trigger();
+  pdl_wait();
   constexpr int NG = kThreads / LPR;  // lane groups walking the row together (32 .. 256)
   using T = Vec<V>;
   __shared__ V red[NG][LPR];
@@ -256,7 +260,7 @@ int launch_block(int mode, bool gather, const V* x, const V* wv, const float* ws
                  const int32_t* row_map, const int32_t* n_rows_dev, int grid_rows, cudaStream_t st) {
   const unsigned grid_x = static_cast<unsigned>(row_map ? grid_rows : n_out);
 #define KGCNN_BLK_L(M, GA, L)                                                                                   \
-  gms_block_kernel<V, M, GA, L><<<dim3(grid_x, static_cast<unsigned>(ceil_div(nvec, L))), kThreads, 0, st>>>(x, wv, ws, rowptr, perm, gidx, gs, gp, n_out, nvec, mean, \
+  launch_pdl(gms_block_kernel<V, M, GA, L>, dim3(grid_x, static_cast<unsigned>(ceil_div(nvec, L))), dim3(kThreads), 0, st, x, wv, ws, rowptr, perm, gidx, gs, gp, n_out, nvec, mean, \
                                                           y, row_map, n_rows_dev)
 #define KGCNN_BLK(M, GA)                                                                                        \
   do {                                                                                                          \
@@ -289,11 +293,11 @@ int launch_shape(int mode, bool gather, const V* x, const V* wv, const float* ws
 #define KGCNN_GMS_LAUNCH(M, GA)                                                                      \
   do {                                                                                               \
     if constexpr (kHasGpr) {                                                                         \
-      if (gpr && exact) gms_kernel<V, LPR, VPL, M, GA, true, true><<<grid, kThreads, 0, st>>>(KGCNN_GMS_ARGS);        \
-      else if (gpr) gms_kernel<V, LPR, VPL, M, GA, false, true><<<grid, kThreads, 0, st>>>(KGCNN_GMS_ARGS);           \
+      if (gpr && exact) launch_pdl(gms_kernel<V, LPR, VPL, M, GA, true, true>, grid, dim3(kThreads), 0, st, KGCNN_GMS_ARGS);        \
+      else if (gpr) launch_pdl(gms_kernel<V, LPR, VPL, M, GA, false, true>, grid, dim3(kThreads), 0, st, KGCNN_GMS_ARGS);           \
     }                                                                                                \
-    if (!gpr && exact) gms_kernel<V, LPR, VPL, M, GA, true, false><<<grid, kThreads, 0, st>>>(KGCNN_GMS_ARGS);        \
-    else if (!gpr) gms_kernel<V, LPR, VPL, M, GA, false, false><<<grid, kThreads, 0, st>>>(KGCNN_GMS_ARGS);           \
+    if (!gpr && exact) launch_pdl(gms_kernel<V, LPR, VPL, M, GA, true, false>, grid, dim3(kThreads), 0, st, KGCNN_GMS_ARGS);        \
+    else if (!gpr) launch_pdl(gms_kernel<V, LPR, VPL, M, GA, false, false>, grid, dim3(kThreads), 0, st, KGCNN_GMS_ARGS);           \
   } while (0)
   if (mode == kMax) { if (gather) return KGCNN_E_UNSUPPORTED; KGCNN_GMS_LAUNCH(kMax, false); }
   else if (mode == kMin) { if (gather) return KGCNN_E_UNSUPPORTED; KGCNN_GMS_LAUNCH(kMin, false); }
