@@ -90,6 +90,7 @@ struct Params {
   float* wg_gpd;           // [E, 128]  mode 3
   int64_t E;
   int R;
+  int static_w;            // W1, b1, W2, b2 are variables no kernel of the running chain writes: staged before pdl_wait()
   float gamma, offset, step;
 };
 
@@ -243,7 +244,10 @@ cfconv_kernel(const Params P) {
       row_s[kBM + 1] = (e0 + kBM < E) ? __ldg(P.rows + e0 + kBM) : -2;
     }
   };
-  pdl_wait();                                                    // first global access below
+  // Weights that are model variables (written only by the optimizer kernel, which is launched without the PDL
+  // attribute and therefore complete before any kernel of this chain started) are staged BEFORE the grid dependency
+  // is awaited: the 80 KB weight fetch + split runs under the previous kernel's tail.
+  if (!P.static_w) pdl_wait();
   // weights -> operand planes, once per CTA; every global load is in flight before the first split
   if (warp < kWorkers / 32) {
     const int kk = 8 * (warp & 3) + (lane & 7), mn8 = 4 * (warp >> 2) + (lane >> 3);
@@ -272,6 +276,7 @@ cfconv_kernel(const Params P) {
     if (threadIdx.x < kF) { b1_s[threadIdx.x] = bv1; b2_s[threadIdx.x] = bv2; }
     CTL(18);
   }
+  if (P.static_w) pdl_wait();                                    // everything below reads the chain's tensors
   CTL(2);
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
@@ -738,7 +743,7 @@ int kgcnn_gauss_basis(const float* dist, int64_t E, int R, float gamma, float of
 
 int kgcnn_cfconv_fused(int mode, const float* dist, int64_t E, int R, float gamma, float offset, float step,
                        const float* W1, const float* b1, const float* W2, const float* b2, int units, int act,
-                       const int32_t* rowptr, const int32_t* rows, const int32_t* other, const int32_t* eperm,
+                       int static_weights, const int32_t* rowptr, const int32_t* rows, const int32_t* other, const int32_t* eperm,
                        int64_t n_out, const float* a, const float* b, const float* c, const float* tang, float* out,
                        float* edge_out, float* const* wg, void* workspace, size_t workspace_bytes,
                        kgcnn_stream_t stream) {
@@ -772,6 +777,7 @@ int kgcnn_cfconv_fused(int mode, const float* dist, int64_t E, int R, float gamm
       if (E > 0 && (!P.wg_rbf1 || !P.wg_hd || !P.wg_Bt || !P.wg_gpd)) return KGCNN_E_INVALID;
     }
   }
+  P.static_w = static_weights ? 1 : 0;
   P.E = E; P.R = R; P.gamma = gamma; P.offset = offset; P.step = step;
   cudaStream_t st = as_stream(stream);
   switch (mode) {

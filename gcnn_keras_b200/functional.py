@@ -969,6 +969,9 @@ def raw_cfconv(mode, spec, d, w1, b1, w2, b2, rel_out, rel_other, a, b=None, c=N
     b = None if b is None else _f32c(b)
     c = None if c is None else _f32c(c)
     tang = None if tang is None else _f32c(tang.reshape(-1))
+    # model variables (leaves that require a gradient) are written by the optimizer kernel only: safe to stage before
+    # the kernel waits for its launch dependency (csrc/common.cuh, programmatic dependent launch)
+    static_w = int(all(t is None or (t.is_leaf and t.requires_grad) for t in (w1, b1, w2, b2)))
     w1, w2 = _f32c(w1), _f32c(w2)
     b1 = None if b1 is None else _f32c(b1)
     b2 = None if b2 is None else _f32c(b2)
@@ -989,7 +992,8 @@ def raw_cfconv(mode, spec, d, w1, b1, w2, b2, rel_out, rel_other, a, b=None, c=N
             wg["w1"].append((t[4], t[7], False))
     check(_lib.lib().kgcnn_cfconv_fused(
         mode, _ptr(d), E, spec.R, spec.gamma, spec.offset, spec.step, _ptr(w1), _ptr(b1), _ptr(w2), _ptr(b2), 128,
-        spec.act, _ptr(rel_out.rowptr), _ptr(rel_out.permuted_ids(rel_out)), _ptr(rel_out.permuted_ids(rel_other)),
+        spec.act, static_w, _ptr(rel_out.rowptr), _ptr(rel_out.permuted_ids(rel_out)),
+        _ptr(rel_out.permuted_ids(rel_other)),
         _ptr(rel_out.perm), rel_out.n_targets, _ptr(a), _ptr(b), _ptr(c), _ptr(tang), _ptr(out), _ptr(edge_out),
         wg_arr, _ptr(ws), nbytes, _stream()), "kgcnn_cfconv_fused")
     return out, edge_out, wg

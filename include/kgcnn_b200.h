@@ -413,12 +413,15 @@ int kgcnn_gauss_basis(const float* dist, int64_t E, int R, float gamma, float of
                       const float* scale /*nullable*/, float* out, kgcnn_stream_t stream);
 int kgcnn_cfconv_fused(int mode, const float* dist, int64_t E, int R, float gamma, float offset, float step,
                        const float* W1, const float* b1 /*nullable*/, const float* W2, const float* b2 /*nullable*/,
-                       int units, int act, const int32_t* rowptr, const int32_t* rows, const int32_t* other,
+                       int units, int act, int static_weights, const int32_t* rowptr, const int32_t* rows,
+                       const int32_t* other,
                        const int32_t* eperm /*nullable*/, int64_t n_out, const float* a, const float* b,
                        const float* c, const float* tang, float* out, float* edge_out,
                        float* const* wg /*nullable; HOST array of 8 device pointers*/, void* workspace,
                        size_t workspace_bytes, kgcnn_stream_t stream);
-/* wg (modes 1 and 3 only): the operands of the filter network's weight gradients, produced in the same pass, rows in
+/* static_weights != 0: W1, b1, W2, b2 are model variables that no kernel launched since the last optimizer update
+ * writes; the kernel then stages them before it waits for its programmatic launch dependency (csrc/common.cuh).
+ * wg (modes 1 and 3 only): the operands of the filter network's weight gradients, produced in the same pass, rows in
  * CSR order of this call:   dW2 += h^T A (+ hd^T Bt),  db2 += colsum A,  dW1 += rbf^T gp (+ rbf1^T gpd),  db1 += colsum gp
  *   wg[0] rbf [E,R]   wg[1] h [E,128]   wg[2] A [E,128] = a[o] b[i] (mode 1) | a[o] c[i] (mode 3)   wg[3] gp [E,128]
  *   mode 3 also:  wg[4] rbf1 [E,R] = t rbf'   wg[5] hd [E,128]   wg[6] Bt [E,128] = a[o] b[i]   wg[7] gpd [E,128]

@@ -38,7 +38,7 @@ int main(int argc, char** argv) {
     int rc = 0;
     for (int rep = 0; rep < 6; ++rep) {
       if (rep == 5) cudaEventRecord(e0);
-      rc = kgcnn_cfconv_fused(mode, d_dist, E, R, 3.125f, 0.f, 0.2f, w1, bb, w2, bb, 128, 1, d_rowptr, d_rows, d_other, nullptr, N,
+      rc = kgcnn_cfconv_fused(mode, d_dist, E, R, 3.125f, 0.f, 0.2f, w1, bb, w2, bb, 128, 1, 0, d_rowptr, d_rows, d_other, nullptr, N,
                               a, a, a, eo, out, eo, v >= 4 ? wg : nullptr, ws, wsb, nullptr);
       if (rep == 5) cudaEventRecord(e1);
     }
