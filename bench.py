@@ -628,6 +628,9 @@ def run_force(args, rank, world, device, kind):
     # C4: the 'kj' angle triples (278 MB per batch) are rebuilt on the device from the pair list in the e2e leg
     device_angles = "kj" if (kind == "hdnnp" and not args.host_angles) else None
     captured = CapturedForceTrainStep(train_step, data, device, device_angles=device_angles)
+    if world > 1:       # replicas start from rank 0's weights (the seed already makes them equal; this makes it a fact)
+        from gcnn_keras_b200.distributed import broadcast_parameters
+        broadcast_parameters(model)
     n_params = sum(p.numel() for p in model.parameters())
 
     ms_step, clocks = timed_steps_with_l2_flush(lambda: captured.run(load=False), args.steps, args.warmup, world,

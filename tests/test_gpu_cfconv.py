@@ -146,3 +146,29 @@ def test_fused_cfconv_empty_edge_set():
     w2 = torch.zeros((128, 128), device="cuda")
     y = F.cfconv_fused(nodes.values, torch.zeros((0,), device="cuda"), w1, None, w2, None, spec)
     assert y.shape == (5, 128) and float(y.abs().max()) == 0.0
+
+
+def test_fused_cfconv_weight_gradients_through_the_grouped_sink():
+    """The training path: the weight gradients of both sweeps are handed to the grouped TN launch as operand pairs
+    and accumulated into the flat gradient buffer."""
+    from gcnn_keras_b200 import functional as F
+    c = _case("unsorted", seed=7)
+    t = [torch.tensor(a, dtype=torch.float32, device="cuda", requires_grad=True) for a in c["arrays"]]
+    cy, cgx, cgd = [torch.tensor(a, dtype=torch.float32, device="cuda") for a in c["cot"]]
+    y = F.cfconv_fused(*t, c["spec"])
+    with F.input_gradients_only(t[0], t[1]):
+        gx, gd = torch.autograd.grad(y, [t[0], t[1]], cy, create_graph=True)
+    params = t[2:]
+    sizes = [p.numel() for p in params]
+    offsets = [int(v) for v in np.concatenate([[0], np.cumsum(sizes)[:-1]])]
+    flat = torch.zeros(sum(sizes), dtype=torch.float32, device="cuda")
+    sink = F.WeightGradSink(params, flat, offsets)
+    launches = F._lib.launch_count()
+    with F.weight_grad_sink(sink):
+        got_x, got_d = torch.autograd.grad((gx * cgx).sum() + (gd * cgd).sum() + 0.5 * (y * y).sum(), [t[0], t[1]])
+    want = _run_oracle(c)
+    assert rel_err(got_x.cpu().numpy(), want[3]) < RTOL and rel_err(got_d.cpu().numpy(), want[4]) < RTOL
+    for off, p, w, name in zip(offsets, params, want[5:9], NAMES[5:9]):
+        g = flat[off:off + p.numel()].reshape(p.shape).cpu().numpy()
+        assert rel_err(g, w) < RTOL, name
+    assert F._lib.launch_count() > launches
