@@ -182,6 +182,7 @@ dense_tc_body(const float* __restrict__ A, const float* __restrict__ B, int64_t 
       mbar_wait(smem_u32(&full[st]), static_cast<uint32_t>((c / kStages) & 1));
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       if (c < 4) TL(20 + 2 * c);
+      if (c == 16) TL(50);
       if (lane == 0) {
         const uint32_t base = smem_u32(planes + static_cast<size_t>(st) * kStageUnits) >> 4;
         const uint64_t a1 = da_hi | (base & 0x3FFF), a2 = a1 + kPlaneUnits, a3 = a2 + kPlaneUnits;
@@ -217,6 +218,8 @@ dense_tc_body(const float* __restrict__ A, const float* __restrict__ B, int64_t 
                      : "memory");
       }
       if (c < 4) TL(21 + 2 * c);
+      if (c == 16) TL(51);
+      if (c == 15) TL(52);
       __syncwarp();
     }
   } else {
@@ -233,7 +236,9 @@ dense_tc_body(const float* __restrict__ A, const float* __restrict__ B, int64_t 
       }
     };
     auto publish = [&](int c) {                                    // hand chunk c to the MMA warp
+      if (c == 16) TL(47);
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // generic-proxy stores -> async proxy (MMA)
+      if (c == 16) TL(48);
       asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
       __syncwarp();
       if (lane == 0)
@@ -260,16 +265,23 @@ dense_tc_body(const float* __restrict__ A, const float* __restrict__ B, int64_t 
       TL(12);
     } else {
       auto step = [&](int c, F8& ra, F8& rb) {
+        if (c == 16) TL(40);
         if (c >= kStages) wait_chunk(c - kStages);         // the MMAs that read this stage are done
+        if (c == 16) TL(41);
         stage(c, ra, rb);
+        if (c == 16) TL(42);
         if (c + 2 < nchunk) load_chunk(static_cast<int64_t>(c + 2) * kKC, ra, rb);   // refill this register set
         publish(c);
+        if (c == 16) TL(43);
         // ---- drain the previous chunk's accumulator while this chunk's MMAs run ----
         if (c > 0) {
           wait_chunk(c - 1);
+          if (c == 16) TL(44);
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
           drain(static_cast<uint32_t>(((c - 1) & 1) * kMaxN));
+          if (c == 16) TL(45);
         }
+        if (c == 17) TL(46);
       };
       for (int c = 0; c < nchunk; c += 2) {
         step(c, va0, vb0);

@@ -11,8 +11,11 @@ namespace tc {
 
 // Timeline probe (tools/tc_timeline.cu defines KGCNN_TC_TIMELINE and includes this file): clock64 stamps of CTA 0.
 #ifdef KGCNN_TC_TIMELINE
+#ifndef KGCNN_TL_THREAD
+#define KGCNN_TL_THREAD 0
+#endif
 __device__ long long g_timeline[64];
-#define TL(slot) do { if (blockIdx.x == 0 && (threadIdx.x == 0 || threadIdx.x == kThreads)) g_timeline[(slot)] = clock64(); } while (0)
+#define TL(slot) do { if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && (threadIdx.x == KGCNN_TL_THREAD || threadIdx.x == kThreads)) g_timeline[(slot)] = clock64(); } while (0)
 #else
 #define TL(slot) do { } while (0)
 #endif

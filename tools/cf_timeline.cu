@@ -3,7 +3,7 @@
 #define KGCNN_CF_TIMELINE 1
 #include <cstdio>
 #include <vector>
-namespace kgcnn { void count_launch(int) {} }
+namespace kgcnn { void count_launch(int) {} bool pdl_enabled() { return false; } }
 #include "../gcnn_keras_b200/csrc/cfconv.cu"
 extern "C" const char* kgcnn_error_string(int) { return ""; }
 

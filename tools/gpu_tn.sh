@@ -4,6 +4,10 @@ mkdir -p gpurun_out
 cat gpurun_out/pytest_tn.log
 for w in schnet painn; do
   b=256; [ $w = painn ] && b=512
-  timeout 600 python tools/profile_step.py $w --batch $b --rows 12 > gpurun_out/step_${w}_tn.txt 2>/dev/null
+  KGCNN_PDL=0 timeout 600 python tools/profile_step.py $w --batch $b --rows 12 > gpurun_out/step_${w}_tn.txt 2>/dev/null
   head -8 gpurun_out/step_${w}_tn.txt | cut -c1-140
+  ( timeout 300 python bench.py --workload $w --steps 10 --warmup 3 --no-cpu-baseline --no-roofline --no-other-workloads 2>/dev/null | tail -1 ) > gpurun_out/bench_${w}_tn.json
+  python -c "
+import json
+d=json.load(open('gpurun_out/bench_${w}_tn.json')); print('$w', 'ms/step %.3f' % d['ms_per_step'], 'e2e %.0f' % d['e2e']['value'])"
 done

@@ -3,7 +3,7 @@
 #define KGCNN_TC_TIMELINE 1
 #include <cstdio>
 #include <vector>
-namespace kgcnn { void count_launch(int) {} }
+namespace kgcnn { void count_launch(int) {} bool pdl_enabled() { return false; } }
 #include "../gcnn_keras_b200/csrc/dense_tc.cu"
 #include "../gcnn_keras_b200/csrc/dense_fast.cu"
 extern "C" const char* kgcnn_error_string(int) { return ""; }
@@ -35,6 +35,18 @@ int main(int argc, char** argv) {
            t[36] - t[31], t[37] - t[31], t[32] - t[31], t[8] - t[31], t[9] - t[31], t[10] - t[31], t[11] - t[31], t[12] - t[31], t[13] - t[31], t[35] - t[31],
            t[20] - t[31], t[21] - t[31], t[22] - t[31], t[23] - t[31], t[24] - t[31], t[25] - t[31], t[26] - t[31], t[27] - t[31]);
     for (int c = 0; c < 4; ++c) printf("  mma warp chunk %d: full seen %7lld  issued %7lld\n", c, t[20 + 2 * c] - t[0], t[21 + 2 * c] - t[0]);
+  }
+  {   // long-reduction loop (TN): steady-state stamps of chunk 16 of CTA 0
+    float* wsb; const size_t wb = kgcnn_dense_tc_workspace_bytes(2, M, K, U); cudaMalloc(&wsb, wb);
+    for (int rep = 0; rep < 4; ++rep) kgcnn_dense_tc(2, x, y, M, K, U, nullptr, y2, wsb, wb, nullptr);
+    cudaError_t e = cudaDeviceSynchronize();
+    long long t[64];
+    cudaMemcpyFromSymbol(t, kgcnn::tc::g_timeline, sizeof(t));
+    printf("TN M=%lld (%s) chunk 16, cycles relative to the start of its step (staging thread 0):\n", (long long)M, cudaGetErrorString(e));
+    printf("  stage freed (MMA c-4 done) %lld  staged %lld  loads issued + published %lld  MMA(c-1) done %lld  drained %lld  next step starts %lld\n",
+           t[41] - t[40], t[42] - t[40], t[43] - t[40], t[44] - t[40], t[45] - t[40], t[46] - t[40]);
+    printf("  loads issued %lld  fence.proxy.async done %lld\n", t[47] - t[40], t[48] - t[40]);
+    printf("  MMA warp: full(16) seen %lld  MMAs issued %lld   (MMAs of chunk 15 issued at %lld)\n", t[50] - t[40], t[51] - t[40], t[52] - t[40]);
   }
   return 0;
 }
