@@ -71,7 +71,12 @@ def broadcast_parameters(module, src=0, group=None):
     if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
         return
     for p in module.parameters():
-        dist.broadcast(p.data, src=src, group=group)
+        if p.data.is_contiguous():
+            dist.broadcast(p.data, src=src, group=group)
+        else:                                  # strided views of a flat / padded buffer (FlatAdam, relational kernels)
+            t = p.data.contiguous()
+            dist.broadcast(t, src=src, group=group)
+            p.data.copy_(t)
 
 
 def broadcast_flat(flat, src=0, group=None):
