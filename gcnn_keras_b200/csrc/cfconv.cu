@@ -177,9 +177,15 @@ cfconv_kernel(const Params P) {
   constexpr bool kEdgeOut = (MODE == 1 || MODE == 3);
   constexpr int Q0 = (MODE == 3) ? 1 : 0;                        // mode 3 never multiplies with phi itself
   static_assert(!WG || kEdgeOut, "weight-gradient operands come out of the two VJP modes");
-  // TMEM columns: p^(q) at 128 q; phi^(q) and the transposed products G behind / over them once they are dead
-  constexpr uint32_t kColO0 = (MODE == 0) ? 128u : 256u;
-  constexpr uint32_t kColO1 = 384u;
+  // PIPE (modes 0-2 without the weight-gradient stage): consecutive tiles alternate between the two 256-column halves
+  // of TMEM and between two metadata buffers, and the epilogue of tile i runs AFTER the activation chain of tile i + 1
+  // has been handed to the tensor core, i.e. under that tile's second MMA (48-96 MMAs) instead of in front of it.
+  constexpr bool PIPE = !WG && MODE != 3;
+  // TMEM columns (relative to the tile's half when PIPE): p^(q) at 128 q; phi^(q) and the transposed products G
+  // behind / over them once they are dead
+  constexpr uint32_t kColO0 = (MODE == 0) ? 128u : (PIPE ? 0u : 256u);   // PIPE: over p (in registers by then)
+  constexpr uint32_t kColO1 = PIPE ? 128u : 384u;                         // PIPE: over p'
+
   constexpr uint32_t kColO2 = 256u;                              // over p'' (drained before the MMA is issued)
   constexpr uint32_t kColG0 = (MODE == 3) ? 384u : 256u;         // A W2^T, over a phi^(q) the epilogue has consumed
   constexpr uint32_t kColG1 = 256u;                              // Bt W2^T (mode 3)
@@ -187,8 +193,8 @@ cfconv_kernel(const Params P) {
   __shared__ __align__(8) uint64_t bar_rbf, bar_g1, bar_h[3], bar_g2[3], bar_a[2], bar_g3[2];
   __shared__ uint32_t tmem_base_s;
   __shared__ __align__(16) float b1_s[kF], b2_s[kF];
-  __shared__ int row_s[kBM + 2], oth_s[kBM], eid_s[kBM];
-  __shared__ float d_s[kBM], t_s[kBM];
+  __shared__ int row_sb[2][kBM + 2], oth_sb[2][kBM], eid_sb[2][kBM];
+  __shared__ float d_sb[2][kBM], t_sb[2][kBM];
   __shared__ float pe_s[4][kBM];
 
   uint4* w1planes = reinterpret_cast<uint4*>(smem_raw);         // [piece][kW1Plane]
@@ -221,7 +227,9 @@ cfconv_kernel(const Params P) {
     }
   }
   // tile metadata -> shared memory (threads 0 .. 129 of the workers)
-  auto load_meta = [&](int64_t e0) {
+  auto load_meta = [&](int64_t e0, int mb) {
+    int* row_s = row_sb[mb]; int* oth_s = oth_sb[mb]; int* eid_s = eid_sb[mb];
+    float* d_s = d_sb[mb]; float* t_s = t_sb[mb];
     if (threadIdx.x < kBM) {
       const int64_t e = e0 + threadIdx.x;
       int row = -1, oth = 0, eid = 0;
@@ -300,6 +308,7 @@ cfconv_kernel(const Params P) {
     int it = 0;
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
       const uint32_t par = static_cast<uint32_t>(it & 1);
+      const uint32_t hb = PIPE ? 256u * static_cast<uint32_t>(it & 1) : 0u;     // this tile's half of TMEM
       mbar_wait(smem_u32(&bar_rbf), par);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       CTL(20);
@@ -311,9 +320,9 @@ cfconv_kernel(const Params P) {
           for (int term = 0; term < 6; ++term) {
             const uint64_t wd = w1_hi | ((w1base + pw[term] * kW1Plane) & 0x3FFF);
             const uint64_t rd = r_hi | ((hbase + (q * 3 + ph[term]) * kKPlane) & 0x3FFF);
-            mma_bf16(tmem + 128u * q, wd, rd, idesc1, first);
+            mma_bf16(tmem + hb + 128u * q, wd, rd, idesc1, first);
             first = 1u;
-            mma_bf16(tmem + 128u * q, wd + 16, rd + 2 * kPitchK, idesc1, 1u);
+            mma_bf16(tmem + hb + 128u * q, wd + 16, rd + 2 * kPitchK, idesc1, 1u);
           }
         }
         commit(&bar_g1);
@@ -326,7 +335,7 @@ cfconv_kernel(const Params P) {
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         CTL(22 + 2 * q);
         if (lane == 0) {
-          const uint32_t acc = tmem + (q == 0 ? kColO0 : (q == 1 ? kColO1 : kColO2));
+          const uint32_t acc = tmem + hb + (q == 0 ? kColO0 : (q == 1 ? kColO1 : kColO2));
           uint32_t first = 0u;
 #pragma unroll
           for (int term = 0; term < 6; ++term) {
@@ -384,144 +393,13 @@ cfconv_kernel(const Params P) {
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     };
     const float bias1 = b1_s[u], bias2 = b2_s[u];
-    int it = 0;
-    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
-      const uint32_t par = static_cast<uint32_t>(it & 1);
-      const int64_t e0 = tile * kBM;
-      const int nvalid = static_cast<int>(min(static_cast<int64_t>(kBM), E - e0));
-      // ---- tile metadata ----
-      load_meta(e0);
-      asm volatile("bar.sync 1, %0;" ::"r"(kWorkers) : "memory");
-      CTL(4);
-
-      // ---- Gaussian basis and its derivatives -> K-major planes (thread: 8 basis functions of one edge) ----
-      {
-        const int k8 = threadIdx.x & 3, mn = threadIdx.x >> 2;
-        const float t0 = d_s[mn] - P.offset;
-        const float tt = (MODE == 3) ? t_s[mn] : 0.f;
-        float g0[8], g1[8], g2[8];
-#pragma unroll
-        for (int q = 0; q < 8; ++q) {
-          const int k = 8 * k8 + q;
-          const float t = t0 - P.step * k;
-          const float g = (k < P.R) ? __expf(-P.gamma * t * t) : 0.f;
-          g0[q] = g;
-          if (ORDER >= 1) g1[q] = -2.f * P.gamma * t * g;
-          if (ORDER >= 2) g2[q] = (4.f * P.gamma * P.gamma * t * t - 2.f * P.gamma) * g;
-        }
-        if (WG) {
-          // [E, R] rows of the 8 edges of this warp are one contiguous range: transpose through the unused tail of
-          // the H region (behind the basis planes) and write 128-byte lines
-          float* rs = reinterpret_cast<float*>(hplanes + 9 * kKPlane) + warp * 256;
-          const int el = lane >> 2;
-          const int first = 8 * warp;                                // first edge of this warp within the tile
-          const int cnt = min(8, nvalid - first) * P.R;              // floats to write (<= 0: nothing)
-#pragma unroll
-          for (int which = 0; which < (MODE == 3 ? 2 : 1); ++which) {
-            const float sc = which ? tt : 1.f;
-            const float* g = which ? g1 : g0;
-            if (which) __syncwarp();
-            *reinterpret_cast<float4*>(rs + el * 32 + 8 * k8) = make_float4(sc * g[0], sc * g[1], sc * g[2], sc * g[3]);
-            *reinterpret_cast<float4*>(rs + el * 32 + 8 * k8 + 4) = make_float4(sc * g[4], sc * g[5], sc * g[6], sc * g[7]);
-            __syncwarp();
-            float* dst = (which ? P.wg_rbf1 : P.wg_rbf) + (e0 + first) * P.R;
-            for (int f = lane; f < cnt; f += 32) {
-              const int er = f / P.R, kr = f - er * P.R;
-              dst[f] = rs[er * 32 + kr];
-            }
-          }
-        }
-        {
-          const int slot = k8 * kPitchK + mn;
-          store_unit3(g0, rplanes, slot, kKPlane);
-          if (ORDER >= 1) store_unit3(g1, rplanes + 3 * kKPlane, slot, kKPlane);
-          if (ORDER >= 2) store_unit3(g2, rplanes + 6 * kKPlane, slot, kKPlane);
-        }
-      }
-      publish(&bar_rbf);
-      CTL(5);
-
-      // the 128-byte pieces of the node rows this warp multiplies with in the epilogue: lane i pulls the pieces of
-      // edge gbase + i into L1 while the filter network runs; the first eight also into registers
-      {
-        const int64_t ro = static_cast<int64_t>(oth_s[gbase + lane]) * kF + 32 * cg;
-        const int64_t rr = static_cast<int64_t>(max(row_s[1 + gbase + lane], 0)) * kF + 32 * cg;
-        asm volatile("prefetch.global.L1 [%0];" ::"l"(P.a + ro));
-        if (MODE == 2) asm volatile("prefetch.global.L1 [%0];" ::"l"(P.b + ro));
-        if (MODE == 1 || MODE == 3) asm volatile("prefetch.global.L1 [%0];" ::"l"(P.b + rr));
-        if (MODE == 3) asm volatile("prefetch.global.L1 [%0];" ::"l"(P.c + rr));
-      }
+    // ---- epilogue of one tile: phi^(q) (TMEM half cb) x gathered rows -> segment sums in edge order ----
+    auto epilogue = [&](int64_t e0, int nvalid, int mb, uint32_t cb) {
+      const int* row_s = row_sb[mb]; const int* oth_s = oth_sb[mb]; const int* eid_s = eid_sb[mb];
+      const float* t_s = t_sb[mb];
       float na[8];
 #pragma unroll
       for (int ii = 0; ii < 8; ++ii) na[ii] = __ldg(P.a + static_cast<int64_t>(oth_s[gbase + ii]) * kF + u);
-
-      // ---- activation chain: p^(q) (TMEM) -> h^(q) (planes: k = this thread's hidden unit, edges gbase .. + 31) ----
-      wait_bar(&bar_g1, par);
-      CTL(6);
-      {
-        float sg[32];
-        // q = 0
-#pragma unroll
-        for (int half = 0; half < 2; ++half) {
-          float pre[16], h[16];
-          tmem_ld16(trow + 32 * eg + 16 * half, pre);
-#pragma unroll
-          for (int i = 0; i < 16; ++i) ssp_eval(pre[i] + bias1, h[i], sg[16 * half + i]);
-          if (MODE != 3) {
-            store_unit3(h, hplanes, (4 * eg + 2 * half) * kF + u, kBigPlane);
-            store_unit3(h + 8, hplanes, (4 * eg + 2 * half + 1) * kF + u, kBigPlane);
-          }
-          if (WG) {
-#pragma unroll
-            for (int i = 0; i < 16; ++i)
-              if (gbase + 16 * half + i < nvalid) P.wg_h[(e0 + gbase + 16 * half + i) * kF + u] = h[i];
-          }
-        }
-        if (MODE != 3) publish(&bar_h[0]);
-        CTL(7);
-        if (ORDER >= 1) {
-#pragma unroll
-          for (int half = 0; half < 2; ++half) {
-            float p1[16], h[16];
-            tmem_ld16(trow + 128u + 32 * eg + 16 * half, p1);
-#pragma unroll
-            for (int i = 0; i < 16; ++i) h[i] = sg[16 * half + i] * p1[i];
-            if (MODE != 3 && half == 0) wait_bar(&bar_g2[0], par);   // the previous order's MMAs have read the planes
-            store_unit3(h, hplanes, (4 * eg + 2 * half) * kF + u, kBigPlane);
-            store_unit3(h + 8, hplanes, (4 * eg + 2 * half + 1) * kF + u, kBigPlane);
-            if (WG && MODE == 3) {
-#pragma unroll
-              for (int i = 0; i < 16; ++i)
-                if (gbase + 16 * half + i < nvalid)
-                  P.wg_hd[(e0 + gbase + 16 * half + i) * kF + u] = t_s[gbase + 16 * half + i] * h[i];
-            }
-          }
-          publish(&bar_h[1]);
-          CTL(8);
-        }
-        if (ORDER >= 2) {
-#pragma unroll
-          for (int half = 0; half < 2; ++half) {
-            float p1[16], p2[16], h[16];
-            tmem_ld16(trow + 128u + 32 * eg + 16 * half, p1);
-            tmem_ld16(trow + 256u + 32 * eg + 16 * half, p2);
-#pragma unroll
-            for (int i = 0; i < 16; ++i) {
-              const float s1 = sg[16 * half + i];
-              h[i] = s1 * (1.f - s1) * p1[i] * p1[i] + s1 * p2[i];
-            }
-            if (half == 0) wait_bar(&bar_g2[1], par);
-            store_unit3(h, hplanes, (4 * eg + 2 * half) * kF + u, kBigPlane);
-            store_unit3(h + 8, hplanes, (4 * eg + 2 * half + 1) * kF + u, kBigPlane);
-          }
-          publish(&bar_h[2]);
-          CTL(9);
-        }
-      }
-
-      // ---- epilogue: phi^(q) (TMEM) x gathered rows -> segment sums in edge order ----
-      wait_bar(&bar_g2[ORDER], par);
-      CTL(10);
       {
         const int64_t group = e0 / 32 + eg;
         const int prev_row = row_s[gbase], next_row = row_s[gbase + 33];
@@ -532,9 +410,9 @@ cfconv_kernel(const Params P) {
 #pragma unroll
         for (int sb = 0; sb < 4; ++sb) {
           float w0[8], w1[8], w2[8], pe[8], va[8], vb[8], vc[8], A8[8];
-          if (MODE != 3) tmem_ld8(trow + kColO0 + gbase + 8 * sb, w0);
-          if (ORDER >= 1) tmem_ld8(trow + kColO1 + gbase + 8 * sb, w1);
-          if (ORDER >= 2) tmem_ld8(trow + kColO2 + gbase + 8 * sb, w2);
+          if (MODE != 3) tmem_ld8(trow + cb + kColO0 + gbase + 8 * sb, w0);
+          if (ORDER >= 1) tmem_ld8(trow + cb + kColO1 + gbase + 8 * sb, w1);
+          if (ORDER >= 2) tmem_ld8(trow + cb + kColO2 + gbase + 8 * sb, w2);
 #pragma unroll
           for (int ii = 0; ii < 8; ++ii) {
             const int i = gbase + 8 * sb + ii;
@@ -594,6 +472,145 @@ cfconv_kernel(const Params P) {
         const int i = threadIdx.x;
         P.edge_out[eid_s[i]] = ((pe_s[0][i] + pe_s[1][i]) + pe_s[2][i]) + pe_s[3][i];
       }
+    };
+    int it = 0;
+    int64_t prev_e0 = 0;
+    int prev_nvalid = 0;
+    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+      const uint32_t par = static_cast<uint32_t>(it & 1);
+      const int mb = PIPE ? (it & 1) : 0;                          // metadata buffer / TMEM half of this tile
+      const uint32_t hb = PIPE ? 256u * static_cast<uint32_t>(it & 1) : 0u;
+      const int64_t e0 = tile * kBM;
+      const int nvalid = static_cast<int>(min(static_cast<int64_t>(kBM), E - e0));
+      const int* row_s = row_sb[mb]; const int* oth_s = oth_sb[mb];
+      const float* d_s = d_sb[mb]; const float* t_s = t_sb[mb];
+      (void)row_s; (void)oth_s;
+      // ---- tile metadata ----
+      load_meta(e0, mb);
+      // the previous tile's last MMA has completed: the operand planes (which the basis aliases) are free again
+      if (PIPE && it > 0) wait_bar(&bar_g2[ORDER], par ^ 1u);
+      asm volatile("bar.sync 1, %0;" ::"r"(kWorkers) : "memory");
+      CTL(4);
+
+      // ---- Gaussian basis and its derivatives -> K-major planes (thread: 8 basis functions of one edge) ----
+      {
+        const int k8 = threadIdx.x & 3, mn = threadIdx.x >> 2;
+        const float t0 = d_s[mn] - P.offset;
+        const float tt = (MODE == 3) ? t_s[mn] : 0.f;
+        float g0[8], g1[8], g2[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          const int k = 8 * k8 + q;
+          const float t = t0 - P.step * k;
+          const float g = (k < P.R) ? __expf(-P.gamma * t * t) : 0.f;
+          g0[q] = g;
+          if (ORDER >= 1) g1[q] = -2.f * P.gamma * t * g;
+          if (ORDER >= 2) g2[q] = (4.f * P.gamma * P.gamma * t * t - 2.f * P.gamma) * g;
+        }
+        if (WG) {
+          // [E, R] rows of the 8 edges of this warp are one contiguous range: transpose through the unused tail of
+          // the H region (behind the basis planes) and write 128-byte lines
+          float* rs = reinterpret_cast<float*>(hplanes + 9 * kKPlane) + warp * 256;
+          const int el = lane >> 2;
+          const int first = 8 * warp;                                // first edge of this warp within the tile
+          const int cnt = min(8, nvalid - first) * P.R;              // floats to write (<= 0: nothing)
+#pragma unroll
+          for (int which = 0; which < (MODE == 3 ? 2 : 1); ++which) {
+            const float sc = which ? tt : 1.f;
+            const float* g = which ? g1 : g0;
+            if (which) __syncwarp();
+            *reinterpret_cast<float4*>(rs + el * 32 + 8 * k8) = make_float4(sc * g[0], sc * g[1], sc * g[2], sc * g[3]);
+            *reinterpret_cast<float4*>(rs + el * 32 + 8 * k8 + 4) = make_float4(sc * g[4], sc * g[5], sc * g[6], sc * g[7]);
+            __syncwarp();
+            float* dst = (which ? P.wg_rbf1 : P.wg_rbf) + (e0 + first) * P.R;
+            for (int f = lane; f < cnt; f += 32) {
+              const int er = f / P.R, kr = f - er * P.R;
+              dst[f] = rs[er * 32 + kr];
+            }
+          }
+        }
+        {
+          const int slot = k8 * kPitchK + mn;
+          store_unit3(g0, rplanes, slot, kKPlane);
+          if (ORDER >= 1) store_unit3(g1, rplanes + 3 * kKPlane, slot, kKPlane);
+          if (ORDER >= 2) store_unit3(g2, rplanes + 6 * kKPlane, slot, kKPlane);
+        }
+      }
+      publish(&bar_rbf);
+      CTL(5);
+
+      // ---- activation chain: p^(q) (TMEM) -> h^(q) (planes: k = this thread's hidden unit, edges gbase .. + 31) ----
+      wait_bar(&bar_g1, par);
+      CTL(6);
+      {
+        float sg[32];
+        // q = 0
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+          float pre[16], h[16];
+          tmem_ld16(trow + hb + 32 * eg + 16 * half, pre);
+#pragma unroll
+          for (int i = 0; i < 16; ++i) ssp_eval(pre[i] + bias1, h[i], sg[16 * half + i]);
+          if (MODE != 3) {
+            store_unit3(h, hplanes, (4 * eg + 2 * half) * kF + u, kBigPlane);
+            store_unit3(h + 8, hplanes, (4 * eg + 2 * half + 1) * kF + u, kBigPlane);
+          }
+          if (WG) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i)
+              if (gbase + 16 * half + i < nvalid) P.wg_h[(e0 + gbase + 16 * half + i) * kF + u] = h[i];
+          }
+        }
+        if (MODE != 3) publish(&bar_h[0]);
+        CTL(7);
+        if (ORDER >= 1) {
+#pragma unroll
+          for (int half = 0; half < 2; ++half) {
+            float p1[16], h[16];
+            tmem_ld16(trow + hb + 128u + 32 * eg + 16 * half, p1);
+#pragma unroll
+            for (int i = 0; i < 16; ++i) h[i] = sg[16 * half + i] * p1[i];
+            if (MODE != 3 && half == 0) wait_bar(&bar_g2[0], par);   // the previous order's MMAs have read the planes
+            store_unit3(h, hplanes, (4 * eg + 2 * half) * kF + u, kBigPlane);
+            store_unit3(h + 8, hplanes, (4 * eg + 2 * half + 1) * kF + u, kBigPlane);
+            if (WG && MODE == 3) {
+#pragma unroll
+              for (int i = 0; i < 16; ++i)
+                if (gbase + 16 * half + i < nvalid)
+                  P.wg_hd[(e0 + gbase + 16 * half + i) * kF + u] = t_s[gbase + 16 * half + i] * h[i];
+            }
+          }
+          publish(&bar_h[1]);
+          CTL(8);
+        }
+        if (ORDER >= 2) {
+#pragma unroll
+          for (int half = 0; half < 2; ++half) {
+            float p1[16], p2[16], h[16];
+            tmem_ld16(trow + 128u + 32 * eg + 16 * half, p1);
+            tmem_ld16(trow + 256u + 32 * eg + 16 * half, p2);
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+              const float s1 = sg[16 * half + i];
+              h[i] = s1 * (1.f - s1) * p1[i] * p1[i] + s1 * p2[i];
+            }
+            if (half == 0) wait_bar(&bar_g2[1], par);
+            store_unit3(h, hplanes, (4 * eg + 2 * half) * kF + u, kBigPlane);
+            store_unit3(h + 8, hplanes, (4 * eg + 2 * half + 1) * kF + u, kBigPlane);
+          }
+          publish(&bar_h[2]);
+          CTL(9);
+        }
+      }
+
+      // ---- epilogue: of the PREVIOUS tile when PIPE (it runs under this tile's last MMA, which was handed to the
+      //      tensor core just above), of this tile otherwise ----
+      if (PIPE && it > 0) epilogue(prev_e0, prev_nvalid, mb ^ 1, hb ^ 256u);
+      if (!PIPE) {
+        wait_bar(&bar_g2[ORDER], par);
+        CTL(10);
+        epilogue(e0, nvalid, 0, 0u);
+      }
 
       // ---- weight-gradient operands: gp = (A W2^T) f'(p) (+ second-order terms), rows in CSR order ----
       if (WG) {
@@ -643,7 +660,14 @@ cfconv_kernel(const Params P) {
       }
       CTL(14);
       asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-      if (kEdgeOut || WG) asm volatile("bar.sync 1, %0;" ::"r"(kWorkers) : "memory");
+      if (PIPE || kEdgeOut || WG) asm volatile("bar.sync 1, %0;" ::"r"(kWorkers) : "memory");
+      prev_e0 = e0;
+      prev_nvalid = nvalid;
+    }
+    if (PIPE && it > 0) {                                           // the last tile's epilogue
+      wait_bar(&bar_g2[ORDER], static_cast<uint32_t>((it - 1) & 1));
+      CTL(10);
+      epilogue(prev_e0, prev_nvalid, (it - 1) & 1, 256u * static_cast<uint32_t>((it - 1) & 1));
     }
   }
   CTL(15);
