@@ -48,7 +48,8 @@ inline cudaStream_t as_stream(kgcnn_stream_t s) { return reinterpret_cast<cudaSt
 // TMEM allocation, barrier set-up, address arithmetic) under the current kernel's tail and block in pdl_wait() until
 // the current grid has completed and its writes are visible.  Rule for every converted kernel: NO global-memory access
 // before pdl_wait().  Kernels launched with plain <<<>>> neither wait nor trigger and stay fully serialised on both
-// sides, so the two kinds mix freely.  KGCNN_PDL=0 in the environment turns the attribute off.
+// sides, so the two kinds mix freely (a converted kernel launched WITHOUT the attribute returns from pdl_wait()
+// at once).  KGCNN_PDL=0 in the environment turns the attribute off.
 bool pdl_enabled();
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
@@ -65,7 +66,10 @@ inline cudaError_t launch_pdl(void (*kernel)(Params...), dim3 grid, dim3 block, 
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  // Only for grids of at most 16 CTAs per SM: a grid of 1e5 short-lived CTAs (the segment kernels at C5) pays the
+  // dependency check in every CTA and has nothing to gain from an early start (measured: C5 layer 9.1 -> 13.3 ms).
+  const unsigned long long blocks = static_cast<unsigned long long>(grid.x) * grid.y * grid.z;
+  cfg.numAttrs = (pdl_enabled() && blocks <= 16ull * kNumSM) ? 1 : 0;
   return cudaLaunchKernelEx(&cfg, kernel, static_cast<Params>(args)...);
 }
 
