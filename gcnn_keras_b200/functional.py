@@ -1009,6 +1009,38 @@ def raw_gauss_basis(d, spec, order, scale=None):
     return out
 
 
+class _GaussBasis(torch.autograd.Function):
+    """rbf^(order)_k(d) = (d/dd)^order exp(-gamma (d - offset - k step)^2) on distances that do not come from the fused
+    geometry kernel (models fed with edge distances, kgcnn/literature/Schnet.py make_distance=False;
+    kgcnn/layers/geom.py:567-570).  The VJP of order n is order n + 1 contracted with the cotangent: closed up to the
+    second derivative the kernel provides."""
+
+    @staticmethod
+    def forward(ctx, d, basis, order):
+        ctx.basis, ctx.order = basis, order
+        ctx.save_for_backward(d)
+        return raw_gauss_basis(d, basis, order)
+
+    @staticmethod
+    def backward(ctx, g):
+        (d,) = ctx.saved_tensors
+        if ctx.order >= 2:
+            raise RuntimeError("Gaussian basis: derivatives beyond the third are not provided by kgcnn_gauss_basis")
+        nxt = _GaussBasis.apply(d, ctx.basis, ctx.order + 1)
+        return (g * nxt).sum(dim=1).reshape(d.shape), None, None
+
+
+class GaussBasisParams:
+    def __init__(self, bins, gamma, offset, step):
+        self.R, self.gamma, self.offset, self.step = int(bins), float(gamma), float(offset), float(step)
+
+
+def gauss_basis(d, bins, gamma, offset, step):
+    """[E] or [E,1] distances -> [E, bins] Gaussian expansion (one launch; differentiable twice)."""
+    _need_cuda(d)
+    return _GaussBasis.apply(_f32c(d), GaussBasisParams(bins, gamma, offset, step), 0)
+
+
 def _cfconv_weight_grads(wg, w1, b1, w2, b2):
     """Hand the operand pairs a WG launch produced to the grouped weight-gradient launch (active sink) or contract
     them here.  Returns (gW1, gb1, gW2, gb2); entries that went to the sink are None."""

@@ -208,3 +208,30 @@ def test_coordinate_hessian_kernel_matches_fp64_oracle(kind, add_eps):
     (o_vjp,) = torch.autograd.grad(o_out, ox, torch.tensor(cot), create_graph=True)
     (o_hess,) = torch.autograd.grad(o_vjp, ox, torch.tensor(h))
     assert rel_err(hess.cpu().numpy(), o_hess.numpy()) < RTOL
+
+
+def test_gauss_basis_on_input_distances_matches_fp64_through_two_derivatives():
+    """GaussBasisLayer on distances that are a model INPUT (kgcnn/literature/Schnet.py make_distance=False): one launch
+    of kgcnn_gauss_basis, its VJP and the VJP of that, against the fp64 expansion."""
+    from gcnn_keras_b200 import functional as F
+    from gcnn_keras_b200.layers import geom as G
+    rng = np.random.default_rng(3)
+    el = np.array([7, 0, 12, 30], dtype=np.int64)
+    d_np = rng.uniform(0.5, 4.9, size=(int(el.sum()), 1))
+    d = torch.tensor(d_np, dtype=torch.float32, device="cuda", requires_grad=True)
+    od = torch.tensor(d_np, dtype=torch.float64, requires_grad=True)
+    launches = F._lib.launch_count()
+    from gcnn_keras_b200 import RaggedTensor
+    out = G.GaussBasisLayer(bins=25, distance=5.0, sigma=0.4, offset=0.1)(
+        RaggedTensor.from_row_lengths(d, torch.as_tensor(el).cuda())).values
+    assert F._lib.launch_count() == launches + 1 and tuple(out.shape) == (int(el.sum()), 25)
+    want = OL.gauss_basis(oracle_ragged(np.zeros_like(d_np), el, torch.float64).with_values(od), bins=25, dist=5.0,
+                          sigma=0.4, offset=0.1).values
+    cot, h = rng.standard_normal(tuple(want.shape)), rng.standard_normal(d_np.shape)
+    (g,) = torch.autograd.grad(out, d, torch.tensor(cot, dtype=torch.float32, device="cuda"), create_graph=True)
+    (gg,) = torch.autograd.grad(g, d, torch.tensor(h, dtype=torch.float32, device="cuda"))
+    (og,) = torch.autograd.grad(want, od, torch.tensor(cot), create_graph=True)
+    (ogg,) = torch.autograd.grad(og, od, torch.tensor(h))
+    assert rel_err(out.detach().cpu().numpy(), want.detach().numpy()) < RTOL
+    assert rel_err(g.detach().cpu().numpy(), og.detach().numpy()) < RTOL
+    assert rel_err(gg.cpu().numpy(), ogg.numpy()) < RTOL
