@@ -18,6 +18,14 @@ def _graph(rng, kind):
         n_graphs, n = 12, 9
         pairs = np.array([(i, j) for i in range(n) for j in range(n) if i != j], dtype=np.int64)
         return np.full(n_graphs, n), np.full(n_graphs, len(pairs)), np.concatenate([pairs] * n_graphs)
+    if kind == "many_tiles":             # > 148 x 128 edges: every CTA walks several tiles (the pipelined epilogue)
+        n = 6000
+        deg = rng.integers(0, 21, size=n)
+        deg[100] = 700                    # one row across six tiles
+        recv = np.repeat(np.arange(n), deg)
+        send = rng.integers(0, n, size=recv.shape[0])
+        ii = np.stack([recv, send], 1)[rng.permutation(recv.shape[0])]
+        return np.array([n]), np.array([len(ii)]), ii.astype(np.int64)
     node_len, edge_len, idx = [], [], []
     for g in range(7):
         n = int(rng.integers(3, 40))
@@ -104,7 +112,7 @@ def _run_oracle(c):
 NAMES = ["y", "gx", "gd", "L_x", "L_d", "L_W1", "L_b1", "L_W2", "L_b2", "L_gy"]
 
 
-@pytest.mark.parametrize("kind", ["c2", "sorted", "unsorted", "hub"])
+@pytest.mark.parametrize("kind", ["c2", "sorted", "unsorted", "hub", "many_tiles"])
 def test_fused_cfconv_matches_fp64_restatement(kind):
     c = _case(kind)
     got, want = _run_fused(c), _run_oracle(c)
