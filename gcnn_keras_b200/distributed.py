@@ -85,3 +85,60 @@ def broadcast_flat(flat, src=0, group=None):
     if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
         return
     dist.broadcast(flat, src=src, group=group)
+
+
+class PeerAllReduce:
+    """All-reduce of the flat gradient buffer over NVLink peer memory instead of an NCCL collective.
+
+    The gradient buffer itself lives in symmetric (peer-mapped) memory (`torch.distributed._symmetric_memory`: plumbing
+    only -- allocation, the handle exchange and the device-side barrier); the reduction is OUR kernel
+    (`kgcnn_allreduce_peer`, csrc/collective.cu): after a barrier every rank reads all ranks' buffers directly and adds
+    them in rank order, so the replicas stay bitwise identical.  A second barrier keeps the buffers unchanged until every
+    peer has read them.  Both barriers and the kernel are stream-ordered and captured inside the step's CUDA graph.
+
+    `create()` returns None when the process group, the device or the torch build cannot provide symmetric memory
+    (one rank, gloo, KGCNN_PEER_ALLREDUCE=0): the caller then keeps the NCCL all-reduce."""
+
+    def __init__(self, numel, device, group):
+        import torch.distributed._symmetric_memory as symm
+        self.group = group
+        self.buffer = symm.empty(int(numel), dtype=torch.float32, device=device)
+        self.buffer.zero_()
+        self.handle = symm.rendezvous(self.buffer, group.group_name)          # collective
+        self.world = int(self.handle.world_size)
+        self.ptrs = [int(p) for p in self.handle.buffer_ptrs]
+        self.out = torch.empty(int(numel), dtype=torch.float32, device=device)
+        self.numel = int(numel)
+
+    @classmethod
+    def create(cls, numel, device, group=None):
+        import os
+        import torch.distributed as dist
+        if os.environ.get("KGCNN_PEER_ALLREDUCE", "1") == "0":
+            return None
+        if not (dist.is_available() and dist.is_initialized()):
+            return None
+        group = group or dist.group.WORLD
+        if dist.get_world_size(group) < 2 or dist.get_backend(group) != "nccl" or torch.device(device).type != "cuda":
+            return None
+        ok = torch.zeros(1, device=device)
+        peer = None
+        try:
+            peer = cls(numel, device, group)
+            ok.fill_(1.0)
+        except Exception:
+            peer = None
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)                # every rank or none
+        return peer if float(ok) == 1.0 else None
+
+    def reduce(self, average=True):
+        """Sum (mean) over the ranks of `self.buffer` -> `self.out` (the buffer itself stays untouched)."""
+        import ctypes
+        from . import _lib
+        arr = (ctypes.c_void_p * self.world)(*self.ptrs)
+        self.handle.barrier(channel=0)            # every rank's gradients are complete
+        _lib.check(_lib.lib().kgcnn_allreduce_peer(arr, self.world, self.numel, (1.0 / self.world) if average else 1.0,
+                                                   self.out.data_ptr(), torch.cuda.current_stream().cuda_stream),
+                   "kgcnn_allreduce_peer")
+        self.handle.barrier(channel=1)            # every rank has read them: the buffers may be overwritten
+        return self.out

@@ -121,7 +121,11 @@ class FlatAdam:
             off += padded
         self._real, self._padded = real, sizes
         self.offsets = [int(o) for o in ([0] + list(torch.tensor(sizes).cumsum(0)[:-1]))]
-        self.gflat = torch.zeros_like(self.flat)                 # flat gradient buffer, same layout (padding stays 0)
+        # flat gradient buffer, same layout (padding stays 0).  Data parallel over NCCL ranks: the buffer lives in
+        # peer-mapped memory and the all-reduce is our own kernel over NVLink (distributed.PeerAllReduce)
+        from .distributed import PeerAllReduce
+        self.peer = PeerAllReduce.create(self.total, dev)
+        self.gflat = self.peer.buffer if self.peer is not None else torch.zeros_like(self.flat)
         self.grad_views = [self.gflat[o:o + n].view_as(p) for o, n, p in zip(self.offsets, real, self.params)]
         self.m = torch.zeros_like(self.flat)
         self.v = torch.zeros_like(self.flat)
@@ -157,7 +161,8 @@ class FlatAdam:
         from . import _lib
         from .distributed import allreduce_flat
         F = self._F
-        g = allreduce_flat(self.gflat)                           # data parallel by graph: the step's only collective
+        # data parallel by graph: the step's only collective
+        g = self.peer.reduce() if self.peer is not None else allreduce_flat(self.gflat)
         lr, b1, b2, eps, clip = self.hyper
         sumsq = F.raw_gms(g.unsqueeze(1), g.unsqueeze(1), self.rel, None) if clip > 0 else None
         # inside a captured step the plan-validation flags guard the update: a replayed batch that breaks the

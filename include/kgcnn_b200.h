@@ -427,6 +427,16 @@ int kgcnn_cfconv_fused(int mode, const float* dist, int64_t E, int R, float gamm
  *   mode 3 also:  wg[4] rbf1 [E,R] = t rbf'   wg[5] hd [E,128]   wg[6] Bt [E,128] = a[o] b[i]   wg[7] gpd [E,128]
  * (reverse sweep of kgcnn/layers/conv/schnet_conv.py:74-75 on the edge rows; the pairs go to kgcnn_dense_tn_grouped). */
 
+/* ---------------------------------------------------------------------------------------------
+ * 8e  weight-gradient all-reduce over peer memory (the one exchange of the data-parallel step; the reference has no
+ *   distributed code, SURVEY F-list): out[i] = scale * sum_r bufs[r][i] with the sum in RANK order (bitwise identical
+ *   on every rank).  bufs = HOST array of `world` (<= 16) device pointers to the ranks' flat gradient buffers, all mapped
+ *   into this process (CUDA IPC / symmetric memory); the caller orders the launch after a cross-rank barrier and holds
+ *   the buffers unchanged until a second barrier.  out must not alias any of the buffers.
+ * ------------------------------------------------------------------------------------------- */
+int kgcnn_allreduce_peer(const float* const* bufs, int world, int64_t n, float scale, float* out,
+                         kgcnn_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -59,3 +59,45 @@ def test_halo_exchange_equals_all_gather_scheme_on_two_gpus():
         p.join(300)
         assert p.exitcode == 0
     assert all(ret[r] for r in range(world))
+
+
+def _peer_worker(rank, world, port, ret):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    from gcnn_keras_b200.distributed import PeerAllReduce
+    dev = torch.device("cuda", rank)
+    n = 469_123                                             # not a multiple of 4: the tail path too
+    peer = PeerAllReduce.create(n, dev)
+    ok = peer is not None
+    if ok:
+        for step in range(3):                               # reuse across steps: the two barriers order the reuse
+            torch.manual_seed(100 * step + rank)
+            g = torch.randn(n, device=dev)
+            peer.buffer.copy_(g)
+            out = peer.reduce(average=True).clone()
+            want = g.double().clone()
+            dist.all_reduce(want, op=dist.ReduceOp.SUM)
+            want = want / world
+            ok = ok and float((out.double() - want).abs().max()) <= 1e-6 * float(want.abs().max())
+            gathered = [torch.empty_like(out) for _ in range(world)]
+            dist.all_gather(gathered, out)
+            ok = ok and all(bool(torch.equal(gathered[0], t)) for t in gathered)   # bitwise identical on every rank
+    ret[rank] = bool(ok)
+    dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_peer_memory_all_reduce_matches_nccl_and_is_identical_on_every_rank():
+    world, port = 2, 37500 + (os.getpid() % 2000)
+    ctx = mp.get_context("spawn")
+    ret = ctx.Manager().dict()
+    procs = [ctx.Process(target=_peer_worker, args=(r, world, port, ret)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(300)
+        assert p.exitcode == 0
+    assert all(ret.get(r) for r in range(world)), dict(ret)
