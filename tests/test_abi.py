@@ -86,3 +86,18 @@ def test_registered_layer_names_equal_the_reference_names():
     for key, cls in _REGISTRY.items():
         assert ref.get(cls.__name__) == key, (key, cls.__name__, ref.get(cls.__name__))
     assert get_registered("kgcnn>BesselBasisLayer").__name__ == "BesselBasisLayer"   # kgcnn/layers/geom.py:716
+
+
+def test_peer_all_reduce_is_not_chosen_without_an_nccl_group():
+    """distributed.PeerAllReduce.create: no process group (or gloo, or one rank) -> None, the caller keeps its
+    collective; the kernel entry itself rejects bad arguments without touching a device."""
+    import ctypes
+    from gcnn_keras_b200 import _lib
+    from gcnn_keras_b200.distributed import PeerAllReduce
+    assert PeerAllReduce.create(1024, "cpu") is None
+    assert PeerAllReduce.MAX_WORLD_AUTO == 4
+    lib = _lib.lib()
+    assert lib.kgcnn_allreduce_peer(None, 2, 16, 1.0, None, None) != 0
+    arr = (ctypes.c_void_p * 1)(None)
+    assert lib.kgcnn_allreduce_peer(arr, 1, 0, 1.0, ctypes.c_void_p(16), None) == 0      # n == 0: nothing to do
+    assert lib.kgcnn_allreduce_peer(arr, 17, 16, 1.0, ctypes.c_void_p(16), None) != 0    # more ranks than slots
