@@ -620,6 +620,20 @@ def run_schnet(args, rank, world, device):
     return run_force(args, rank, world, device, "schnet")
 
 
+def force_config(workload, batch, data, n_params, world):
+    """The `config` block of a force-training line: ONE function for the B200 arm and the reference arm, so that both
+    lines carry the identical dict for the same workload."""
+    return {"workload": workload + ", batch %d per GPU" % batch,
+            "batch_per_gpu": batch, "atoms": int(data["node_len"].sum()), "edges": int(data["edge_len"].sum()),
+            "triples": int(data["angle_len"].sum()) if "angle_len" in data else 0,
+            "parameters": int(n_params), "optimizer": "Adam(1e-3), clipnorm 1.0",
+            "step": "fwd + dE/dx + loss + d loss/d weights through the force + Adam (B200 arm: one CUDA graph)",
+            "l2_policy": "256 MB L2 flush between timed steps (per-step CUDA events) on the B200 arm; "
+                         "the CPU reference arm has no device cache to flush",
+            "parallelism": "graphs sharded across %d rank(s); weight-gradient all-reduce only "
+                           "(the CPU reference arm runs on rank 0 alone)" % world}
+
+
 def run_force(args, rank, world, device, kind):
     from gcnn_keras_b200.training import CapturedForceTrainStep
     build, default_batch, metric, workload = FORCE_WORKLOADS[kind]
@@ -643,13 +657,7 @@ def run_force(args, rank, world, device, kind):
         "metric": metric, "value": total_mol / (ms_step * 1e-3), "unit": "molecules/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": workload + ", batch %d per GPU" % batch,
-                   "batch_per_gpu": batch, "atoms": int(data["node_len"].sum()), "edges": int(data["edge_len"].sum()),
-                   "triples": int(data["angle_len"].sum()) if "angle_len" in data else 0,
-                   "parameters": n_params, "optimizer": "Adam(1e-3), clipnorm 1.0",
-                   "step": "fwd + dE/dx + loss + d loss/d weights through the force + Adam, one CUDA graph",
-                   "l2_policy": "256 MB L2 flush between timed steps (per-step CUDA events)",
-                   "parallelism": "graphs sharded across %d rank(s); weight-gradient all-reduce only" % world},
+        "config": force_config(workload, batch, data, n_params, world),
         "loss": loss_value,
         "e2e": {"value": total_mol / (ms_e2e * 1e-3), "unit": "molecules/s",
                 "h2d_bytes_per_step": captured.static.h2d_bytes, "d2h_bytes_per_step": 4 + (
@@ -839,6 +847,7 @@ def cpu_schnet(batch, steps, warmup, threads):
     for _ in range(steps):
         step()
     dt = (time.perf_counter() - t0) / steps
+    cpu_schnet.last = (b, sum(int(p.numel()) for p in plist))      # for the reference arm's config block
     return batch / dt, dt * 1e3
 
 
@@ -859,8 +868,8 @@ def run_reference_schnet(args):
             "n_gpus": int(os.environ.get("WORLD_SIZE", "1")), "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
-            "config": {"workload": "C2: SchNet energy+force training step, synthetic MD17-ethanol-shaped data "
-                                   "(CPU: batch %d per step)" % batch, "batch": batch, "depth": 6, "units": 128},
+            "config": force_config(FORCE_WORKLOADS["schnet"][3], batch, cpu_schnet.last[0], cpu_schnet.last[1],
+                                   int(os.environ.get("WORLD_SIZE", "1"))),
             "cpu_baseline": {"value": mps, "unit": "molecules/s", "cores": cores, "kind": "port",
                              "sample": "oracle torch-CPU restatement of the reference TF op chain, batch %d" % batch},
             "e2e": {"value": mps, "unit": "molecules/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
