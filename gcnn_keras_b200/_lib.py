@@ -43,6 +43,7 @@ SIGNATURES = {
     "kgcnn_bias_act_pair": (_i, [_p, _p, _p, _p, _i, _i, _l, _i, _p, _p, _p]),
     "kgcnn_colsum_workspace_bytes": (_z, [_l, _i]),
     "kgcnn_colsum": (_i, [_p, _l, _i, _p, _p, _z, _p]),
+    "kgcnn_colsum_static": (_i, [_p, _l, _i, _p, _p]),
     "kgcnn_dense_tc_workspace_bytes": (_z, [_i, _l, _i, _i]),
     "kgcnn_dense_tc": (_i, [_i, _p, _p, _l, _i, _i, _p, _p, _p, _z, _p]),
     "kgcnn_dense_act": (_i, [_p, _p, _l, _i, _i, _p, _i, _p, _p, _p]),

@@ -210,3 +210,72 @@ int kgcnn_colsum(const float* a, int64_t M, int U, float* out, void* workspace, 
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------
+// kgcnn_colsum_static: the column sum for hosts that have no way to hand over a workspace.
+//
+// kgcnn_colsum needs `ceil(M / 512) * U` floats of scratch between its two stages and expects the caller to bring
+// them.  Some callers cannot: a TensorFlow op whose runtime has already reserved nearly all of HBM for its own arena
+// (a raw cudaMalloc from inside the op then reports out-of-memory), a plain-C host that was given a fixed device
+// budget at start-up, or a serving thread that must not run cudaMalloc / cudaFree because both synchronise the
+// whole device.  For them the scratch below is part of the library image: KGCNN_COLSUM_STATIC_MAX_FLOATS floats
+// (1 MiB) that every GPU which loads libkgcnn_b200.so keeps until the process exits.
+//
+// g_colsum_static_partial is a DEVICE symbol.  Host code that spells its name gets the address of a host-side shadow
+// object, not device memory, so the launcher never passes the name to a kernel: it asks the runtime once per device
+// (with that device current) for the real address and passes that.
+// ---------------------------------------------------------------------------------------------------------------
+static __device__ __align__(256) float g_colsum_static_partial[KGCNN_COLSUM_STATIC_MAX_FLOATS];
+
+namespace kgcnn {
+namespace {
+
+constexpr int kMaxStaticDevices = 64;
+std::mutex g_colsum_static_mu;
+float* g_colsum_static_addr[kMaxStaticDevices] = {};  // device address of the array, per device ordinal
+
+// Device address of g_colsum_static_partial on the CURRENT device; resolved by the runtime on the first call per
+// device (this may load the module on that device, which is why that call belongs before any stream capture).
+int colsum_static_scratch(float** ptr) {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) { cudaGetLastError(); return KGCNN_E_CUDA; }
+  if (dev < 0 || dev >= kMaxStaticDevices) return KGCNN_E_UNSUPPORTED;
+  std::lock_guard<std::mutex> lock(g_colsum_static_mu);
+  if (!g_colsum_static_addr[dev]) {
+    float* p = nullptr;
+    if (cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_colsum_static_partial) != cudaSuccess || !p) {
+      cudaGetLastError();
+      return KGCNN_E_CUDA;
+    }
+    g_colsum_static_addr[dev] = p;
+  }
+  *ptr = g_colsum_static_addr[dev];
+  return KGCNN_OK;
+}
+
+}  // namespace
+}  // namespace kgcnn
+
+extern "C" int kgcnn_colsum_static(const float* a, int64_t M, int U, float* out, kgcnn_stream_t stream) {
+  if (M < 0 || U <= 0 || !out) return KGCNN_E_INVALID;
+  if (M > 0 && !a) return KGCNN_E_INVALID;
+  const int64_t nblk = ceil_div<int64_t>(M, kRowsPerBlock);
+  // the limit is checked before anything touches the device: a too-large problem leaves no trace
+  if (nblk > 1 && nblk * U > static_cast<int64_t>(KGCNN_COLSUM_STATIC_MAX_FLOATS)) return KGCNN_E_STATIC_LIMIT;
+  float* partial = nullptr;
+  const int rc = colsum_static_scratch(&partial);  // every call, so the first call on a device always does the set-up
+  if (rc != KGCNN_OK) return rc;
+  cudaStream_t st = as_stream(stream);
+  if (M == 0) return cudaMemsetAsync(out, 0, sizeof(float) * U, st) == cudaSuccess ? KGCNN_OK : KGCNN_E_CUDA;
+  dim3 block(kColTile * kRowThreads);
+  if (nblk == 1) {
+    colsum_kernel<<<dim3(ceil_div(U, kColTile), 1), block, 0, st>>>(a, M, U, kRowsPerBlock, out);
+    return finish_launch();
+  }
+  // Stage 1 writes partial[0 .. nblk*U) completely before stage 2 (same stream) reads exactly that range, so what an
+  // earlier call left in the array is never seen and nothing has to be cleared.
+  colsum_kernel<<<dim3(ceil_div(U, kColTile), static_cast<unsigned>(nblk)), block, 0, st>>>(a, M, U, kRowsPerBlock,
+                                                                                             partial);
+  colsum_kernel<<<dim3(ceil_div(U, kColTile), 1), block, 0, st>>>(partial, nblk, U, nblk, out);
+  return finish_launch(2);
+}

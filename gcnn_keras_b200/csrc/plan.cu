@@ -152,6 +152,7 @@ const char* kgcnn_error_string(int code) {
     case KGCNN_E_UNSUPPORTED: return "unsupported shape";
     case KGCNN_E_CUDA: return "CUDA launch error";
     case KGCNN_E_WORKSPACE: return "workspace too small";
+    case KGCNN_E_STATIC_LIMIT: return "problem larger than the fixed scratch array of a *_static entry point";
     default: return "unknown error";
   }
 }

@@ -11,7 +11,8 @@
  *  - every pointer is a DEVICE pointer owned by the caller; outputs and workspaces are pre-allocated
  *    by the host framework (torch.empty / TF allocate_output);
  *  - every call is asynchronous on `stream`, never synchronises, never allocates, and is re-entrant
- *    (the only process-global state is a monotonically increasing launch counter);
+ *    (the only process-global state is a monotonically increasing launch counter; the one exception is
+ *    kgcnn_colsum_static, which owns a scratch array shared by all of its calls -- see its comment);
  *  - float tensors are fp32 row-major contiguous; indices are int32 after kgcnn_shift_index (the
  *    int64 -> int32 conversion happens once per batch, the reference redoes it in every layer);
  *  - return value: 0 = KGCNN_OK, negative = KGCNN_E_*; no C++ exception crosses the ABI;
@@ -34,7 +35,8 @@ enum {
   KGCNN_E_INVALID = -1,     /* bad argument (null pointer, negative size, unknown enum) */
   KGCNN_E_UNSUPPORTED = -2, /* shape outside what the kernels are instantiated for */
   KGCNN_E_CUDA = -3,        /* a CUDA launch error was pending after the launch */
-  KGCNN_E_WORKSPACE = -4    /* workspace smaller than *_workspace_bytes() */
+  KGCNN_E_WORKSPACE = -4,   /* workspace smaller than *_workspace_bytes() */
+  KGCNN_E_STATIC_LIMIT = -5 /* problem needs more scratch than a *_static entry point owns */
 };
 
 /* segment_ops_by_name names (kgcnn/ops/segment.py:39-46) */
@@ -177,6 +179,23 @@ int kgcnn_bias_act_pair(const float* pre, const float* bias, const float* gy, co
 size_t kgcnn_colsum_workspace_bytes(int64_t M, int U);
 int kgcnn_colsum(const float* a, int64_t M, int U, float* out, void* workspace, size_t workspace_bytes,
                  kgcnn_stream_t stream);
+/* kgcnn_colsum_static -- no counterpart in the reference; it exists for the host side of this library.
+ *     Same result as kgcnn_colsum (same kernels, same summation order, bit for bit), but the caller brings only the
+ *     input and the output: the scratch between the two stages is a 1 MiB array inside the library image.  Meant for
+ *     hosts that cannot produce a device workspace -- an op running under a framework that has already claimed all of
+ *     HBM for its own arena (cudaMalloc then fails), a C program with a device budget fixed at start-up, a serving
+ *     thread that may not call cudaMalloc / cudaFree because they synchronise the device.  It calls no allocator.
+ *   Limit: ceil(M / 512) * U <= KGCNN_COLSUM_STATIC_MAX_FLOATS when M > 512 (e.g. M <= 1 048 576 rows at U = 128);
+ *     anything larger returns KGCNN_E_STATIC_LIMIT before touching the device -- use kgcnn_colsum there.
+ *   Cost: every GPU that loads the library holds the 1 MiB until the process exits.
+ *   First call on each device (with that device current) looks up the array's device address; make that call before
+ *     any stream capture begins.  Later calls only launch.
+ *   The array is shared by ALL calls on a device and keeps the previous call's partial sums.  Nothing needs clearing
+ *     (stage 1 overwrites every element stage 2 reads), but two calls that can overlap on the GPU -- different
+ *     streams, or different host threads on different streams -- race on it: keep them on one stream or order them
+ *     with events.  This is the one entry point of the library that is not re-entrant in that sense. */
+#define KGCNN_COLSUM_STATIC_MAX_FLOATS (1 << 18)
+int kgcnn_colsum_static(const float* a, int64_t M, int U, float* out, kgcnn_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
  * a19  Dense contractions on the tcgen05 tensor cores (three-piece bf16 split, fp32 TMEM accumulators):
