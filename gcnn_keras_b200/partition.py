@@ -116,7 +116,10 @@ class HaloPlan:
     halo_ids   : sorted unique GLOBAL ids of the remote senders of this rank's edges = the row order of the halo buffer
     need_counts: rows of the halo buffer owned by each rank (receive split sizes)
     send_ids   : LOCAL row ids this rank sends, grouped by destination rank (int32, device); send_counts per rank
-    rel_back   : CSR relation send_ids -> local row (sums the returned partial gradients in a fixed order)"""
+    rel_back   : CSR relation send_ids -> local row (sums the returned partial gradients in a fixed order)
+    exchange_needed: True if ANY rank has rows crossing the cut (MAX over the group at plan build, so identical on
+                 every rank): the all-to-all is a collective, and a rank with nothing to send or receive -- an isolated
+                 shard, a last rank that is all padding -- still has to join it with zero counts."""
 
     def __init__(self, send_global, rank, world, per, device):
         send_global = np.asarray(send_global, dtype=np.int64)
@@ -143,6 +146,21 @@ class HaloPlan:
         self.n_halo, self.n_send = int(len(self.halo_ids)), int(len(send_ids))
         self.send_ids = torch.as_tensor(send_ids, dtype=torch.int32, device=device)
         self.rel_back = Relation(self.send_ids, per) if self.n_send else None
+        self.exchange_needed = False
+        if dist is not None and world > 1:
+            crossing = torch.tensor([self.n_halo + self.n_send], dtype=torch.int64, device=device)
+            dist.all_reduce(crossing, op=dist.ReduceOp.MAX)
+            self.exchange_needed = bool(int(crossing.item()) > 0)
+
+    def exchange_rows(self, rows, reverse=False):
+        """The per-layer all-to-all: forward sends `rows` (grouped by destination, send_counts) and returns the halo
+        buffer; reverse=True sends halo-shaped rows back to their owners.  Returns (work handle or None, buffer), or
+        (None, None) when no rank of the group has a row crossing the cut.  Every rank calls it or none does."""
+        if not self.exchange_needed:
+            return None, None
+        if reverse:
+            return _all_to_all_rows(rows, self.need_counts, self.send_counts)
+        return _all_to_all_rows(rows, self.send_counts, self.need_counts)
 
     @staticmethod
     def _a2a_sync(buf, send_counts, recv_counts):
@@ -167,9 +185,9 @@ class _Aggregate(torch.autograd.Function):
         h = h.contiguous()
         if not transpose:
             work = halo = None
-            if plan.n_send or plan.n_halo:
+            if plan.exchange_needed:                                       # a group-wide decision, never rank-local
                 send_buf = F.raw_gather_rows(h, plan.send_ids) if plan.n_send else h.new_empty((0, h.shape[1]))
-                work, halo = _all_to_all_rows(send_buf, plan.send_counts, plan.need_counts)
+                work, halo = plan.exchange_rows(send_buf)
             y = F.raw_gms(h, g.w_loc, g.recv_loc, g.send_loc)              # local senders, while the rows travel
             if work is not None:
                 work.wait()
@@ -177,9 +195,9 @@ class _Aggregate(torch.autograd.Function):
                 y += F.raw_gms(halo, g.w_rem, g.recv_rem, g.send_rem)
             return y
         work = back = None
-        if plan.n_send or plan.n_halo:
+        if plan.exchange_needed:
             g_halo = F.raw_gms(h, g.w_rem, g.send_rem, g.recv_rem) if plan.n_halo else h.new_empty((0, h.shape[1]))
-            work, back = _all_to_all_rows(g_halo, plan.need_counts, plan.send_counts)
+            work, back = plan.exchange_rows(g_halo, reverse=True)
         dx = F.raw_gms(h, g.w_loc, g.send_loc, g.recv_loc)                 # local senders, while the rows travel
         if work is not None:
             work.wait()

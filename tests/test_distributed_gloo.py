@@ -137,3 +137,67 @@ def test_halo_plan_exchanges_only_referenced_rows_and_is_adjoint_world2():
         p.join(120)
         assert p.exitcode == 0
     assert all(ret[r] for r in range(world))
+
+
+def _isolated_shard_worker(rank, world, port, ret):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    from gcnn_keras_b200.partition import HaloPlan, partition_bounds
+    n_nodes, feat = 12, 2
+    per, _ = partition_bounds(n_nodes, world)             # 4 rows per rank
+    # ranks 0 and 1 read each other's rows; rank 2's edges stay inside its own block and nobody reads its rows
+    send = {0: [0, 1, 5, 6], 1: [4, 2, 3, 7], 2: [8, 9, 10, 11, 8]}[rank]
+    plan = HaloPlan(np.asarray(send), rank, world, per, torch.device("cpu"))
+    ok = plan.exchange_needed                             # the same answer on all three ranks
+    if rank == 2:
+        ok = ok and plan.n_halo == 0 and plan.n_send == 0
+    table = torch.arange(per * world * feat, dtype=torch.float32).reshape(per * world, feat)
+    local = table[rank * per:(rank + 1) * per]
+    for _ in range(2):                                    # two layers: the collective sequence stays aligned
+        _, halo = plan.exchange_rows(local[plan.send_ids.long()])
+        ok = ok and torch.equal(halo, table[torch.as_tensor(plan.halo_ids, dtype=torch.int64)])
+        _, back = plan.exchange_rows(halo, reverse=True)
+        ok = ok and torch.equal(back, local[plan.send_ids.long()])
+    ret[rank] = bool(ok)
+    dist.destroy_process_group()
+
+
+def test_isolated_shard_still_joins_the_halo_exchange_world3():
+    """A rank with no row crossing the cut calls the all-to-all with zero counts instead of skipping it (the gloo
+    emulation is built from true collectives: it hangs if one rank stays out)."""
+    world, port = 3, 35500 + (os.getpid() % 2000)
+    ctx = mp.get_context("spawn")
+    ret = ctx.Manager().dict()
+    procs = [ctx.Process(target=_isolated_shard_worker, args=(r, world, port, ret)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(120)
+        assert p.exitcode == 0
+    assert all(ret[r] for r in range(world))
+
+
+def _no_crossing_worker(rank, world, port, ret):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    from gcnn_keras_b200.partition import HaloPlan
+    plan = HaloPlan(np.asarray([rank * 4, rank * 4 + 3]), rank, world, 4, torch.device("cpu"))   # block-diagonal graph
+    ret[rank] = (not plan.exchange_needed) and plan.exchange_rows(torch.zeros(0, 2)) == (None, None)
+    dist.destroy_process_group()
+
+
+def test_block_diagonal_graph_needs_no_exchange_on_any_rank_world2():
+    world, port = 2, 37500 + (os.getpid() % 2000)
+    ctx = mp.get_context("spawn")
+    ret = ctx.Manager().dict()
+    procs = [ctx.Process(target=_no_crossing_worker, args=(r, world, port, ret)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(120)
+        assert p.exitcode == 0
+    assert all(ret[r] for r in range(world))
