@@ -954,6 +954,40 @@ class CfconvSpec:
                 and w1.is_cuda and w1.dtype == torch.float32 and w2.dtype == torch.float32)
 
 
+_STATIC_WEIGHT_RANGE = None          # [lo, hi) device addresses of the flat buffer whose owner vouches for its writers
+
+
+class static_weights:
+    """Opt-in of the code that OWNS the model variables: while this context is active, tensors that live inside `flat`
+    (FlatAdam's parameter buffer) are written by nothing but the owner's own update kernel, which is never the launch
+    right before a layer kernel -- so the fused cfconv may stage them before its launch-dependency wait
+    (csrc/common.cuh: otherwise no global access before pdl_wait()).  Without it (the default) the kernel waits first:
+    a foreign optimizer, an EMA / constraint kernel or a load_state_dict copy may have written the weights last.
+    `flat=None` is a no-op (the optimizer does not exist yet)."""
+
+    def __init__(self, flat):
+        self.range = None if flat is None else (flat.data_ptr(), flat.data_ptr() + flat.numel() * flat.element_size())
+
+    def __enter__(self):
+        global _STATIC_WEIGHT_RANGE
+        self._prev, _STATIC_WEIGHT_RANGE = _STATIC_WEIGHT_RANGE, (self.range or _STATIC_WEIGHT_RANGE)
+        return self
+
+    def __exit__(self, *exc):
+        global _STATIC_WEIGHT_RANGE
+        _STATIC_WEIGHT_RANGE = self._prev
+
+
+def static_weight_flag(tensors):
+    """1 only if an owner has opted in (static_weights) and every tensor handed to the kernel -- AFTER the contiguous /
+    fp32 conversion, so a fresh copy never qualifies -- lies inside the owner's buffer."""
+    if _STATIC_WEIGHT_RANGE is None:
+        return 0
+    lo, hi = _STATIC_WEIGHT_RANGE
+    return int(all(t is None or (t.numel() > 0 and lo <= t.data_ptr() and
+                                 t.data_ptr() + t.numel() * t.element_size() <= hi) for t in tensors))
+
+
 def raw_cfconv(mode, spec, d, w1, b1, w2, b2, rel_out, rel_other, a, b=None, c=None, tang=None, want_wg=False):
     """One launch of kgcnn_cfconv_fused (+ its fix-up): (out [n_out,128], edge_out [E] | None, wg | None).
     want_wg (modes 1, 3): also the operand pairs of the filter network's weight gradients, as a dict
@@ -969,12 +1003,12 @@ def raw_cfconv(mode, spec, d, w1, b1, w2, b2, rel_out, rel_other, a, b=None, c=N
     b = None if b is None else _f32c(b)
     c = None if c is None else _f32c(c)
     tang = None if tang is None else _f32c(tang.reshape(-1))
-    # model variables (leaves that require a gradient) are written by the optimizer kernel only: safe to stage before
-    # the kernel waits for its launch dependency (csrc/common.cuh, programmatic dependent launch)
-    static_w = int(all(t is None or (t.is_leaf and t.requires_grad) for t in (w1, b1, w2, b2)))
     w1, w2 = _f32c(w1), _f32c(w2)
     b1 = None if b1 is None else _f32c(b1)
     b2 = None if b2 is None else _f32c(b2)
+    # staged before the kernel waits for its launch dependency only when the variables' owner has vouched for their
+    # writers (static_weights); decided on the tensors the kernel really reads, after any copy
+    static_w = static_weight_flag((w1, b1, w2, b2))
     out = torch.empty((rel_out.n_targets, 128), dtype=torch.float32, device=dev)
     edge_out = torch.empty((E,), dtype=torch.float32, device=dev) if mode in (1, 3) else None
     nbytes = int(_lib.lib().kgcnn_cfconv_fused_workspace_bytes(E))

@@ -210,16 +210,19 @@ class ForceTrainStep:
                 + self.w_f * weighted_mse(force, f_target, sample_weight, inv_graphs))
 
     def step(self, inputs, e_target, f_target, weights=None):
-        loss = self.loss(inputs, e_target, f_target, weights)
+        from .functional import WeightGradSink, no_coordinate_hessian, static_weights, weight_grad_sink
+        # the variables live in FlatAdam's buffer and its update kernel (followed by the step-counter kernel) is their
+        # only writer between two steps: this step vouches for that, so the fused kernels may stage them early
+        with static_weights(None if self.optimizer is None else self.optimizer.flat):
+            loss = self.loss(inputs, e_target, f_target, weights)
         self._ensure_optimizer()
-        from .functional import WeightGradSink, no_coordinate_hessian, weight_grad_sink
         opt = self.optimizer
         if self.sink is None:
             self.sink = WeightGradSink(self.params, opt.gflat, opt.offsets)
         opt.zero_grad()
         # weights only: no d2/dx2 through the fused geometry kernels; the Dense weight gradients (leaves of this
         # sweep) are deferred into the sink and computed by ONE grouped tensor-core launch at its exit
-        with no_coordinate_hessian(), weight_grad_sink(self.sink):
+        with no_coordinate_hessian(), weight_grad_sink(self.sink), static_weights(opt.flat):
             grads = torch.autograd.grad(loss, self.params, allow_unused=True)
         opt.step(grads, accumulate=True)
         return loss

@@ -101,3 +101,20 @@ def test_peer_all_reduce_is_not_chosen_without_an_nccl_group():
     arr = (ctypes.c_void_p * 1)(None)
     assert lib.kgcnn_allreduce_peer(arr, 1, 0, 1.0, ctypes.c_void_p(16), None) == 0      # n == 0: nothing to do
     assert lib.kgcnn_allreduce_peer(arr, 17, 16, 1.0, ctypes.c_void_p(16), None) != 0    # more ranks than slots
+
+
+def test_static_weight_flag_needs_the_owner_to_opt_in():
+    """cfconv stages its weights before the launch-dependency wait only for tensors inside a buffer whose owner has
+    opted in (functional.static_weights); a copy made on the way to the kernel never qualifies."""
+    from gcnn_keras_b200 import functional as F
+    flat = torch.zeros(256)
+    w, b = flat[:128].view(8, 16), flat[128:144]
+    assert F.static_weight_flag((w, b, None)) == 0                      # default: wait first
+    with F.static_weights(flat):
+        assert F.static_weight_flag((w, b, None)) == 1
+        assert F.static_weight_flag((w, b.clone())) == 0                # a fresh copy lies outside the buffer
+        assert F.static_weight_flag((w, torch.zeros(4))) == 0
+        with F.static_weights(None):                                    # no-op, the outer owner stays
+            assert F.static_weight_flag((w,)) == 1
+    assert F.static_weight_flag((w, b)) == 0
+    assert F.static_weight_flag((torch.nn.Parameter(torch.zeros(3)),)) == 0   # being a leaf variable is not enough
