@@ -151,6 +151,14 @@ class PoolingLocalEdgesAttention(GraphBaseLayer):
 PoolingLocalMessagesAttention = PoolingLocalEdgesAttention
 
 
+def _snake(name):
+    """'GlorotUniform' / 'glorot_uniform' / 'Zeros' -> 'glorot_uniform' / 'zeros' (Keras accepts both spellings)."""
+    if not isinstance(name, str):
+        return name
+    out = "".join(("_" + ch.lower()) if ch.isupper() else ch for ch in name)
+    return out.lstrip("_")
+
+
 @register_keras_serializable(package="kgcnn", name="PoolingLocalEdgesLSTM")
 class PoolingLocalEdgesLSTM(GraphBaseLayer):
     """kgcnn/layers/pooling.py:288-460.  call([nodes, edges, tensor_index]) -> the LAST hidden state of an LSTM run
@@ -178,6 +186,18 @@ class PoolingLocalEdgesLSTM(GraphBaseLayer):
                              "(the pooled output is the last hidden state per node)")
         if dropout or recurrent_dropout:
             raise ValueError("PoolingLocalEdgesLSTM: dropout inside the recurrence is not supported")
+        # the variables are always glorot-uniform / orthogonal / zeros and unconstrained: a config that asks for
+        # anything else is refused instead of being echoed by get_config and ignored
+        for key, given, default in (("kernel_initializer", kernel_initializer, "glorot_uniform"),
+                                    ("recurrent_initializer", recurrent_initializer, "orthogonal"),
+                                    ("bias_initializer", bias_initializer, "zeros")):
+            name = given.get("class_name") if isinstance(given, dict) else given
+            if _snake(name) != default:
+                raise ValueError("PoolingLocalEdgesLSTM: %s=%r is not supported (only %r)" % (key, given, default))
+        for key, given in (("kernel_constraint", kernel_constraint), ("recurrent_constraint", recurrent_constraint),
+                           ("bias_constraint", bias_constraint)):
+            if given is not None:
+                raise ValueError("PoolingLocalEdgesLSTM: %s is not supported" % key)
         self.units = int(units)
         self.pooling_method = pooling_method
         self.pooling_index = pooling_index
@@ -240,7 +260,7 @@ class PoolingLocalEdgesLSTM(GraphBaseLayer):
             zx = F.permute_rows(zx, perm, inv)
         rowptr = rel.rowptr.to(torch.int64)
         deg = rowptr[1:] - rowptr[:-1]
-        max_len = int(deg.max())                                               # one host sync per call
+        max_len = rel.max_degree()                                             # host int cached with the plan
         zp = F.pad(zx, rowptr, max_len)                                        # [N, max_len, 4u]
         c = torch.zeros_like(h)
         for step in range(max_len):

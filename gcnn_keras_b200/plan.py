@@ -123,6 +123,14 @@ class Relation:
 
     LONG_THRESH = 1024      # segments longer than this are reduced by a whole CTA (hub nodes)
 
+    def max_degree(self):
+        """Longest segment (host int).  One device read the first time; cached on the relation, and relations are cached
+        per index tensor (get_plan), so a layer called again on the same graph does not synchronise."""
+        if getattr(self, "_max_degree", None) is None:
+            rp = self.rowptr
+            self._max_degree = int((rp[1:] - rp[:-1]).max()) if self.n_targets > 0 and self.n_elements > 0 else 0
+        return self._max_degree
+
     def _find_long_rows(self):
         """Hub rows would serialise one lane group for thousands of edges; list them once per batch."""
         self.long_rows = self.n_long = None

@@ -58,3 +58,21 @@ def test_pooling_local_edges_lstm_config_and_errors():
         assert key in cfg
     with pytest.raises(ValueError):
         PoolingLocalEdgesLSTM(units=8, return_sequences=True)
+    # initializers / constraints other than the ones the layer implements are refused, not echoed and ignored
+    PoolingLocalEdgesLSTM(units=8, kernel_initializer="GlorotUniform", bias_initializer={"class_name": "Zeros", "config": {}})
+    with pytest.raises(ValueError, match="kernel_initializer"):
+        PoolingLocalEdgesLSTM(units=8, kernel_initializer="he_normal")
+    with pytest.raises(ValueError, match="recurrent_initializer"):
+        PoolingLocalEdgesLSTM(units=8, recurrent_initializer="glorot_uniform")
+    with pytest.raises(ValueError, match="bias_constraint"):
+        PoolingLocalEdgesLSTM(units=8, bias_constraint="non_neg")
+
+
+def test_relation_max_degree_is_cached_with_the_plan():
+    from gcnn_keras_b200.plan import Relation
+    ids = torch.tensor([0, 0, 0, 2, 2, 5], dtype=torch.int32).cuda()
+    rel = Relation(ids, 7)
+    assert rel.max_degree() == 3
+    rel._rowptr = None                      # a second call must not touch the device plan again
+    assert rel.max_degree() == 3
+    assert Relation(ids[:0], 4).max_degree() == 0
