@@ -70,6 +70,7 @@ SIGNATURES = {
     "kgcnn_gauss_basis": (_i, [_p, _l, _i, _f, _f, _f, _i, _p, _p, _p]),
     "kgcnn_cfconv_fused": (_i, [_i, _p, _l, _i, _f, _f, _f, _p, _p, _p, _p, _i, _i, _i, _p, _p, _p, _p, _l, _p, _p, _p, _p, _p, _p, _p, _p, _z, _p]),
     "kgcnn_allreduce_peer": (_i, [_p, _i, _l, _f, _p, _p]),
+    "kgcnn_guard_fold": (_i, [_p, _p, _i, _p, _p]),
     "kgcnn_adam_clipnorm": (_i, [_p, _p, _p, _p, _p, _p, _l, _f, _p, _f, _f, _f, _f, _p, _p, _p, _i, _p]),
 }
 

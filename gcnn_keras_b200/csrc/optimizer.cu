@@ -47,6 +47,11 @@ __global__ void bump_step_kernel(int32_t* step, const int32_t* __restrict__ guar
   if (!guard_tripped(guard, guard_mask, n_guard)) *step += 1;
 }
 
+__global__ void guard_fold_kernel(const int32_t* __restrict__ guard, const int32_t* __restrict__ guard_mask, int n_guard,
+                                  float* __restrict__ word) {
+  *word = guard_tripped(guard, guard_mask, n_guard) ? 1.f : 0.f;
+}
+
 }  // namespace
 }  // namespace kgcnn
 
@@ -68,4 +73,11 @@ extern "C" int kgcnn_adam_clipnorm(float* params, const float* grads, float* m, 
                                              step, guard, guard_mask, n_guard);
   bump_step_kernel<<<1, 1, 0, st>>>(step, guard, guard_mask, n_guard);
   return finish_launch(2);
+}
+
+extern "C" int kgcnn_guard_fold(const int32_t* guard, const int32_t* guard_mask, int n_guard, float* word,
+                                kgcnn_stream_t stream) {
+  if (n_guard < 0 || !word || (n_guard > 0 && (!guard || !guard_mask))) return KGCNN_E_INVALID;
+  guard_fold_kernel<<<1, 1, 0, as_stream(stream)>>>(guard, guard_mask, n_guard, word);
+  return finish_launch();
 }

@@ -123,9 +123,16 @@ class FlatAdam:
         self.offsets = [int(o) for o in ([0] + list(torch.tensor(sizes).cumsum(0)[:-1]))]
         # flat gradient buffer, same layout (padding stays 0).  Data parallel over NCCL ranks: the buffer lives in
         # peer-mapped memory and the all-reduce is our own kernel over NVLink (distributed.PeerAllReduce)
-        from .distributed import PeerAllReduce
-        self.peer = PeerAllReduce.create(self.total, dev)
-        self.gflat = self.peer.buffer if self.peer is not None else torch.zeros_like(self.flat)
+        from .distributed import PeerAllReduce, world_info
+        self.world = world_info()[1]
+        # with more than one rank the gradient buffer carries one more (256 B aligned) slot behind the last variable:
+        # word [total] is the captured step's plan-validation verdict, reduced with the gradients (step_flat)
+        self.gtotal = self.total + (64 if self.world > 1 else 0)
+        self.peer = PeerAllReduce.create(self.gtotal, dev)
+        self.gflat = self.peer.buffer if self.peer is not None else torch.zeros(self.gtotal, dtype=torch.float32,
+                                                                                device=dev)
+        self.all_bits = torch.full((1,), -1, dtype=torch.int32, device=dev)
+        self.reduced_guard = None          # after a captured step at world > 1: view of the reduced verdict word
         self.grad_views = [self.gflat[o:o + n].view_as(p) for o, n, p in zip(self.offsets, real, self.params)]
         self.m = torch.zeros_like(self.flat)
         self.v = torch.zeros_like(self.flat)
@@ -161,21 +168,32 @@ class FlatAdam:
         from . import _lib
         from .distributed import allreduce_flat
         F = self._F
-        # data parallel by graph: the step's only collective
-        g = self.peer.reduce() if self.peer is not None else allreduce_flat(self.gflat)
-        lr, b1, b2, eps, clip = self.hyper
-        sumsq = F.raw_gms(g.unsqueeze(1), g.unsqueeze(1), self.rel, None) if clip > 0 else None
         # inside a captured step the plan-validation flags guard the update: a replayed batch that breaks the
         # recorded sortedness / index-range assumptions leaves parameters, moments and step counter untouched
         from .plan import current_mode
         mode = current_mode()
         guard = mode.flag_buf if (mode is not None and mode.kind == "capture") else None
+        guard_ptr = None if guard is None else guard.data_ptr()
+        mask_ptr = None if guard is None else mode.mask_buf.data_ptr()
+        n_guard = 0 if guard is None else guard.numel()
+        stream = torch.cuda.current_stream().cuda_stream
+        if guard is not None and self.world > 1:
+            # the verdict must be the GROUP's: this rank's word rides behind the gradients through the all-reduce
+            _lib.check(_lib.lib().kgcnn_guard_fold(guard_ptr, mask_ptr, n_guard, self.gflat[self.total:].data_ptr(),
+                                                   stream), "kgcnn_guard_fold")
+        # data parallel by graph: the step's only collective
+        g = self.peer.reduce() if self.peer is not None else allreduce_flat(self.gflat)
+        if guard is not None and self.world > 1:
+            # mean of the 0/1 words: non-zero bits on every rank iff any rank tripped -> all replicas skip together
+            self.reduced_guard = g[self.total:self.total + 1]
+            guard_ptr, mask_ptr, n_guard = self.reduced_guard.data_ptr(), self.all_bits.data_ptr(), 1
+        g = g[:self.total]
+        lr, b1, b2, eps, clip = self.hyper
+        sumsq = F.raw_gms(g.unsqueeze(1), g.unsqueeze(1), self.rel, None) if clip > 0 else None
         _lib.check(_lib.lib().kgcnn_adam_clipnorm(
             self.flat.data_ptr(), g.data_ptr(), self.m.data_ptr(), self.v.data_ptr(), self.var_of.data_ptr(),
             None if sumsq is None else sumsq.data_ptr(), self.total, lr, self.lr_device.data_ptr(), b1, b2, eps, clip,
-            self.step_count.data_ptr(), None if guard is None else guard.data_ptr(),
-            None if guard is None else mode.mask_buf.data_ptr(), 0 if guard is None else guard.numel(),
-            torch.cuda.current_stream().cuda_stream), "kgcnn_adam_clipnorm")
+            self.step_count.data_ptr(), guard_ptr, mask_ptr, n_guard, stream), "kgcnn_adam_clipnorm")
 
 
 class ForceTrainStep:
@@ -379,6 +397,9 @@ class CapturedForceTrainStep:
         self._flags_event, self._flags_pending = torch.cuda.Event(), False
         self.kernels_per_step = _lib.launch_count()      # our kernels recorded in the graph
         self.loss_host = torch.zeros((), dtype=torch.float32).pin_memory()
+        # more than one rank: the reduced verdict word (non-zero on EVERY rank when any rank's batch broke its plan)
+        self.group_guard = getattr(train_step.optimizer, "reduced_guard", None)
+        self.group_guard_host = None if self.group_guard is None else torch.zeros(1, dtype=torch.float32).pin_memory()
         self.flags_host = None if self.flags is None else torch.zeros_like(self.flags, device="cpu").pin_memory()
 
     def run(self, batch=None, load=True):
@@ -407,6 +428,8 @@ class CapturedForceTrainStep:
         self.loss_host.copy_(self.loss.detach(), non_blocking=True)
         if self.flags is not None:
             self.flags_host.copy_(self.flags, non_blocking=True)
+            if self.group_guard is not None:
+                self.group_guard_host.copy_(self.group_guard, non_blocking=True)
             self._flags_event.record()
             self._flags_pending = True
         return self.loss_host
@@ -415,6 +438,8 @@ class CapturedForceTrainStep:
         """After a synchronize: were the sortedness / index-range assumptions of the capture still true?"""
         if self.flags is None:
             return True
+        if self.group_guard_host is not None and float(self.group_guard_host[0]) != 0.0:
+            return False                   # some rank of the group tripped: every rank skipped, every rank reports it
         return not self.mode.violated(list(self.flags_host))
 
 

@@ -355,6 +355,13 @@ int kgcnn_adam_clipnorm(float* params, const float* grads, float* m, float* v, c
                         float beta1, float beta2, float eps, float clipnorm, int32_t* step,
                         const int32_t* guard /*nullable*/,
                         const int32_t* guard_mask /*nullable*/, int n_guard, kgcnn_stream_t stream);
+/* kgcnn_guard_fold: *word = 1.0f if (guard[i] & guard_mask[i]) != 0 for any i, else 0.0f.  Data-parallel training:
+ * the word sits behind the last variable of the flat gradient buffer and travels through the step's ONE all-reduce
+ * (SURVEY 8e), so that after it every rank holds the same non-zero word when ANY rank's batch broke its captured plan;
+ * kgcnn_adam_clipnorm then takes that reduced word as its guard (mask = all bits) and all replicas skip the update
+ * together instead of one rank skipping while the others apply its garbage gradients.  No reference counterpart
+ * (kgcnn/utils/devices.py:11-64 is all the distributed code the reference has). */
+int kgcnn_guard_fold(const int32_t* guard, const int32_t* guard_mask, int n_guard, float* word, kgcnn_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Batch graph construction (the step in front of the path).  Two-pass: count -> offsets ->

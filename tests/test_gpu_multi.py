@@ -101,3 +101,79 @@ def test_peer_memory_all_reduce_matches_nccl_and_is_identical_on_every_rank():
         p.join(300)
         assert p.exitcode == 0
     assert all(ret.get(r) for r in range(world)), dict(ret)
+
+
+def _group_guard_worker(rank, world, port, ret):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    from test_gpu_guard import small_schnet_step, unsorted_copy
+    from gcnn_keras_b200.training import CapturedForceTrainStep
+    dev = torch.device("cuda", rank)
+    model, step, good = small_schnet_step(dev, seed=rank)
+    captured = CapturedForceTrainStep(step, good, dev, warmup=2)
+    opt = step.optimizer
+
+    def same_on_all_ranks(t):
+        parts = [torch.empty_like(t) for _ in range(world)]
+        dist.all_gather(parts, t.contiguous())
+        return all(bool(torch.equal(parts[0], q)) for q in parts)
+
+    captured.run(good)
+    torch.cuda.synchronize()
+    ok = captured.check() and same_on_all_ranks(opt.flat)
+    before = [t.clone() for t in (opt.flat, opt.m, opt.v, opt.step_count)]
+    # ONLY rank 1 gets a batch that breaks its plan; rank 0's batch is fine
+    captured.run(unsorted_copy(good) if rank == 1 else good)
+    torch.cuda.synchronize()
+    ok = ok and not captured.check()                               # reported on BOTH ranks
+    ok = ok and all(bool(torch.equal(a, b)) for a, b in zip(before, (opt.flat, opt.m, opt.v, opt.step_count)))
+    try:
+        captured.run(good)
+        ok = False
+    except RuntimeError:
+        pass                                                       # raised on both ranks, nobody is left in a barrier
+    captured.run(good)
+    torch.cuda.synchronize()
+    ok = ok and captured.check() and int(opt.step_count) == int(before[3]) + 1
+    ok = ok and same_on_all_ranks(opt.flat) and not torch.equal(before[0], opt.flat)
+    ret[rank] = (bool(ok), "peer" if opt.peer is not None else "nccl")
+    # a CUDA graph that captured an NCCL collective keeps a reference on the communicator: release it before the
+    # process group goes away, or the communicator's destruction waits for it
+    captured.graph = None
+    del captured
+    import gc
+    gc.collect()
+    torch.cuda.synchronize()
+    dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+@pytest.mark.parametrize("peer", ["auto", "0"])
+def test_one_rank_breaking_its_plan_makes_every_replica_skip_the_update(peer):
+    """The guard word travels through the step's all-reduce (peer-memory kernel and NCCL path): replicas stay
+    bitwise identical and every rank raises."""
+    world, port = 2, 39500 + (os.getpid() % 2000) + (7 if peer == "0" else 0)
+    os.environ["KGCNN_PEER_ALLREDUCE"] = peer
+    try:
+        ctx = mp.get_context("spawn")
+        ret = ctx.Manager().dict()
+        procs = [ctx.Process(target=_group_guard_worker, args=(r, world, port, ret)) for r in range(world)]
+        for p in procs:
+            p.start()
+        for p in procs:
+            p.join(150)
+        hung = [p for p in procs if p.is_alive()]
+        for p in hung:                                   # never leave a rank behind: pytest would wait for it at exit
+            p.kill()
+            p.join(10)
+        assert not hung, "a rank did not finish: %s" % dict(ret)
+        assert all(p.exitcode == 0 for p in procs)
+    finally:
+        os.environ.pop("KGCNN_PEER_ALLREDUCE", None)
+    assert all(ret.get(r, (False,))[0] for r in range(world)), dict(ret)
+    if peer == "0":
+        assert all(ret[r][1] == "nccl" for r in range(world))
