@@ -414,6 +414,29 @@ def profile_traffic(csv_name, kernel_substr, skip=0, count=None):
     return sum(float(r[i_r]) * scale(hdr[i_r]) + float(r[i_w]) * scale(hdr[i_w]) for r in sel) / len(sel)
 
 
+def profile_traffic_named(csv_name, kernel_substr, grids, count):
+    """As profile_traffic, but the rows are chosen by kernel-name substring AND launch__grid_size; None unless exactly
+    `count` rows match (a summary regenerated from a different build or shape list then yields null, not a wrong row)."""
+    import csv
+    path = os.path.join(ROOT, "profiles", csv_name)
+    if not os.path.exists(path):
+        return None
+    with open(path) as fh:
+        rows = list(csv.reader(fh))
+    hdr = rows[0]
+    try:
+        i_g = next(i for i, h in enumerate(hdr) if h.startswith("launch__grid_size"))
+        i_r = next(i for i, h in enumerate(hdr) if h.startswith("dram__bytes_read.sum"))
+        i_w = next(i for i, h in enumerate(hdr) if h.startswith("dram__bytes_write.sum"))
+    except StopIteration:
+        return None
+    scale = lambda h: {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}.get(h.split("[")[-1].rstrip("]"), 1.0)
+    sel = [r for r in rows[1:] if kernel_substr in r[0] and int(float(r[i_g])) in grids]
+    if len(sel) != count:
+        return None
+    return sum(float(r[i_r]) * scale(hdr[i_r]) + float(r[i_w]) * scale(hdr[i_w]) for r in sel) / len(sel)
+
+
 def roofline_shapes(device):
     """Generator over the measured shapes of the north-star kernel family: (key, workload text, kernel text,
     algorithmic bytes, edges, [launch callables]).  Used by gss_roofline (timing) and tools/ncu_gms.py (one launch of
@@ -558,8 +581,11 @@ def cfconv_roofline(device, iters=5):
 
 
 GMS_PROFILE = "r2_gms_full.csv"     # ncu --set full of tools/ncu_gms.py on the final build (rows in launch order)
-_PROFILE_ROWS = {"plain": [("gms_kernel", 0, 2)], "weighted": [("gms_kernel", 2, 2), ("gather2_mul", 0, 1)],
-                 "gss_g": [("gms_kernel", 4, 2)], "cached_shape": [("gms_kernel", 6, 2)]}
+# rows of the ncu summary by kernel instantiation AND grid size (not by position): (name substring, grid sizes, launches)
+_PROFILE_ROWS = {"plain": [("gms_kernel<float4, 8, 4, 0,", (62500,), 2)],
+                 "weighted": [("gms_kernel<float4, 8, 4, 2,", (31250,), 2), ("gather2_mul_kernel<float4, 32, 0>", (500000,), 1)],
+                 "gss_g": [("gms_kernel<float4, 8, 4, 1,", (7813, 62500), 2)],
+                 "cached_shape": [("gms_kernel<float4, 8, 2, 0,", (40960,), 2)]}
 
 
 def gss_roofline(device, iters=10):
@@ -572,7 +598,7 @@ def gss_roofline(device, iters=10):
     out = {}
     for key, workload, kernel, alg_bytes, edges, fns in roofline_shapes(device):
         ms = _time(lambda: [f() for f in fns], iters if key != "weighted" else max(3, iters // 2))
-        parts = [profile_traffic(GMS_PROFILE, k, sk, cnt) for k, sk, cnt in _PROFILE_ROWS[key]]
+        parts = [profile_traffic_named(GMS_PROFILE, k, grids, cnt) for k, grids, cnt in _PROFILE_ROWS[key]]
         traffic = None if any(p is None for p in parts) else sum(
             p * cnt for p, (_, _, cnt) in zip(parts, _PROFILE_ROWS[key]))
         ach = alg_bytes / (ms * 1e-3) / 1e9
