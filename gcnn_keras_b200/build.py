@@ -69,5 +69,37 @@ def build(force=False, verbose=False):
     return LIB
 
 
+LIB_PRECISE = os.path.join(HERE, "libkgcnn_b200_precise.so")
+
+
+def build_precise(force=False):
+    """The same library with csrc/cfconv.cu compiled under -DKGCNN_CF_PRECISE (libm expf / log1pf / division in the
+    fused cfconv's softplus chain instead of the fast intrinsics) -> libkgcnn_b200_precise.so.  Only that one source is
+    recompiled; every other object is the regular build's.  Used by tests/test_gpu_cfconv.py so that the precise path
+    keeps compiling and keeps its parity."""
+    build(force=force)
+    src = os.path.join(CSRC, "cfconv.cu")
+    obj = os.path.join(OBJ, "cfconv_precise.o")
+    stamp = obj + ".sha"
+    dig = _digest(src) + "+precise"
+    if force or not (os.path.exists(obj) and os.path.exists(stamp) and open(stamp).read() == dig):
+        res = subprocess.run([NVCC] + FLAGS + ["-DKGCNN_CF_PRECISE", "-c", src, "-o", obj], capture_output=True, text=True)
+        if res.returncode != 0:
+            raise RuntimeError("nvcc failed for cfconv.cu (precise):\n%s\n%s" % (res.stdout, res.stderr))
+        with open(stamp, "w") as fh:
+            fh.write(dig)
+    objs = [os.path.join(OBJ, s[:-3] + ".o") for s in _sources() if s != "cfconv.cu"] + [obj]
+    newest = max(os.path.getmtime(o) for o in objs)
+    if force or not os.path.exists(LIB_PRECISE) or os.path.getmtime(LIB_PRECISE) < newest:
+        res = subprocess.run([NVCC, "-shared", "-o", LIB_PRECISE] + objs + ["-gencode", "arch=compute_100a,code=sm_100a"],
+                             capture_output=True, text=True)
+        if res.returncode != 0:
+            raise RuntimeError("link failed (precise):\n%s\n%s" % (res.stdout, res.stderr))
+    return LIB_PRECISE
+
+
 if __name__ == "__main__":
+    if "--precise" in sys.argv:
+        print(build_precise(force="--force" in sys.argv))
+        sys.exit(0)
     print(build(force="--force" in sys.argv, verbose="--verbose" in sys.argv))

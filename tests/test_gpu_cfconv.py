@@ -180,3 +180,31 @@ def test_fused_cfconv_weight_gradients_through_the_grouped_sink():
         g = flat[off:off + p.numel()].reshape(p.shape).cpu().numpy()
         assert rel_err(g, w) < RTOL, name
     assert F._lib.launch_count() > launches
+
+
+def test_fused_cfconv_precise_build_keeps_its_parity(monkeypatch):
+    """csrc/cfconv.cu compiled with -DKGCNN_CF_PRECISE (libm exp / log1p / division instead of the fast intrinsics;
+    gcnn_keras_b200.build.build_precise): the variant must keep compiling and meet the same bar.  The library handle of
+    the binding is swapped for the precise build for the duration of this test."""
+    import ctypes
+    import os
+    from gcnn_keras_b200 import _lib
+    from gcnn_keras_b200.build import LIB_PRECISE
+    assert os.path.exists(LIB_PRECISE), "run `python -m gcnn_keras_b200.build --precise` (or __graft_entry__.build())"
+    regular = _lib.lib()
+    handle = ctypes.CDLL(LIB_PRECISE)
+    for name, (res, args) in _lib.SIGNATURES.items():
+        fn = getattr(handle, name)
+        fn.restype, fn.argtypes = res, args
+    c = _case("hub")
+    want = _run_oracle(c)
+    fast = _run_fused(c)
+    monkeypatch.setattr(_lib, "_lib", handle)
+    before = handle.kgcnn_launch_count()
+    precise = _run_fused(c)
+    assert handle.kgcnn_launch_count() > before          # the precise library really ran
+    monkeypatch.setattr(_lib, "_lib", regular)
+    errs = {n: rel_err(g, w) for n, g, w in zip(NAMES, precise, want)}
+    assert all(e < RTOL for e in errs.values()), errs
+    errs_fast = {n: rel_err(g, w) for n, g, w in zip(NAMES, fast, want)}
+    assert max(errs.values()) <= 2 * max(errs_fast.values()) + 1e-7, (errs, errs_fast)

@@ -40,6 +40,30 @@ def _worker(rank, world, port, ret):
         if mode == "halo":
             n_halo = graph.halo.n_halo
     ok = n_halo < per * (world - 1)                        # fewer rows travel than the all-gather moves
+    # both schemes against the fp64 oracle of the UNPARTITIONED layer (oracle.conv.gcn): this rank's rows of y and dx,
+    # and the weight gradients summed over the ranks
+    from oracle import R
+    from oracle import conv as OC
+    ox = x_full[:n_nodes].detach().cpu().double().requires_grad_(True)
+    prm = {"lay_dense.kernel": kernel.detach().cpu().double().requires_grad_(True),
+           "lay_dense.bias": bias.detach().cpu().double().requires_grad_(True)}
+    want = OC.gcn(OC.P(prm), R.from_row_lengths(ox, np.array([n_nodes])),
+                  R.from_row_lengths(torch.tensor(w, dtype=torch.float64).reshape(-1, 1), np.array([len(recv)])),
+                  R.from_row_lengths(torch.tensor(np.stack([recv, send], 1)), np.array([len(recv)])),
+                  "relu", "sum", False).values
+    dy_all = [torch.empty_like(dy) for _ in range(world)]
+    dist.all_gather(dy_all, dy.contiguous())
+    cot = torch.cat(dy_all, 0)[:n_nodes].cpu().double()
+    ogx, ogk, ogb = torch.autograd.grad(want, [ox, prm["lay_dense.kernel"], prm["lay_dense.bias"]], cot)
+    lo, hi = bounds[rank]
+    for mode in ("halo", "allgather"):
+        y, gx, gk, gb = outs[mode]
+        gk, gb = gk.clone(), gb.clone()
+        dist.all_reduce(gk)
+        dist.all_reduce(gb)
+        for a, b in ((y[:hi - lo], want[lo:hi]), (gx[:hi - lo], ogx[lo:hi]), (gk, ogk), (gb, ogb)):
+            b = b.detach()
+            ok = ok and float((a.cpu().double() - b).abs().max()) <= 1e-5 * (float(b.abs().max()) + 1e-30)
     for a, b in zip(outs["halo"], outs["allgather"]):
         scale = float(b.abs().max()) + 1e-30
         ok = ok and float((a - b).abs().max()) <= 2e-6 * scale

@@ -10,9 +10,14 @@ Two error measures are recorded per tensor:
     max-norm  relative error   max|a - b| / max|b|                        (the north-star's "1e-5 relative")
     element-wise relative error max_i |a_i - b_i| / max(|b_i|, FLOOR * max|b|),  FLOOR = 1e-2
 together with err32 = the max-norm error of the fp32 evaluation of the oracle itself (the reference's op order in
-fp32, the "TF-CPU-like" comparand).  Everything goes to gpurun_out/parity_r2.json (copied to profiles/parity_r2.json).
-Bar: max-norm < 1e-5; a tensor may exceed it only where the fp32 restatement of the reference exceeds it too, and
-then by no more than 2x that error -- the JSON shows every such tensor with both numbers."""
+fp32, the "TF-CPU-like" comparand).  Bar: max-norm < 1e-5 on every tensor, no allowance; element-wise (floored) error < 30 x that.
+
+Full benchmarked batch sizes (C3 at 512 molecules, C4 at 256 systems): graphs do not interact, so the fp64 oracle is
+evaluated in chunks of 64 / 16 molecules; energies and forces are concatenated, and the weight gradients of the
+batch-mean loss are the sums of the chunk gradients of the same loss written with the batch-wide denominators.
+C2-captured: the path bench.py times (CapturedForceTrainStep: weight-gradient sink -> grouped TN launch -> flat gradient
+buffer -> clipnorm + Adam kernel) after ONE replay from known weights.  C5: the partitioned GCN layer against
+oracle.conv.gcn.  Everything goes to gpurun_out/parity_r3.json (copied to profiles/parity_r3.json)."""
 import json
 import os
 
@@ -65,22 +70,16 @@ def _dump_record():
             "above_1e-5": {n: {"err": r["err_maxnorm"], "err32": r.get("err32_maxnorm")} for n, r in over.items()}}
     d = os.path.join(ROOT, "gpurun_out")
     os.makedirs(d, exist_ok=True)
-    with open(os.path.join(d, "parity_r2.json"), "w") as fh:
+    with open(os.path.join(d, "parity_r3.json"), "w") as fh:
         json.dump(out, fh, indent=1, sort_keys=True)
 
 
-def _check(config, rows_needing_fp32_allowance=()):
-    """max-norm bar on every recorded tensor of `config`; the fp32 allowance applies only where err32 itself is
-    above the bar."""
-    bad = []
-    for name, r in _RECORD[config].items():
-        bar = RTOL
-        if r.get("err32_maxnorm") is not None and r["err32_maxnorm"] >= RTOL:
-            bar = 2 * r["err32_maxnorm"]
-        if not r["err_maxnorm"] < bar:
-            bad.append((name, r["err_maxnorm"], r.get("err32_maxnorm")))
-        assert r["err_elementwise"] < 100 * max(bar, RTOL), (name, r)
+def _check(config):
+    """max-norm bar (1e-5) on every recorded tensor of `config`, no allowance; element-wise error below 30 x the bar."""
+    bad = [(name, r["err_maxnorm"]) for name, r in _RECORD[config].items() if not r["err_maxnorm"] < RTOL]
     assert not bad, bad
+    for name, r in _RECORD[config].items():
+        assert r["err_elementwise"] < 30 * RTOL, (name, r)
 
 
 # --------------------------------------------------------------------------------------------------------
@@ -134,8 +133,44 @@ def test_c1_gather_dense_pool_chain_at_full_size():
 # --------------------------------------------------------------------------------------------------------
 # shared: energy / force / loss / every weight gradient through the force
 # --------------------------------------------------------------------------------------------------------
-def _force_training_parity(config, model, inputs, b, oracle_fn, force_loss_factor, min_grads):
-    """oracle_fn(dtype) -> (params dict, energy, force[N,3]) of the oracle in `dtype`."""
+def _slice_batch(b, lo, hi):
+    """Molecules [lo, hi) of a ragged batch dict (index columns are per-molecule local ids: slicing rows is enough)."""
+    out = {}
+    for values, lengths in (("z", "node_len"), ("xyz", "node_len"), ("force", "node_len"), ("index", "edge_len"),
+                            ("angle_index", "angle_len")):
+        if values in b:
+            off = np.concatenate([[0], np.cumsum(b[lengths])])
+            out[values] = b[values][off[lo]:off[hi]]
+    for k in ("node_len", "edge_len", "angle_len", "energy"):
+        if k in b:
+            out[k] = b[k][lo:hi]
+    return out
+
+
+def _chunked_oracle(b, named, chunk_fn, force_loss_factor, chunk):
+    """fp64 oracle of the full batch in chunks of `chunk` molecules.  chunk_fn(dtype, sub_batch) -> (params, energy,
+    force).  loss = w_e mean_B (E - E^)^2 + w_f mean_{N,3} (F - F^)^2 = sum over chunks of the squared-error SUMS over
+    the batch-wide element counts, so the gradients add."""
+    n_mol = len(b["node_len"])
+    w_e = 1.0 / force_loss_factor
+    eng, force, total, grads = [], [], 0.0, None
+    for lo in range(0, n_mol, chunk):
+        sub = _slice_batch(b, lo, min(n_mol, lo + chunk))
+        prm, oe, of = chunk_fn(torch.float64, sub)
+        part = (w_e * ((oe - torch.tensor(sub["energy"], dtype=torch.float64)) ** 2).sum() / b["energy"].size
+                + (1 - w_e) * ((of - torch.tensor(sub["force"], dtype=torch.float64)) ** 2).sum() / b["force"].size)
+        og = torch.autograd.grad(part, [prm[n] for n, _ in named], allow_unused=True)
+        grads = [None if g is None else g.numpy() for g in og] if grads is None else \
+            [a if g is None else (g.numpy() if a is None else a + g.numpy()) for a, g in zip(grads, og)]
+        eng.append(oe.detach().numpy())
+        force.append(of.detach().numpy())
+        total += float(part)
+    return np.concatenate(eng), np.concatenate(force), total, grads
+
+
+def _force_training_parity(config, model, inputs, b, oracle_fn, force_loss_factor, min_grads, chunk=None):
+    """oracle_fn(dtype) -> (params dict, energy, force[N,3]) of the oracle in `dtype`; with `chunk` it is
+    oracle_fn(dtype, sub_batch) and the fp64 oracle runs chunk molecules at a time (no fp32 column then)."""
     from gcnn_keras_b200.functional import no_coordinate_hessian
     eng, force = model(inputs, training=True)
     e_t, f_t = torch.tensor(b["energy"]).cuda(), torch.tensor(b["force"]).cuda()
@@ -152,11 +187,16 @@ def _force_training_parity(config, model, inputs, b, oracle_fn, force_loss_facto
         og = torch.autograd.grad(ol, [prm[n] for n, _ in named], allow_unused=True)
         return oe.detach().numpy(), of.detach().numpy(), float(ol), [None if g is None else g.numpy() for g in og]
 
-    e64, f64, l64, g64 = oracle(torch.float64)
-    e32, f32, l32, g32 = oracle(torch.float32)
+    if chunk is None:
+        e64, f64, l64, g64 = oracle(torch.float64)
+        e32, f32, l32, g32 = oracle(torch.float32)
+    else:
+        e64, f64, l64, g64 = _chunked_oracle(b, named, oracle_fn, force_loss_factor, chunk)
+        e32 = f32 = None
+        l32, g32 = None, [None] * len(g64)
     _record(config, "energy", eng.detach().cpu().numpy(), e64, e32)
     _record(config, "force", force.values.detach().cpu().numpy(), f64, f32)
-    _record(config, "loss", np.array([loss.item()]), np.array([l64]), np.array([l32]))
+    _record(config, "loss", np.array([loss.item()]), np.array([l64]), None if l32 is None else np.array([l32]))
     n_checked = 0
     for (n, _), g, og, og32 in zip(named, grads, g64, g32):
         if og is None or float(np.abs(og).max()) == 0.0:
@@ -264,3 +304,164 @@ def test_c4_hdnnp2nd_16_systems_of_64_atoms_against_fp64_oracle():
         return prm, eng, force.squeeze(-1)
 
     _force_training_parity("C4", model, inputs, b, oracle_fn, 200.0, min_grads=6)
+
+
+# --------------------------------------------------------------------------------------------------------
+# C3 and C4 at the BENCHMARKED batch sizes (512 molecules / 256 systems): chunked fp64 oracle
+# --------------------------------------------------------------------------------------------------------
+def test_c3_painn_at_the_benchmarked_batch_of_512_against_chunked_fp64_oracle():
+    from gcnn_keras_b200.literature.PAiNN import make_model
+    from gcnn_keras_b200.synthetic import PAINN_C3_CONFIG, painn_c3_batch
+    torch.manual_seed(1234)
+    cfg = PAINN_C3_CONFIG
+    b = painn_c3_batch(512, 0, n_atoms=30)
+    model = _force_model(make_model(**cfg))
+    inputs = _inputs(b)
+    model(inputs, training=False)
+
+    def oracle_fn(dtype, sub):
+        prm = _oracle_params(model, dtype)
+        z, edi = oracle_ragged(sub["z"], sub["node_len"]), oracle_ragged(sub["index"], sub["edge_len"])
+        xyz = oracle_ragged(sub["xyz"], sub["node_len"], dtype)
+        eng, force = OM.energy_force(
+            lambda x: OM.painn_energy(prm, z, x, edi, cfg["depth"], cfg["bessel_basis"], cfg["conv_args"],
+                                      cfg["equiv_initialize_kwargs"]["method"], cfg["output_mlp"]["activation"]), xyz)
+        return prm, eng, force.squeeze(-1)
+
+    _force_training_parity("C3@512", model, inputs, b, oracle_fn, 95.0, min_grads=60, chunk=64)
+
+
+def test_c4_hdnnp2nd_at_the_benchmarked_batch_of_256_against_chunked_fp64_oracle():
+    from gcnn_keras_b200.literature.HDNNP2nd import make_model_behler
+    from gcnn_keras_b200.synthetic import HDNNP_C4_CONFIG, hdnnp_c4_batch
+    torch.manual_seed(1234)
+    cfg = HDNNP_C4_CONFIG
+    b = hdnnp_c4_batch(256, 0, n_atoms=64, max_neighbours=25)
+    model = _force_model(make_model_behler(**cfg))
+    inputs = _inputs(b)
+    model(inputs, training=False)
+
+    def oracle_fn(dtype, sub):
+        prm = _oracle_params(model, dtype)
+        z, eij = oracle_ragged(sub["z"], sub["node_len"]), oracle_ragged(sub["index"], sub["edge_len"])
+        ijk = oracle_ragged(sub["angle_index"], sub["angle_len"])
+        xyz = oracle_ragged(sub["xyz"], sub["node_len"], dtype)
+        eng, force = OM.energy_force(
+            lambda x: OM.hdnnp2nd_energy(prm, z, x, eij, ijk, cfg["g2_kwargs"], cfg["g4_kwargs"],
+                                         cfg["mlp_kwargs"]["activation"]), xyz)
+        return prm, eng, force.squeeze(-1)
+
+    _force_training_parity("C4@256", model, inputs, b, oracle_fn, 200.0, min_grads=6, chunk=16)
+
+
+# --------------------------------------------------------------------------------------------------------
+# C2 through the CAPTURED training step (what bench.py times): flat gradient buffer and one Adam update
+# --------------------------------------------------------------------------------------------------------
+def test_c2_captured_training_step_gradients_and_first_adam_update_against_fp64_oracle():
+    """One replay of CapturedForceTrainStep at batch 256 from known weights (keep_weights: the capture's warm-up
+    updates are undone).  (1) every variable's slice of the flat gradient buffer -- filled by the weight-gradient sink's
+    grouped TN launch plus the directly accumulated gradients -- equals the fp64 oracle's gradient to 1e-5 max-norm;
+    (2) the updated flat parameters equal Keras' Adam(1e-3) + clipnorm 1.0 rule (force_schnet.py:196-203) evaluated in
+    fp64 ON the device's gradient to 1e-6 of the update size.  (2) is anchored on the device's gradient because the first
+    Adam step is lr * g / (|g| + eps / sqrt(1 - beta2)): for the few elements with |g| below ~3e-6 it amplifies a
+    1e-6-relative gradient difference to a finite fraction of lr, which says nothing about either side."""
+    from gcnn_keras_b200.literature.Schnet import make_model
+    from gcnn_keras_b200.model.force import EnergyForceModel
+    from gcnn_keras_b200.synthetic import SCHNET_C2_CONFIG, schnet_c2_batch
+    from gcnn_keras_b200.training import CapturedForceTrainStep, ForceTrainStep
+    torch.manual_seed(1234)
+    cfg = SCHNET_C2_CONFIG
+    b = schnet_c2_batch(256, 0)
+    dev = torch.device("cuda:0")
+    model = EnergyForceModel(model_energy=make_model(**cfg), energy_output=0, output_to_tensor=True,
+                             output_as_dict=False, output_squeeze_states=True, is_physical_force=False)
+    step = ForceTrainStep(model, lr=1e-3, force_loss_factor=200.0, clipnorm=1.0)
+    captured = CapturedForceTrainStep(step, b, dev, keep_weights=True)
+    opt = step.optimizer
+    assert int(opt.step_count) == 0
+    p0 = opt.flat.detach().clone()
+    name_of = {id(p): n for n, p in model.energy_model.named_parameters()}
+    names = [name_of[id(p)] for p in step.params]
+
+    prm = _oracle_params(model, torch.float64)                   # the weights the replay starts from
+    z, edi = oracle_ragged(b["z"], b["node_len"]), oracle_ragged(b["index"], b["edge_len"])
+    xyz = oracle_ragged(b["xyz"], b["node_len"], torch.float64)
+    oe, of = OM.energy_force(
+        lambda x: OM.schnet_energy(prm, z, x, edi, cfg["depth"], cfg["gauss_args"], cfg["interaction_args"],
+                                   cfg["last_mlp"]["activation"], "sum", None), xyz)
+    ol = OM.force_training_loss(oe, of.squeeze(-1), torch.tensor(b["energy"], dtype=torch.float64),
+                                torch.tensor(b["force"], dtype=torch.float64), force_loss_factor=200.0)
+    og = torch.autograd.grad(ol, [prm[n] for n in names], allow_unused=True)
+
+    loss = captured.run(b)
+    torch.cuda.synchronize()
+    assert captured.check() and int(opt.step_count) == 1
+    _record("C2-captured", "loss", np.array([float(loss)]), np.array([float(ol)]))
+    n_checked = 0
+    for n, view, g in zip(names, opt.grad_views, og):
+        if g is None or float(g.abs().max()) == 0.0:
+            assert float(view.abs().max()) < 1e-10, n
+            continue
+        _record("C2-captured", "gflat:" + n, view.detach().cpu().numpy(), g.numpy())
+        n_checked += 1
+    assert n_checked >= 60
+    # Keras Adam, first step, per-variable clipnorm -- fp64 on the device's gradient
+    lr, b1, b2, eps, clip = opt.hyper
+    want = p0.double().cpu().clone()
+    gdev = opt.gflat.detach().double().cpu()
+    for off, n_real in zip(opt.offsets, opt._real):
+        g = gdev[off:off + n_real]
+        g = g * clip / max(float(g.norm()), clip)
+        m, v = (1 - b1) * g, (1 - b2) * g * g
+        want[off:off + n_real] -= lr * np.sqrt(1 - b2) / (1 - b1) * m / (v.sqrt() + eps)
+    delta_want = (want - p0.double().cpu()).numpy()
+    delta_got = (opt.flat.detach().double().cpu() - p0.double().cpu()).numpy()
+    # fp32 parameters: the update is rounded to the parameter's ulp (|p| <~ 1 -> 6e-8), i.e. 6e-5 of lr at worst
+    assert float(np.abs(delta_got - delta_want).max()) <= 1e-4 * lr
+    # recorded relative to the parameters (what the next step reads); the bound on the UPDATE is the assertion above
+    _record("C2-captured", "updated_parameters_adam_on_device_gradient", opt.flat.detach().cpu().numpy(), want.numpy())
+    bad = [(k, r["err_maxnorm"]) for k, r in _RECORD["C2-captured"].items() if not r["err_maxnorm"] < RTOL]
+    assert not bad, bad
+
+
+# --------------------------------------------------------------------------------------------------------
+# C5: the partitioned GCN layer against oracle.conv.gcn (BASELINE configs[4] at reduced size, one rank)
+# --------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("n_nodes,with_grad", [(200_000, False), (25_000, True)])
+def test_c5_partitioned_gcn_layer_against_the_oracle(n_nodes, with_grad):
+    """gcn_layer_partitioned (Dense -> halo plan -> fused weighted aggregation -> relu) with the C5 generator of
+    bench.py at 1/10 size (forward; the fp64 oracle materialises [E, 128] like the reference) and at 1/80 size with the
+    gradients of x, kernel and bias."""
+    from bench import gcn_c5_shard
+    from gcnn_keras_b200.partition import PartitionedGraph, gcn_layer_partitioned
+    from oracle import conv as OC
+    feat = 128
+    recv, send, w = gcn_c5_shard(n_nodes, 0, n_nodes)
+    rng = np.random.default_rng(5)
+    x = rng.standard_normal((n_nodes, feat)).astype(np.float32)
+    kernel = (rng.standard_normal((feat, feat)) / np.sqrt(feat)).astype(np.float32)
+    bias = (rng.standard_normal(feat) * 0.1).astype(np.float32)
+    cot = rng.standard_normal((n_nodes, feat)).astype(np.float32)
+
+    graph = PartitionedGraph(n_nodes, recv, send, w, 0, 1, torch.device("cuda:0"))
+    dx = torch.tensor(x, device="cuda", requires_grad=with_grad)
+    dk = torch.tensor(kernel, device="cuda", requires_grad=with_grad)
+    db = torch.tensor(bias, device="cuda", requires_grad=with_grad)
+    y = gcn_layer_partitioned(graph, dx, dk, db, "relu")
+
+    ox = torch.tensor(x, dtype=torch.float64, requires_grad=with_grad)
+    ok = torch.tensor(kernel, dtype=torch.float64, requires_grad=with_grad)
+    ob = torch.tensor(bias, dtype=torch.float64, requires_grad=with_grad)
+    lengths = np.array([n_nodes]), np.array([len(recv)])
+    with torch.set_grad_enabled(with_grad):
+        want = OC.gcn(OC.P({"lay_dense.kernel": ok, "lay_dense.bias": ob}), R.from_row_lengths(ox, lengths[0]),
+                      oracle_ragged(w.reshape(-1, 1), lengths[1], torch.float64),
+                      oracle_ragged(np.stack([recv, send], 1), lengths[1]), "relu", "sum", False).values
+    cfg = "C5/%d" % n_nodes
+    _record(cfg, "y", y.detach().cpu().numpy(), want.detach().numpy())
+    if with_grad:
+        got = torch.autograd.grad(y, [dx, dk, db], torch.tensor(cot, device="cuda"))
+        ref = torch.autograd.grad(want, [ox, ok, ob], torch.tensor(cot, dtype=torch.float64))
+        for name, g, o in zip(("dx", "dkernel", "dbias"), got, ref):
+            _record(cfg, name, g.cpu().numpy(), o.numpy())
+    _check(cfg)
